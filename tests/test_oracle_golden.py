@@ -1,0 +1,136 @@
+"""Pins oracle/nerfw_oracle.py to the reference: every function is checked against vectors that
+oracle/make_golden.py produced by running the unmodified reference (SURVEY.md §8c KATs 1-6)."""
+import pytest
+import torch
+
+from nerf_fl_b200 import synthetic as syn
+from oracle import nerfw_oracle as O
+
+
+def close(a, b, tol=1e-6):
+    assert a.shape == b.shape, (a.shape, b.shape)
+    err = (a.double() - b.double()).abs().max().item() if a.numel() else 0.0
+    assert err <= tol, err
+
+
+@pytest.mark.parametrize("L", [4, 10, 15])
+def test_posenc(golden, L):
+    g = golden("posenc")
+    assert torch.equal(O.posenc(g["x"], L), g[f"L{L}"])     # same ops -> bit-exact
+
+
+@pytest.mark.parametrize("scale", [1, 3])
+def test_field_forward(golden, scale):
+    g = golden("field")
+    x = g["x"]
+    pc = syn.make_field_params(21, "coarse", weight_scale=float(scale))
+    pa = syn.make_field_params(22, "fine", True, False, weight_scale=float(scale))
+    pt = syn.make_field_params(23, "fine", True, True, weight_scale=float(scale))
+    close(O.field_forward(pc, x[:, :63], sigma_only=True), g[f"sigma_only_s{scale}"])
+    close(O.field_forward(pc, x[:, :90], output_transient=False), g[f"plain_s{scale}"])
+    close(O.field_forward(pa, x[:, :138], in_dir_a=75, output_transient=False), g[f"a_s{scale}"])
+    close(O.field_forward(pt, x, in_dir_a=75, output_transient=True), g[f"at_s{scale}"])
+
+
+def test_field_macs_match_param_counts():
+    # MACs + biases == parameter count
+    for (ea, et, n) in [(False, False, 595844), (True, True, 687113)]:
+        shapes = syn.field_param_shapes("fine", ea, et)
+        params = sum(o * i + o for o, i in shapes.values())
+        assert params == n
+        assert O.field_macs(ea, et) == sum(o * i for o, i in shapes.values())
+    assert O.field_macs(False, False, sigma_only=True) == 491264
+
+
+def test_sample_pdf(golden):
+    g = golden("sample_pdf")
+    s, cdf, u, inds = O.sample_pdf(g["bins"], g["weights"], 64, det=False, u=g["u"], return_aux=True)
+    assert torch.equal(cdf, g["cdf"])
+    assert torch.equal(inds, g["inds_sto"])            # indices bit-exact
+    close(s, g["samples_sto"], 0.0)
+    s, cdf, u, inds = O.sample_pdf(g["bins"], g["weights"], 64, det=True, return_aux=True)
+    assert torch.equal(u, g["u_det"]) and torch.equal(inds, g["inds_det"])
+    close(s, g["samples_det"], 0.0)
+    assert inds.max().item() == 63                     # u==1 edge exercised (above clamp)
+
+
+@pytest.mark.parametrize("transient", [False, True])
+@pytest.mark.parametrize("white_back", [False, True])
+@pytest.mark.parametrize("test_time", [False, True])
+def test_composite(golden, transient, white_back, test_time):
+    g = golden("composite")
+    tag = f"t{int(transient)}_w{int(white_back)}_x{int(test_time)}/"
+    typ = "fine" if transient else "coarse"
+    raw = g["raw"] if transient else g["raw"][..., :4]
+    out = O.composite(raw, g["z"], typ=typ, transient=transient, white_back=white_back,
+                      test_time=test_time, beta_min=0.1, noise=g["noise"], noise_std=0.7)
+    want = {k[len(tag):]: v for k, v in g.items() if k.startswith(tag)}
+    assert set(out) == set(want)
+    for k in want:
+        close(out[k], want[k], 1e-6)
+
+
+def _e2e_inputs(g):
+    rng = {k[4:]: v for k, v in g.items() if k.startswith("rng_")}
+    return g["rays"], g["ts"], rng, syn.make_embedding(31, 100, 48), syn.make_embedding(32, 100, 16)
+
+
+def _want(g, tag):
+    return {k[len(tag) + 1:]: v for k, v in g.items()
+            if k.startswith(tag + "/") and "/grad_" not in k and not k.endswith("/loss")}
+
+
+@pytest.mark.parametrize("scale", [1, 3])
+def test_render_rays_variants(golden, scale):
+    g = golden("render_rays")
+    rays, ts, rng, ea, et = _e2e_inputs(g)
+    pc = syn.make_field_params(41, "coarse", weight_scale=float(scale))
+    pf = syn.make_field_params(42, "fine", True, True, weight_scale=float(scale))
+    pp = syn.make_field_params(43, "fine", weight_scale=float(scale))
+    cases = {
+        f"nerfw_train_s{scale}": dict(p_fine=pf, ts=ts, perturb=1.0, noise_std=0.0, white_back=True,
+                                      encode_a=True, encode_t=True, beta_min=0.1),
+        f"nerfw_test_s{scale}": dict(p_fine=pf, ts=ts, perturb=0, noise_std=0, white_back=True,
+                                     test_time=True, encode_a=True, encode_t=True, beta_min=0.1),
+        f"nerfw_test_disp_notransient_s{scale}": dict(
+            p_fine=pf, ts=ts, perturb=0, noise_std=0, white_back=False, test_time=True, use_disp=True,
+            encode_a=True, encode_t=True, beta_min=0.1, output_transient=False),
+        f"plain_train_s{scale}": dict(p_fine=pp, ts=None, perturb=1.0, noise_std=1.0, white_back=False),
+        f"plain_test_s{scale}": dict(p_fine=pp, ts=None, perturb=0, noise_std=0, white_back=True,
+                                     test_time=True),
+        f"coarse_only_s{scale}": dict(p_fine=None, ts=None, perturb=0, noise_std=0, n_importance=0),
+    }
+    with torch.no_grad():
+        for tag, kw in cases.items():
+            kw = dict(kw)
+            p_fine, ts_ = kw.pop("p_fine"), kw.pop("ts")
+            kw.setdefault("n_importance", 64)
+            out = O.render_rays(pc, p_fine, ea, et, rays, ts_, n_samples=64, rng=rng, **kw)
+            want = _want(g, tag)
+            assert set(out) == set(want), (tag, set(out) ^ set(want))
+            for k in want:
+                close(out[k], want[k], 2e-6)
+
+
+@pytest.mark.parametrize("scale", [1, 3])
+def test_render_rays_gradients(golden, scale):
+    g = golden("render_rays")
+    rays, ts, rng, ea, et = _e2e_inputs(g)
+    pc = syn.make_field_params(41, "coarse", weight_scale=float(scale))
+    pf = syn.make_field_params(42, "fine", True, True, weight_scale=float(scale))
+    named = [(f"coarse.{k}", v) for k, v in pc.items()] + [(f"fine.{k}", v) for k, v in pf.items()] \
+        + [("emb_a", ea), ("emb_t", et)]
+    for _, v in named:
+        v.requires_grad_(True)
+    out = O.render_rays(pc, pf, ea, et, rays, ts, n_samples=64, n_importance=64, perturb=1.0,
+                        noise_std=0.0, white_back=True, encode_a=True, encode_t=True, beta_min=0.1,
+                        rng=rng)
+    loss = sum(O.nerfw_loss(out, g["targets"]).values())
+    tag = f"nerfw_train_s{scale}"
+    assert abs(loss.item() - g[tag + "/loss"].item()) < 1e-5
+    grads = torch.autograd.grad(loss, [v for _, v in named])
+    for (k, _), gr in zip(named, grads):
+        ref_norm = g[f"{tag}/grad_norm/{k}"]
+        assert abs(gr.norm().item() - ref_norm.item()) <= 1e-4 * max(ref_norm.item(), 1e-6) + 1e-9, k
+        ref_head = g[f"{tag}/grad_head/{k}"]
+        close(gr.flatten()[:32], ref_head, 1e-5 * max(1.0, ref_head.abs().max().item()))
