@@ -1,0 +1,229 @@
+/*
+ * nerfw_b200.h -- C ABI of the B200-native NeRF-W per-ray hot path.
+ *
+ * The reference (nmerty/nerf-fl) is pure Python on top of ATen; it has no FFI of its own, so
+ * every entry point below cites the reference Python lines whose work it replaces (paths relative
+ * to /root/reference).  The binding a maintainer adds is a ctypes stub -- see INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain pointers + sizes, no torch types; all pointers are DEVICE pointers unless noted
+ *   - every call is stream-ordered on `stream` (a cudaStream_t passed as void*), never syncs the
+ *     device, never allocates: the caller owns every buffer (workspaces included)
+ *   - return 0 on success, <0 on error (NWB_E_*); nwb_last_error() gives the thread-local text
+ *   - fp32 row-major tensors unless stated; "image" buffers are opaque bf16 tile images whose
+ *     size is given by the nwb_*_bytes() queries
+ */
+#ifndef NERFW_B200_H
+#define NERFW_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NWB_OK 0
+#define NWB_E_ARG (-1)      /* bad argument / unsupported shape                     */
+#define NWB_E_CUDA (-2)     /* a CUDA runtime call or launch failed                 */
+#define NWB_E_RANGE (-3)    /* embedding index out of range (README.md:124 hazard)  */
+
+int nwb_abi_version(void);
+const char* nwb_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (a1) coarse depth sampling -- models/rendering.py:244-259
+ * rays: (n_rays, ray_stride>=8) [o3 d3 near far]; z_out: (n_rays, n_samples).
+ * perturb>0: stratified jitter with `perturb_rand` (n_rays,n_samples) U[0,1) if non-NULL, else an
+ * in-kernel Philox4x32-10 stream keyed by `seed`.
+ * ---------------------------------------------------------------------------------------- */
+int nwb_sample_coarse(const float* rays, int ray_stride, int n_rays, int n_samples, int use_disp,
+                      float perturb, const float* perturb_rand, uint64_t seed, float* z_out,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (a2) PosEmbedding.forward -- models/nerf.py:19-32 (logscale freqs 2^k, nerf.py:15)
+ * x: (n, 3) -> out: (n, 3 + 6*n_freqs)
+ * ---------------------------------------------------------------------------------------- */
+int nwb_posenc(const float* x, int64_t n, int n_freqs, float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (a6) sample_pdf + merge -- models/rendering.py:7-46 and :267-272
+ * z_coarse, w_coarse: (n_rays, n_samples).  bins = midpoints, weights = w_coarse[:,1:-1].
+ * det!=0: u = linspace(0,1,n_importance); else u (n_rays,n_importance) if non-NULL, else Philox.
+ * z_out: (n_rays, n_samples + n_importance) sorted ascending.
+ * Optional debug outputs (may be NULL): z_new (n_rays,n_importance) unsorted samples,
+ * inds (n_rays,n_importance) int64 searchsorted(right) indices.
+ * cdf_in (may be NULL): (n_rays, n_samples-1) externally supplied CDF used instead of the one
+ * built in-kernel (the "bit-exact given identical CDFs" contract).
+ * ---------------------------------------------------------------------------------------- */
+int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse, int n_rays, int n_samples,
+                         int n_importance, int det, const float* u, uint64_t seed,
+                         const float* cdf_in, float* z_out, float* z_new, int64_t* inds,
+                         void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (a5) volume rendering -- models/rendering.py:141-226
+ * raw: (n_rays, S, C) with C = 1 (sigma only), 4 (rgb,sigma) or 9 (+rgb_t,sigma_t,beta).
+ * ---------------------------------------------------------------------------------------- */
+#define NWB_COMP_TRANSIENT 1u   /* C==9 and output_transient                     */
+#define NWB_COMP_WHITE_BACK 2u
+#define NWB_COMP_TEST_TIME 4u
+#define NWB_COMP_COARSE 8u      /* typ == 'coarse' (test_time: weights/opacity only) */
+
+typedef struct nwb_composite_out {
+    float* weights;          /* (n,S)  weights_{typ}                    rendering.py:162,165 */
+    float* opacity;          /* (n)    opacity_{typ}                    :163,166             */
+    float* rgb;              /* (n,3)  rgb_{typ}; transient: rgb_fine   :190,219-223         */
+    float* depth;            /* (n)    depth_{typ}                      :225                 */
+    float* transient_sigmas; /* (n,S)                                   :168                 */
+    float* beta;             /* (n)    incl. +beta_min                  :182-185             */
+    float* rgb_static;       /* (n,3)  _rgb_fine_static                 :174-177,188         */
+    float* rgb_transient;    /* (n,3)  _rgb_fine_transient              :179-181,189         */
+    float* tt_rgb_static;    /* (n,3)  rgb_fine_static    (test_time)   :196-205             */
+    float* tt_depth_static;  /* (n)    depth_fine_static                :206-207             */
+    float* tt_rgb_transient; /* (n,3)  rgb_fine_transient               :209-215             */
+    float* tt_depth_transient; /* (n)  depth_fine_transient             :216-217             */
+} nwb_composite_out;
+
+int nwb_composite_fwd(const float* raw, int C, const float* z, const float* noise,
+                      float noise_std, int n_rays, int S, uint32_t flags, float beta_min,
+                      const nwb_composite_out* out, void* stream);
+
+/* cotangents of the training-mode outputs (NULL = zero).  d_raw: (n_rays,S,C) is overwritten. */
+typedef struct nwb_composite_grads {
+    const float* d_weights;          /* (n,S) */
+    const float* d_opacity;          /* (n)   */
+    const float* d_rgb;              /* (n,3) rgb_{typ} / rgb_fine */
+    const float* d_depth;            /* (n)   */
+    const float* d_transient_sigmas; /* (n,S) */
+    const float* d_beta;             /* (n)   */
+    const float* d_rgb_static;       /* (n,3) _rgb_fine_static    */
+    const float* d_rgb_transient;    /* (n,3) _rgb_fine_transient */
+} nwb_composite_grads;
+
+int nwb_composite_bwd(const float* raw, int C, const float* z, const float* noise,
+                      float noise_std, int n_rays, int S, uint32_t flags,
+                      const nwb_composite_grads* g, float* d_raw, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (a3,a4) field network -- models/nerf.py:81-212 + the per-sample input assembly of
+ * models/rendering.py:96-139.  W=256, D=8, skips=[4] (the only shape the reference ever builds).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct nwb_field_desc {
+    int in_xyz;        /* 3+6*N_emb_xyz, <= 128                      nerf.py:83  */
+    int in_dir;        /* 3+6*N_emb_dir                              nerf.py:83  */
+    int in_a;          /* appearance width, 0 = no encode_appearance nerf.py:84  */
+    int in_t;          /* transient width,  0 = no encode_transient  nerf.py:85  */
+} nwb_field_desc;
+
+/* fp32 parameter pointers with the reference's state_dict names */
+typedef struct nwb_field_params {
+    const float* trunk_w[8];   /* xyz_encoding_{1..8}.0.weight  (256, in) */
+    const float* trunk_b[8];   /* xyz_encoding_{1..8}.0.bias              */
+    const float* final_w;      /* xyz_encoding_final.weight (256,256)     */
+    const float* final_b;
+    const float* dir_w;        /* dir_encoding.0.weight (128, 256+in_dir+in_a) */
+    const float* dir_b;
+    const float* sigma_w;      /* static_sigma.0 (1,256) */
+    const float* sigma_b;
+    const float* rgb_w;        /* static_rgb.0 (3,128) */
+    const float* rgb_b;
+    const float* tenc_w[4];    /* transient_encoding.{0,2,4,6}.weight */
+    const float* tenc_b[4];
+    const float* tsigma_w;     /* transient_sigma.0 (1,128) */
+    const float* tsigma_b;
+    const float* trgb_w;       /* transient_rgb.0 (3,128) */
+    const float* trgb_b;
+    const float* tbeta_w;      /* transient_beta.0 (1,128) */
+    const float* tbeta_b;
+} nwb_field_params;
+
+/* same layout, mutable: gradient sinks (accumulated into, caller zeroes) */
+typedef struct nwb_field_grads {
+    float* trunk_w[8];
+    float* trunk_b[8];
+    float* final_w;
+    float* final_b;
+    float* dir_w;
+    float* dir_b;
+    float* sigma_w;
+    float* sigma_b;
+    float* rgb_w;
+    float* rgb_b;
+    float* tenc_w[4];
+    float* tenc_b[4];
+    float* tsigma_w;
+    float* tsigma_b;
+    float* trgb_w;
+    float* trgb_b;
+    float* tbeta_w;
+    float* tbeta_b;
+} nwb_field_grads;
+
+/* bytes of the packed operand cache (bf16 swizzled weight slabs + fp32 head/bias block) */
+size_t nwb_field_pack_bytes(const nwb_field_desc* d);
+/* (re)build the packed cache from fp32 parameters; call after every optimizer step */
+int nwb_field_pack(const nwb_field_desc* d, const nwb_field_params* p, void* packed, void* stream);
+
+/* modes of one field evaluation */
+#define NWB_MLP_SIGMA_ONLY 1u   /* NeRF.forward(sigma_only=True)            nerf.py:191-192 */
+#define NWB_MLP_TRANSIENT 2u    /* output_transient=True                    nerf.py:200-212 */
+#define NWB_MLP_SAVE 4u         /* keep activations for the backward pass                   */
+
+/* per-ray operands of dir_encoding / transient_encoding.0: gathers embedding rows, encodes the
+ * view direction and folds them through the matching weight columns into per-ray bias vectors
+ * (rendering.py:113-130 repeat+cat, never materialised per sample).
+ *   dirs      (n_rays, dir_stride) raw directions (PosEmbedding applied here, n_freq_dir) or, if
+ *             dir_is_encoded, already-encoded (n_rays, in_dir) rows
+ *   a_rows/t_rows: (n_rays, in_a)/(n_rays, in_t) explicit rows (kwargs a_embedded/t_embedded,
+ *             rendering.py:277-285) or NULL to gather emb_a/emb_t[ts]
+ *   ray_feat  (n_rays, in_dir+in_a+in_t) fp32 out: [dir_enc | a | t], kept for the backward
+ *   ray_bias  (n_rays, 256) fp32 out: [dir bias (128) | transient bias (128)]
+ * returns NWB_E_RANGE if any ts is outside [0, n_vocab) (checked on device, reported via
+ * *err_flag, a device int the caller reads when it next syncs).
+ */
+int nwb_ray_consts_fwd(const nwb_field_desc* d, const nwb_field_params* p, const float* dirs,
+                       int dir_stride, int dir_is_encoded, int n_freq_dir, const int64_t* ts,
+                       const float* emb_a, const float* emb_t, int n_vocab, const float* a_rows,
+                       const float* t_rows, int n_rays, uint32_t mode, float* ray_feat,
+                       float* ray_bias, int* err_flag, void* stream);
+
+/* bytes of the saved-activation buffer of one nwb_mlp_fwd(NWB_MLP_SAVE) over n_points */
+size_t nwb_mlp_save_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode);
+
+/* fused field forward over n_rays*S points.
+ *   xyz source: either (rays, z) -- points o + d*z are generated and encoded in-kernel
+ *   (rendering.py:261,273 + nerf.py:27-32, n_freq_xyz) -- or x_enc (n_points, in_xyz) explicit
+ *   encoded rows (the NeRF.forward surface); exactly one of z / x_enc is non-NULL.
+ *   raw_out: (n_points, C) C = 1 | 4 | 9 by mode (column order nerf.py:198,209-212)
+ */
+int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const float* rays, int ray_stride,
+                const float* z, const float* x_enc, int n_freq_xyz, const float* ray_bias,
+                int n_rays, int S, uint32_t mode, float* raw_out, void* saved, void* stream);
+
+/* backward of nwb_mlp_fwd: d_raw (n_points, C) -> parameter gradients (accumulated) and the
+ * per-ray cotangent d_ray_bias (n_rays,256).  workspace: nwb_mlp_bwd_workspace_bytes(). */
+size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode);
+int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const nwb_field_params* p,
+                const float* d_raw, const void* saved, int n_rays, int S, uint32_t mode,
+                const nwb_field_grads* grads, float* d_ray_bias, void* workspace, void* stream);
+
+/* backward of nwb_ray_consts_fwd: d_ray_bias -> dir_encoding / transient_encoding.0 weight
+ * columns [256:] (+ their biases) and, scattered by ts, the embedding-table gradients. */
+int nwb_ray_consts_bwd(const nwb_field_desc* d, const nwb_field_params* p, const float* ray_feat,
+                       const float* d_ray_bias, const int64_t* ts, int n_vocab, int n_rays,
+                       uint32_t mode, const nwb_field_grads* grads, float* d_emb_a,
+                       float* d_emb_t, float* d_a_rows, float* d_t_rows, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T
+ * from bf16 tile images, through the same smem layouts / descriptors the field kernels use.
+ * ---------------------------------------------------------------------------------------- */
+int nwb_selftest_umma(const void* a_img, const void* b_img, int N, int K, int variant,
+                      const uint32_t* overrides /* host, may be NULL */, float* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERFW_B200_H */

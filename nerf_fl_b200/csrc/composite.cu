@@ -1,0 +1,341 @@
+// (a5) volume rendering, forward and backward -- models/rendering.py:141-226.
+// One warp per ray.  Per 32-sample chunk the warp pulls the AoS raw rows (C = 1|4|9 floats per
+// sample) through a coalesced, float4-vectorised copy into its shared-memory slab, each lane
+// then owns one sample; transmittance is a warp product-scan carried across chunks.  Backward
+// keeps T in shared memory and runs the division-free reverse suffix scan of SURVEY.md A.3.
+#include "common.cuh"
+#include <algorithm>
+
+namespace nwb {
+
+constexpr int kCompWarps = 4;
+
+__device__ __forceinline__ void stage_rows(float* slab, const float* __restrict__ src, int nfl, int lane) {
+    // nfl floats, contiguous; float4 path when the source is 16B aligned
+    if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (nfl & 3) == 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(slab);
+        for (int i = lane; i < (nfl >> 2); i += 32) d4[i] = __ldg(s4 + i);
+    } else {
+        for (int i = lane; i < nfl; i += 32) slab[i] = __ldg(src + i);
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ float excl_prod_scan(float om, float& carry, int lane) {
+    // returns carry * prod_{j<lane} om_j ; updates carry *= prod_{j<32} om_j
+    float p = om;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float t = __shfl_up_sync(0xffffffffu, p, o);
+        if (lane >= o) p *= t;
+    }
+    float ex = __shfl_up_sync(0xffffffffu, p, 1);
+    if (lane == 0) ex = 1.0f;
+    const float T = carry * ex;
+    carry *= __shfl_sync(0xffffffffu, p, 31);
+    return T;
+}
+
+template <int C>
+__global__ void __launch_bounds__(kCompWarps * 32)
+composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
+                     const float* __restrict__ noise, float noise_std, int n_rays, int S,
+                     uint32_t flags, float beta_min, nwb_composite_out o) {
+    __shared__ __align__(16) float slabs[kCompWarps][32 * C];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* slab = slabs[warp];
+    const bool transient = (C == 9) && (flags & NWB_COMP_TRANSIENT);
+    const bool white = flags & NWB_COMP_WHITE_BACK;
+    const bool test_time = flags & NWB_COMP_TEST_TIME;
+    const bool weights_only = (C == 1) || (test_time && (flags & NWB_COMP_COARSE));
+
+    for (int ray = blockIdx.x * kCompWarps + warp; ray < n_rays; ray += gridDim.x * kCompWarps) {
+        const int64_t row = static_cast<int64_t>(ray) * S;
+        float cT = 1.0f, cTs = 1.0f, cTt = 1.0f;
+        float opac = 0, depth = 0, beta = 0, sr = 0, sg = 0, sb = 0, tr = 0, tg = 0, tb = 0;
+        float xsr = 0, xsg = 0, xsb = 0, xsd = 0, xtr = 0, xtg = 0, xtb = 0, xtd = 0;
+        for (int base = 0; base < S; base += 32) {
+            const int cnt = min(32, S - base);
+            stage_rows(slab, raw + (row + base) * C, cnt * C, lane);
+            const int i = base + lane;
+            const bool live = lane < cnt;
+            float zi = 0, delta = 0, sig_s = 0, sig_t = 0, cr = 0, cg = 0, cb = 0, qr = 0, qg = 0, qb = 0, bt = 0;
+            if (live) {
+                zi = __ldg(z + row + i);
+                delta = (i + 1 < S) ? __fsub_rn(__ldg(z + row + i + 1), zi) : 1e2f;
+                const float* v = slab + lane * C;
+                if (C == 1) {
+                    sig_s = v[0];
+                } else {
+                    cr = v[0]; cg = v[1]; cb = v[2]; sig_s = v[3];
+                }
+                if (C == 9) { qr = v[4]; qg = v[5]; qb = v[6]; sig_t = v[7]; bt = v[8]; }
+            }
+            __syncwarp();
+            float alpha, a_s = 0, a_t = 0;
+            if (transient) {
+                a_s = __fsub_rn(1.0f, expf(-__fmul_rn(delta, sig_s)));
+                a_t = __fsub_rn(1.0f, expf(-__fmul_rn(delta, sig_t)));
+                alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, __fadd_rn(sig_s, sig_t))));
+            } else {
+                float s = sig_s;
+                if (noise != nullptr && live) s = __fadd_rn(s, __fmul_rn(__ldg(noise + row + i), noise_std));
+                alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, fmaxf(s, 0.0f))));
+            }
+            if (!live) { alpha = 0; a_s = 0; a_t = 0; }
+            const float T = excl_prod_scan(__fsub_rn(1.0f, alpha), cT, lane);
+            const float w = alpha * T;
+            if (live) {
+                if (o.weights) o.weights[row + i] = w;
+                if (transient && o.transient_sigmas) o.transient_sigmas[row + i] = sig_t;
+            }
+            opac += w;
+            if (!weights_only) {
+                depth += w * zi;
+                if (transient) {
+                    const float ws = a_s * T, wt = a_t * T;
+                    sr += ws * cr; sg += ws * cg; sb += ws * cb;
+                    tr += wt * qr; tg += wt * qg; tb += wt * qb;
+                    beta += wt * bt;
+                    if (test_time) {
+                        const float Ts = excl_prod_scan(__fsub_rn(1.0f, a_s), cTs, lane);
+                        const float Tt = excl_prod_scan(__fsub_rn(1.0f, a_t), cTt, lane);
+                        const float w1 = a_s * Ts, w2 = a_t * Tt;
+                        xsr += w1 * cr; xsg += w1 * cg; xsb += w1 * cb; xsd += w1 * zi;
+                        xtr += w2 * qr; xtg += w2 * qg; xtb += w2 * qb; xtd += w2 * zi;
+                    }
+                } else {
+                    sr += w * cr; sg += w * cg; sb += w * cb;
+                }
+            }
+        }
+        opac = warp_sum(opac);
+        if (lane == 0 && o.opacity) o.opacity[ray] = opac;
+        if (weights_only) continue;
+        depth = warp_sum(depth);
+        sr = warp_sum(sr); sg = warp_sum(sg); sb = warp_sum(sb);
+        const float bg = white ? (1.0f - opac) : 0.0f;
+        if (transient) {
+            tr = warp_sum(tr); tg = warp_sum(tg); tb = warp_sum(tb);
+            beta = warp_sum(beta);
+            if (test_time) {
+                xsr = warp_sum(xsr); xsg = warp_sum(xsg); xsb = warp_sum(xsb); xsd = warp_sum(xsd);
+                xtr = warp_sum(xtr); xtg = warp_sum(xtg); xtb = warp_sum(xtb); xtd = warp_sum(xtd);
+            }
+            if (lane == 0) {
+                const float mr = sr + bg, mg = sg + bg, mb = sb + bg;
+                if (o.rgb_static) { o.rgb_static[ray * 3 + 0] = mr; o.rgb_static[ray * 3 + 1] = mg; o.rgb_static[ray * 3 + 2] = mb; }
+                if (o.rgb_transient) { o.rgb_transient[ray * 3 + 0] = tr; o.rgb_transient[ray * 3 + 1] = tg; o.rgb_transient[ray * 3 + 2] = tb; }
+                if (o.rgb) { o.rgb[ray * 3 + 0] = mr + tr; o.rgb[ray * 3 + 1] = mg + tg; o.rgb[ray * 3 + 2] = mb + tb; }
+                if (o.beta) o.beta[ray] = beta + beta_min;
+                if (o.depth) o.depth[ray] = depth;
+                if (test_time) {
+                    // static-only map keeps the COMBINED opacity in its white-back term (:203-204)
+                    if (o.tt_rgb_static) { o.tt_rgb_static[ray * 3 + 0] = xsr + bg; o.tt_rgb_static[ray * 3 + 1] = xsg + bg; o.tt_rgb_static[ray * 3 + 2] = xsb + bg; }
+                    if (o.tt_depth_static) o.tt_depth_static[ray] = xsd;
+                    if (o.tt_rgb_transient) { o.tt_rgb_transient[ray * 3 + 0] = xtr; o.tt_rgb_transient[ray * 3 + 1] = xtg; o.tt_rgb_transient[ray * 3 + 2] = xtb; }
+                    if (o.tt_depth_transient) o.tt_depth_transient[ray] = xtd;
+                }
+            }
+        } else if (lane == 0) {
+            if (o.rgb) { o.rgb[ray * 3 + 0] = sr + bg; o.rgb[ray * 3 + 1] = sg + bg; o.rgb[ray * 3 + 2] = sb + bg; }
+            if (o.depth) o.depth[ray] = depth;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward.  With G_j the cotangent reaching each weight kind and q_j = G w + Gs ws + Gt wt,
+//   dL/dsigma^x_j = delta_j * [ T_j (G_j e_j + G^x_j e^x_j) - sum_{k>j} q_k ]     
+// pass 1 (forward order): recompute T, stash T_j in smem; pass 2 (reverse order): suffix scan.
+// dynamic smem per warp: 32*C staging floats + S floats of T.
+// ------------------------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(kCompWarps * 32)
+composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
+                     const float* __restrict__ noise, float noise_std, int n_rays, int S,
+                     uint32_t flags, nwb_composite_grads g, float* __restrict__ d_raw) {
+    extern __shared__ __align__(16) float dsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int Sp = (S + 3) & ~3;
+    float* slab = dsm + warp * (32 * C + Sp);
+    float* Tbuf = slab + 32 * C;
+    const bool transient = (C == 9) && (flags & NWB_COMP_TRANSIENT);
+    const bool white = flags & NWB_COMP_WHITE_BACK;
+
+    for (int ray = blockIdx.x * kCompWarps + warp; ray < n_rays; ray += gridDim.x * kCompWarps) {
+        const int64_t row = static_cast<int64_t>(ray) * S;
+        // per-ray cotangents
+        const float g_op = g.d_opacity ? __ldg(g.d_opacity + ray) : 0.0f;
+        const float g_dp = g.d_depth ? __ldg(g.d_depth + ray) : 0.0f;
+        const float g_be = (transient && g.d_beta) ? __ldg(g.d_beta + ray) : 0.0f;
+        float Gs[3], Gt[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float gr = g.d_rgb ? __ldg(g.d_rgb + ray * 3 + c) : 0.0f;
+            Gs[c] = gr + ((transient && g.d_rgb_static) ? __ldg(g.d_rgb_static + ray * 3 + c) : 0.0f);
+            Gt[c] = gr + ((transient && g.d_rgb_transient) ? __ldg(g.d_rgb_transient + ray * 3 + c) : 0.0f);
+        }
+        const float g_bg = white ? -(Gs[0] + Gs[1] + Gs[2]) : 0.0f;   // d(1 - sum w)/dw
+
+        // pass 1: transmittance
+        float cT = 1.0f;
+        for (int base = 0; base < S; base += 32) {
+            const int i = base + lane;
+            const bool live = i < S;
+            float alpha = 0.0f;
+            if (live) {
+                const float zi = __ldg(z + row + i);
+                const float delta = (i + 1 < S) ? __fsub_rn(__ldg(z + row + i + 1), zi) : 1e2f;
+                float s;
+                if (C == 1) s = __ldg(raw + row + i);
+                else s = __ldg(raw + (row + i) * C + 3);
+                if (transient) s = __fadd_rn(s, __ldg(raw + (row + i) * C + 7));
+                else {
+                    if (noise != nullptr) s = __fadd_rn(s, __fmul_rn(__ldg(noise + row + i), noise_std));
+                    s = fmaxf(s, 0.0f);
+                }
+                alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, s)));
+            }
+            const float T = excl_prod_scan(__fsub_rn(1.0f, alpha), cT, lane);
+            if (live) Tbuf[i] = T;
+        }
+        __syncwarp();
+
+        // pass 2: reverse chunks, suffix sums of q
+        float suffix = 0.0f;   // sum of q over all samples after the current chunk
+        const int last_base = ((S - 1) / 32) * 32;
+        for (int base = last_base; base >= 0; base -= 32) {
+            const int cnt = min(32, S - base);
+            stage_rows(slab, raw + (row + base) * C, cnt * C, lane);
+            const int i = base + lane;
+            const bool live = lane < cnt;
+            float q = 0.0f, dsig_s = 0.0f, dsig_t = 0.0f, dcs[3] = {0, 0, 0}, dct[3] = {0, 0, 0}, dbeta = 0.0f;
+            float delta = 0, T = 0, head_s = 0, head_t = 0;
+            bool pass_s = true;
+            if (live) {
+                const float* v = slab + lane * C;
+                const float zi = __ldg(z + row + i);
+                delta = (i + 1 < S) ? __fsub_rn(__ldg(z + row + i + 1), zi) : 1e2f;
+                T = Tbuf[i];
+                float Gw = g_op + g_dp * zi + g_bg + (g.d_weights ? __ldg(g.d_weights + row + i) : 0.0f);
+                if (transient) {
+                    const float ss = v[3], st = v[7];
+                    const float es = expf(-__fmul_rn(delta, ss)), et = expf(-__fmul_rn(delta, st));
+                    const float e = expf(-__fmul_rn(delta, __fadd_rn(ss, st)));
+                    const float ws = (1.0f - es) * T, wt = (1.0f - et) * T, w = (1.0f - e) * T;
+                    const float Gws = Gs[0] * v[0] + Gs[1] * v[1] + Gs[2] * v[2];
+                    const float Gwt = Gt[0] * v[4] + Gt[1] * v[5] + Gt[2] * v[6] + g_be * v[8];
+                    q = Gw * w + Gws * ws + Gwt * wt;
+                    head_s = T * (Gw * e + Gws * es);
+                    head_t = T * (Gw * e + Gwt * et);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) { dcs[c] = ws * Gs[c]; dct[c] = wt * Gt[c]; }
+                    dbeta = wt * g_be;
+                } else {
+                    float s = (C == 1) ? v[0] : v[3];
+                    if (noise != nullptr) s = __fadd_rn(s, __fmul_rn(__ldg(noise + row + i), noise_std));
+                    pass_s = s > 0.0f;
+                    const float e = expf(-__fmul_rn(delta, fmaxf(s, 0.0f)));
+                    const float w = (1.0f - e) * T;
+                    if (C != 1) {
+                        Gw += Gs[0] * v[0] + Gs[1] * v[1] + Gs[2] * v[2];
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) dcs[c] = w * Gs[c];
+                    }
+                    q = Gw * w;
+                    head_s = T * Gw * e;
+                }
+            }
+            __syncwarp();
+            // exclusive suffix sum within the chunk (lanes above me) + carried suffix
+            float incl = q;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const float t = __shfl_down_sync(0xffffffffu, incl, o);
+                if (lane + o < 32) incl += t;
+            }
+            const float R = suffix + (incl - q);
+            suffix += __shfl_sync(0xffffffffu, incl, 0);
+            if (live) {
+                dsig_s = pass_s ? delta * (head_s - R) : 0.0f;
+                float* v = slab + lane * C;
+                if (C == 1) {
+                    v[0] = dsig_s;
+                } else {
+                    v[0] = dcs[0]; v[1] = dcs[1]; v[2] = dcs[2]; v[3] = dsig_s;
+                }
+                if (C == 9) {
+                    if (transient) {
+                        dsig_t = delta * (head_t - R) + (g.d_transient_sigmas ? __ldg(g.d_transient_sigmas + row + i) : 0.0f);
+                        v[4] = dct[0]; v[5] = dct[1]; v[6] = dct[2]; v[7] = dsig_t; v[8] = dbeta;
+                    } else {
+                        v[4] = v[5] = v[6] = v[7] = v[8] = 0.0f;
+                    }
+                }
+            }
+            __syncwarp();
+            // coalesced write-back of the chunk's d_raw rows
+            float* dst = d_raw + (row + base) * C;
+            const int nfl = cnt * C;
+            if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0 && (nfl & 3) == 0) {
+                for (int k = lane; k < (nfl >> 2); k += 32)
+                    reinterpret_cast<float4*>(dst)[k] = reinterpret_cast<const float4*>(slab)[k];
+            } else {
+                for (int k = lane; k < nfl; k += 32) dst[k] = slab[k];
+            }
+            __syncwarp();
+        }
+    }
+}
+
+}  // namespace nwb
+
+using namespace nwb;
+
+extern "C" int nwb_composite_fwd(const float* raw, int C, const float* z, const float* noise,
+                                 float noise_std, int n_rays, int S, uint32_t flags,
+                                 float beta_min, const nwb_composite_out* out, void* stream) {
+    NWB_REQUIRE(raw && z && out, "nwb_composite_fwd: null pointer");
+    NWB_REQUIRE(C == 1 || C == 4 || C == 9, "nwb_composite_fwd: C must be 1, 4 or 9 (got %d)", C);
+    NWB_REQUIRE(S >= 1 && n_rays >= 0, "nwb_composite_fwd: bad shape");
+    NWB_REQUIRE(!(flags & NWB_COMP_TRANSIENT) || C == 9, "nwb_composite_fwd: transient needs C==9");
+    if (n_rays == 0) return NWB_OK;
+    const int blocks = std::min((n_rays + kCompWarps - 1) / kCompWarps, kNumSMs * 16);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (C == 1) composite_fwd_kernel<1><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out);
+    else if (C == 4) composite_fwd_kernel<4><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out);
+    else composite_fwd_kernel<9><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
+extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const float* noise,
+                                 float noise_std, int n_rays, int S, uint32_t flags,
+                                 const nwb_composite_grads* g, float* d_raw, void* stream) {
+    NWB_REQUIRE(raw && z && g && d_raw, "nwb_composite_bwd: null pointer");
+    NWB_REQUIRE(C == 1 || C == 4 || C == 9, "nwb_composite_bwd: C must be 1, 4 or 9 (got %d)", C);
+    NWB_REQUIRE(S >= 1 && n_rays >= 0, "nwb_composite_bwd: bad shape");
+    NWB_REQUIRE(!(flags & NWB_COMP_TEST_TIME), "nwb_composite_bwd: test_time outputs carry no gradient");
+    NWB_REQUIRE(!(flags & NWB_COMP_TRANSIENT) || C == 9, "nwb_composite_bwd: transient needs C==9");
+    if (n_rays == 0) return NWB_OK;
+    const int blocks = std::min((n_rays + kCompWarps - 1) / kCompWarps, kNumSMs * 16);
+    const size_t smem = static_cast<size_t>(kCompWarps) * (32 * C + ((S + 3) & ~3)) * sizeof(float);
+    NWB_REQUIRE(smem <= 200 * 1024, "nwb_composite_bwd: S too large for shared memory");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define NWB_BWD(CC)                                                                                 \
+    do {                                                                                            \
+        if (smem > 48 * 1024)                                                                       \
+            NWB_CUDA(cudaFuncSetAttribute(composite_bwd_kernel<CC>,                                 \
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        composite_bwd_kernel<CC><<<blocks, kCompWarps * 32, smem, st>>>(raw, z, noise, noise_std,   \
+                                                                        n_rays, S, flags, *g, d_raw); \
+    } while (0)
+    if (C == 1) NWB_BWD(1);
+    else if (C == 4) NWB_BWD(4);
+    else NWB_BWD(9);
+#undef NWB_BWD
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}

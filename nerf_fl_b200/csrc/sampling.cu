@@ -1,0 +1,234 @@
+// (a1) coarse depth sampling, (a2) standalone PosEmbedding, (a6) sample_pdf + merge.
+// HBM-bound integer/float work: coalesced loads, one warp per ray, everything else in smem/regs.
+#include "common.cuh"
+#include <math.h>
+#include <algorithm>
+
+namespace nwb {
+
+// ------------------------------------------------------------------------------------------------
+// (a1) models/rendering.py:244-259.  One thread per (ray, sample); z written coalesced.
+// Explicit round-to-nearest intrinsics keep the op order of the reference's separate ATen ops
+// (no FMA contraction), so z is bit-identical to the oracle's.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float coarse_z(float near, float far, int i, int n, bool disp) {
+    const float s = linspace01(i, n);
+    const float oms = __fsub_rn(1.0f, s);
+    if (!disp) return __fadd_rn(__fmul_rn(near, oms), __fmul_rn(far, s));
+    const float a = __fmul_rn(__fdiv_rn(1.0f, near), oms);
+    const float b = __fmul_rn(__fdiv_rn(1.0f, far), s);
+    return __fdiv_rn(1.0f, __fadd_rn(a, b));
+}
+
+__global__ void __launch_bounds__(256)
+sample_coarse_kernel(const float* __restrict__ rays, int ray_stride, int n_rays, int n_samples,
+                     int use_disp, float perturb, const float* __restrict__ perturb_rand,
+                     uint64_t seed, float* __restrict__ z_out) {
+    const int64_t total = static_cast<int64_t>(n_rays) * n_samples;
+    for (int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; idx < total;
+         idx += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int r = static_cast<int>(idx / n_samples);
+        const int i = static_cast<int>(idx - static_cast<int64_t>(r) * n_samples);
+        const float near = __ldg(rays + static_cast<int64_t>(r) * ray_stride + 6);
+        const float far = __ldg(rays + static_cast<int64_t>(r) * ray_stride + 7);
+        float z = coarse_z(near, far, i, n_samples, use_disp != 0);
+        if (perturb > 0.0f) {
+            // lower/upper interval bounds around sample i (rendering.py:253-256)
+            const float zp = (i > 0) ? coarse_z(near, far, i - 1, n_samples, use_disp != 0) : z;
+            const float zn = (i + 1 < n_samples) ? coarse_z(near, far, i + 1, n_samples, use_disp != 0) : z;
+            const float lower = (i > 0) ? __fmul_rn(0.5f, __fadd_rn(zp, z)) : z;
+            const float upper = (i + 1 < n_samples) ? __fmul_rn(0.5f, __fadd_rn(z, zn)) : z;
+            float u;
+            if (perturb_rand != nullptr) {
+                u = __ldg(perturb_rand + idx);
+            } else {
+                const uint4 rnd = philox4x32(seed, static_cast<uint64_t>(idx) >> 2);
+                const uint32_t w = (idx & 3) == 0 ? rnd.x : (idx & 3) == 1 ? rnd.y : (idx & 3) == 2 ? rnd.z : rnd.w;
+                u = u01(w);
+            }
+            z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), __fmul_rn(perturb, u)));
+        }
+        z_out[idx] = z;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// (a2) models/nerf.py:19-32.  One thread per output element -> fully coalesced stores; sinf/cosf
+// are the accurate libdevice versions (arguments reach 2^14*|x| rad; no fast-math).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+posenc_kernel(const float* __restrict__ x, int64_t n, int n_freqs, float* __restrict__ out) {
+    const int width = 3 + 6 * n_freqs;
+    const int64_t total = n * width;
+    for (int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; idx < total;
+         idx += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t b = idx / width;
+        const int c = static_cast<int>(idx - b * width);
+        float v;
+        if (c < 3) {
+            v = __ldg(x + b * 3 + c);
+        } else {
+            const int k = (c - 3) / 6, r = (c - 3) % 6;
+            const float arg = __fmul_rn(__ldg(x + b * 3 + (r % 3)), exp2f(static_cast<float>(k)));
+            v = (r < 3) ? sinf(arg) : cosf(arg);
+        }
+        out[idx] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// (a6) models/rendering.py:7-46 + :267-272.  One warp per ray:
+//   stage z / w rows in smem (coalesced), warp-scan the CDF, per-lane binary search
+//   (searchsorted right=True), inverse-CDF lerp, then a warp bitonic sort of [z_coarse | z_new].
+// smem per warp: cdf[Ns-1], bins[Ns-1], keys[P] with P = next_pow2(Ns+Ni).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse,
+                        int n_rays, int Ns, int Ni, int det, const float* __restrict__ u_in,
+                        uint64_t seed, const float* __restrict__ cdf_in, float* __restrict__ z_out,
+                        float* __restrict__ z_new_out, int64_t* __restrict__ inds_out, int P) {
+    extern __shared__ float smem[];
+    const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int M = Ns - 2;        // number of pdf bins (weights[:,1:-1])
+    const int nb = Ns - 1;       // number of bin edges == cdf entries
+    const int per_warp = 2 * nb + P;
+    float* cdf = smem + warp * per_warp;
+    float* bins = cdf + nb;
+    float* keys = bins + nb;
+    const float eps = 1e-5f;
+
+    for (int ray = blockIdx.x * warps + warp; ray < n_rays; ray += gridDim.x * warps) {
+        const float* zr = z_coarse + static_cast<int64_t>(ray) * Ns;
+        const float* wr = w_coarse + static_cast<int64_t>(ray) * Ns;
+        // z row -> keys[0..Ns), midpoints -> bins
+        for (int i = lane; i < Ns; i += 32) keys[i] = __ldg(zr + i);
+        __syncwarp();
+        for (int i = lane; i < nb; i += 32) bins[i] = __fmul_rn(0.5f, __fadd_rn(keys[i], keys[i + 1]));
+        // pdf normaliser
+        float part = 0.0f;
+        for (int i = lane; i < M; i += 32) part += __ldg(wr + 1 + i) + eps;
+        const float total = warp_sum(part);
+        // cdf = [0, cumsum(pdf)]
+        if (cdf_in != nullptr) {
+            for (int i = lane; i < nb; i += 32) cdf[i] = __ldg(cdf_in + static_cast<int64_t>(ray) * nb + i);
+        } else {
+            float carry = 0.0f;
+            if (lane == 0) cdf[0] = 0.0f;
+            for (int base = 0; base < M; base += 32) {
+                const int i = base + lane;
+                float v = (i < M) ? __fdiv_rn(__ldg(wr + 1 + i) + eps, total) : 0.0f;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const float t = __shfl_up_sync(0xffffffffu, v, o);
+                    if (lane >= o) v += t;
+                }
+                v += carry;
+                if (i < M) cdf[i + 1] = v;
+                carry = __shfl_sync(0xffffffffu, v, 31);
+            }
+        }
+        __syncwarp();
+        // inverse-CDF samples
+        for (int j = lane; j < Ni; j += 32) {
+            float u;
+            if (det) {
+                u = linspace01(j, Ni);
+            } else if (u_in != nullptr) {
+                u = __ldg(u_in + static_cast<int64_t>(ray) * Ni + j);
+            } else {
+                const uint64_t ctr = static_cast<uint64_t>(ray) * Ni + j;
+                const uint4 rnd = philox4x32(seed ^ 0x5DEECE66DULL, ctr >> 2);
+                const uint32_t w = (ctr & 3) == 0 ? rnd.x : (ctr & 3) == 1 ? rnd.y : (ctr & 3) == 2 ? rnd.z : rnd.w;
+                u = u01(w);
+            }
+            // first index with cdf[idx] > u  (searchsorted right=True), idx in [0, nb]
+            int lo = 0, hi = nb;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (cdf[mid] > u) hi = mid; else lo = mid + 1;
+            }
+            const int below = max(lo - 1, 0);
+            const int above = min(lo, M);
+            const float c0 = cdf[below], c1 = cdf[above];
+            const float b0 = bins[below], b1 = bins[above];
+            float denom = __fsub_rn(c1, c0);
+            if (denom < eps) denom = 1.0f;
+            const float t = __fdiv_rn(__fsub_rn(u, c0), denom);
+            const float s = __fadd_rn(b0, __fmul_rn(t, __fsub_rn(b1, b0)));
+            keys[Ns + j] = s;
+            if (z_new_out != nullptr) z_new_out[static_cast<int64_t>(ray) * Ni + j] = s;
+            if (inds_out != nullptr) inds_out[static_cast<int64_t>(ray) * Ni + j] = lo;
+        }
+        for (int i = Ns + Ni + lane; i < P; i += 32) keys[i] = INFINITY;
+        __syncwarp();
+        // warp bitonic sort of P keys in smem
+        for (int k = 2; k <= P; k <<= 1) {
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int t = lane; t < (P >> 1); t += 32) {
+                    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));   // index with bit j clear
+                    const int l = i | j;
+                    const bool up = ((i & k) == 0);
+                    const float a = keys[i], b = keys[l];
+                    if ((a > b) == up) { keys[i] = b; keys[l] = a; }
+                }
+                __syncwarp();
+            }
+        }
+        float* zo = z_out + static_cast<int64_t>(ray) * (Ns + Ni);
+        for (int i = lane; i < Ns + Ni; i += 32) zo[i] = keys[i];
+        __syncwarp();
+    }
+}
+
+}  // namespace nwb
+
+using namespace nwb;
+
+extern "C" int nwb_sample_coarse(const float* rays, int ray_stride, int n_rays, int n_samples,
+                                 int use_disp, float perturb, const float* perturb_rand,
+                                 uint64_t seed, float* z_out, void* stream) {
+    NWB_REQUIRE(rays && z_out, "nwb_sample_coarse: null pointer");
+    NWB_REQUIRE(ray_stride >= 8 && n_rays >= 0 && n_samples >= 1, "nwb_sample_coarse: bad shape");
+    if (n_rays == 0) return NWB_OK;
+    const int64_t total = static_cast<int64_t>(n_rays) * n_samples;
+    const int blocks = static_cast<int>(std::min<int64_t>((total + 255) / 256, kNumSMs * 8));
+    sample_coarse_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        rays, ray_stride, n_rays, n_samples, use_disp, perturb, perturb_rand, seed, z_out);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
+extern "C" int nwb_posenc(const float* x, int64_t n, int n_freqs, float* out, void* stream) {
+    NWB_REQUIRE(x && out, "nwb_posenc: null pointer");
+    NWB_REQUIRE(n >= 0 && n_freqs >= 0 && n_freqs <= 24, "nwb_posenc: bad shape");
+    if (n == 0) return NWB_OK;
+    const int64_t total = n * (3 + 6 * n_freqs);
+    const int blocks = static_cast<int>(std::min<int64_t>((total + 255) / 256, kNumSMs * 8));
+    posenc_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, n_freqs, out);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
+extern "C" int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse, int n_rays,
+                                    int n_samples, int n_importance, int det, const float* u,
+                                    uint64_t seed, const float* cdf_in, float* z_out, float* z_new,
+                                    int64_t* inds, void* stream) {
+    NWB_REQUIRE(z_coarse && w_coarse && z_out, "nwb_sample_pdf_merge: null pointer");
+    NWB_REQUIRE(n_samples >= 3 && n_importance >= 1 && n_rays >= 0,
+                "nwb_sample_pdf_merge: need n_samples>=3, n_importance>=1");
+    NWB_REQUIRE(n_samples + n_importance <= 4096, "nwb_sample_pdf_merge: too many samples per ray");
+    if (n_rays == 0) return NWB_OK;
+    int P = 1;
+    while (P < n_samples + n_importance) P <<= 1;
+    const int warps = 4;
+    const size_t smem = static_cast<size_t>(warps) * (2 * (n_samples - 1) + P) * sizeof(float);
+    if (smem > 48 * 1024)
+        NWB_CUDA(cudaFuncSetAttribute(sample_pdf_merge_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const int blocks = std::min((n_rays + warps - 1) / warps, kNumSMs * 8);
+    sample_pdf_merge_kernel<<<blocks, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+        z_coarse, w_coarse, n_rays, n_samples, n_importance, det, u, seed, cdf_in, z_out, z_new,
+        inds, P);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}

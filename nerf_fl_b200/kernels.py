@@ -1,0 +1,155 @@
+"""Thin torch-tensor wrappers over the C ABI (one function per entry point).
+
+PyTorch is used for device memory and streams only; every computation below happens inside
+libnerfw_b200.so on the current CUDA stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.float().contiguous()
+
+
+def sample_coarse(rays: torch.Tensor, n_samples: int, use_disp: bool = False, perturb: float = 0.0,
+                  perturb_rand: torch.Tensor | None = None, seed: int = 0) -> torch.Tensor:
+    """z_vals (N, n_samples) of models/rendering.py:244-259."""
+    rays = _f32(rays)
+    n = rays.shape[0]
+    z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
+    pr = _f32(perturb_rand) if perturb_rand is not None else None
+    L.check(L.lib().nwb_sample_coarse(L.ptr(rays), rays.shape[1], n, n_samples, int(bool(use_disp)),
+                                      float(perturb), L.ptr(pr), int(seed) & (2 ** 64 - 1), L.ptr(z),
+                                      L.stream_ptr(rays.device)), "nwb_sample_coarse")
+    return z
+
+
+def posenc(x: torch.Tensor, n_freqs: int) -> torch.Tensor:
+    """PosEmbedding.forward, models/nerf.py:19-32."""
+    x = _f32(x)
+    assert x.dim() == 2 and x.shape[1] == 3, "PosEmbedding expects (B, 3)"
+    out = torch.empty(x.shape[0], 3 + 6 * n_freqs, device=x.device, dtype=torch.float32)
+    L.check(L.lib().nwb_posenc(L.ptr(x), x.shape[0], n_freqs, L.ptr(out), L.stream_ptr(x.device)),
+            "nwb_posenc")
+    return out
+
+
+def sample_pdf_merge(z_coarse: torch.Tensor, w_coarse: torch.Tensor, n_importance: int, det: bool,
+                     u: torch.Tensor | None = None, seed: int = 0, cdf: torch.Tensor | None = None,
+                     debug: bool = False):
+    """sort(cat[z, sample_pdf(mid(z), w[:,1:-1])]) of models/rendering.py:267-272 (+ :7-46)."""
+    z_coarse, w_coarse = _f32(z_coarse), _f32(w_coarse)
+    n, ns = z_coarse.shape
+    dev = z_coarse.device
+    z_out = torch.empty(n, ns + n_importance, device=dev, dtype=torch.float32)
+    z_new = torch.empty(n, n_importance, device=dev, dtype=torch.float32) if debug else None
+    inds = torch.empty(n, n_importance, device=dev, dtype=torch.int64) if debug else None
+    u_ = _f32(u) if u is not None else None
+    cdf_ = _f32(cdf) if cdf is not None else None
+    L.check(L.lib().nwb_sample_pdf_merge(L.ptr(z_coarse), L.ptr(w_coarse), n, ns, n_importance,
+                                         int(bool(det)), L.ptr(u_), int(seed) & (2 ** 64 - 1),
+                                         L.ptr(cdf_), L.ptr(z_out), L.ptr(z_new), L.ptr(inds),
+                                         L.stream_ptr(dev)), "nwb_sample_pdf_merge")
+    return (z_out, z_new, inds) if debug else z_out
+
+
+def composite_flags(transient: bool, white_back: bool, test_time: bool, coarse: bool) -> int:
+    return ((L.NWB_COMP_TRANSIENT if transient else 0) | (L.NWB_COMP_WHITE_BACK if white_back else 0)
+            | (L.NWB_COMP_TEST_TIME if test_time else 0) | (L.NWB_COMP_COARSE if coarse else 0))
+
+
+def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bool, white_back: bool,
+                  test_time: bool, beta_min: float = 0.0, noise: torch.Tensor | None = None,
+                  noise_std: float = 0.0) -> dict:
+    """One inference() compositing pass (models/rendering.py:141-226) -> result-dict entries."""
+    raw, z = _f32(raw), _f32(z)
+    n, S = z.shape
+    Cc = raw.shape[-1]
+    dev = z.device
+    new = lambda *s: torch.empty(*s, device=dev, dtype=torch.float32)  # noqa: E731
+    coarse = typ == "coarse"
+    res, o = {}, L.CompositeOut()
+    res[f"weights_{typ}"] = new(n, S)
+    res[f"opacity_{typ}"] = new(n)
+    o.weights, o.opacity = L.ptr(res[f"weights_{typ}"]), L.ptr(res[f"opacity_{typ}"])
+    if transient:
+        res["transient_sigmas"] = new(n, S)
+        o.transient_sigmas = L.ptr(res["transient_sigmas"])
+    if not (test_time and coarse) and Cc != 1:
+        if transient:
+            res["beta"] = new(n)
+            res["_rgb_fine_static"], res["_rgb_fine_transient"] = new(n, 3), new(n, 3)
+            res["rgb_fine"] = new(n, 3)
+            o.beta, o.rgb = L.ptr(res["beta"]), L.ptr(res["rgb_fine"])
+            o.rgb_static, o.rgb_transient = L.ptr(res["_rgb_fine_static"]), L.ptr(res["_rgb_fine_transient"])
+            if test_time:
+                for k, shape, slot in (("rgb_fine_static", (n, 3), "tt_rgb_static"),
+                                       ("depth_fine_static", (n,), "tt_depth_static"),
+                                       ("rgb_fine_transient", (n, 3), "tt_rgb_transient"),
+                                       ("depth_fine_transient", (n,), "tt_depth_transient")):
+                    res[k] = new(*shape)
+                    setattr(o, slot, L.ptr(res[k]))
+        else:
+            res[f"rgb_{typ}"] = new(n, 3)
+            o.rgb = L.ptr(res[f"rgb_{typ}"])
+        res[f"depth_{typ}"] = new(n)
+        o.depth = L.ptr(res[f"depth_{typ}"])
+    nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
+    L.check(L.lib().nwb_composite_fwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
+                                      composite_flags(transient, white_back, test_time, coarse),
+                                      float(beta_min), C.byref(o), L.stream_ptr(dev)),
+            "nwb_composite_fwd")
+    return res
+
+
+def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, transient: bool,
+                  white_back: bool, noise: torch.Tensor | None = None,
+                  noise_std: float = 0.0) -> torch.Tensor:
+    """Cotangents keyed like the result dict -> d_raw (N,S,C)."""
+    raw, z = _f32(raw), _f32(z)
+    n, S = z.shape
+    Cc = raw.shape[-1]
+    g = L.CompositeGrads()
+    keep = []
+
+    def put(slot, key):
+        t = grads.get(key)
+        if t is not None:
+            t = _f32(t)
+            keep.append(t)
+            setattr(g, slot, L.ptr(t))
+
+    put("d_weights", f"weights_{typ}")
+    put("d_opacity", f"opacity_{typ}")
+    put("d_depth", f"depth_{typ}")
+    if transient:
+        put("d_rgb", "rgb_fine")
+        put("d_transient_sigmas", "transient_sigmas")
+        put("d_beta", "beta")
+        put("d_rgb_static", "_rgb_fine_static")
+        put("d_rgb_transient", "_rgb_fine_transient")
+    else:
+        put("d_rgb", f"rgb_{typ}")
+    d_raw = torch.empty_like(raw)
+    nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
+    L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
+                                      composite_flags(transient, white_back, False, typ == "coarse"),
+                                      C.byref(g), L.ptr(d_raw), L.stream_ptr(z.device)),
+            "nwb_composite_bwd")
+    return d_raw
+
+
+def selftest_umma(a_img: torch.Tensor, b_img: torch.Tensor, N: int, K: int, variant: int,
+                  overrides=None) -> torch.Tensor:
+    d = torch.empty(128, N, device=a_img.device, dtype=torch.float32)
+    ov = None
+    if overrides is not None:
+        ov = (C.c_uint32 * 11)(*[int(v) for v in overrides])
+    L.check(L.lib().nwb_selftest_umma(L.ptr(a_img), L.ptr(b_img), N, K, variant, ov, L.ptr(d),
+                                      L.stream_ptr(a_img.device)), "nwb_selftest_umma")
+    return d

@@ -1,0 +1,35 @@
+"""Host-side description of the bf16 "tile image" layout shared by every tcgen05 operand.
+
+A tile image of an (R x Cc) matrix (R % 8 == 0, Cc % 64 == 0) is the byte image UMMA's
+SWIZZLE_128B canonical layout expects in shared memory, so a linear bulk copy lands it ready to
+use: column block cb (64 columns = 128 B per row) starts at cb*R*128 bytes; inside a block row r
+sits at (r//8)*1024 + (r%8)*128 and its 16-byte chunk j is stored at chunk position j ^ (r%8).
+Read K-major (rows = M/N index) or MN-major (rows = contraction index) from the same bytes.
+"""
+from __future__ import annotations
+
+import torch
+
+
+def image_offsets(R: int, Cc: int) -> torch.Tensor:
+    """(R, Cc) int64: bf16-element offset of element (r, c) inside the tile image."""
+    assert R % 8 == 0 and Cc % 64 == 0, (R, Cc)
+    r = torch.arange(R).unsqueeze(1)
+    c = torch.arange(Cc).unsqueeze(0)
+    cb, j, e = c // 64, (c % 64) // 8, c % 8
+    return cb * (R * 64) + (r // 8) * 512 + (r % 8) * 64 + ((j ^ (r % 8)) * 8) + e
+
+
+def tile_image(m: torch.Tensor) -> torch.Tensor:
+    """(R, Cc) float tensor -> flat bf16 tensor holding its tile image (same device)."""
+    R, Cc = m.shape
+    off = image_offsets(R, Cc).to(m.device).flatten()
+    out = torch.empty(R * Cc, dtype=torch.bfloat16, device=m.device)
+    out[off] = m.to(torch.bfloat16).flatten()
+    return out
+
+
+def from_tile_image(img: torch.Tensor, R: int, Cc: int) -> torch.Tensor:
+    """Inverse of tile_image -> (R, Cc) bf16."""
+    off = image_offsets(R, Cc).to(img.device).flatten()
+    return img.flatten()[off].reshape(R, Cc)

@@ -1,0 +1,205 @@
+"""GPU parity of the CUDA-core kernels (a1, a2, a5, a6) and of the tcgen05 tile engine, through
+the C ABI, against the oracle and the committed golden vectors."""
+import pytest
+import torch
+
+from nerf_fl_b200 import kernels as K
+from nerf_fl_b200 import layout, synthetic as syn
+from oracle import nerfw_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def maxerr(a, b):
+    return (a.double().cpu() - b.double().cpu()).abs().max().item()
+
+
+# ---- (a1) coarse depths ------------------------------------------------------------------------
+@pytest.mark.parametrize("use_disp", [False, True])
+@pytest.mark.parametrize("perturb", [0.0, 1.0, 0.5])
+@pytest.mark.parametrize("ns", [64, 33, 128])
+def test_sample_coarse_bit_exact(use_disp, perturb, ns):
+    rays = syn.blender_rays(257, seed=7, phototourism=True)
+    g = torch.Generator().manual_seed(1)
+    pr = torch.rand(257, ns, generator=g)
+    want = O.coarse_depths(rays[:, 6:7], rays[:, 7:8], ns, use_disp, perturb, pr)
+    got = K.sample_coarse(rays.to(DEV), ns, use_disp, perturb, pr.to(DEV))
+    if use_disp:
+        assert maxerr(got, want) <= 5e-7 * want.abs().max().item()   # division rounding only
+    else:
+        assert torch.equal(got.cpu(), want)
+
+
+def test_sample_coarse_philox_in_range():
+    rays = syn.blender_rays(4096, seed=7).to(DEV)
+    z0 = K.sample_coarse(rays, 64, False, 0.0)
+    z1 = K.sample_coarse(rays, 64, False, 1.0, None, seed=123)
+    z2 = K.sample_coarse(rays, 64, False, 1.0, None, seed=124)
+    step = 4.0 / 63
+    assert ((z1 - z0).abs() <= step / 2 + 1e-5).all() and not torch.equal(z1, z2)
+    assert (z1[:, 1:] >= z1[:, :-1]).all()
+    jit = ((z1 - z0) / step)[:, 1:-1]
+    assert abs(jit.mean().item()) < 0.01 and abs(jit.std().item() - (1 / 12) ** 0.5) < 0.01
+
+
+# ---- (a2) PosEmbedding -------------------------------------------------------------------------
+@pytest.mark.parametrize("L", [4, 10, 15])
+def test_posenc_golden(golden, L):
+    g = golden("posenc")
+    got = K.posenc(g["x"].to(DEV), L)
+    assert got.shape == g[f"L{L}"].shape
+    assert maxerr(got, g[f"L{L}"]) <= 4e-6      # libdevice sinf/cosf vs libm: a few ulp near 1
+
+
+def test_posenc_empty_and_large():
+    assert K.posenc(torch.zeros(0, 3, device=DEV), 10).shape == (0, 63)
+    x = (torch.rand(100003, 3, generator=torch.Generator().manual_seed(2)) * 8 - 4)
+    assert maxerr(K.posenc(x.to(DEV), 10), O.posenc(x, 10)) <= 4e-6
+
+
+# ---- (a6) sample_pdf + merge -------------------------------------------------------------------
+def _pdf_inputs(g):
+    # golden bins/weights are free-standing; rebuild a (z, w) pair whose midpoints/inner weights
+    # reproduce them is not possible in general, so the KAT drives the kernel with z = edges that
+    # the kernel turns into midpoints: use the oracle on the kernel's own midpoints instead.
+    N, Ns = 40, 64
+    gen = torch.Generator().manual_seed(5)
+    z = torch.sort(torch.rand(N, Ns, generator=gen) * 4 + 2, dim=-1)[0]
+    w = torch.rand(N, Ns, generator=gen) ** 4
+    w[3] = 0.0
+    w[5, 10:50] = 0.0
+    u = torch.rand(N, 64, generator=gen)
+    u[7, -1] = 1.0
+    u[8, 0] = 0.0
+    return z, w, u
+
+
+@pytest.mark.parametrize("det", [False, True])
+def test_sample_pdf_indices_bit_exact_given_cdf(det):
+    z, w, u = _pdf_inputs(None)
+    mid = 0.5 * (z[:, :-1] + z[:, 1:])
+    s, cdf, uu, inds = O.sample_pdf(mid, w[:, 1:-1], 64, det=det, u=None if det else u, return_aux=True)
+    zo, zn, ii = K.sample_pdf_merge(z.to(DEV), w.to(DEV), 64, det, None if det else u.to(DEV),
+                                    cdf=cdf.to(DEV), debug=True)
+    assert torch.equal(ii.cpu(), inds)                       # bit-exact bin indices
+    assert torch.equal(zn.cpu(), s)                          # same fp32 op order -> identical samples
+    want = torch.sort(torch.cat([z, s], -1), -1)[0]
+    assert torch.equal(zo.cpu(), want)
+    assert inds.max().item() == 63 or det
+
+
+@pytest.mark.parametrize("ns,ni", [(64, 64), (128, 128), (64, 128), (33, 17)])
+def test_sample_pdf_merge_own_cdf(ns, ni):
+    gen = torch.Generator().manual_seed(9)
+    N = 301
+    z = torch.sort(torch.rand(N, ns, generator=gen) * 4 + 2, dim=-1)[0]
+    w = torch.rand(N, ns, generator=gen) ** 6
+    u = torch.rand(N, ni, generator=gen)
+    mid = 0.5 * (z[:, :-1] + z[:, 1:])
+    s = O.sample_pdf(mid, w[:, 1:-1], ni, det=False, u=u)
+    want = torch.sort(torch.cat([z, s], -1), -1)[0]
+    zo, zn, ii = K.sample_pdf_merge(z.to(DEV), w.to(DEV), ni, False, u.to(DEV), debug=True)
+    assert (zo[:, 1:] >= zo[:, :-1]).all()                   # sortedness
+    # CDF summation order differs (warp scan vs sequential): samples move by ~1e-6 of a bin
+    assert maxerr(zo, want) <= 2e-5
+    # Philox path: in range, sorted, right shape
+    zr = K.sample_pdf_merge(z.to(DEV), w.to(DEV), ni, False, None, seed=3)
+    assert zr.shape == (N, ns + ni) and (zr[:, 1:] >= zr[:, :-1]).all()
+    assert zr.min() >= z.min() - 1e-6 and zr.max() <= z.max() + 1e-6
+
+
+def test_sample_pdf_golden_det(golden):
+    # the committed golden (reference sample_pdf) pins det-mode u == torch.linspace bit for bit
+    g = golden("sample_pdf")
+    z, w, _ = _pdf_inputs(None)
+    _, _, ii = K.sample_pdf_merge(z.to(DEV), w.to(DEV), 64, True, None, debug=True)
+    mid = 0.5 * (z[:, :-1] + z[:, 1:])
+    _, cdf, uu, inds = O.sample_pdf(mid, w[:, 1:-1], 64, det=True, return_aux=True)
+    assert torch.equal(uu, g["u_det"])
+    assert (ii.cpu() != inds).float().mean().item() < 2e-3    # own CDF: flips only at exact ties
+
+
+# ---- (a5) compositing --------------------------------------------------------------------------
+@pytest.mark.parametrize("transient", [False, True])
+@pytest.mark.parametrize("white_back", [False, True])
+@pytest.mark.parametrize("test_time", [False, True])
+def test_composite_fwd_golden(golden, transient, white_back, test_time):
+    g = golden("composite")
+    tag = f"t{int(transient)}_w{int(white_back)}_x{int(test_time)}/"
+    typ = "fine" if transient else "coarse"
+    raw = (g["raw"] if transient else g["raw"][..., :4]).contiguous()
+    got = K.composite_fwd(raw.to(DEV), g["z"].to(DEV), typ=typ, transient=transient,
+                          white_back=white_back, test_time=test_time, beta_min=0.1,
+                          noise=g["noise"].to(DEV), noise_std=0.7)
+    want = {k[len(tag):]: v for k, v in g.items() if k.startswith(tag)}
+    assert set(got) == set(want)
+    for k in want:
+        assert maxerr(got[k], want[k]) <= 2e-6, k
+
+
+@pytest.mark.parametrize("S,C", [(1, 4), (31, 9), (64, 4), (128, 9), (256, 9), (100, 1), (257, 4)])
+def test_composite_fwd_bwd_vs_oracle(S, C):
+    gen = torch.Generator().manual_seed(S * 10 + C)
+    N = 203
+    z = torch.sort(torch.rand(N, S, generator=gen) * 4 + 2, dim=-1)[0]
+    raw = torch.rand(N, S, C, generator=gen)
+    raw[..., 3 if C > 1 else 0] = raw[..., 3 if C > 1 else 0] ** 3 * 20
+    if C == 9:
+        raw[..., 7] = raw[..., 7] ** 3 * 6
+    transient = C == 9
+    typ = "fine" if transient else "coarse"
+    noise = torch.randn(N, S, generator=gen)
+    raw_o = raw.clone().requires_grad_(True)
+    want = O.composite(raw_o, z, typ=typ, transient=transient, white_back=True, test_time=False,
+                       beta_min=0.03, noise=noise, noise_std=0.5)
+    got = K.composite_fwd(raw.to(DEV), z.to(DEV), typ=typ, transient=transient, white_back=True,
+                          test_time=False, beta_min=0.03, noise=noise.to(DEV), noise_std=0.5)
+    assert set(got) == set(want)
+    for k in want:
+        assert maxerr(got[k], want[k]) <= 5e-6, k
+    # backward: random cotangents on every differentiable output
+    cot = {k: torch.randn(v.shape, generator=gen) for k, v in want.items()}
+    loss = sum((want[k] * cot[k]).sum() for k in want)
+    (d_ref,) = torch.autograd.grad(loss, raw_o)
+    d_got = K.composite_bwd(raw.to(DEV), z.to(DEV), {k: v.to(DEV) for k, v in cot.items()}, typ=typ,
+                            transient=transient, white_back=True, noise=noise.to(DEV), noise_std=0.5)
+    scale = d_ref.abs().max().item()
+    assert maxerr(d_got, d_ref) <= 2e-5 * max(scale, 1.0), (maxerr(d_got, d_ref), scale)
+
+
+def test_composite_empty():
+    out = K.composite_fwd(torch.zeros(0, 8, 4, device=DEV), torch.zeros(0, 8, device=DEV), typ="coarse",
+                          transient=False, white_back=False, test_time=False)
+    assert out["rgb_coarse"].shape == (0, 3)
+
+
+# ---- tcgen05 tile engine -----------------------------------------------------------------------
+@pytest.mark.parametrize("N,Kd", [(256, 256), (256, 64), (128, 256), (128, 128), (16, 64), (256, 192)])
+def test_umma_k_major(N, Kd):
+    gen = torch.Generator().manual_seed(N + Kd)
+    A = torch.randn(128, Kd, generator=gen).to(torch.bfloat16)
+    B = torch.randn(N, Kd, generator=gen).to(torch.bfloat16)
+    d = K.selftest_umma(layout.tile_image(A).to(DEV), layout.tile_image(B).to(DEV), N, Kd, 0)
+    want = A.float() @ B.float().T
+    assert maxerr(d, want) <= 1e-3 * Kd ** 0.5, maxerr(d, want)
+
+
+@pytest.mark.parametrize("N,Kd", [(256, 128), (128, 128), (64, 64), (256, 16)])
+def test_umma_mn_major(N, Kd):
+    gen = torch.Generator().manual_seed(N * 3 + Kd)
+    X = torch.randn(Kd, 128, generator=gen).to(torch.bfloat16)     # contraction index = rows
+    Y = torch.randn(Kd, N, generator=gen).to(torch.bfloat16)
+    d = K.selftest_umma(layout.tile_image(X).to(DEV), layout.tile_image(Y).to(DEV), N, Kd, 1)
+    want = X.float().T @ Y.float()
+    assert maxerr(d, want) <= 1e-3 * Kd ** 0.5, maxerr(d, want)
+
+
+@pytest.mark.parametrize("N,Kd", [(256, 256), (128, 128), (64, 64), (256, 128)])
+def test_umma_a_kmajor_b_mnmajor(N, Kd):
+    gen = torch.Generator().manual_seed(N * 5 + Kd)
+    A = torch.randn(128, Kd, generator=gen).to(torch.bfloat16)
+    Wt = torch.randn(Kd, N, generator=gen).to(torch.bfloat16)       # contraction index = rows
+    d = K.selftest_umma(layout.tile_image(A).to(DEV), layout.tile_image(Wt).to(DEV), N, Kd, 2)
+    want = A.float() @ Wt.float()
+    assert maxerr(d, want) <= 1e-3 * Kd ** 0.5, maxerr(d, want)
