@@ -297,7 +297,7 @@ using namespace nwb;
 extern "C" int nwb_composite_fwd(const float* raw, int C, const float* z, const float* noise,
                                  float noise_std, int n_rays, int S, uint32_t flags,
                                  float beta_min, const nwb_composite_out* out, void* stream) {
-    NWB_REQUIRE(raw && z && out, "nwb_composite_fwd: null pointer");
+    NWB_REQUIRE(n_rays == 0 || (raw && z && out), "nwb_composite_fwd: null pointer");
     NWB_REQUIRE(C == 1 || C == 4 || C == 9, "nwb_composite_fwd: C must be 1, 4 or 9 (got %d)", C);
     NWB_REQUIRE(S >= 1 && n_rays >= 0, "nwb_composite_fwd: bad shape");
     NWB_REQUIRE(!(flags & NWB_COMP_TRANSIENT) || C == 9, "nwb_composite_fwd: transient needs C==9");
@@ -314,7 +314,7 @@ extern "C" int nwb_composite_fwd(const float* raw, int C, const float* z, const 
 extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const float* noise,
                                  float noise_std, int n_rays, int S, uint32_t flags,
                                  const nwb_composite_grads* g, float* d_raw, void* stream) {
-    NWB_REQUIRE(raw && z && g && d_raw, "nwb_composite_bwd: null pointer");
+    NWB_REQUIRE(n_rays == 0 || (raw && z && g && d_raw), "nwb_composite_bwd: null pointer");
     NWB_REQUIRE(C == 1 || C == 4 || C == 9, "nwb_composite_bwd: C must be 1, 4 or 9 (got %d)", C);
     NWB_REQUIRE(S >= 1 && n_rays >= 0, "nwb_composite_bwd: bad shape");
     NWB_REQUIRE(!(flags & NWB_COMP_TEST_TIME), "nwb_composite_bwd: test_time outputs carry no gradient");

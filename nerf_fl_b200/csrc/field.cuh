@@ -1,0 +1,104 @@
+// Static description of the NeRF-W field network (models/nerf.py:121-151) as a schedule of
+// tensor-core GEMM layers, shared by the pack / forward / backward / wgrad kernels.
+//
+// GEMM layers g (N = output features, K-blocks of 64 input features):
+//   g=0      xyz_encoding_1            N=256  A = [X]                (X = encoded xyz, 64-col blocks)
+//   g=1..3   xyz_encoding_2..4         N=256  A = [H0..H3]
+//   g=4      xyz_encoding_5 (skip)     N=256  A = [X, H0..H3]        (input first, nerf.py:187)
+//   g=5..7   xyz_encoding_6..8         N=256  A = [H0..H3]           (g=7 epilogue: sigma head)
+//   g=8      xyz_encoding_final        N=256  A = [H0..H3]           (no activation)
+//   g=9      dir_encoding | tenc.0     N=128|256  A = [H0..H3]       (feature part; dir/a/t parts
+//                                                                     arrive as a per-ray bias)
+//   g=10..12 transient_encoding.2,4,6  N=128  A = [H2,H3]            (g=12 epilogue: transient heads)
+// Heads (N = 1|3|5) run on CUDA cores inside the producing layer's epilogue.
+#pragma once
+#include "common.cuh"
+
+namespace nwb {
+
+constexpr int kW = 256;          // trunk width
+constexpr int kHalf = 128;       // W/2
+constexpr int kTileM = 128;      // points per tile
+constexpr int kMaxG = 13;
+
+struct FieldShape {
+    int in_xyz, in_dir, in_a, in_t;
+    int kx;                      // 64-column blocks of the encoded-xyz operand (1 or 2)
+    __host__ __device__ bool has_t() const { return in_t > 0; }
+    __host__ __device__ int n_layers(uint32_t mode) const {
+        if (mode & NWB_MLP_SIGMA_ONLY) return 8;
+        return (mode & NWB_MLP_TRANSIENT) ? 13 : 10;
+    }
+    __host__ __device__ int layer_n(int g, uint32_t mode) const {      // MMA N of layer g
+        if (g <= 8) return kW;
+        if (g == 9) return (mode & NWB_MLP_TRANSIENT) ? kW : kHalf;
+        return kHalf;
+    }
+    __host__ __device__ int packed_n(int g) const {                    // rows stored in the pack
+        if (g <= 8) return kW;
+        if (g == 9) return has_t() ? kW : kHalf;
+        return kHalf;
+    }
+    __host__ __device__ int layer_kb(int g) const {                    // number of 64-wide K-blocks
+        if (g == 0) return kx;
+        if (g == 4) return kx + 4;
+        if (g >= 10) return 2;
+        return 4;
+    }
+    // byte offset of layer g's slab image inside the packed buffer; slab kb = rows x 128 B
+    __host__ __device__ size_t w_off(int g) const {
+        size_t o = 0;
+        for (int i = 0; i < g; ++i) o += static_cast<size_t>(packed_n(i)) * 128 * layer_kb(i);
+        return o;
+    }
+    __host__ __device__ int n_packed_layers() const { return has_t() ? 13 : 10; }
+    __host__ __device__ size_t w_bytes() const { return w_off(n_packed_layers()); }
+};
+
+// fp32 constant block that follows the weight slabs in the packed buffer (float offsets)
+struct ConstOff {
+    static constexpr int trunk_b = 0;              // 8 x 256
+    static constexpr int final_b = 8 * 256;        // 256
+    static constexpr int tenc_b = 9 * 256;         // 3 x 128 (transient_encoding.2,4,6)
+    static constexpr int sigma_w = tenc_b + 3 * 128;   // 256
+    static constexpr int rgb_w = sigma_w + 256;        // 3 x 128
+    static constexpr int tsigma_w = rgb_w + 384;       // 128
+    static constexpr int trgb_w = tsigma_w + 128;      // 3 x 128
+    static constexpr int tbeta_w = trgb_w + 384;       // 128
+    static constexpr int head_b = tbeta_w + 128;       // sigma_b, rgb_b[3], tsigma_b, trgb_b[3], tbeta_b
+    static constexpr int count = head_b + 16;
+};
+
+inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
+    NWB_REQUIRE(d != nullptr, "field desc is null");
+    NWB_REQUIRE(d->in_xyz >= 3 && d->in_xyz <= 64,
+                "in_channels_xyz = %d unsupported (this build stages one 64-column xyz block; N_emb_xyz <= 10)",
+                d->in_xyz);
+    NWB_REQUIRE(d->in_dir >= 3 && d->in_dir <= 256 && d->in_a >= 0 && d->in_a <= 256 && d->in_t >= 0 && d->in_t <= 256,
+                "unsupported dir/appearance/transient widths");
+    s->in_xyz = d->in_xyz; s->in_dir = d->in_dir; s->in_a = d->in_a; s->in_t = d->in_t;
+    s->kx = (d->in_xyz + 63) / 64;
+    return NWB_OK;
+}
+
+// saved-activation layout per tile (bf16 tile images, bytes), forward NWB_MLP_SAVE:
+//   [X: kx*16K][h1..h8: 8 x 64K][feat: 64K][dir|t0: 32K or 64K][t2,t4,t6: 3 x 32K]
+struct SaveLayout {
+    int kx; bool transient;
+    __host__ __device__ size_t x_off() const { return 0; }
+    __host__ __device__ size_t act_off(int g) const {   // image written by layer g's epilogue
+        size_t o = static_cast<size_t>(kx) * 16384;
+        if (g <= 8) return o + static_cast<size_t>(g) * 65536;
+        o += 9 * 65536;
+        if (g == 9) return o;
+        o += transient ? 65536 : 32768;
+        return o + static_cast<size_t>(g - 10) * 32768;
+    }
+    __host__ __device__ size_t tile_bytes(int n_layers) const {
+        if (n_layers <= 8) return act_off(7) + 65536;
+        if (n_layers <= 10) return act_off(9) + (transient ? 65536 : 32768);
+        return act_off(12) + 32768;
+    }
+};
+
+}  // namespace nwb

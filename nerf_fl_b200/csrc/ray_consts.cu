@@ -1,0 +1,194 @@
+// Per-ray operands of dir_encoding / transient_encoding.0 (models/rendering.py:113-130,
+// models/nerf.py:195,203).  The reference repeats dir/appearance/transient rows to every sample
+// and concatenates them into the layer input; here the ray-constant part of the product,
+//     W[:, 256:] . [PosEmbedding(dir) | a | t]  + b,
+// is evaluated once per ray in fp32 and enters the fused MLP as a per-ray bias.  Forward: one
+// warp per ray.  Backward: per-ray cotangents -> weight-column / bias / embedding-row gradients.
+#include "field.cuh"
+#include <algorithm>
+
+namespace nwb {
+
+constexpr int kRcWarps = 4;
+constexpr int kMaxFeat = 768;
+
+__global__ void __launch_bounds__(kRcWarps * 32)
+ray_consts_fwd_kernel(FieldShape fs, nwb_field_params p, const float* __restrict__ dirs, int dir_stride,
+                      int dir_is_encoded, int n_freq_dir, const int64_t* __restrict__ ts,
+                      const float* __restrict__ emb_a, const float* __restrict__ emb_t, int n_vocab,
+                      const float* __restrict__ a_rows, const float* __restrict__ t_rows, int n_rays,
+                      uint32_t mode, float* __restrict__ ray_feat, float* __restrict__ ray_bias,
+                      int* __restrict__ err_flag) {
+    extern __shared__ float sm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool use_t = (mode & NWB_MLP_TRANSIENT) != 0;
+    const int nd = fs.in_dir, na = fs.in_a, nt = use_t ? fs.in_t : 0;
+    const int nf = nd + na + nt;
+    const int feat_ld = fs.in_dir + fs.in_a + fs.in_t;
+    float* feat = sm + warp * kMaxFeat;
+    for (int ray = blockIdx.x * kRcWarps + warp; ray < n_rays; ray += gridDim.x * kRcWarps) {
+        int64_t t_idx = 0;
+        if ((na > 0 && a_rows == nullptr) || (nt > 0 && t_rows == nullptr)) {
+            t_idx = ts[ray];
+            if (t_idx < 0 || t_idx >= n_vocab) {
+                if (lane == 0) atomicExch(err_flag, 1);
+                t_idx = 0;
+            }
+        }
+        for (int e = lane; e < nf; e += 32) {
+            float v;
+            if (e < nd) {
+                if (dir_is_encoded) {
+                    v = dirs[static_cast<int64_t>(ray) * dir_stride + e];
+                } else if (e < 3) {
+                    v = dirs[static_cast<int64_t>(ray) * dir_stride + e];
+                } else {
+                    const int k = (e - 3) / 6, r = (e - 3) % 6;
+                    const float arg = __fmul_rn(dirs[static_cast<int64_t>(ray) * dir_stride + (r % 3)],
+                                                exp2f(static_cast<float>(k)));
+                    v = (r < 3) ? sinf(arg) : cosf(arg);
+                }
+            } else if (e < nd + na) {
+                const int j = e - nd;
+                v = a_rows ? a_rows[static_cast<int64_t>(ray) * na + j] : emb_a[t_idx * na + j];
+            } else {
+                const int j = e - nd - na;
+                v = t_rows ? t_rows[static_cast<int64_t>(ray) * nt + j] : emb_t[t_idx * nt + j];
+            }
+            feat[e] = v;
+            if (ray_feat) ray_feat[static_cast<int64_t>(ray) * feat_ld + e] = v;
+        }
+        __syncwarp();
+        const int ld_dir = kW + fs.in_dir + fs.in_a;
+        const int ld_t = kW + fs.in_t;
+        for (int j = lane; j < 2 * kHalf; j += 32) {
+            float acc = 0.0f;
+            if (j < kHalf) {
+                const float* w = p.dir_w + static_cast<int64_t>(j) * ld_dir + kW;
+                acc = p.dir_b[j];
+                for (int k = 0; k < nd + na; ++k) acc = fmaf(w[k], feat[k], acc);
+            } else if (use_t) {
+                const int jj = j - kHalf;
+                const float* w = p.tenc_w[0] + static_cast<int64_t>(jj) * ld_t + kW;
+                acc = p.tenc_b[0][jj];
+                for (int k = 0; k < nt; ++k) acc = fmaf(w[k], feat[nd + na + k], acc);
+            }
+            ray_bias[static_cast<int64_t>(ray) * 256 + j] = acc;
+        }
+        __syncwarp();
+    }
+}
+
+// backward: one block per chunk of rays; d_ray_bias (n,256) -> dW[:, 256:], db, d_emb rows.
+// Rays are few (<= batch), so plain fp32 atomics on a small grid are sufficient here.
+__global__ void __launch_bounds__(128)
+ray_consts_bwd_kernel(FieldShape fs, nwb_field_params p, nwb_field_grads g, const float* __restrict__ ray_feat,
+                      const float* __restrict__ d_ray_bias, const int64_t* __restrict__ ts, int n_vocab,
+                      int n_rays, uint32_t mode, float* __restrict__ d_emb_a, float* __restrict__ d_emb_t,
+                      float* __restrict__ d_a_rows, float* __restrict__ d_t_rows, int rays_per_block) {
+    extern __shared__ float sm[];
+    const bool use_t = (mode & NWB_MLP_TRANSIENT) != 0;
+    const int nd = fs.in_dir, na = fs.in_a, nt = use_t ? fs.in_t : 0;
+    const int feat_ld = fs.in_dir + fs.in_a + fs.in_t;
+    const int ld_dir = kW + fs.in_dir + fs.in_a, ld_t = kW + fs.in_t;
+    const int r0 = blockIdx.x * rays_per_block, r1 = min(n_rays, r0 + rays_per_block);
+    const int nr = r1 - r0;
+    if (nr <= 0) return;
+    // stage this block's d_ray_bias rows (nr x 256) and features (nr x feat_ld)
+    float* sg = sm;
+    float* sf = sm + rays_per_block * 256;
+    for (int i = threadIdx.x; i < nr * 256; i += blockDim.x) sg[i] = d_ray_bias[static_cast<int64_t>(r0) * 256 + i];
+    for (int i = threadIdx.x; i < nr * feat_ld; i += blockDim.x) sf[i] = ray_feat[static_cast<int64_t>(r0) * feat_ld + i];
+    __syncthreads();
+    // (1) weight-column and bias gradients: thread j owns output feature j (0..127) of dir, then of t
+    for (int j = threadIdx.x; j < kHalf; j += blockDim.x) {
+        float bsum = 0.0f;
+        for (int r = 0; r < nr; ++r) bsum += sg[r * 256 + j];
+        atomicAdd(g.dir_b + j, bsum);
+        for (int k = 0; k < nd + na; ++k) {
+            float acc = 0.0f;
+            for (int r = 0; r < nr; ++r) acc = fmaf(sg[r * 256 + j], sf[r * feat_ld + k], acc);
+            atomicAdd(g.dir_w + static_cast<int64_t>(j) * ld_dir + kW + k, acc);
+        }
+        if (use_t) {
+            float bt = 0.0f;
+            for (int r = 0; r < nr; ++r) bt += sg[r * 256 + kHalf + j];
+            atomicAdd(g.tenc_b[0] + j, bt);
+            for (int k = 0; k < nt; ++k) {
+                float acc = 0.0f;
+                for (int r = 0; r < nr; ++r) acc = fmaf(sg[r * 256 + kHalf + j], sf[r * feat_ld + nd + na + k], acc);
+                atomicAdd(g.tenc_w[0] + static_cast<int64_t>(j) * ld_t + kW + k, acc);
+            }
+        }
+    }
+    // (2) embedding-row gradients: d a = W_dir[:, 256+nd:]^T . g_dir ; d t = W_t0[:, 256:]^T . g_t
+    for (int idx = threadIdx.x; idx < nr * (na + nt); idx += blockDim.x) {
+        const int r = idx / (na + nt), e = idx - r * (na + nt);
+        float acc = 0.0f;
+        if (e < na) {
+            for (int j = 0; j < kHalf; ++j) acc = fmaf(p.dir_w[static_cast<int64_t>(j) * ld_dir + kW + nd + e], sg[r * 256 + j], acc);
+            if (d_a_rows) d_a_rows[static_cast<int64_t>(r0 + r) * na + e] = acc;
+            else if (d_emb_a) atomicAdd(d_emb_a + ts[r0 + r] * na + e, acc);
+        } else {
+            const int k = e - na;
+            for (int j = 0; j < kHalf; ++j) acc = fmaf(p.tenc_w[0][static_cast<int64_t>(j) * ld_t + kW + k], sg[r * 256 + kHalf + j], acc);
+            if (d_t_rows) d_t_rows[static_cast<int64_t>(r0 + r) * nt + k] = acc;
+            else if (d_emb_t) atomicAdd(d_emb_t + ts[r0 + r] * nt + k, acc);
+        }
+    }
+}
+
+}  // namespace nwb
+
+using namespace nwb;
+
+extern "C" int nwb_ray_consts_fwd(const nwb_field_desc* d, const nwb_field_params* p, const float* dirs,
+                                  int dir_stride, int dir_is_encoded, int n_freq_dir, const int64_t* ts,
+                                  const float* emb_a, const float* emb_t, int n_vocab, const float* a_rows,
+                                  const float* t_rows, int n_rays, uint32_t mode, float* ray_feat,
+                                  float* ray_bias, int* err_flag, void* stream) {
+    FieldShape fs;
+    int rc = make_shape(d, &fs);
+    if (rc != NWB_OK) return rc;
+    if (n_rays == 0) return NWB_OK;
+    NWB_REQUIRE(p && dirs && ray_bias && err_flag, "nwb_ray_consts_fwd: null pointer");
+    NWB_REQUIRE(p->dir_w && p->dir_b, "nwb_ray_consts_fwd: dir_encoding parameters are null");
+    NWB_REQUIRE(dir_is_encoded || fs.in_dir == 3 + 6 * n_freq_dir, "nwb_ray_consts_fwd: in_dir != 3+6*n_freq_dir");
+    NWB_REQUIRE(dir_stride >= (dir_is_encoded ? fs.in_dir : 3), "nwb_ray_consts_fwd: dir_stride too small");
+    const bool use_t = (mode & NWB_MLP_TRANSIENT) != 0;
+    NWB_REQUIRE(!use_t || fs.in_t > 0, "nwb_ray_consts_fwd: transient requested but in_t == 0");
+    NWB_REQUIRE(!use_t || (p->tenc_w[0] && p->tenc_b[0]), "nwb_ray_consts_fwd: transient parameters are null");
+    NWB_REQUIRE(fs.in_a == 0 || a_rows || (emb_a && ts), "nwb_ray_consts_fwd: appearance needs a_rows or (emb_a, ts)");
+    NWB_REQUIRE(!use_t || t_rows || (emb_t && ts), "nwb_ray_consts_fwd: transient needs t_rows or (emb_t, ts)");
+    NWB_REQUIRE(fs.in_dir + fs.in_a + fs.in_t <= kMaxFeat, "nwb_ray_consts_fwd: feature row too wide");
+    const int blocks = std::min((n_rays + kRcWarps - 1) / kRcWarps, kNumSMs * 8);
+    const size_t smem = kRcWarps * kMaxFeat * sizeof(float);
+    ray_consts_fwd_kernel<<<blocks, kRcWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+        fs, *p, dirs, dir_stride, dir_is_encoded, n_freq_dir, ts, emb_a, emb_t, n_vocab, a_rows, t_rows, n_rays,
+        mode, ray_feat, ray_bias, err_flag);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
+extern "C" int nwb_ray_consts_bwd(const nwb_field_desc* d, const nwb_field_params* p, const float* ray_feat,
+                                  const float* d_ray_bias, const int64_t* ts, int n_vocab, int n_rays,
+                                  uint32_t mode, const nwb_field_grads* grads, float* d_emb_a, float* d_emb_t,
+                                  float* d_a_rows, float* d_t_rows, void* stream) {
+    FieldShape fs;
+    int rc = make_shape(d, &fs);
+    if (rc != NWB_OK) return rc;
+    if (n_rays == 0) return NWB_OK;
+    NWB_REQUIRE(p && ray_feat && d_ray_bias && grads, "nwb_ray_consts_bwd: null pointer");
+    NWB_REQUIRE(grads->dir_w && grads->dir_b, "nwb_ray_consts_bwd: dir_encoding gradient sinks are null");
+    const bool use_t = (mode & NWB_MLP_TRANSIENT) != 0;
+    NWB_REQUIRE(!use_t || (grads->tenc_w[0] && grads->tenc_b[0]), "nwb_ray_consts_bwd: transient gradient sinks are null");
+    NWB_REQUIRE(fs.in_a == 0 || d_a_rows || !d_emb_a || ts, "nwb_ray_consts_bwd: ts needed for the embedding scatter");
+    const int feat_ld = fs.in_dir + fs.in_a + fs.in_t;
+    const int rpb = 16;
+    const size_t smem = static_cast<size_t>(rpb) * (256 + feat_ld) * sizeof(float);
+    const int blocks = (n_rays + rpb - 1) / rpb;
+    ray_consts_bwd_kernel<<<blocks, 128, smem, static_cast<cudaStream_t>(stream)>>>(
+        fs, *p, *grads, ray_feat, d_ray_bias, ts, n_vocab, n_rays, mode, d_emb_a, d_emb_t, d_a_rows, d_t_rows, rpb);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}

@@ -187,7 +187,7 @@ using namespace nwb;
 extern "C" int nwb_sample_coarse(const float* rays, int ray_stride, int n_rays, int n_samples,
                                  int use_disp, float perturb, const float* perturb_rand,
                                  uint64_t seed, float* z_out, void* stream) {
-    NWB_REQUIRE(rays && z_out, "nwb_sample_coarse: null pointer");
+    NWB_REQUIRE(n_rays == 0 || (rays && z_out), "nwb_sample_coarse: null pointer");
     NWB_REQUIRE(ray_stride >= 8 && n_rays >= 0 && n_samples >= 1, "nwb_sample_coarse: bad shape");
     if (n_rays == 0) return NWB_OK;
     const int64_t total = static_cast<int64_t>(n_rays) * n_samples;
@@ -199,7 +199,7 @@ extern "C" int nwb_sample_coarse(const float* rays, int ray_stride, int n_rays, 
 }
 
 extern "C" int nwb_posenc(const float* x, int64_t n, int n_freqs, float* out, void* stream) {
-    NWB_REQUIRE(x && out, "nwb_posenc: null pointer");
+    NWB_REQUIRE(n == 0 || (x && out), "nwb_posenc: null pointer");
     NWB_REQUIRE(n >= 0 && n_freqs >= 0 && n_freqs <= 24, "nwb_posenc: bad shape");
     if (n == 0) return NWB_OK;
     const int64_t total = n * (3 + 6 * n_freqs);
@@ -213,7 +213,7 @@ extern "C" int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse
                                     int n_samples, int n_importance, int det, const float* u,
                                     uint64_t seed, const float* cdf_in, float* z_out, float* z_new,
                                     int64_t* inds, void* stream) {
-    NWB_REQUIRE(z_coarse && w_coarse && z_out, "nwb_sample_pdf_merge: null pointer");
+    NWB_REQUIRE(n_rays == 0 || (z_coarse && w_coarse && z_out), "nwb_sample_pdf_merge: null pointer");
     NWB_REQUIRE(n_samples >= 3 && n_importance >= 1 && n_rays >= 0,
                 "nwb_sample_pdf_merge: need n_samples>=3, n_importance>=1");
     NWB_REQUIRE(n_samples + n_importance <= 4096, "nwb_sample_pdf_merge: too many samples per ray");
