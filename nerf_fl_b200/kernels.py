@@ -153,3 +153,114 @@ def selftest_umma(a_img: torch.Tensor, b_img: torch.Tensor, N: int, K: int, vari
     L.check(L.lib().nwb_selftest_umma(L.ptr(a_img), L.ptr(b_img), N, K, variant, ov, L.ptr(d),
                                       L.stream_ptr(a_img.device)), "nwb_selftest_umma")
     return d
+
+
+# ---- field network (a3, a4) ----------------------------------------------------------------------
+_i, _u32, _i64, _sz = C.c_int, C.c_uint32, C.c_int64, C.c_size_t
+_vp = C.c_void_p
+_bound = {}
+
+
+def _fn(name, argtypes, restype=C.c_int):
+    if name not in _bound:
+        _bound[name] = L.bind(name, argtypes, restype)
+    return _bound[name]
+
+
+def aligned_empty(nbytes: int, device, align: int = 1024) -> torch.Tensor:
+    """uint8 CUDA buffer whose data_ptr is `align`-byte aligned (tile images need 1 KB)."""
+    raw = torch.empty(nbytes + align, dtype=torch.uint8, device=device)
+    off = (-raw.data_ptr()) % align
+    return raw[off:off + nbytes]
+
+
+def field_desc(in_xyz=63, in_dir=27, in_a=0, in_t=0) -> L.FieldDesc:
+    return L.FieldDesc(in_xyz, in_dir, in_a, in_t)
+
+
+_SLOT_KEYS = ([(f"trunk_w", i, f"xyz_encoding_{i + 1}.0.weight") for i in range(8)] +
+              [(f"trunk_b", i, f"xyz_encoding_{i + 1}.0.bias") for i in range(8)] +
+              [("final_w", None, "xyz_encoding_final.weight"), ("final_b", None, "xyz_encoding_final.bias"),
+               ("dir_w", None, "dir_encoding.0.weight"), ("dir_b", None, "dir_encoding.0.bias"),
+               ("sigma_w", None, "static_sigma.0.weight"), ("sigma_b", None, "static_sigma.0.bias"),
+               ("rgb_w", None, "static_rgb.0.weight"), ("rgb_b", None, "static_rgb.0.bias")] +
+              [("tenc_w", j, f"transient_encoding.{2 * j}.weight") for j in range(4)] +
+              [("tenc_b", j, f"transient_encoding.{2 * j}.bias") for j in range(4)] +
+              [("tsigma_w", None, "transient_sigma.0.weight"), ("tsigma_b", None, "transient_sigma.0.bias"),
+               ("trgb_w", None, "transient_rgb.0.weight"), ("trgb_b", None, "transient_rgb.0.bias"),
+               ("tbeta_w", None, "transient_beta.0.weight"), ("tbeta_b", None, "transient_beta.0.bias")])
+
+
+def field_slots(sd: dict, cls=L.FieldParams):
+    """state_dict-keyed tensors (reference names) -> the C struct of device pointers.
+    Returns (struct, keepalive list)."""
+    st, keep = cls(), []
+    for slot, idx, key in _SLOT_KEYS:
+        t = sd.get(key)
+        if t is None:
+            continue
+        assert t.dtype == torch.float32 and t.is_cuda and t.is_contiguous(), key
+        keep.append(t)
+        if idx is None:
+            setattr(st, slot, t.data_ptr())
+        else:
+            getattr(st, slot)[idx] = t.data_ptr()
+    return st, keep
+
+
+def field_pack(desc: L.FieldDesc, sd: dict, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp32 nn.Linear parameters -> packed operand cache (bf16 tile images + fp32 constants)."""
+    dev = sd["xyz_encoding_1.0.weight"].device
+    nbytes = _fn("nwb_field_pack_bytes", [C.POINTER(L.FieldDesc)], _sz)(C.byref(desc))
+    if nbytes == 0:
+        L.check(-1, "nwb_field_pack_bytes")
+    if out is None:
+        out = aligned_empty(nbytes, dev)
+    st, keep = field_slots(sd)
+    L.check(_fn("nwb_field_pack", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp])(
+        C.byref(desc), C.byref(st), L.ptr(out), L.stream_ptr(dev)), "nwb_field_pack")
+    return out
+
+
+def ray_consts_fwd(desc, sd, dirs, *, dir_is_encoded=False, n_freq_dir=4, ts=None, emb_a=None, emb_t=None,
+                   a_rows=None, t_rows=None, transient=False, err_flag=None):
+    """Per-ray [dir|a|t] feature rows and the per-ray bias of dir_encoding / transient_encoding.0."""
+    dirs = _f32(dirs)
+    n = dirs.shape[0]
+    dev = dirs.device
+    mode = L.NWB_MLP_TRANSIENT if transient else 0
+    feat = torch.empty(n, desc.in_dir + desc.in_a + desc.in_t, device=dev, dtype=torch.float32)
+    bias = torch.empty(n, 256, device=dev, dtype=torch.float32)
+    if err_flag is None:
+        err_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    st, keep = field_slots(sd)
+    n_vocab = emb_a.shape[0] if emb_a is not None else (emb_t.shape[0] if emb_t is not None else 0)
+    fn = _fn("nwb_ray_consts_fwd", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _i, _i, _i, _vp, _vp, _vp,
+                                    _i, _vp, _vp, _i, _u32, _vp, _vp, _vp, _vp])
+    L.check(fn(C.byref(desc), C.byref(st), L.ptr(dirs), dirs.shape[1], int(dir_is_encoded), n_freq_dir, L.ptr(ts),
+               L.ptr(emb_a), L.ptr(emb_t), n_vocab, L.ptr(a_rows), L.ptr(t_rows), n, mode, L.ptr(feat), L.ptr(bias),
+               L.ptr(err_flag), L.stream_ptr(dev)), "nwb_ray_consts_fwd")
+    return feat, bias, err_flag
+
+
+def mlp_mode(sigma_only=False, transient=False, save=False) -> int:
+    return ((L.NWB_MLP_SIGMA_ONLY if sigma_only else 0) | (L.NWB_MLP_TRANSIENT if transient else 0)
+            | (L.NWB_MLP_SAVE if save else 0))
+
+
+def mlp_save_bytes(desc, n_points: int, mode: int) -> int:
+    return _fn("nwb_mlp_save_bytes", [C.POINTER(L.FieldDesc), _i64, _u32], _sz)(C.byref(desc), n_points, mode)
+
+
+def mlp_fwd(desc, packed, *, n_rays, S, mode, ray_bias=None, rays=None, z=None, x_enc=None, n_freq_xyz=10,
+            saved=None, out=None):
+    """Fused field forward over n_rays*S points -> raw (n_points, 1|4|9)."""
+    dev = packed.device
+    Cc = 1 if (mode & L.NWB_MLP_SIGMA_ONLY) else (9 if (mode & L.NWB_MLP_TRANSIENT) else 4)
+    if out is None:
+        out = torch.empty(n_rays * S, Cc, device=dev, dtype=torch.float32)
+    fn = _fn("nwb_mlp_fwd", [C.POINTER(L.FieldDesc), _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _u32, _vp, _vp, _vp])
+    L.check(fn(C.byref(desc), L.ptr(packed), L.ptr(rays), rays.shape[1] if rays is not None else 0, L.ptr(z),
+               L.ptr(x_enc), n_freq_xyz, L.ptr(ray_bias), n_rays, S, mode, L.ptr(out), L.ptr(saved),
+               L.stream_ptr(dev)), "nwb_mlp_fwd")
+    return out
