@@ -202,12 +202,17 @@ int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const float* rays, 
                 const float* z, const float* x_enc, int n_freq_xyz, const float* ray_bias,
                 int n_rays, int S, uint32_t mode, float* raw_out, void* saved, void* stream);
 
-/* backward of nwb_mlp_fwd: d_raw (n_points, C) -> parameter gradients (accumulated) and the
- * per-ray cotangent d_ray_bias (n_rays,256).  workspace: nwb_mlp_bwd_workspace_bytes(). */
+/* backward of nwb_mlp_fwd: raw (the forward's output) and its cotangent d_raw (n_points, C) ->
+ * parameter gradients (ACCUMULATED into the sinks with fp32 atomics; the caller zeroes them) and the
+ * per-ray cotangent d_ray_bias (n_rays,256), also accumulated (caller zeroes).  `saved` is the buffer
+ * the forward filled under NWB_MLP_SAVE; workspace: nwb_mlp_bwd_workspace_bytes() bytes, 16 B aligned.
+ * Two kernels: the dgrad chain (tcgen05, W read MN-major from the packed cache) and the weight-gradient
+ * contraction over points (tcgen05, both operands MN-major).  grads->dir_b / tenc_b[0] and the
+ * [256:] columns of dir_w / tenc_w[0] are produced by nwb_ray_consts_bwd from d_ray_bias. */
 size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode);
-int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const nwb_field_params* p,
-                const float* d_raw, const void* saved, int n_rays, int S, uint32_t mode,
-                const nwb_field_grads* grads, float* d_ray_bias, void* workspace, void* stream);
+int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                float* d_ray_bias, void* workspace, void* stream);
 
 /* backward of nwb_ray_consts_fwd: d_ray_bias -> dir_encoding / transient_encoding.0 weight
  * columns [256:] (+ their biases) and, scattered by ts, the embedding-table gradients. */

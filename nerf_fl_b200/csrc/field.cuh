@@ -81,8 +81,10 @@ inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
     return NWB_OK;
 }
 
-// saved-activation layout per tile (bf16 tile images, bytes), forward NWB_MLP_SAVE:
-//   [X: kx*16K][h1..h8: 8 x 64K][feat: 64K][dir|t0: 32K or 64K][t2,t4,t6: 3 x 32K]
+// saved-activation layout per tile (forward NWB_MLP_SAVE): bf16 tile images followed by ReLU sign masks
+//   [X: kx*16K][h1..h8: 8 x 64K][feat: 64K][dir|t0: 32K or 64K][t2,t4,t6: 3 x 32K][masks: 13 x 4K]
+// masks: per layer g, per row 8 x uint32; word w covers columns 32w..32w+31, bit (31-j) = 1 iff the
+// pre-activation of column 32w+j was negative (ReLU gate closed).
 struct SaveLayout {
     int kx; bool transient;
     __host__ __device__ size_t x_off() const { return 0; }
@@ -94,11 +96,27 @@ struct SaveLayout {
         o += transient ? 65536 : 32768;
         return o + static_cast<size_t>(g - 10) * 32768;
     }
-    __host__ __device__ size_t tile_bytes(int n_layers) const {
+    __host__ __device__ size_t acts_bytes(int n_layers) const {
         if (n_layers <= 8) return act_off(7) + 65536;
         if (n_layers <= 10) return act_off(9) + (transient ? 65536 : 32768);
         return act_off(12) + 32768;
     }
+    __host__ __device__ size_t mask_off(int g, int n_layers) const { return acts_bytes(n_layers) + static_cast<size_t>(g) * 4096; }
+    __host__ __device__ size_t tile_bytes(int n_layers) const { return acts_bytes(n_layers) + kMaxG * 4096; }
+};
+
+// backward workspace per tile (written by the dgrad kernel, read by the wgrad kernel):
+//   [dZ g0..g8: 9 x 64K][dZ9: 64K (dir|t0) or 32K (dir)][dZ10..12: 3 x 32K][dpre: 16K]
+// dZ_g = cotangent of layer g's pre-activation (bf16 tile image); dpre = cotangents of the head
+// pre-activations, one 64-column block: [sigma, rgb(3), t_sigma, t_rgb(3), t_beta, 0...].
+struct DzLayout {
+    bool transient;
+    __host__ __device__ size_t dz_off(int g) const {
+        if (g <= 9) return static_cast<size_t>(g) * 65536;
+        return 9 * 65536 + 65536 + static_cast<size_t>(g - 10) * 32768;
+    }
+    __host__ __device__ size_t dpre_off() const { return transient ? dz_off(12) + 32768 : 9 * 65536 + 32768; }
+    __host__ __device__ size_t tile_bytes() const { return dpre_off() + 16384; }
 };
 
 }  // namespace nwb

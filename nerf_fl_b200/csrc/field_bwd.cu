@@ -1,0 +1,392 @@
+// Backward of the fused field network, part 1: the dgrad chain.
+//
+// Mirror image of field_fwd.cu: one persistent warp-specialised CTA per 128-point tile walks the
+// layers in reverse.  For every layer g it forms dZ_g = dA_g (.) relu'(z_g) -- dA_g comes out of
+// TMEM (the previous step's tcgen05 product dZ_{g+1} . W_{g+1}) and/or from the head cotangents on
+// CUDA cores, the ReLU gate from the sign masks the forward saved -- writes it as a bf16 tile image
+// into shared memory (the A operand of the next product, in place), streams the same image to the
+// workspace for the wgrad kernel (field_wgrad.cu), and lets the MMA warp issue
+// dA_{g-1} = dZ_g . W_g with W_g read MN-major from the very slab images the forward uses.
+// Also produced here: the head-bias gradients, the per-ray cotangent d_ray_bias (sum of dZ_9 over
+// the samples of a ray) and the head pre-activation cotangents (dpre block) for the wgrad kernel.
+#include "field_dev.cuh"
+#include <algorithm>
+
+namespace nwb {
+
+constexpr int kBwdThreads = 192;
+constexpr int kBStageBytes = 16384;
+constexpr int kBNumStages = 2;
+constexpr int kBOffP = 0;                       // 16 KB  dpre block image
+constexpr int kBOffD = 16384;                   // 64 KB  dZ image (A operand)
+constexpr int kBOffW = kBOffD + 65536;
+constexpr int kBOffBar = kBOffW + kBNumStages * kBStageBytes;
+constexpr int kBwdSmem = kBOffBar + 256;
+
+struct BwdArgs {
+    FieldShape fs;
+    const uint8_t* packed;
+    const float* raw;
+    const float* d_raw;
+    const uint8_t* saved;
+    size_t save_tile_bytes;
+    uint8_t* dz;
+    size_t dz_tile_bytes;
+    float* d_ray_bias;
+    float* g_head_b[5];       // sigma_b, rgb_b, tsigma_b, trgb_b, tbeta_b gradient sinks
+    int S;
+    long long n_points;
+    int n_tiles;
+    uint32_t mode;
+};
+
+// one 32-column slice of dZ for this thread's row
+//   kAcc: take dA from TMEM;  kHeads > 0: add sum_h dp[h] * hw[h][c];  negmask bit (31-j): gate closed
+template <bool kAcc, int kHeads, bool kMask>
+__device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* __restrict__ hw, int hw_ld, const float* dp,
+                                          uint32_t negmask, uint8_t* sD, int row, int c_out) {
+    float x[32];
+    if (kAcc) {
+        uint32_t v[32];
+        ptx::tmem_ld32(taddr, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = 0.0f;
+    }
+    if (kHeads > 0) {
+#pragma unroll
+        for (int h = 0; h < kHeads; ++h) {
+            const float d = dp[h];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(hw + h * hw_ld) + q);
+                x[4 * q] = fmaf(d, t.x, x[4 * q]); x[4 * q + 1] = fmaf(d, t.y, x[4 * q + 1]);
+                x[4 * q + 2] = fmaf(d, t.z, x[4 * q + 2]); x[4 * q + 3] = fmaf(d, t.w, x[4 * q + 3]);
+            }
+        }
+    }
+    if (kMask) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if ((negmask >> (31 - j)) & 1u) x[j] = 0.0f;
+    }
+    store_slice_bf16(sD, row, c_out, x);
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 2)
+field_dgrad_kernel(const BwdArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sP = smem + kBOffP;
+    uint8_t* sD = smem + kBOffD;
+    uint8_t* sW = smem + kBOffW;
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kBOffBar);
+    uint64_t* bar_empty = bar_full + kBNumStages;
+    uint64_t* bar_acc = bar_empty + kBNumStages;
+    uint64_t* bar_act = bar_acc + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_act + 1);
+    uint32_t* s_woff = tmem_slot + 2;              // [kMaxG]
+    float* s_hb = reinterpret_cast<float*>(s_woff + kMaxG + 1);   // [9] head-bias gradient partials
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const FieldShape& fs = a.fs;
+    const int nl = fs.n_layers(a.mode);            // 10 or 13
+    const bool transient = (a.mode & NWB_MLP_TRANSIENT) != 0;
+
+    if (threadIdx.x == 0) {
+        if ((ptx::smem_u32(smem) & 1023u) != 0) {
+            printf("nwb: dynamic shared memory is not 1 KB aligned\n");
+            __trap();
+        }
+        for (int s = 0; s < kBNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], 1); }
+        ptx::mbar_init(bar_acc, 1);
+        ptx::mbar_init(bar_act, 128);
+        ptx::fence_mbar_init();
+        for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
+        for (int i = 0; i < 9; ++i) s_hb[i] = 0.0f;
+    }
+    if (warp == 1) ptx::tmem_alloc<256>(tmem_slot);
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ============================ weight producer ============================================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                for (int g = nl - 1; g >= 1; --g) {
+                    const uint8_t* wsrc = a.packed + s_woff[g];
+                    const int KBO = (g >= 10) ? 2 : 4, NH = fs.layer_n(g, a.mode) >> 7, PN = fs.packed_n(g);
+                    const int kshift = (g == 4) ? fs.kx : 0;       // skip the encoded-xyz slab: no d/dx needed
+                    for (int kbo = 0; kbo < KBO; ++kbo) {
+                        for (int nh = 0; nh < NH; ++nh, ++it) {
+                            const uint32_t s = it % kBNumStages;
+                            ptx::mbar_wait(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
+                            ptx::mbar_arrive_expect_tx(&bar_full[s], kBStageBytes);
+                            ptx::bulk_g2s(sW + s * kBStageBytes,
+                                          wsrc + static_cast<size_t>(kbo + kshift) * PN * 128 + nh * kBStageBytes, kBStageBytes,
+                                          &bar_full[s]);
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ============================ MMA issuer =================================================
+        if (lane == 0) {
+            // D(128 x 64) += dZ(128 x 16, K-major) . W(16 n-rows x 64 k-cols, MN-major)
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, 64, false, true);
+            const uint32_t da = ptx::smem_u32(sD), wa = ptx::smem_u32(sW);
+            uint32_t it = 0, ev = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                for (int g = nl - 1; g >= 1; --g) {
+                    ptx::mbar_wait(bar_act, ev & 1u);
+                    ++ev;
+                    ptx::tc_fence_after_sync();
+                    const int KBO = (g >= 10) ? 2 : 4, NH = fs.layer_n(g, a.mode) >> 7;
+                    const uint32_t dcol = (g == 10) ? 128u : 0u;
+                    for (int kbo = 0; kbo < KBO; ++kbo) {
+                        for (int nh = 0; nh < NH; ++nh, ++it) {
+                            const uint32_t s = it % kBNumStages;
+                            ptx::mbar_wait(&bar_full[s], (it / kBNumStages) & 1u);
+                            ptx::tc_fence_after_sync();
+                            const uint32_t wb = wa + s * kBStageBytes;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                ptx::umma_bf16(tmem + dcol + kbo * 64,
+                                               ptx::umma_desc_sw128(da + (2 * nh + (j >> 2)) * 16384 + (j & 3) * 32, 16, 1024),
+                                               ptx::umma_desc_sw128(wb + j * 2048, 16384, 1024), idesc, (nh | j) != 0);
+                            ptx::umma_commit(&bar_empty[s]);
+                        }
+                    }
+                    ptx::umma_commit(bar_acc);
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ============================ epilogue warps (thread == point) ===========================
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;
+        const int et = threadIdx.x - 64;                   // 0..127 among the epilogue threads
+        const uint32_t tlane = tmem + (static_cast<uint32_t>(quad * 32) << 16);
+        const bool leader = (et == 0);
+        const float* cst = reinterpret_cast<const float*>(a.packed + fs.w_bytes());
+        const SaveLayout sl{fs.kx, transient};
+        const DzLayout dl{transient};
+        const int C = transient ? 9 : 4;
+        uint32_t acc_ev = 0;
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            const long long p0 = static_cast<long long>(tile) * kTileM;
+            const long long p = p0 + row;
+            const bool valid = p < a.n_points;
+            const uint8_t* save_tile = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
+            uint8_t* dz_tile = a.dz + static_cast<size_t>(tile) * a.dz_tile_bytes;
+
+            // ---- head pre-activation cotangents (nerf.py:190,197,205-207 backward) --------------
+            float dp[9];                                    // [sigma, rgb3, tsigma, trgb3, tbeta]
+#pragma unroll
+            for (int i = 0; i < 9; ++i) dp[i] = 0.0f;
+            if (valid) {
+                const float* y = a.raw + p * C;
+                const float* dy = a.d_raw + p * C;
+#pragma unroll
+                for (int i = 0; i < 3; ++i) { const float v = __ldg(y + i); dp[1 + i] = __ldg(dy + i) * v * (1.0f - v); }
+                dp[0] = __ldg(dy + 3) * (1.0f - expf(-__ldg(y + 3)));          // softplus' = sigmoid(pre) = 1 - exp(-softplus)
+                if (transient) {
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) { const float v = __ldg(y + 4 + i); dp[5 + i] = __ldg(dy + 4 + i) * v * (1.0f - v); }
+                    dp[4] = __ldg(dy + 7) * (1.0f - expf(-__ldg(y + 7)));
+                    dp[8] = __ldg(dy + 8) * (1.0f - expf(-__ldg(y + 8)));
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 9; ++i) {
+                const float s = warp_sum(dp[i]);
+                if (lane == 0 && s != 0.0f) atomicAdd(&s_hb[i], s);
+            }
+            if (leader) ptx::bulk_wait_read<0>();           // previous tile's bulk stores have read sP / sD
+            epi_bar();
+            {
+                uint4 c0, c1, zz = make_uint4(0, 0, 0, 0);
+                c0.x = pack_bf16(dp[0], dp[1]); c0.y = pack_bf16(dp[2], dp[3]);
+                c0.z = pack_bf16(dp[4], dp[5]); c0.w = pack_bf16(dp[6], dp[7]);
+                c1 = zz; c1.x = pack_bf16(dp[8], 0.0f);
+                *reinterpret_cast<uint4*>(sP + ptx::image_chunk_off(row, 0)) = c0;
+                *reinterpret_cast<uint4*>(sP + ptx::image_chunk_off(row, 1)) = c1;
+#pragma unroll
+                for (int q = 2; q < 8; ++q) *reinterpret_cast<uint4*>(sP + ptx::image_chunk_off(row, q)) = zz;
+            }
+            ptx::fence_proxy_async_smem();
+            epi_bar();
+            if (leader) { ptx::bulk_s2g(dz_tile + dl.dpre_off(), sP, 16384); ptx::bulk_commit(); }
+
+            for (int g = nl - 1; g >= 0; --g) {
+                // ReLU gates of layer g (prefetched before waiting for the accumulator)
+                uint32_t mw[8];
+                if (g != 8) {
+                    const uint4* mp = reinterpret_cast<const uint4*>(save_tile + sl.mask_off(g, nl) + row * 32);
+                    const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
+                    mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w;
+                    mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
+                }
+                if (g < nl - 1) {
+                    ptx::mbar_wait(bar_acc, acc_ev & 1u);
+                    ++acc_ev;
+                    ptx::tc_fence_after_sync();
+                }
+                if (leader) ptx::bulk_wait_read<0>();       // the previous image's bulk store has read sD
+                epi_bar();
+                uint32_t dz_bytes = 65536;
+                if (g >= 10) {
+                    dz_bytes = 32768;
+                    if (g == 12) {
+#pragma unroll 1
+                        for (int c0 = 0; c0 < 128; c0 += 32)
+                            bwd_slice<false, 5, true>(0, cst + ConstOff::tsigma_w + c0, 128, dp + 4, mw[c0 >> 5], sD, row, c0);
+                    } else {
+#pragma unroll 1
+                        for (int c0 = 0; c0 < 128; c0 += 32)
+                            bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
+                    }
+                } else if (g == 9) {
+#pragma unroll 1
+                    for (int c0 = 0; c0 < 128; c0 += 32)
+                        bwd_slice<false, 3, true>(0, cst + ConstOff::rgb_w + c0, 128, dp + 1, mw[c0 >> 5], sD, row, c0);
+                    if (transient) {
+#pragma unroll 1
+                        for (int c0 = 128; c0 < 256; c0 += 32)
+                            bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
+                    } else {
+                        dz_bytes = 32768;
+                    }
+                    // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples
+                    epi_bar();
+                    {
+                        const int ncols = transient ? 256 : 128;
+                        const int c = 2 * et;
+                        if (c < ncols) {
+                            const uint8_t* colp = sD + (c >> 6) * 16384 + (c & 7) * 2;
+                            const int chunk = (c & 63) >> 3;
+                            long long ray = p0 / a.S;
+                            int in_ray = static_cast<int>(p0 - ray * a.S);
+                            float s0 = 0.0f, s1 = 0.0f;
+                            const int nrow = static_cast<int>(min(static_cast<long long>(kTileM), a.n_points - p0));
+                            for (int r = 0; r < nrow; ++r) {
+                                const uint32_t w = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r, chunk));
+                                s0 += __uint_as_float(w << 16);
+                                s1 += __uint_as_float(w & 0xFFFF0000u);
+                                if (++in_ray == a.S || r == nrow - 1) {
+                                    atomicAdd(a.d_ray_bias + ray * 256 + c, s0);
+                                    atomicAdd(a.d_ray_bias + ray * 256 + c + 1, s1);
+                                    s0 = s1 = 0.0f; in_ray = 0; ++ray;
+                                }
+                            }
+                        }
+                    }
+                } else if (g == 8) {
+#pragma unroll 1
+                    for (int c0 = 0; c0 < 256; c0 += 32)
+                        bwd_slice<true, 0, false>(tlane + c0, nullptr, 0, nullptr, 0u, sD, row, c0);
+                } else if (g == 7) {
+#pragma unroll 1
+                    for (int c0 = 0; c0 < 256; c0 += 32)
+                        bwd_slice<true, 1, true>(tlane + c0, cst + ConstOff::sigma_w + c0, 0, dp, mw[c0 >> 5], sD, row, c0);
+                } else {
+#pragma unroll 1
+                    for (int c0 = 0; c0 < 256; c0 += 32)
+                        bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
+                }
+                ptx::fence_proxy_async_smem();
+                epi_bar();
+                if (leader) { ptx::bulk_s2g(dz_tile + dl.dz_off(g), sD, dz_bytes); ptx::bulk_commit(); }
+                if (g >= 1) {
+                    ptx::tc_fence_before_sync();
+                    ptx::mbar_arrive(bar_act);
+                }
+            }
+        }
+        if (leader) ptx::bulk_wait_all<0>();
+    }
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<256>(tmem);
+    if (threadIdx.x < 9) {
+        const int i = threadIdx.x;
+        float* dst = (i == 0) ? a.g_head_b[0] : (i < 4) ? a.g_head_b[1] + (i - 1) : (i == 4) ? a.g_head_b[2]
+                   : (i < 8) ? a.g_head_b[3] + (i - 5) : a.g_head_b[4];
+        if (dst != nullptr && (i < 4 || transient)) atomicAdd(dst, s_hb[i]);
+    }
+}
+
+}  // namespace nwb
+
+using namespace nwb;
+
+int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* grads, const uint8_t* saved, size_t save_tile_bytes,
+                     const uint8_t* dz, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st);
+
+extern "C" size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode) {
+    FieldShape fs;
+    if (make_shape(d, &fs) != NWB_OK || n_points <= 0) return 0;
+    const DzLayout dl{(mode & NWB_MLP_TRANSIENT) != 0};
+    const int64_t n_tiles = (n_points + kTileM - 1) / kTileM;
+    return static_cast<size_t>(n_tiles) * dl.tile_bytes();
+}
+
+extern "C" int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                           const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                           float* d_ray_bias, void* workspace, void* stream) {
+    FieldShape fs;
+    int rc = make_shape(d, &fs);
+    if (rc != NWB_OK) return rc;
+    NWB_REQUIRE(n_rays >= 0 && S >= 1, "nwb_mlp_bwd: bad shape");
+    if (n_rays == 0) return NWB_OK;
+    NWB_REQUIRE(packed && raw && d_raw && saved && grads && d_ray_bias && workspace, "nwb_mlp_bwd: null pointer");
+    const bool transient = (mode & NWB_MLP_TRANSIENT) != 0;
+    NWB_REQUIRE(!(mode & NWB_MLP_SIGMA_ONLY), "nwb_mlp_bwd: sigma_only passes carry no gradient (test_time only)");
+    NWB_REQUIRE(!transient || fs.has_t(), "nwb_mlp_bwd: transient requested but the field has no transient head");
+    NWB_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 1023u) == 0, "nwb_mlp_bwd: packed buffer must be 1 KB aligned");
+    NWB_REQUIRE((reinterpret_cast<uintptr_t>(saved) & 15u) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 15u) == 0,
+                "nwb_mlp_bwd: saved / workspace buffers must be 16 B aligned");
+    for (int i = 0; i < 8; ++i) NWB_REQUIRE(grads->trunk_w[i] && grads->trunk_b[i], "nwb_mlp_bwd: trunk gradient sink %d is null", i);
+    NWB_REQUIRE(grads->final_w && grads->final_b && grads->dir_w && grads->sigma_w && grads->sigma_b && grads->rgb_w && grads->rgb_b,
+                "nwb_mlp_bwd: static gradient sink is null");
+    if (transient) {
+        for (int i = 0; i < 4; ++i) NWB_REQUIRE(grads->tenc_w[i] && (i == 0 || grads->tenc_b[i]), "nwb_mlp_bwd: transient gradient sink %d is null", i);
+        NWB_REQUIRE(grads->tsigma_w && grads->tsigma_b && grads->trgb_w && grads->trgb_b && grads->tbeta_w && grads->tbeta_b,
+                    "nwb_mlp_bwd: transient head gradient sink is null");
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    BwdArgs a{};
+    a.fs = fs; a.packed = static_cast<const uint8_t*>(packed); a.raw = raw; a.d_raw = d_raw;
+    a.saved = static_cast<const uint8_t*>(saved);
+    a.n_points = static_cast<long long>(n_rays) * S;
+    a.n_tiles = static_cast<int>((a.n_points + kTileM - 1) / kTileM);
+    const SaveLayout sl{fs.kx, transient};
+    const DzLayout dl{transient};
+    a.save_tile_bytes = sl.tile_bytes(fs.n_layers(mode));
+    a.dz = static_cast<uint8_t*>(workspace);
+    a.dz_tile_bytes = dl.tile_bytes();
+    a.d_ray_bias = d_ray_bias;
+    a.g_head_b[0] = grads->sigma_b; a.g_head_b[1] = grads->rgb_b; a.g_head_b[2] = grads->tsigma_b;
+    a.g_head_b[3] = grads->trgb_b; a.g_head_b[4] = grads->tbeta_b;
+    a.S = S; a.mode = mode;
+
+    static bool configured = false;
+    if (!configured) {
+        NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        configured = true;
+    }
+    const int grid = std::min(a.n_tiles, 2 * kNumSMs);
+    field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+    NWB_LAUNCH_CHECK();
+    return nwb_wgrad_launch(fs, grads, a.saved, a.save_tile_bytes, a.dz, a.dz_tile_bytes, a.n_tiles, mode, st);
+}

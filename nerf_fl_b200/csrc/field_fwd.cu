@@ -12,8 +12,7 @@
 //                     layer tcgen05.ld -> +bias (+per-ray bias) -> ReLU -> bf16 -> next layer's A
 //                     image in place; sigma / rgb / transient heads on CUDA cores in fp32.
 // Activations never leave the SM unless NWB_MLP_SAVE asks for them (bf16 tile images for backward).
-#include "field.cuh"
-#include "ptx.cuh"
+#include "field_dev.cuh"
 #include <algorithm>
 
 namespace nwb {
@@ -45,21 +44,13 @@ struct FwdArgs {
     size_t save_tile_bytes;
 };
 
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
-    __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&t);
-}
-__device__ __forceinline__ float softplus_f(float x) { return x > 20.0f ? x : log1pf(expf(x)); }
-__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
-
 // One 32-column slice of a layer epilogue for this thread's row.
 //   x = acc + bias[c] (+ rbias[c]);  optional ReLU;  optional head dot products (fp32, unrounded x);
 //   bf16 pack -> 4 x 16 B chunks of the A image at column c_out (same row).
 template <bool kRelu, int kHeads>
 __device__ __forceinline__ void epi_slice(uint32_t taddr, const float* __restrict__ bias,
                                           const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
-                                          float* hacc, uint8_t* sH, int row, int c_out) {
+                                          float* hacc, uint8_t* sH, int row, int c_out, uint32_t* mask_dst) {
     uint32_t v[32];
     ptx::tmem_ld32(taddr, v);
     float b[32];
@@ -82,11 +73,16 @@ __device__ __forceinline__ void epi_slice(uint32_t taddr, const float* __restric
     }
     ptx::tmem_ld_wait();
     float x[32];
+    uint32_t neg = 0;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
         x[j] = __uint_as_float(v[j]) + b[j];
-        if (kRelu) x[j] = fmaxf(x[j], 0.0f);
+        if (kRelu) {
+            neg = __funnelshift_l(__float_as_uint(x[j]), neg, 1);   // bit (31-j) = sign of the pre-activation
+            x[j] = fmaxf(x[j], 0.0f);
+        }
     }
+    if (kRelu && mask_dst != nullptr) *mask_dst = neg;
     if (kHeads > 0) {
 #pragma unroll
         for (int h = 0; h < kHeads; ++h) {
@@ -100,17 +96,7 @@ __device__ __forceinline__ void epi_slice(uint32_t taddr, const float* __restric
             hacc[h] = a;
         }
     }
-    uint8_t* blk = sH + (c_out >> 6) * 16384;
-    const int chunk0 = (c_out & 63) >> 3;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint4 pk;
-        pk.x = pack_bf16(x[8 * q], x[8 * q + 1]);
-        pk.y = pack_bf16(x[8 * q + 2], x[8 * q + 3]);
-        pk.z = pack_bf16(x[8 * q + 4], x[8 * q + 5]);
-        pk.w = pack_bf16(x[8 * q + 6], x[8 * q + 7]);
-        *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0 + q)) = pk;
-    }
+    store_slice_bf16(sH, row, c_out, x);
 }
 
 __global__ void __launch_bounds__(kFwdThreads, 2)
@@ -291,42 +277,43 @@ field_fwd_kernel(const FwdArgs a) {
                     epi_bar();
                 }
                 float hacc[5] = {0, 0, 0, 0, 0};
+                uint32_t* mrow = save ? reinterpret_cast<uint32_t*>(save_tile + sl.mask_off(g, nl)) + row * 8 : nullptr;
                 if (g < 7) {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
-                        epi_slice<true, 0>(tlane + c0, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, sH, row, c0);
+                        epi_slice<true, 0>(tlane + c0, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
                 } else if (g == 7) {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
                         epi_slice<true, 1>(tlane + c0, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                           hacc, sH, row, c0);
+                                           hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
                     sigma = softplus_f(hacc[0] + __ldg(cst + ConstOff::head_b));                // nerf.py:190
                 } else if (g == 8) {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
-                        epi_slice<false, 0>(tlane + c0, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, sH, row, c0);
+                        epi_slice<false, 0>(tlane + c0, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
                 } else if (g == 9) {
                     // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
 #pragma unroll 1
                     for (int c0 = 0; c0 < 128; c0 += 32)
-                        epi_slice<true, 3>(tlane + c0, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, sH, row, c0);
+                        epi_slice<true, 3>(tlane + c0, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
 #pragma unroll
                     for (int i = 0; i < 3; ++i) rgb[i] = sigmoid_f(hacc[i] + __ldg(cst + ConstOff::head_b + 1 + i));   // nerf.py:197
                     if (transient) {
 #pragma unroll 1
                         for (int c0 = 128; c0 < 256; c0 += 32)
-                            epi_slice<true, 0>(tlane + c0, nullptr, rb + c0, nullptr, 0, hacc, sH, row, c0);
+                            epi_slice<true, 0>(tlane + c0, nullptr, rb + c0, nullptr, 0, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
                     }
                 } else if (g < 12) {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 128; c0 += 32)
-                        epi_slice<true, 0>(tlane + c0, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, sH, row, 128 + c0);
+                        epi_slice<true, 0>(tlane + c0, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, sH, row, 128 + c0, mrow ? mrow + (c0 >> 5) : nullptr);
                 } else {
                     // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
 #pragma unroll 1
                     for (int c0 = 0; c0 < 128; c0 += 32)
                         epi_slice<true, 5>(tlane + c0, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                           hacc, sH, row, 128 + c0);
+                                           hacc, sH, row, 128 + c0, mrow ? mrow + (c0 >> 5) : nullptr);
                 }
                 ptx::fence_proxy_async_smem();
                 if (save) {

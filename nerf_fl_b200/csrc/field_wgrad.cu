@@ -1,0 +1,265 @@
+// Backward of the fused field network, part 2: weight / bias / head-weight gradients.
+//
+// Every parameter gradient of the field is a contraction over points of two bf16 tile images that
+// already sit in HBM: dW_g = dZ_g^T . A_g (dZ_g from the dgrad kernel's workspace, A_g = the layer's
+// input activation saved by the forward).  Both images have rows == points, so both are fed to
+// tcgen05.mma MN-major with no transpose anywhere.  The work is cut into "units" -- one 128-row half
+// of one layer's dZ (the M side) against one activation image (the N side, <= 256 columns) -- and each
+// unit is split over points across CTAs in proportion to its byte traffic (the kernel is HBM/L2-bound:
+// 96 KB of operands per 1024 tensor cycles).  A CTA keeps its (128 x <=256) fp32 partial in TMEM over
+// its whole tile range, and flushes it once with fp32 atomics.  Bias gradients ride along as one more
+// N=16 MMA per k-step against a constant block of ones; head-weight gradients are units whose M side
+// is the head's input activation and whose N side is the dpre block.
+#include "field_dev.cuh"
+#include <algorithm>
+
+namespace nwb {
+
+constexpr int kWgThreads = 192;
+constexpr int kWgStages = 2;
+constexpr int kWgMBytes = 32768;                 // M side: 128 points x 128 columns
+constexpr int kWgNBytes = 65536;                 // N side: 128 points x <= 256 columns
+constexpr int kWgStageBytes = kWgMBytes + kWgNBytes;
+constexpr int kWgOffOnes = kWgStages * kWgStageBytes;
+constexpr int kWgOffBar = kWgOffOnes + 2048;
+constexpr int kWgSmem = kWgOffBar + 128;
+constexpr int kWgMaxUnits = 40;
+
+struct WUnit {
+    uint32_t m_off, n_off;        // byte offsets inside the tile record
+    uint8_t m_src, n_src;         // 0 = dgrad workspace, 1 = forward save buffer
+    uint8_t n_blocks;             // N side 64-column blocks (1..4)
+    uint8_t ones;                 // also accumulate sum_p dZ[p, m] (bias gradient)
+    uint8_t head_lo, head_hi;     // head unit: D[m][n], n in [head_lo, head_hi) -> head_out[n][m_base + m]
+    uint16_t n_valid;             // valid N columns (e.g. 63 of 64 for the encoded-xyz block)
+    uint16_t m_base;              // first output row (normal) / first head column (head unit)
+    uint16_t n_base;              // first output column
+    uint16_t ld;                  // output row stride (floats)
+    float* out;                   // normal unit: out[(m_base+m)*ld + n_base + n]
+    float* out_b;                 // ones: out_b[m_base + m]
+    uint16_t cta0, splits;        // CTAs [cta0, cta0+splits) work on this unit
+};
+
+struct WgArgs {
+    const uint8_t* dz;
+    const uint8_t* saved;
+    size_t dz_tile_bytes, save_tile_bytes;
+    int n_tiles, n_units;
+    float* head_out[9];
+    WUnit units[kWgMaxUnits];
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+field_wgrad_kernel(const __grid_constant__ WgArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sOnes = smem + kWgOffOnes;
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kWgOffBar);
+    uint64_t* bar_empty = bar_full + kWgStages;
+    uint64_t* bar_done = bar_empty + kWgStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // which unit / which slice of the tiles is mine
+    int ui = 0;
+    while (ui + 1 < a.n_units && static_cast<int>(blockIdx.x) >= a.units[ui + 1].cta0) ++ui;
+    const WUnit& u = a.units[ui];
+    const int split = blockIdx.x - u.cta0;
+    const int t0 = static_cast<int>(static_cast<long long>(a.n_tiles) * split / u.splits);
+    const int t1 = static_cast<int>(static_cast<long long>(a.n_tiles) * (split + 1) / u.splits);
+    const uint32_t m_stride = static_cast<uint32_t>(u.m_src ? a.save_tile_bytes : a.dz_tile_bytes);
+    const uint32_t n_stride = static_cast<uint32_t>(u.n_src ? a.save_tile_bytes : a.dz_tile_bytes);
+    const uint8_t* m_base = (u.m_src ? a.saved : a.dz) + u.m_off;
+    const uint8_t* n_base = (u.n_src ? a.saved : a.dz) + u.n_off;
+    const uint32_t n_bytes = static_cast<uint32_t>(u.n_blocks) * 16384u;
+
+    if (threadIdx.x == 0) {
+        if ((ptx::smem_u32(smem) & 1023u) != 0) {
+            printf("nwb: dynamic shared memory is not 1 KB aligned\n");
+            __trap();
+        }
+        for (int s = 0; s < kWgStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], 1); }
+        ptx::mbar_init(bar_done, 1);
+        ptx::fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < 512; i += blockDim.x) reinterpret_cast<uint32_t*>(sOnes)[i] = 0x3F803F80u;   // bf16 1.0
+    ptx::fence_proxy_async_smem();
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int t = t0; t < t1; ++t, ++it) {
+                const uint32_t s = it % kWgStages;
+                ptx::mbar_wait(&bar_empty[s], ((it / kWgStages) & 1u) ^ 1u);
+                ptx::mbar_arrive_expect_tx(&bar_full[s], kWgMBytes + n_bytes);
+                uint8_t* st = smem + s * kWgStageBytes;
+                ptx::bulk_g2s(st, m_base + static_cast<size_t>(t) * m_stride, kWgMBytes, &bar_full[s]);
+                ptx::bulk_g2s(st + kWgMBytes, n_base + static_cast<size_t>(t) * n_stride, n_bytes, &bar_full[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // D(128 m x N) += M_img^T (16 points x 128 m, MN-major) . N_img (16 points x N, MN-major)
+            const uint32_t idesc = ptx::umma_idesc_bf16(128, u.n_blocks * 64, true, true);
+            constexpr uint32_t idesc1 = ptx::umma_idesc_bf16(128, 16, true, true);
+            const uint32_t ones = ptx::smem_u32(sOnes);
+            uint32_t it = 0;
+            for (int t = t0; t < t1; ++t, ++it) {
+                const uint32_t s = it % kWgStages;
+                ptx::mbar_wait(&bar_full[s], (it / kWgStages) & 1u);
+                ptx::tc_fence_after_sync();
+                const uint32_t ma = ptx::smem_u32(smem + s * kWgStageBytes), na = ma + kWgMBytes;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint64_t ad = ptx::umma_desc_sw128(ma + j * 2048, 16384, 1024);
+                    ptx::umma_bf16(tmem, ad, ptx::umma_desc_sw128(na + j * 2048, 16384, 1024), idesc, (it | j) != 0);
+                    if (u.ones) ptx::umma_bf16(tmem + 256, ad, ptx::umma_desc_sw128(ones, 16384, 1024), idesc1, (it | j) != 0);
+                }
+                ptx::umma_commit(&bar_empty[s]);
+            }
+            ptx::umma_commit(bar_done);
+        }
+        __syncwarp();
+    } else if (t1 > t0) {
+        // ---- flush: thread == D row m ------------------------------------------------------------
+        const int quad = warp & 3;
+        const int m = quad * 32 + lane;
+        const uint32_t tlane = tmem + (static_cast<uint32_t>(quad * 32) << 16);
+        ptx::mbar_wait(bar_done, 0);
+        ptx::tc_fence_after_sync();
+        if (u.head_hi > u.head_lo) {
+            uint32_t v[32];
+            ptx::tmem_ld32(tlane, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int n = 0; n < 9; ++n)
+                if (n >= u.head_lo && n < u.head_hi) atomicAdd(a.head_out[n] + u.m_base + m, __uint_as_float(v[n]));
+        } else {
+            float* orow = u.out + static_cast<size_t>(u.m_base + m) * u.ld + u.n_base;
+            for (int c0 = 0; c0 < u.n_valid; c0 += 32) {
+                uint32_t v[32];
+                ptx::tmem_ld32(tlane + c0, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (c0 + j < u.n_valid) atomicAdd(orow + c0 + j, __uint_as_float(v[j]));
+            }
+            if (u.ones && u.out_b != nullptr) {
+                uint32_t v[32];
+                ptx::tmem_ld32(tlane + 256, v);
+                ptx::tmem_ld_wait();
+                atomicAdd(u.out_b + u.m_base + m, __uint_as_float(v[0]));
+            }
+        }
+    }
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem);
+}
+
+}  // namespace nwb
+
+using namespace nwb;
+
+int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8_t* saved, size_t save_tile_bytes,
+                     const uint8_t* dz, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st) {
+    const bool transient = (mode & NWB_MLP_TRANSIENT) != 0;
+    const SaveLayout sl{fs.kx, transient};
+    const DzLayout dl{transient};
+    static WgArgs a;                       // host staging (passed by value at launch)
+    a = WgArgs{};
+    a.dz = dz; a.saved = saved; a.dz_tile_bytes = dz_tile_bytes; a.save_tile_bytes = save_tile_bytes;
+    a.n_tiles = n_tiles;
+    int nu = 0;
+    auto add = [&](uint32_t m_off, int m_src, uint32_t n_off, int n_src, int n_blocks, int n_valid, bool ones, float* out,
+                   int ld, int m_base_, int n_base_, float* out_b) -> WUnit& {
+        WUnit& u = a.units[nu++];
+        u.m_off = m_off; u.m_src = static_cast<uint8_t>(m_src); u.n_off = n_off; u.n_src = static_cast<uint8_t>(n_src);
+        u.n_blocks = static_cast<uint8_t>(n_blocks); u.n_valid = static_cast<uint16_t>(n_valid); u.ones = ones ? 1 : 0;
+        u.out = out; u.ld = static_cast<uint16_t>(ld); u.m_base = static_cast<uint16_t>(m_base_);
+        u.n_base = static_cast<uint16_t>(n_base_); u.out_b = out_b; u.head_lo = u.head_hi = 0;
+        return u;
+    };
+    const int xcols = 64 * fs.kx;
+    for (int gq = 0; gq <= 8; ++gq) {
+        float* W = (gq < 8) ? g->trunk_w[gq] : g->final_w;
+        float* B = (gq < 8) ? g->trunk_b[gq] : g->final_b;
+        for (int mh = 0; mh < 2; ++mh) {
+            const uint32_t m_off = static_cast<uint32_t>(dl.dz_off(gq)) + mh * 32768u;
+            if (gq == 0) {
+                add(m_off, 0, static_cast<uint32_t>(sl.x_off()), 1, fs.kx, fs.in_xyz, true, W, fs.in_xyz, mh * 128, 0, B);
+            } else if (gq == 4) {
+                add(m_off, 0, static_cast<uint32_t>(sl.x_off()), 1, fs.kx, fs.in_xyz, false, W, fs.in_xyz + kW, mh * 128, 0, nullptr);
+                add(m_off, 0, static_cast<uint32_t>(sl.act_off(3)), 1, 4, 256, true, W, fs.in_xyz + kW, mh * 128, fs.in_xyz, B);
+            } else {
+                add(m_off, 0, static_cast<uint32_t>(sl.act_off(gq - 1)), 1, 4, 256, true, W, kW, mh * 128, 0, B);
+            }
+        }
+    }
+    (void)xcols;
+    // g = 9: feature columns of dir_encoding.0 / transient_encoding.0 (their other columns and biases
+    // come from the per-ray operands, ray_consts.cu)
+    add(static_cast<uint32_t>(dl.dz_off(9)), 0, static_cast<uint32_t>(sl.act_off(8)), 1, 4, 256, false, g->dir_w,
+        kW + fs.in_dir + fs.in_a, 0, 0, nullptr);
+    if (transient) {
+        add(static_cast<uint32_t>(dl.dz_off(9)) + 32768u, 0, static_cast<uint32_t>(sl.act_off(8)), 1, 4, 256, false, g->tenc_w[0],
+            kW + fs.in_t, 0, 0, nullptr);
+        for (int gq = 10; gq <= 12; ++gq) {
+            const uint32_t n_off = (gq == 10) ? static_cast<uint32_t>(sl.act_off(9)) + 32768u : static_cast<uint32_t>(sl.act_off(gq - 1));
+            add(static_cast<uint32_t>(dl.dz_off(gq)), 0, n_off, 1, 2, 128, true, g->tenc_w[gq - 9], kHalf, 0, 0, g->tenc_b[gq - 9]);
+        }
+    }
+    // heads: M side = the head's input activation, N side = dpre block
+    const uint32_t dpre = static_cast<uint32_t>(dl.dpre_off());
+    for (int mh = 0; mh < 2; ++mh) {
+        WUnit& u = add(static_cast<uint32_t>(sl.act_off(7)) + mh * 32768u, 1, dpre, 0, 1, 16, false, nullptr, 0, mh * 128, 0, nullptr);
+        u.head_lo = 0; u.head_hi = 1;
+    }
+    { WUnit& u = add(static_cast<uint32_t>(sl.act_off(9)), 1, dpre, 0, 1, 16, false, nullptr, 0, 0, 0, nullptr); u.head_lo = 1; u.head_hi = 4; }
+    if (transient) { WUnit& u = add(static_cast<uint32_t>(sl.act_off(12)), 1, dpre, 0, 1, 16, false, nullptr, 0, 0, 0, nullptr); u.head_lo = 4; u.head_hi = 9; }
+    a.head_out[0] = g->sigma_w;
+    for (int i = 0; i < 3; ++i) a.head_out[1 + i] = g->rgb_w + i * kHalf;
+    if (transient) {
+        a.head_out[4] = g->tsigma_w;
+        for (int i = 0; i < 3; ++i) a.head_out[5 + i] = g->trgb_w + i * kHalf;
+        a.head_out[8] = g->tbeta_w;
+    }
+    a.n_units = nu;
+    // split every unit over points in proportion to its operand bytes per tile
+    double cost[kWgMaxUnits], total = 0;
+    int sp[kWgMaxUnits], cta = 0;
+    for (int i = 0; i < nu; ++i) { cost[i] = kWgMBytes + 16384.0 * a.units[i].n_blocks; total += cost[i]; }
+    const int budget = std::max(nu, std::min(kNumSMs, nu * n_tiles));      // one CTA per SM, never a second wave
+    for (int i = 0; i < nu; ++i) { sp[i] = std::max(1, std::min(static_cast<int>(cost[i] / total * budget), n_tiles)); cta += sp[i]; }
+    while (cta > budget) {                       // trim the unit with the least work per CTA
+        int k = -1;
+        for (int i = 0; i < nu; ++i) if (sp[i] > 1 && (k < 0 || cost[i] / sp[i] < cost[k] / sp[k])) k = i;
+        if (k < 0) break;
+        --sp[k]; --cta;
+    }
+    while (cta < budget) {                       // grow the unit with the most work per CTA
+        int k = -1;
+        for (int i = 0; i < nu; ++i) if (sp[i] < n_tiles && (k < 0 || cost[i] / sp[i] > cost[k] / sp[k])) k = i;
+        if (k < 0) break;
+        ++sp[k]; ++cta;
+    }
+    cta = 0;
+    for (int i = 0; i < nu; ++i) {
+        a.units[i].cta0 = static_cast<uint16_t>(cta);
+        a.units[i].splits = static_cast<uint16_t>(sp[i]);
+        cta += sp[i];
+    }
+    static bool configured = false;
+    if (!configured) {
+        NWB_CUDA(cudaFuncSetAttribute(field_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
+        configured = true;
+    }
+    field_wgrad_kernel<<<cta, kWgThreads, kWgSmem, st>>>(a);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}

@@ -264,3 +264,35 @@ def mlp_fwd(desc, packed, *, n_rays, S, mode, ray_bias=None, rays=None, z=None, 
                L.ptr(x_enc), n_freq_xyz, L.ptr(ray_bias), n_rays, S, mode, L.ptr(out), L.ptr(saved),
                L.stream_ptr(dev)), "nwb_mlp_fwd")
     return out
+
+
+def mlp_bwd_workspace_bytes(desc, n_points: int, mode: int) -> int:
+    return _fn("nwb_mlp_bwd_workspace_bytes", [C.POINTER(L.FieldDesc), _i64, _u32], _sz)(C.byref(desc), n_points, mode)
+
+
+def mlp_bwd(desc, packed, raw, d_raw, saved, *, n_rays, S, mode, grads: dict, d_ray_bias, workspace=None):
+    """Backward of mlp_fwd: accumulates into `grads` (state_dict-keyed fp32 tensors, caller zeroes)
+    and into d_ray_bias (n_rays, 256)."""
+    dev = packed.device
+    mode &= ~L.NWB_MLP_SAVE
+    if workspace is None:
+        workspace = aligned_empty(mlp_bwd_workspace_bytes(desc, n_rays * S, mode), dev, 16)
+    st, keep = field_slots(grads, L.FieldGrads)
+    fn = _fn("nwb_mlp_bwd", [C.POINTER(L.FieldDesc), _vp, _vp, _vp, _vp, _i, _i, _u32, C.POINTER(L.FieldGrads), _vp, _vp, _vp])
+    L.check(fn(C.byref(desc), L.ptr(packed), L.ptr(raw), L.ptr(d_raw), L.ptr(saved), n_rays, S, mode, C.byref(st),
+               L.ptr(d_ray_bias), L.ptr(workspace), L.stream_ptr(dev)), "nwb_mlp_bwd")
+    return workspace
+
+
+def ray_consts_bwd(desc, sd, ray_feat, d_ray_bias, *, ts=None, n_vocab=0, transient=False, grads: dict,
+                   d_emb_a=None, d_emb_t=None, d_a_rows=None, d_t_rows=None):
+    """d_ray_bias -> dir_encoding / transient_encoding.0 columns [256:], their biases, embedding rows."""
+    dev = ray_feat.device
+    mode = L.NWB_MLP_TRANSIENT if transient else 0
+    st, keep = field_slots(sd)
+    gt, keep2 = field_slots(grads, L.FieldGrads)
+    fn = _fn("nwb_ray_consts_bwd", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp, _vp, _i, _i, _u32,
+                                    C.POINTER(L.FieldGrads), _vp, _vp, _vp, _vp, _vp])
+    L.check(fn(C.byref(desc), C.byref(st), L.ptr(ray_feat), L.ptr(d_ray_bias), L.ptr(ts), n_vocab, ray_feat.shape[0],
+               mode, C.byref(gt), L.ptr(d_emb_a), L.ptr(d_emb_t), L.ptr(d_a_rows), L.ptr(d_t_rows),
+               L.stream_ptr(dev)), "nwb_ray_consts_bwd")

@@ -318,3 +318,50 @@ def nerfw_loss(res: dict, targets: torch.Tensor, coef: float = 1.0, lambda_u: fl
             terms["b_l"] = 3 + torch.log(res["beta"]).mean()
             terms["s_l"] = lambda_u * res["transient_sigmas"].mean()
     return {k: coef * v for k, v in terms.items()}
+
+
+# ----------------------------------------------------------------------------------------------
+# Operand-rounding model of the product's tensor-core path (test infrastructure, like the rest of
+# this file).  Same algorithm as field_forward (models/nerf.py:153-212), but every GEMM operand
+# that the CUDA kernels feed to tcgen05 -- activations and the matching weight columns -- is
+# rounded to bf16 first (fp32 accumulate); per-ray columns (dir / appearance / transient inputs)
+# and the 1|3|5-wide heads stay fp32, as in the kernels.  Rounding is straight-through for autograd.
+# Needed because ReLU gates of pre-activations within ~2^-9 of zero differ between an fp32 and a
+# bf16-operand forward, which makes per-sample gradients of the two differ by a few percent no
+# matter how the kernel is written; against THIS model the kernels must agree tightly.
+# ----------------------------------------------------------------------------------------------
+class _RoundBf16(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def field_forward_bf16(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor, tt: torch.Tensor | None,
+                       output_transient: bool) -> torch.Tensor:
+    r = _RoundBf16.apply
+
+    def lin(n, x):
+        return F.linear(r(x), r(p[n + ".weight"]), p[n + ".bias"])
+
+    h = xyz
+    for i in range(8):
+        if i == 4:
+            h = torch.cat([xyz, h], 1)
+        h = torch.relu(lin(f"xyz_encoding_{i + 1}.0", h))
+    sigma = F.softplus(_lin(p, "static_sigma.0", h))
+    feat = lin("xyz_encoding_final", h)
+    Wd = p["dir_encoding.0.weight"]
+    hd = torch.relu(F.linear(r(feat), r(Wd[:, :256])) + F.linear(dir_a, Wd[:, 256:], p["dir_encoding.0.bias"]))
+    out = [torch.sigmoid(_lin(p, "static_rgb.0", hd)), sigma]
+    if output_transient:
+        Wt = p["transient_encoding.0.weight"]
+        ht = torch.relu(F.linear(r(feat), r(Wt[:, :256])) + F.linear(tt, Wt[:, 256:], p["transient_encoding.0.bias"]))
+        for j in (2, 4, 6):
+            ht = torch.relu(lin(f"transient_encoding.{j}", ht))
+        out += [torch.sigmoid(_lin(p, "transient_rgb.0", ht)), F.softplus(_lin(p, "transient_sigma.0", ht)),
+                F.softplus(_lin(p, "transient_beta.0", ht))]
+    return torch.cat(out, 1)

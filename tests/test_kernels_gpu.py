@@ -286,3 +286,85 @@ def test_field_forward_rays_vs_oracle(n_rays, S, transient):
         parts.append(emb_t[ts].repeat_interleave(S, 0))
     want = O.field_forward(sd, torch.cat(parts, -1), in_dir_a=27 + 48, output_transient=transient)
     assert maxerr(got, want) <= 3e-3 * max(1.0, want.abs().max().item()), maxerr(got, want)
+
+
+def _relerr(got, ref):
+    got, ref = got.detach().double().cpu().flatten(), ref.detach().double().cpu().flatten()
+    l2 = (got - ref).norm().item() / max(ref.norm().item(), 1e-30)
+    cos = torch.nn.functional.cosine_similarity(got, ref, dim=0).item()
+    return l2, cos
+
+
+@pytest.mark.parametrize("n_rays,S,transient,scale", [(6, 64, True, 1.0), (41, 128, True, 3.0), (9, 64, False, 1.0),
+                                                     (130, 96, True, 1.0)])
+def test_field_backward_vs_oracle(n_rays, S, transient, scale):
+    """Every parameter / embedding gradient of one field evaluation, with random cotangents, against
+    autograd through (i) the oracle's bf16-operand model of the kernel and (ii) the plain fp32 oracle.
+    Per-sample gradients of a ReLU net are discontinuous in the forward's rounding (a gate whose
+    pre-activation sits within 2^-9 of zero opens in one forward and not the other), so with bf16
+    operands the fp32 comparison is bounded by gate noise, not by the kernel: (i) is the tight check,
+    (ii) bounds direction and size.  Head gradients (no gate downstream) must meet 1e-2 in both."""
+    gen = torch.Generator().manual_seed(n_rays * 7 + S)
+    rays = syn.blender_rays(n_rays, seed=3)
+    z = torch.sort(torch.rand(n_rays, S, generator=gen) * 4 + 2, dim=-1)[0]
+    sd = syn.make_field_params(33, "fine", True, transient, weight_scale=scale)
+    n_vocab = 7
+    emb_a, emb_t = syn.make_embedding(5, n_vocab, 48), syn.make_embedding(6, n_vocab, 16)
+    ts = torch.randint(0, n_vocab, (n_rays,), generator=gen)
+    C9 = 9 if transient else 4
+    d_raw = torch.randn(n_rays * S, C9, generator=gen)
+
+    def oracle_grads(emulate):
+        sd_o = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        ea_o, et_o = emb_a.clone().requires_grad_(True), emb_t.clone().requires_grad_(True)
+        xyz = (rays[:, None, 0:3] + rays[:, None, 3:6] * z[:, :, None]).reshape(-1, 3)
+        x_e = O.posenc(xyz, 10)
+        dir_a = torch.cat([O.posenc(rays[:, 3:6], 4).repeat_interleave(S, 0), ea_o[ts].repeat_interleave(S, 0)], -1)
+        tt = et_o[ts].repeat_interleave(S, 0) if transient else None
+        if emulate:
+            raw_o = O.field_forward_bf16(sd_o, x_e, dir_a, tt, transient)
+        else:
+            raw_o = O.field_forward(sd_o, torch.cat([x_e, dir_a] + ([tt] if transient else []), -1), in_dir_a=27 + 48,
+                                    output_transient=transient)
+        (raw_o * d_raw).sum().backward()
+        g = {k: v.grad for k, v in sd_o.items()}
+        g["emb_a"] = ea_o.grad
+        if transient:
+            g["emb_t"] = et_o.grad
+        return g
+
+    # ---- product ----
+    desc = K.field_desc(63, 27, 48, 16 if transient else 0)
+    sdd = _sd_dev(sd)
+    packed = K.field_pack(desc, sdd)
+    ts_d, ea_d, et_d = ts.to(DEV), emb_a.to(DEV), emb_t.to(DEV)
+    feat, rb, _ = K.ray_consts_fwd(desc, sdd, rays[:, 3:6].to(DEV).contiguous(), n_freq_dir=4, ts=ts_d, emb_a=ea_d,
+                                   emb_t=et_d if transient else None, transient=transient)
+    mode = K.mlp_mode(transient=transient, save=True)
+    saved = K.aligned_empty(K.mlp_save_bytes(desc, n_rays * S, mode), DEV, 16)
+    raw = K.mlp_fwd(desc, packed, n_rays=n_rays, S=S, mode=mode, ray_bias=rb, rays=rays.to(DEV), z=z.to(DEV), saved=saved)
+    grads = {k: torch.zeros_like(v) for k, v in sdd.items()}
+    d_rb = torch.zeros(n_rays, 256, device=DEV)
+    K.mlp_bwd(desc, packed, raw, d_raw.to(DEV), saved, n_rays=n_rays, S=S, mode=mode, grads=grads, d_ray_bias=d_rb)
+    d_ea, d_et = torch.zeros_like(ea_d), torch.zeros_like(et_d)
+    K.ray_consts_bwd(desc, sdd, feat, d_rb, ts=ts_d, n_vocab=n_vocab, transient=transient, grads=grads, d_emb_a=d_ea,
+                     d_emb_t=d_et if transient else None)
+    torch.cuda.synchronize()
+    grads["emb_a"] = d_ea
+    if transient:
+        grads["emb_t"] = d_et
+    g_emu, g_f32 = oracle_grads(True), oracle_grads(False)
+    bad = []
+    for k in g_f32:
+        l2e, cose = _relerr(grads[k], g_emu[k])
+        l2f, cosf = _relerr(grads[k], g_f32[k])
+        ungated = k.startswith(("static_sigma", "static_rgb", "transient_sigma", "transient_rgb", "transient_beta")) \
+            and k.endswith("bias")
+        if ungated:
+            # scalar sums of signed terms: ill-conditioned under the x3 weights' larger forward differences
+            ok = (l2e <= 1e-2 and l2f <= 1e-2) if scale == 1.0 else l2e <= 5e-2
+        else:
+            ok = l2e <= 8e-2 and cose >= 0.997 and l2f <= 0.25 and cosf >= 0.97
+        if not ok:
+            bad.append((k, round(l2e, 4), round(cose, 5), round(l2f, 4), round(cosf, 5)))
+    assert not bad, bad
