@@ -213,6 +213,14 @@ size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n_points, ui
 int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
                 const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
                 float* d_ray_bias, void* workspace, void* stream);
+/* the two kernels of nwb_mlp_bwd as separate calls (same arguments; dgrad first, then wgrad on the
+ * workspace it filled) -- lets a caller time them apart or overlap wgrad with other work */
+int nwb_mlp_dgrad(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                  const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                  float* d_ray_bias, void* workspace, void* stream);
+int nwb_mlp_wgrad(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                  const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                  float* d_ray_bias, void* workspace, void* stream);
 
 /* backward of nwb_ray_consts_fwd: d_ray_bias -> dir_encoding / transient_encoding.0 weight
  * columns [256:] (+ their biases) and, scattered by ts, the embedding-table gradients. */
@@ -220,6 +228,15 @@ int nwb_ray_consts_bwd(const nwb_field_desc* d, const nwb_field_params* p, const
                        const float* d_ray_bias, const int64_t* ts, int n_vocab, int n_rays,
                        uint32_t mode, const nwb_field_grads* grads, float* d_emb_a,
                        float* d_emb_t, float* d_a_rows, float* d_t_rows, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * optimizer step on flat buffers -- utils/__init__.py:24-33 (torch.optim.Adam(lr, eps=1e-8,
+ * weight_decay)), train.py:139-142.  p, g, m, v: n fp32 each (16 B aligned); `step` counts from 1;
+ * g is multiplied by grad_scale first (1/world_size turns an allreduce-sum into DDP's mean);
+ * zero_grad != 0 clears g afterwards (the kernels of the next step accumulate into it).
+ * ---------------------------------------------------------------------------------------- */
+int nwb_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                  float eps, float weight_decay, int step, float grad_scale, int zero_grad, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T

@@ -339,9 +339,9 @@ extern "C" size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n
     return static_cast<size_t>(n_tiles) * dl.tile_bytes();
 }
 
-extern "C" int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
-                           const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
-                           float* d_ray_bias, void* workspace, void* stream) {
+static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                          const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                          float* d_ray_bias, void* workspace, void* stream, bool run_dgrad, bool run_wgrad) {
     FieldShape fs;
     int rc = make_shape(d, &fs);
     if (rc != NWB_OK) return rc;
@@ -379,14 +379,34 @@ extern "C" int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const fl
     a.g_head_b[3] = grads->trgb_b; a.g_head_b[4] = grads->tbeta_b;
     a.S = S; a.mode = mode;
 
-    static bool configured = false;
-    if (!configured) {
-        NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
-        NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        configured = true;
+    if (run_dgrad) {
+        static bool configured = false;
+        if (!configured) {
+            NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+            NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            configured = true;
+        }
+        const int grid = std::min(a.n_tiles, 2 * kNumSMs);
+        field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+        NWB_LAUNCH_CHECK();
     }
-    const int grid = std::min(a.n_tiles, 2 * kNumSMs);
-    field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
-    NWB_LAUNCH_CHECK();
-    return nwb_wgrad_launch(fs, grads, a.saved, a.save_tile_bytes, a.dz, a.dz_tile_bytes, a.n_tiles, mode, st);
+    if (run_wgrad)
+        return nwb_wgrad_launch(fs, grads, a.saved, a.save_tile_bytes, a.dz, a.dz_tile_bytes, a.n_tiles, mode, st);
+    return NWB_OK;
+}
+
+extern "C" int nwb_mlp_bwd(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                           const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                           float* d_ray_bias, void* workspace, void* stream) {
+    return mlp_bwd_phases(d, packed, raw, d_raw, saved, n_rays, S, mode, grads, d_ray_bias, workspace, stream, true, true);
+}
+extern "C" int nwb_mlp_dgrad(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                             const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                             float* d_ray_bias, void* workspace, void* stream) {
+    return mlp_bwd_phases(d, packed, raw, d_raw, saved, n_rays, S, mode, grads, d_ray_bias, workspace, stream, true, false);
+}
+extern "C" int nwb_mlp_wgrad(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
+                             const void* saved, int n_rays, int S, uint32_t mode, const nwb_field_grads* grads,
+                             float* d_ray_bias, void* workspace, void* stream) {
+    return mlp_bwd_phases(d, packed, raw, d_raw, saved, n_rays, S, mode, grads, d_ray_bias, workspace, stream, false, true);
 }

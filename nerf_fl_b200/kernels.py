@@ -12,6 +12,50 @@ import torch
 from . import _lib as L
 
 
+# ---- optional per-call device timing (bench.py's roofline leg) -------------------------------------
+_timing = None     # None, or a list collecting (name, units, mode, start_event, end_event)
+launch_count = 0   # kernels launched through this module since import (bench.py's gpu_launches)
+
+
+class _timed:
+    """Brackets one C-ABI call with CUDA events on the launching stream when timing is on."""
+
+    def __init__(self, name, units, mode=0):
+        self.name, self.units, self.mode = name, units, mode
+
+    def __enter__(self):
+        global launch_count
+        launch_count += 1
+        if _timing is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _timing is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _timing.append((self.name, self.units, self.mode, self.e0, e1))
+        return False
+
+
+def timing_start():
+    global _timing
+    _timing = []
+
+
+def timing_stop():
+    """-> {(name, mode): (launches, total_ms, total_units)}; synchronises."""
+    global _timing
+    rec, _timing = _timing, None
+    torch.cuda.synchronize()
+    out = {}
+    for name, units, mode, e0, e1 in rec or []:
+        n, ms, u = out.get((name, mode), (0, 0.0, 0))
+        out[(name, mode)] = (n + 1, ms + e0.elapsed_time(e1), u + units)
+    return out
+
+
 def _f32(t: torch.Tensor) -> torch.Tensor:
     return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.float().contiguous()
 
@@ -23,9 +67,10 @@ def sample_coarse(rays: torch.Tensor, n_samples: int, use_disp: bool = False, pe
     n = rays.shape[0]
     z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
     pr = _f32(perturb_rand) if perturb_rand is not None else None
-    L.check(L.lib().nwb_sample_coarse(L.ptr(rays), rays.shape[1], n, n_samples, int(bool(use_disp)),
-                                      float(perturb), L.ptr(pr), int(seed) & (2 ** 64 - 1), L.ptr(z),
-                                      L.stream_ptr(rays.device)), "nwb_sample_coarse")
+    with _timed("nwb_sample_coarse", n):
+        L.check(L.lib().nwb_sample_coarse(L.ptr(rays), rays.shape[1], n, n_samples, int(bool(use_disp)),
+                                          float(perturb), L.ptr(pr), int(seed) & (2 ** 64 - 1), L.ptr(z),
+                                          L.stream_ptr(rays.device)), "nwb_sample_coarse")
     return z
 
 
@@ -51,10 +96,11 @@ def sample_pdf_merge(z_coarse: torch.Tensor, w_coarse: torch.Tensor, n_importanc
     inds = torch.empty(n, n_importance, device=dev, dtype=torch.int64) if debug else None
     u_ = _f32(u) if u is not None else None
     cdf_ = _f32(cdf) if cdf is not None else None
-    L.check(L.lib().nwb_sample_pdf_merge(L.ptr(z_coarse), L.ptr(w_coarse), n, ns, n_importance,
-                                         int(bool(det)), L.ptr(u_), int(seed) & (2 ** 64 - 1),
-                                         L.ptr(cdf_), L.ptr(z_out), L.ptr(z_new), L.ptr(inds),
-                                         L.stream_ptr(dev)), "nwb_sample_pdf_merge")
+    with _timed("nwb_sample_pdf_merge", n):
+        L.check(L.lib().nwb_sample_pdf_merge(L.ptr(z_coarse), L.ptr(w_coarse), n, ns, n_importance,
+                                             int(bool(det)), L.ptr(u_), int(seed) & (2 ** 64 - 1),
+                                             L.ptr(cdf_), L.ptr(z_out), L.ptr(z_new), L.ptr(inds),
+                                             L.stream_ptr(dev)), "nwb_sample_pdf_merge")
     return (z_out, z_new, inds) if debug else z_out
 
 
@@ -100,10 +146,11 @@ def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bo
         res[f"depth_{typ}"] = new(n)
         o.depth = L.ptr(res[f"depth_{typ}"])
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
-    L.check(L.lib().nwb_composite_fwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
-                                      composite_flags(transient, white_back, test_time, coarse),
-                                      float(beta_min), C.byref(o), L.stream_ptr(dev)),
-            "nwb_composite_fwd")
+    with _timed("nwb_composite_fwd", n, Cc * 1000 + S):
+        L.check(L.lib().nwb_composite_fwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
+                                          composite_flags(transient, white_back, test_time, coarse),
+                                          float(beta_min), C.byref(o), L.stream_ptr(dev)),
+                "nwb_composite_fwd")
     return res
 
 
@@ -137,10 +184,11 @@ def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, 
         put("d_rgb", f"rgb_{typ}")
     d_raw = torch.empty_like(raw)
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
-    L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
-                                      composite_flags(transient, white_back, False, typ == "coarse"),
-                                      C.byref(g), L.ptr(d_raw), L.stream_ptr(z.device)),
-            "nwb_composite_bwd")
+    with _timed("nwb_composite_bwd", n, Cc * 1000 + S):
+        L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
+                                          composite_flags(transient, white_back, False, typ == "coarse"),
+                                          C.byref(g), L.ptr(d_raw), L.stream_ptr(z.device)),
+                "nwb_composite_bwd")
     return d_raw
 
 
@@ -217,8 +265,9 @@ def field_pack(desc: L.FieldDesc, sd: dict, out: torch.Tensor | None = None) -> 
     if out is None:
         out = aligned_empty(nbytes, dev)
     st, keep = field_slots(sd)
-    L.check(_fn("nwb_field_pack", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp])(
-        C.byref(desc), C.byref(st), L.ptr(out), L.stream_ptr(dev)), "nwb_field_pack")
+    with _timed("nwb_field_pack", 1):
+        L.check(_fn("nwb_field_pack", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp])(
+            C.byref(desc), C.byref(st), L.ptr(out), L.stream_ptr(dev)), "nwb_field_pack")
     return out
 
 
@@ -237,9 +286,10 @@ def ray_consts_fwd(desc, sd, dirs, *, dir_is_encoded=False, n_freq_dir=4, ts=Non
     n_vocab = emb_a.shape[0] if emb_a is not None else (emb_t.shape[0] if emb_t is not None else 0)
     fn = _fn("nwb_ray_consts_fwd", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _i, _i, _i, _vp, _vp, _vp,
                                     _i, _vp, _vp, _i, _u32, _vp, _vp, _vp, _vp])
-    L.check(fn(C.byref(desc), C.byref(st), L.ptr(dirs), dirs.shape[1], int(dir_is_encoded), n_freq_dir, L.ptr(ts),
-               L.ptr(emb_a), L.ptr(emb_t), n_vocab, L.ptr(a_rows), L.ptr(t_rows), n, mode, L.ptr(feat), L.ptr(bias),
-               L.ptr(err_flag), L.stream_ptr(dev)), "nwb_ray_consts_fwd")
+    with _timed("nwb_ray_consts_fwd", n, mode):
+        L.check(fn(C.byref(desc), C.byref(st), L.ptr(dirs), dirs.shape[1], int(dir_is_encoded), n_freq_dir, L.ptr(ts),
+                   L.ptr(emb_a), L.ptr(emb_t), n_vocab, L.ptr(a_rows), L.ptr(t_rows), n, mode, L.ptr(feat), L.ptr(bias),
+                   L.ptr(err_flag), L.stream_ptr(dev)), "nwb_ray_consts_fwd")
     return feat, bias, err_flag
 
 
@@ -260,9 +310,10 @@ def mlp_fwd(desc, packed, *, n_rays, S, mode, ray_bias=None, rays=None, z=None, 
     if out is None:
         out = torch.empty(n_rays * S, Cc, device=dev, dtype=torch.float32)
     fn = _fn("nwb_mlp_fwd", [C.POINTER(L.FieldDesc), _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _u32, _vp, _vp, _vp])
-    L.check(fn(C.byref(desc), L.ptr(packed), L.ptr(rays), rays.shape[1] if rays is not None else 0, L.ptr(z),
-               L.ptr(x_enc), n_freq_xyz, L.ptr(ray_bias), n_rays, S, mode, L.ptr(out), L.ptr(saved),
-               L.stream_ptr(dev)), "nwb_mlp_fwd")
+    with _timed("nwb_mlp_fwd", n_rays * S, mode):
+        L.check(fn(C.byref(desc), L.ptr(packed), L.ptr(rays), rays.shape[1] if rays is not None else 0, L.ptr(z),
+                   L.ptr(x_enc), n_freq_xyz, L.ptr(ray_bias), n_rays, S, mode, L.ptr(out), L.ptr(saved),
+                   L.stream_ptr(dev)), "nwb_mlp_fwd")
     return out
 
 
@@ -270,17 +321,22 @@ def mlp_bwd_workspace_bytes(desc, n_points: int, mode: int) -> int:
     return _fn("nwb_mlp_bwd_workspace_bytes", [C.POINTER(L.FieldDesc), _i64, _u32], _sz)(C.byref(desc), n_points, mode)
 
 
-def mlp_bwd(desc, packed, raw, d_raw, saved, *, n_rays, S, mode, grads: dict, d_ray_bias, workspace=None):
+def mlp_bwd(desc, packed, raw, d_raw, saved, *, n_rays, S, mode, grads: dict, d_ray_bias, workspace=None,
+            phases=("dgrad", "wgrad")):
     """Backward of mlp_fwd: accumulates into `grads` (state_dict-keyed fp32 tensors, caller zeroes)
-    and into d_ray_bias (n_rays, 256)."""
+    and into d_ray_bias (n_rays, 256).  Two kernels (dgrad chain, then wgrad), launched as separate
+    C-ABI calls so the timing hook sees them apart."""
     dev = packed.device
     mode &= ~L.NWB_MLP_SAVE
     if workspace is None:
         workspace = aligned_empty(mlp_bwd_workspace_bytes(desc, n_rays * S, mode), dev, 16)
     st, keep = field_slots(grads, L.FieldGrads)
-    fn = _fn("nwb_mlp_bwd", [C.POINTER(L.FieldDesc), _vp, _vp, _vp, _vp, _i, _i, _u32, C.POINTER(L.FieldGrads), _vp, _vp, _vp])
-    L.check(fn(C.byref(desc), L.ptr(packed), L.ptr(raw), L.ptr(d_raw), L.ptr(saved), n_rays, S, mode, C.byref(st),
-               L.ptr(d_ray_bias), L.ptr(workspace), L.stream_ptr(dev)), "nwb_mlp_bwd")
+    sig = [C.POINTER(L.FieldDesc), _vp, _vp, _vp, _vp, _i, _i, _u32, C.POINTER(L.FieldGrads), _vp, _vp, _vp]
+    for ph in phases:
+        name = "nwb_mlp_" + ph
+        with _timed(name, n_rays * S, mode):
+            L.check(_fn(name, sig)(C.byref(desc), L.ptr(packed), L.ptr(raw), L.ptr(d_raw), L.ptr(saved), n_rays, S, mode,
+                                   C.byref(st), L.ptr(d_ray_bias), L.ptr(workspace), L.stream_ptr(dev)), name)
     return workspace
 
 
@@ -293,6 +349,7 @@ def ray_consts_bwd(desc, sd, ray_feat, d_ray_bias, *, ts=None, n_vocab=0, transi
     gt, keep2 = field_slots(grads, L.FieldGrads)
     fn = _fn("nwb_ray_consts_bwd", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp, _vp, _i, _i, _u32,
                                     C.POINTER(L.FieldGrads), _vp, _vp, _vp, _vp, _vp])
-    L.check(fn(C.byref(desc), C.byref(st), L.ptr(ray_feat), L.ptr(d_ray_bias), L.ptr(ts), n_vocab, ray_feat.shape[0],
-               mode, C.byref(gt), L.ptr(d_emb_a), L.ptr(d_emb_t), L.ptr(d_a_rows), L.ptr(d_t_rows),
-               L.stream_ptr(dev)), "nwb_ray_consts_bwd")
+    with _timed("nwb_ray_consts_bwd", ray_feat.shape[0], mode):
+        L.check(fn(C.byref(desc), C.byref(st), L.ptr(ray_feat), L.ptr(d_ray_bias), L.ptr(ts), n_vocab, ray_feat.shape[0],
+                   mode, C.byref(gt), L.ptr(d_emb_a), L.ptr(d_emb_t), L.ptr(d_a_rows), L.ptr(d_t_rows),
+                   L.stream_ptr(dev)), "nwb_ray_consts_bwd")

@@ -1,0 +1,137 @@
+"""Data-parallel plumbing for the ray path: rays are independent, so the only
+exchange step of a training iteration is the gradient all-reduce that Lightning's DDP performs for
+the reference (train.py:235-236), and inference shards each image into contiguous ray blocks with
+one final gather (the eval.py:186-194 loop, sharded).
+
+``FlatTrainState`` re-homes every trainable tensor of the NeRF models and embedding tables into ONE
+flat fp32 parameter buffer and ONE flat gradient buffer.  The backward kernels accumulate straight
+into the gradient views (no per-tensor autograd traffic), so a single in-place NCCL all-reduce on
+the flat buffer -- enqueued on the compute stream right behind the wgrad kernel -- is the whole
+collective, and ``nwb_adam_step`` (csrc/optim.cu) is the whole optimizer.  One process per GPU,
+torch.distributed for the plumbing (NCCL on GPUs; gloo in the CPU tests of the host logic).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+import torch.distributed as dist
+
+__all__ = ["FlatTrainState", "shard_range", "gather_rays", "dist_info"]
+
+
+def dist_info():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous block partition of n rays: rank r owns [lo, hi); sizes differ by at most one."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def gather_rays(local: torch.Tensor, n_total: int, group=None) -> torch.Tensor:
+    """All-gather of per-ray results (n_local, C) from block-sharded ranks -> (n_total, C) on every
+    rank (16 B/ray for rgb+depth: 10 MB per 800x800 image).  Shards are padded to the largest block so
+    one all_gather_into_tensor moves everything."""
+    rank, world = dist_info()
+    if world == 1:
+        return local
+    width = local.shape[1:]
+    per = math.ceil(n_total / world)
+    pad = torch.zeros((per, *width), dtype=local.dtype, device=local.device)
+    pad[:local.shape[0]] = local
+    out = torch.empty((world * per, *width), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    parts = []
+    for r in range(world):
+        lo, hi = shard_range(n_total, r, world)
+        parts.append(out[r * per:r * per + (hi - lo)])
+    return torch.cat(parts, 0)
+
+
+class FlatTrainState:
+    """Flat parameter / gradient / Adam-moment buffers over ``modules`` (NeRF models, nn.Embedding).
+
+    After construction every parameter's ``.data`` and ``.grad`` are views into the flat buffers
+    (state_dict keys and shapes are untouched, so checkpoints keep loading) and the parameters are
+    tagged so the render_rays backward accumulates into ``.grad`` in place."""
+
+    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        self.modules = list(modules)
+        params, seen = [], set()
+        for m in self.modules:
+            for p in m.parameters():
+                if p.requires_grad and id(p) not in seen:
+                    seen.add(id(p))
+                    params.append(p)
+        if not params:
+            raise ValueError("FlatTrainState: nothing to train")
+        dev = params[0].device
+        self.params = params
+        # each tensor starts on a 16 B boundary (vectorised kernels, wgrad flush)
+        offs, off = [], 0
+        for p in params:
+            offs.append(off)
+            off += (p.numel() + 3) // 4 * 4
+        self.numel = off
+        self.flat_p = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
+        for p, o in zip(params, offs):
+            n = p.numel()
+            self.flat_p[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.flat_p[o:o + n].view(p.shape)
+            p.grad = self.flat_g[o:o + n].view(p.shape)
+            p._nwb_direct_grad = True
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.step_count = 0
+        self.n_params = sum(p.numel() for p in params)
+
+    # ---- collective -------------------------------------------------------------------------
+    def allreduce_grads(self, group=None):
+        """Sum over ranks, in place on the flat buffer, stream-ordered behind the wgrad kernels; the
+        1/world of DDP's mean is folded into the optimizer kernel's grad_scale."""
+        rank, world = dist_info()
+        if world > 1:
+            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=group)
+        return world
+
+    def zero_grad(self):
+        self.flat_g.zero_()
+
+    # ---- optimizer ---------------------------------------------------------------------------
+    def adam_step(self, world: int = 1, zero_grad: bool = True):
+        """utils/__init__.py:31 Adam on the flat buffers (CUDA) -- or, for the gloo CPU tests of the
+        host logic, the same update written with torch ops."""
+        self.step_count += 1
+        b1, b2 = self.betas
+        if self.flat_p.is_cuda:
+            from . import _lib as L
+            from . import kernels as K
+            K.launch_count += 1
+            fn = L.bind("nwb_adam_step", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 5 + [C.c_int, C.c_float, C.c_int,
+                                                                                           C.c_void_p])
+            L.check(fn(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
+                       self.exp_avg_sq.data_ptr(), self.numel, self.lr, b1, b2, self.eps, self.weight_decay,
+                       self.step_count, 1.0 / world, int(zero_grad), L.stream_ptr(self.flat_p.device)), "nwb_adam_step")
+        else:
+            g = self.flat_g / world + self.weight_decay * self.flat_p
+            self.exp_avg.mul_(b1).add_(g, alpha=1 - b1)
+            self.exp_avg_sq.mul_(b2).addcmul_(g, g, value=1 - b2)
+            bc1, bc2 = 1 - b1 ** self.step_count, 1 - b2 ** self.step_count
+            self.flat_p.addcdiv_(self.exp_avg, self.exp_avg_sq.sqrt() / math.sqrt(bc2) + self.eps, value=-self.lr / bc1)
+            if zero_grad:
+                self.flat_g.zero_()
+        for m in self.modules:                       # packed bf16 operand caches are stale now
+            if hasattr(m, "_nwb_cache"):
+                m._nwb_dirty = True
+
+    def step(self, group=None):
+        """all-reduce + Adam: everything that follows backward in one training iteration."""
+        self.adam_step(self.allreduce_grads(group))
