@@ -238,8 +238,9 @@ def render_rays(p_coarse: dict, p_fine: dict | None, emb_a: torch.Tensor | None,
                 test_time: bool = False, n_freq_xyz: int = 10, n_freq_dir: int = 4,
                 encode_a: bool = False, encode_t: bool = False, beta_min: float = 0.03,
                 rng: dict | None = None, a_embedded=None, t_embedded=None,
-                output_transient: bool = True, view_dir=None) -> dict:
-    """Functional restatement of render_rays.  ``rng`` may hold pre-drawn tensors
+                output_transient: bool = True, view_dir=None, bf16_operands: bool = False) -> dict:
+    """Functional restatement of render_rays.  ``bf16_operands=True`` swaps the field for
+    field_forward_bf16 (the operand-rounding model of the tensor-core path, bottom of this file).  ``rng`` may hold pre-drawn tensors
     ``perturb_rand`` (N,Ns) U[0,1), ``noise_coarse`` (N,Ns) N(0,1), ``u`` (N,Ni) U[0,1),
     ``noise_fine`` (N,Ns+Ni) N(0,1); anything missing is drawn here in the reference's order
     (SURVEY.md §3.3), so under one ``torch.manual_seed`` this matches the reference bit for bit.
@@ -262,7 +263,13 @@ def render_rays(p_coarse: dict, p_fine: dict | None, emb_a: torch.Tensor | None,
         S = zv.shape[1]
         xyz = (o.unsqueeze(1) + d.unsqueeze(1) * zv.unsqueeze(-1)).reshape(-1, 3)       # :261,273
         xe = posenc(xyz, n_freq_xyz)
-        if typ == "coarse" and test_time:                                               # :103-111
+        if bf16_operands:
+            so = typ == "coarse" and test_time
+            da = dir_e if a_e is None else torch.cat([dir_e, a_e], 1)
+            raw = field_forward_bf16(p, xe, None if so else da.repeat_interleave(S, dim=0),
+                                     t_e.repeat_interleave(S, dim=0) if transient else None, transient,
+                                     sigma_only=so)
+        elif typ == "coarse" and test_time:                                             # :103-111
             raw = field_forward(p, xe, sigma_only=True)
         else:                                                                           # :112-139
             cols = [xe, dir_e.repeat_interleave(S, dim=0)]
@@ -340,8 +347,8 @@ class _RoundBf16(torch.autograd.Function):
         return g
 
 
-def field_forward_bf16(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor, tt: torch.Tensor | None,
-                       output_transient: bool) -> torch.Tensor:
+def field_forward_bf16(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor | None, tt: torch.Tensor | None,
+                       output_transient: bool, sigma_only: bool = False) -> torch.Tensor:
     r = _RoundBf16.apply
 
     def lin(n, x):
@@ -353,6 +360,8 @@ def field_forward_bf16(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor, tt: torc
             h = torch.cat([xyz, h], 1)
         h = torch.relu(lin(f"xyz_encoding_{i + 1}.0", h))
     sigma = F.softplus(_lin(p, "static_sigma.0", h))
+    if sigma_only:
+        return sigma
     feat = lin("xyz_encoding_final", h)
     Wd = p["dir_encoding.0.weight"]
     hd = torch.relu(F.linear(r(feat), r(Wd[:, :256])) + F.linear(dir_a, Wd[:, 256:], p["dir_encoding.0.bias"]))
