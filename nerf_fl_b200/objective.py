@@ -1,0 +1,63 @@
+"""Training objective over the maps render_rays returns -- the role of the reference's ``losses.py``
+(ColorLoss :4-16, NerfWLoss :19-50; NeRF-W eq. 13), which sits just outside the per-ray hot path
+ and decides which outputs receive cotangents: rgb_coarse, rgb_fine, beta and
+transient_sigmas.  A handful of device-side reductions over (N,3) / (N,S) tensors written with torch
+ops; ``NerfWLoss`` / ``ColorLoss`` / ``loss_dict`` keep the reference's names so train.py:80 can import
+them from here.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+__all__ = ["ColorLoss", "NerfWLoss", "loss_dict", "nerfw_terms"]
+
+
+def _sq_err(results, key, targets):
+    diff = results[key] - targets
+    return diff * diff
+
+
+def nerfw_terms(results: dict, targets: torch.Tensor, lambda_u: float = 0.01) -> dict:
+    """c_l: half the mean squared error of the coarse colour (:37).  With a fine pass: f_l is the same on
+    rgb_fine when there is no transient head (:40), otherwise the beta-weighted error mean(err / (2 beta^2))
+    (:42-43) together with b_l = 3 + mean(log beta) (the offset keeps it positive, :44) and
+    s_l = lambda_u * mean(transient_sigmas) (:45)."""
+    terms = {"c_l": _sq_err(results, "rgb_coarse", targets).mean() * 0.5}
+    if "rgb_fine" not in results:
+        return terms
+    err = _sq_err(results, "rgb_fine", targets)
+    beta = results.get("beta")
+    if beta is None:
+        terms["f_l"] = err.mean() * 0.5
+        return terms
+    terms["f_l"] = (err / (2.0 * beta[:, None] ** 2)).mean()
+    terms["b_l"] = beta.log().mean() + 3.0
+    terms["s_l"] = results["transient_sigmas"].mean() * lambda_u
+    return terms
+
+
+class NerfWLoss(nn.Module):
+    def __init__(self, coef=1, lambda_u=0.01):
+        super().__init__()
+        self.coef, self.lambda_u = coef, lambda_u
+
+    def forward(self, inputs, targets):
+        return {name: self.coef * val for name, val in nerfw_terms(inputs, targets, self.lambda_u).items()}
+
+
+class ColorLoss(nn.Module):
+    """Plain-NeRF objective: mean squared error of rgb_coarse (+ rgb_fine), times coef (:10-16)."""
+
+    def __init__(self, coef=1):
+        super().__init__()
+        self.coef = coef
+
+    def forward(self, inputs, targets):
+        total = _sq_err(inputs, "rgb_coarse", targets).mean()
+        if "rgb_fine" in inputs:
+            total = total + _sq_err(inputs, "rgb_fine", targets).mean()
+        return total * self.coef
+
+
+loss_dict = {"color": ColorLoss, "nerfw": NerfWLoss}
