@@ -79,59 +79,80 @@ ray_consts_fwd_kernel(FieldShape fs, nwb_field_params p, const float* __restrict
     }
 }
 
-// backward: one block per chunk of rays; d_ray_bias (n,256) -> dW[:, 256:], db, d_emb rows.
-// Rays are few (<= batch), so plain fp32 atomics on a small grid are sufficient here.
-__global__ void __launch_bounds__(128)
+// backward: one 256-thread block per kRcbRays rays; d_ray_bias (n,256) -> dW[:, 256:], db, d_emb rows.
+// Thread j owns output feature j (0..127 dir_encoding, 128..255 transient_encoding.0): it walks the
+// block's rays once per 32-column chunk of the per-ray feature row, keeping 32 partial sums of
+// dW[j, 256+k] in registers, so each block issues ONE atomic per weight element (n_rays/kRcbRays-way
+// contention instead of one atomic per ray group and element).  Embedding-row cotangents
+// W[:, 256+nd:]^T g are taken against a shared-memory copy of the weight columns.
+constexpr int kRcbRays = 32;
+constexpr int kRcbThreads = 256;
+
+__global__ void __launch_bounds__(kRcbThreads)
 ray_consts_bwd_kernel(FieldShape fs, nwb_field_params p, nwb_field_grads g, const float* __restrict__ ray_feat,
                       const float* __restrict__ d_ray_bias, const int64_t* __restrict__ ts, int n_vocab,
                       int n_rays, uint32_t mode, float* __restrict__ d_emb_a, float* __restrict__ d_emb_t,
-                      float* __restrict__ d_a_rows, float* __restrict__ d_t_rows, int rays_per_block) {
+                      float* __restrict__ d_a_rows, float* __restrict__ d_t_rows) {
     extern __shared__ float sm[];
     const bool use_t = (mode & NWB_MLP_TRANSIENT) != 0;
     const int nd = fs.in_dir, na = fs.in_a, nt = use_t ? fs.in_t : 0;
     const int feat_ld = fs.in_dir + fs.in_a + fs.in_t;
     const int ld_dir = kW + fs.in_dir + fs.in_a, ld_t = kW + fs.in_t;
-    const int r0 = blockIdx.x * rays_per_block, r1 = min(n_rays, r0 + rays_per_block);
-    const int nr = r1 - r0;
+    const int r0 = blockIdx.x * kRcbRays, nr = min(n_rays - r0, kRcbRays);
     if (nr <= 0) return;
-    // stage this block's d_ray_bias rows (nr x 256) and features (nr x feat_ld)
-    float* sg = sm;
-    float* sf = sm + rays_per_block * 256;
-    for (int i = threadIdx.x; i < nr * 256; i += blockDim.x) sg[i] = d_ray_bias[static_cast<int64_t>(r0) * 256 + i];
-    for (int i = threadIdx.x; i < nr * feat_ld; i += blockDim.x) sf[i] = ray_feat[static_cast<int64_t>(r0) * feat_ld + i];
+    float* sg = sm;                                   // [kRcbRays][256]   d_ray_bias rows
+    float* sf = sg + kRcbRays * 256;                  // [kRcbRays][feat_ld] per-ray features
+    float* sw = sf + kRcbRays * feat_ld;              // [128][na + nt]    weight columns of the embedding inputs
+    for (int i = threadIdx.x; i < nr * 256; i += kRcbThreads) sg[i] = d_ray_bias[static_cast<int64_t>(r0) * 256 + i];
+    for (int i = threadIdx.x; i < nr * feat_ld; i += kRcbThreads) sf[i] = ray_feat[static_cast<int64_t>(r0) * feat_ld + i];
+    const int ne = na + nt;
+    for (int i = threadIdx.x; i < kHalf * ne; i += kRcbThreads) {
+        const int j = i / ne, e = i - j * ne;
+        sw[i] = (e < na) ? p.dir_w[static_cast<int64_t>(j) * ld_dir + kW + nd + e]
+                         : p.tenc_w[0][static_cast<int64_t>(j) * ld_t + kW + (e - na)];
+    }
     __syncthreads();
-    // (1) weight-column and bias gradients: thread j owns output feature j (0..127) of dir, then of t
-    for (int j = threadIdx.x; j < kHalf; j += blockDim.x) {
-        float bsum = 0.0f;
-        for (int r = 0; r < nr; ++r) bsum += sg[r * 256 + j];
-        atomicAdd(g.dir_b + j, bsum);
-        for (int k = 0; k < nd + na; ++k) {
-            float acc = 0.0f;
-            for (int r = 0; r < nr; ++r) acc = fmaf(sg[r * 256 + j], sf[r * feat_ld + k], acc);
-            atomicAdd(g.dir_w + static_cast<int64_t>(j) * ld_dir + kW + k, acc);
-        }
-        if (use_t) {
-            float bt = 0.0f;
-            for (int r = 0; r < nr; ++r) bt += sg[r * 256 + kHalf + j];
-            atomicAdd(g.tenc_b[0] + j, bt);
-            for (int k = 0; k < nt; ++k) {
-                float acc = 0.0f;
-                for (int r = 0; r < nr; ++r) acc = fmaf(sg[r * 256 + kHalf + j], sf[r * feat_ld + nd + na + k], acc);
-                atomicAdd(g.tenc_w[0] + static_cast<int64_t>(j) * ld_t + kW + k, acc);
+    // (1) weight-column and bias gradients
+    {
+        const int j = threadIdx.x;                    // 0..255
+        const bool is_t = j >= kHalf;
+        if (!is_t || use_t) {
+            const int jj = is_t ? j - kHalf : j;
+            const int k_lo = is_t ? nd + na : 0, k_n = is_t ? nt : nd + na;
+            float* wrow = is_t ? g.tenc_w[0] + static_cast<int64_t>(jj) * ld_t + kW
+                               : g.dir_w + static_cast<int64_t>(jj) * ld_dir + kW;
+            float bsum = 0.0f;
+            for (int r = 0; r < nr; ++r) bsum += sg[r * 256 + j];
+            atomicAdd((is_t ? g.tenc_b[0] : g.dir_b) + jj, bsum);
+            for (int k0 = 0; k0 < k_n; k0 += 32) {
+                float acc[32];
+#pragma unroll
+                for (int q = 0; q < 32; ++q) acc[q] = 0.0f;
+                for (int r = 0; r < nr; ++r) {
+                    const float gv = sg[r * 256 + j];
+                    const float* fr = sf + r * feat_ld + k_lo + k0;
+#pragma unroll
+                    for (int q = 0; q < 32; ++q)
+                        if (k0 + q < k_n) acc[q] = fmaf(gv, fr[q], acc[q]);
+                }
+#pragma unroll
+                for (int q = 0; q < 32; ++q)
+                    if (k0 + q < k_n) atomicAdd(wrow + k0 + q, acc[q]);
             }
         }
     }
     // (2) embedding-row gradients: d a = W_dir[:, 256+nd:]^T . g_dir ; d t = W_t0[:, 256:]^T . g_t
-    for (int idx = threadIdx.x; idx < nr * (na + nt); idx += blockDim.x) {
-        const int r = idx / (na + nt), e = idx - r * (na + nt);
+    for (int idx = threadIdx.x; idx < nr * ne; idx += kRcbThreads) {
+        const int r = idx / ne, e = idx - r * ne;
+        const float* gr = sg + r * 256 + (e < na ? 0 : kHalf);
         float acc = 0.0f;
+#pragma unroll 8
+        for (int j = 0; j < kHalf; ++j) acc = fmaf(sw[j * ne + e], gr[j], acc);
         if (e < na) {
-            for (int j = 0; j < kHalf; ++j) acc = fmaf(p.dir_w[static_cast<int64_t>(j) * ld_dir + kW + nd + e], sg[r * 256 + j], acc);
             if (d_a_rows) d_a_rows[static_cast<int64_t>(r0 + r) * na + e] = acc;
             else if (d_emb_a) atomicAdd(d_emb_a + ts[r0 + r] * na + e, acc);
         } else {
             const int k = e - na;
-            for (int j = 0; j < kHalf; ++j) acc = fmaf(p.tenc_w[0][static_cast<int64_t>(j) * ld_t + kW + k], sg[r * 256 + kHalf + j], acc);
             if (d_t_rows) d_t_rows[static_cast<int64_t>(r0 + r) * nt + k] = acc;
             else if (d_emb_t) atomicAdd(d_emb_t + ts[r0 + r] * nt + k, acc);
         }
@@ -184,11 +205,17 @@ extern "C" int nwb_ray_consts_bwd(const nwb_field_desc* d, const nwb_field_param
     NWB_REQUIRE(!use_t || (grads->tenc_w[0] && grads->tenc_b[0]), "nwb_ray_consts_bwd: transient gradient sinks are null");
     NWB_REQUIRE(fs.in_a == 0 || d_a_rows || !d_emb_a || ts, "nwb_ray_consts_bwd: ts needed for the embedding scatter");
     const int feat_ld = fs.in_dir + fs.in_a + fs.in_t;
-    const int rpb = 16;
-    const size_t smem = static_cast<size_t>(rpb) * (256 + feat_ld) * sizeof(float);
-    const int blocks = (n_rays + rpb - 1) / rpb;
-    ray_consts_bwd_kernel<<<blocks, 128, smem, static_cast<cudaStream_t>(stream)>>>(
-        fs, *p, *grads, ray_feat, d_ray_bias, ts, n_vocab, n_rays, mode, d_emb_a, d_emb_t, d_a_rows, d_t_rows, rpb);
+    const int ne = fs.in_a + (use_t ? fs.in_t : 0);
+    const size_t smem = (static_cast<size_t>(kRcbRays) * (256 + feat_ld) + static_cast<size_t>(kHalf) * ne) * sizeof(float);
+    NWB_REQUIRE(smem <= 200 * 1024, "nwb_ray_consts_bwd: feature rows too wide for the staging buffer");
+    static size_t configured = 0;
+    if (smem > configured) {
+        NWB_CUDA(cudaFuncSetAttribute(ray_consts_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        configured = smem;
+    }
+    const int blocks = (n_rays + kRcbRays - 1) / kRcbRays;
+    ray_consts_bwd_kernel<<<blocks, kRcbThreads, smem, static_cast<cudaStream_t>(stream)>>>(
+        fs, *p, *grads, ray_feat, d_ray_bias, ts, n_vocab, n_rays, mode, d_emb_a, d_emb_t, d_a_rows, d_t_rows);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }

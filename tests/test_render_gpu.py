@@ -98,9 +98,9 @@ def test_render_rays_golden(golden, case, scale):
                           encode_a=c["nerfw"], encode_t=c["nerfw"], beta_min=0.1,
                           rng={k: v.cpu() for k, v in rng.items()}, bf16_operands=True, **ok)
     assert set(model) == set(want)
-    # the product must sit no farther from the operand-rounding model than the fp32 reference itself does
+    # the product must sit within twice the distance between the operand-rounding model and the fp32 reference
     for k, w in model.items():
-        lim = max(5e-3 * max(1.0, w.abs().max().item()), maxerr(want[k], w))
+        lim = max(5e-3 * max(1.0, w.abs().max().item()), 2.0 * maxerr(want[k], w))
         assert maxerr(out[k], w) <= lim, (k, maxerr(out[k], w), maxerr(want[k], w))
 
 
