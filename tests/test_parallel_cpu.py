@@ -1,0 +1,117 @@
+"""Host-side data-parallel logic on CPU: ray-block sharding, the gather of per-ray results and the
+flat-buffer gradient all-reduce + Adam, at world_size 2 over gloo; plus the objective
+module against the oracle's restatement of losses.py."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from nerf_fl_b200 import objective
+from nerf_fl_b200.parallel import FlatTrainState, gather_rays, shard_range
+from oracle import nerfw_oracle as O
+
+
+def test_shard_range_partitions_exactly():
+    for n in (0, 1, 7, 640000, 640001):
+        for world in (1, 2, 3, 8):
+            spans = [shard_range(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _toy_modules(seed):
+    torch.manual_seed(seed)
+    return [torch.nn.Linear(5, 3), torch.nn.Embedding(7, 4)]
+
+
+def test_flat_state_adam_matches_torch_adam_single_process():
+    mods, ref = _toy_modules(0), _toy_modules(0)
+    state = FlatTrainState(mods, lr=5e-4)
+    opt = torch.optim.Adam([p for m in ref for p in m.parameters()], lr=5e-4, eps=1e-8)
+    for step in range(3):
+        x = torch.randn(6, 5, generator=torch.Generator().manual_seed(step))
+        idx = torch.tensor([1, 1, 4])
+        for ms, flat in ((mods, True), (ref, False)):
+            loss = ms[0](x).pow(2).sum() + ms[1](idx).sum() * 0.3
+            grads = torch.autograd.grad(loss, [p for m in ms for p in m.parameters()])
+            for p, g in zip([p for m in ms for p in m.parameters()], grads):
+                if flat:
+                    p.grad.add_(g)                         # kernels accumulate into the flat views
+                else:
+                    p.grad = g
+        state.step()
+        opt.step()
+        assert state.flat_g.abs().max().item() == 0.0      # zero_grad folded into the step
+        for a, b in zip([p for m in mods for p in m.parameters()], [p for m in ref for p in m.parameters()]):
+            assert torch.allclose(a, b, atol=1e-7, rtol=1e-6)
+    # state_dict keys and shapes are untouched by the re-homing
+    assert list(mods[0].state_dict()) == ["weight", "bias"] and mods[1].weight.shape == (7, 4)
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mods = _toy_modules(0)
+        state = FlatTrainState(mods, lr=1e-2)
+        # each rank contributes its own gradient; DDP semantics = mean over ranks
+        for p in state.params:
+            p.grad.add_(torch.full_like(p, float(rank + 1)))
+        state.step()
+        # ray-sharded render: rank r owns a contiguous block, results gathered everywhere
+        n = 11
+        lo, hi = shard_range(n, rank, world)
+        local = torch.arange(lo, hi, dtype=torch.float32)[:, None].repeat(1, 4)
+        full = gather_rays(local, n)
+        out.put((rank, state.flat_p.clone(), full))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_allreduce_adam_and_gather_world2_gloo():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # both ranks hold identical parameters after the step
+    assert torch.equal(res[0][1], res[1][1])
+    # and they equal a single-process Adam step on the mean gradient (1+2)/2
+    mods = _toy_modules(0)
+    ref = FlatTrainState(mods, lr=1e-2)
+    for p in ref.params:
+        p.grad.add_(torch.full_like(p, 1.5))
+    ref.step()
+    assert torch.allclose(res[0][1], ref.flat_p, atol=1e-7)
+    want = torch.arange(11, dtype=torch.float32)[:, None].repeat(1, 4)
+    assert torch.equal(res[0][2], want) and torch.equal(res[1][2], want)
+
+
+@pytest.mark.parametrize("with_beta", [True, False])
+def test_objective_matches_oracle_loss(with_beta):
+    gen = torch.Generator().manual_seed(4)
+    res = {"rgb_coarse": torch.rand(40, 3, generator=gen), "rgb_fine": torch.rand(40, 3, generator=gen)}
+    if with_beta:
+        res["beta"] = torch.rand(40, generator=gen) + 0.1
+        res["transient_sigmas"] = torch.rand(40, 128, generator=gen)
+    tgt = torch.rand(40, 3, generator=gen)
+    got = objective.NerfWLoss()(res, tgt)
+    want = O.nerfw_loss(res, tgt)
+    assert set(got) == set(want)
+    for k in want:
+        assert torch.allclose(got[k], want[k], atol=0, rtol=1e-6), k
+    c = objective.ColorLoss()(res, tgt)
+    assert torch.allclose(c, ((res["rgb_coarse"] - tgt) ** 2).mean() + ((res["rgb_fine"] - tgt) ** 2).mean())
