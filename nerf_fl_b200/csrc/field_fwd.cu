@@ -1,30 +1,45 @@
 // (a2,a3,a4) fused NeRF-W field forward -- models/nerf.py:153-212 + the per-sample input assembly of
 // models/rendering.py:96-139, as one persistent warp-specialised tcgen05 kernel.
 //
-// One CTA owns one 128-point tile at a time (two CTAs are co-resident per SM so one CTA's epilogue
-// overlaps the other's MMAs).  Roles:
-//   warp 0 / lane 0   weight producer: streams the packed bf16 slab images (field_pack.cu) from L2
-//                     into a 2-stage ring with linear bulk copies (TMA engine) + mbarrier tx counts
+// One CTA per SM owns one 128-point tile at a time and pipelines the layer chain INSIDE the tile:
+//   * activations ping-pong between two 64 KB tile images (layer g reads H[(g-1)&1], writes H[g&1]) and the
+//     fp32 accumulators ping-pong between the two halves of TMEM (layer g accumulates into columns
+//     [(g&1)*256, +256)), so the epilogue of layer g and the MMAs of layer g+1 never touch the same bytes;
+//   * the epilogue walks a layer's output in four 64-column quarters -- exactly the K-blocks of the next
+//     layer's A operand -- and signals one mbarrier per quarter, the MMA issuer runs K-outer and starts
+//     K-block kb of layer g+1 as soon as quarter kb of layer g is in shared memory.  The tensor pipe idles
+//     only for the first quarter's latency per layer.
+// Roles:
+//   warp 0 / lane 0   weight producer: streams the packed bf16 slab images (field_pack.cu) from L2 into a
+//                     5-stage ring with linear bulk copies (TMA engine, SASS UBLKCP) + mbarrier tx counts
 //   warp 1 / lane 0   MMA issuer: tcgen05.mma M=128 N=128 K=16, A = activation tile image in smem,
-//                     B = ring stage, D = fp32 accumulators in TMEM (256 columns)
-//   warps 2..5        epilogue, thread == point: build the encoded-xyz operand tile (o + d*z,
-//                     sin/cos octaves, bf16, written straight into the swizzled A image), then per
-//                     layer tcgen05.ld -> +bias (+per-ray bias) -> ReLU -> bf16 -> next layer's A
-//                     image in place; sigma / rgb / transient heads on CUDA cores in fp32.
+//                     B = ring stage, D = fp32 accumulators in TMEM
+//   warp 2 / lane 0   (NWB_MLP_SAVE) activation storer: bulk-stores every finished quarter to the saved-
+//                     activation record and hands the buffer back when the copy engine has read it
+//   warps 3..10       epilogue, two threads per point (column halves of each quarter): build the encoded-
+//                     xyz operand tile (o + d*z, sin/cos octaves, bf16, written straight into the swizzled
+//                     A image), then per layer tcgen05.ld -> +bias (+per-ray bias) -> ReLU -> bf16 -> next
+//                     layer's A image; sigma / rgb / transient heads on CUDA cores in fp32.
 // Activations never leave the SM unless NWB_MLP_SAVE asks for them (bf16 tile images for backward).
 #include "field_dev.cuh"
 #include <algorithm>
 
 namespace nwb {
 
-constexpr int kFwdThreads = 192;
+constexpr int kFwdThreads = 608;              // 19 warps
+constexpr int kEpiWarp0 = 3;                  // first epilogue warp
+constexpr int kEpiWarps = 16;
+constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kStageBytes = 16384;            // 128 weight rows x 64 k (one SW128 K-block)
-constexpr int kNumStages = 2;
+constexpr int kNumStages = 4;
 constexpr int kOffX = 0;                      // 16 KB  encoded xyz, 128 x 64
-constexpr int kOffH = 16384;                  // 64 KB  activations, 128 x 256 (4 K-blocks)
-constexpr int kOffW = kOffH + 65536;          // ring
-constexpr int kOffBar = kOffW + kNumStages * kStageBytes;
-constexpr int kFwdSmem = kOffBar + 256;
+constexpr int kOffH = 16384;                  // 2 x 64 KB  activations, 128 x 256 (4 K-blocks) each
+constexpr int kOffW = kOffH + 2 * 65536;      // ring
+constexpr int kOffC = kOffW + kNumStages * kStageBytes;      // 16 KB  fp32 biases + head weights (ConstOff block)
+constexpr int kOffBar = kOffC + 16384;
+static_assert(ConstOff::count * 4 <= 16384, "constant block does not fit its shared-memory slot");
+constexpr int kFwdSmem = kOffBar + 320;
+static_assert(kFwdSmem <= 232448, "forward kernel exceeds the 227 KB shared-memory limit");
 
 struct FwdArgs {
     FieldShape fs;
@@ -42,74 +57,107 @@ struct FwdArgs {
     float* raw_out;
     uint8_t* saved;
     size_t save_tile_bytes;
+    long long* trace;      // debug: block 0 timestamps (tools/trace_fwd.py), else nullptr
 };
 
-// One 32-column slice of a layer epilogue for this thread's row.
-//   x = acc + bias[c] (+ rbias[c]);  optional ReLU;  optional head dot products (fp32, unrounded x);
-//   bf16 pack -> 4 x 16 B chunks of the A image at column c_out (same row).
-template <bool kRelu, int kHeads>
-__device__ __forceinline__ void epi_slice(uint32_t taddr, const float* __restrict__ bias,
-                                          const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
-                                          float* hacc, uint8_t* sH, int row, int c_out, uint32_t* mask_dst) {
-    uint32_t v[32];
-    ptx::tmem_ld32(taddr, v);
-    float b[32];
+// named barrier of the epilogue threads (barrier 0 is __syncthreads)
+__device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); }
+
+// One 16-column slice of a layer epilogue for this thread's row.
+//   x = acc + bias[c] (+ rbias[c]);  optional head dot products (fp32, unrounded x, after ReLU);
+//   bf16 pack, ReLU on the packed pairs (rounding is monotonic and keeps the sign, so max(rn(x), 0) ==
+//   rn(max(x, 0))) -> 2 x 16 B chunks of the output image at column c_out (same row).
+//   kSave: the sign bits of the 16 pre-activations go to *mask_dst, bit (15-j) = column j.
+template <bool kRelu, int kHeads, bool kSave>
+__device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restrict__ bias,
+                                            const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
+                                            float* hacc, uint8_t* sH, int row, int c_out, uint16_t* mask_dst) {
+    uint32_t v[16];
+    ptx::tmem_ld16(taddr, v);
+    float b[16];
     if (bias != nullptr) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const float4 t = __ldg(reinterpret_cast<const float4*>(bias) + q);
+        for (int q = 0; q < 4; ++q) {
+            const float4 t = reinterpret_cast<const float4*>(bias)[q];                 // shared memory
             b[4 * q] = t.x; b[4 * q + 1] = t.y; b[4 * q + 2] = t.z; b[4 * q + 3] = t.w;
         }
     } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) b[j] = 0.0f;
-    }
-    if (rbias != nullptr) {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
+        for (int q = 0; q < 4; ++q) {
             const float4 t = __ldg(reinterpret_cast<const float4*>(rbias) + q);
-            b[4 * q] += t.x; b[4 * q + 1] += t.y; b[4 * q + 2] += t.z; b[4 * q + 3] += t.w;
+            b[4 * q] = t.x; b[4 * q + 1] = t.y; b[4 * q + 2] = t.z; b[4 * q + 3] = t.w;
         }
     }
     ptx::tmem_ld_wait();
-    float x[32];
-    uint32_t neg = 0;
+    float x[16];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-        x[j] = __uint_as_float(v[j]) + b[j];
-        if (kRelu) {
-            neg = __funnelshift_l(__float_as_uint(x[j]), neg, 1);   // bit (31-j) = sign of the pre-activation
-            x[j] = fmaxf(x[j], 0.0f);
+    for (int j = 0; j < 16; ++j) x[j] = __uint_as_float(v[j]) + b[j];
+    uint32_t pk[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(x[2 * j], x[2 * j + 1]);
+    if (kRelu && kSave) {
+        uint32_t neg = 0;                                  // packed word j: bit 15 = column 2j, bit 31 = column 2j+1
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            neg |= (((pk[j] >> 15) & 1u) << (15 - 2 * j)) | ((pk[j] >> 31) << (14 - 2 * j));
+        *mask_dst = static_cast<uint16_t>(neg);
+    }
+    if (kRelu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            __nv_bfloat162 t = *reinterpret_cast<__nv_bfloat162*>(&pk[j]);
+            t = __hmax2(t, __floats2bfloat162_rn(0.0f, 0.0f));
+            pk[j] = *reinterpret_cast<uint32_t*>(&t);
         }
     }
-    if (kRelu && mask_dst != nullptr) *mask_dst = neg;
     if (kHeads > 0) {
 #pragma unroll
         for (int h = 0; h < kHeads; ++h) {
             float a = hacc[h];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(hw + h * hw_ld) + q);
-                a = fmaf(x[4 * q], t.x, a); a = fmaf(x[4 * q + 1], t.y, a);
-                a = fmaf(x[4 * q + 2], t.z, a); a = fmaf(x[4 * q + 3], t.w, a);
+            for (int q = 0; q < 4; ++q) {
+                const float4 t = reinterpret_cast<const float4*>(hw + h * hw_ld)[q];     // shared memory
+                a = fmaf(kRelu ? fmaxf(x[4 * q], 0.0f) : x[4 * q], t.x, a);
+                a = fmaf(kRelu ? fmaxf(x[4 * q + 1], 0.0f) : x[4 * q + 1], t.y, a);
+                a = fmaf(kRelu ? fmaxf(x[4 * q + 2], 0.0f) : x[4 * q + 2], t.z, a);
+                a = fmaf(kRelu ? fmaxf(x[4 * q + 3], 0.0f) : x[4 * q + 3], t.w, a);
             }
             hacc[h] = a;
         }
     }
-    store_slice_bf16(sH, row, c_out, x);
+    uint8_t* blk = sH + (c_out >> 6) * 16384;
+    const int chunk0 = (c_out & 63) >> 3;
+    *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0 + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
 }
 
-__global__ void __launch_bounds__(kFwdThreads, 2)
+__device__ __forceinline__ void trace_ev(long long* tr, int slot) {
+    if (tr != nullptr && blockIdx.x == 0) tr[slot] = clock64();
+}
+
+// quarters (64-column blocks) of layer g's output
+__device__ __forceinline__ int layer_quarters(int g, bool transient) {
+    if (g <= 8) return 4;
+    if (g == 9) return transient ? 4 : 2;
+    return 2;
+}
+
+template <bool kSave>
+__global__ void __launch_bounds__(kFwdThreads, 1)
 field_fwd_kernel(const FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sX = smem + kOffX;
-    uint8_t* sH = smem + kOffH;
+    uint8_t* sH = smem + kOffH;                                          // two 64 KB images
     uint8_t* sW = smem + kOffW;
-    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kOffBar);   // [kNumStages]
-    uint64_t* bar_empty = bar_full + kNumStages;                        // [kNumStages]
-    uint64_t* bar_acc = bar_empty + kNumStages;                         // MMA -> epilogue
-    uint64_t* bar_act = bar_acc + 1;                                    // epilogue -> MMA
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_act + 1);
+    float* s_part = reinterpret_cast<float*>(smem + kOffX);             // [3][5][128] head partial sums: sX is dead
+                                                                        // once layer 4's MMAs are done
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kOffBar);   // [kNumStages] producer -> MMA
+    uint64_t* bar_empty = bar_full + kNumStages;                        // [kNumStages] MMA -> producer
+    uint64_t* bar_acc = bar_empty + kNumStages;                         // [2] MMA -> epilogue (N half 0 / 1 done)
+    uint64_t* bar_act = bar_acc + 2;                                    // [4] epilogue -> MMA, per quarter
+    uint64_t* bar_st = bar_act + 4;                                     // [5] epilogue -> storer (4 quarters, X)
+    uint64_t* bar_done = bar_st + 5;                                    // [3] storer -> epilogue (H0, H1, X)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 3);
     uint32_t* s_woff = tmem_slot + 2;                                   // [kMaxG] slab offsets
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -117,7 +165,7 @@ field_fwd_kernel(const FwdArgs a) {
     const int nl = fs.n_layers(a.mode);
     const bool transient = (a.mode & NWB_MLP_TRANSIENT) != 0;
     const bool sigma_only = (a.mode & NWB_MLP_SIGMA_ONLY) != 0;
-    const bool save = (a.mode & NWB_MLP_SAVE) != 0;
+    constexpr bool save = kSave;
 
     if (threadIdx.x == 0) {
         if ((ptx::smem_u32(smem) & 1023u) != 0) {
@@ -125,12 +173,20 @@ field_fwd_kernel(const FwdArgs a) {
             __trap();
         }
         for (int s = 0; s < kNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], 1); }
-        ptx::mbar_init(bar_acc, 1);
-        ptx::mbar_init(bar_act, 128);
+        ptx::mbar_init(&bar_acc[0], 1);
+        ptx::mbar_init(&bar_acc[1], 1);
+        for (int q = 0; q < 4; ++q) ptx::mbar_init(&bar_act[q], kEpiWarps);   // one arrival per epilogue warp
+        for (int q = 0; q < 5; ++q) ptx::mbar_init(&bar_st[q], kEpiWarps);
+        for (int q = 0; q < 3; ++q) ptx::mbar_init(&bar_done[q], 1);
         ptx::fence_mbar_init();
         for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
     }
-    if (warp == 1) ptx::tmem_alloc<256>(tmem_slot);
+    {   // biases and head weights: L1 is carved down to nothing by the 227 KB of shared memory, so keep them here
+        const float4* src = reinterpret_cast<const float4*>(a.packed + fs.w_bytes());
+        float4* dst = reinterpret_cast<float4*>(smem + kOffC);
+        for (int i = threadIdx.x; i < ConstOff::count / 4; i += kFwdThreads) dst[i] = __ldg(src + i);
+    }
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
     ptx::tc_fence_before_sync();
     __syncthreads();
     ptx::tc_fence_after_sync();
@@ -147,7 +203,7 @@ field_fwd_kernel(const FwdArgs a) {
                     for (int kb = 0; kb < KB; ++kb) {
                         for (int nh = 0; nh < NH; ++nh, ++it) {
                             const uint32_t s = it % kNumStages;
-                            ptx::mbar_wait(&bar_empty[s], ((it / kNumStages) & 1u) ^ 1u);
+                            ptx::mbar_wait_sleepy(&bar_empty[s], ((it / kNumStages) & 1u) ^ 1u);
                             ptx::mbar_arrive_expect_tx(&bar_full[s], kStageBytes);
                             ptx::bulk_g2s(sW + s * kStageBytes, wsrc + static_cast<size_t>(kb) * PN * 128 + nh * kStageBytes,
                                           kStageBytes, &bar_full[s]);
@@ -159,55 +215,119 @@ field_fwd_kernel(const FwdArgs a) {
         __syncwarp();
     } else if (warp == 1) {
         // ============================ MMA issuer =================================================
-        if (lane == 0) {
+        // The whole warp walks the schedule (uniform control flow); one elected lane issues.  Per 16 KB stage:
+        // 4 x tcgen05.mma (K = 16 each) + the commits.  Everything the loop touches is a 32-bit shared-memory
+        // address or a descriptor low word, kept in registers (the loop has ~64 tensor cycles per MMA to spare).
+        {
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, 128, false, false);
-            const uint32_t xa = ptx::smem_u32(sX), ha = ptx::smem_u32(sH), wa = ptx::smem_u32(sW);
-            uint32_t it = 0, ev = 0;
+            const uint32_t x_lo = ptx::umma_desc_lo(ptx::smem_u32(sX)), h_lo = ptx::umma_desc_lo(ptx::smem_u32(sH));
+            const uint32_t w_lo = ptx::umma_desc_lo(ptx::smem_u32(sW));
+            const uint32_t full_a = ptx::smem_u32(bar_full), empty_a = ptx::smem_u32(bar_empty);
+            const uint32_t acc_a = ptx::smem_u32(bar_acc), act_a = ptx::smem_u32(bar_act);
+            uint32_t s = 0, ph = 0;                          // ring slot and its phase
+            uint32_t act_par = 0;                            // bit q = parity of the next phase of bar_act[q]
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 for (int g = 0; g < nl; ++g) {
-                    ptx::mbar_wait(bar_act, ev & 1u);
-                    ++ev;
-                    ptx::tc_fence_after_sync();
                     const int KB = fs.layer_kb(g), NH = fs.layer_n(g, a.mode) >> 7;
+                    const uint32_t hin_lo = h_lo + ((g - 1) & 1) * 4096;       // input image of layer g (64 KB >> 4)
+                    const uint32_t dcol = tmem + (g & 1) * 256;
                     for (int kb = 0; kb < KB; ++kb) {
-                        uint32_t abase;
-                        if (g == 0) abase = xa;
-                        else if (g == 4) abase = (kb == 0) ? xa : ha + (kb - 1) * 16384;
-                        else if (g >= 10) abase = ha + (kb + 2) * 16384;
-                        else abase = ha + kb * 16384;
-                        for (int nh = 0; nh < NH; ++nh, ++it) {
-                            const uint32_t s = it % kNumStages;
-                            ptx::mbar_wait(&bar_full[s], (it / kNumStages) & 1u);
+                        // ---- which quarter of the previous epilogue feeds this K-block (16 KB >> 4 = 1024) --------
+                        uint32_t a_lo;
+                        int q;
+                        if (g == 0) { a_lo = x_lo; q = 0; }                                   // X-ready rides on act[0]
+                        else if (g == 4) { a_lo = (kb == 0) ? x_lo : hin_lo + (kb - 1) * 1024; q = kb - 1; }
+                        else if (g == 10) {
+                            if (kb == 0) {                    // layer 9's dir quarters feed no MMA: consume their phases
+                                ptx::mbar_wait_a(act_a, act_par & 1u);
+                                ptx::mbar_wait_a(act_a + 8, (act_par >> 1) & 1u);
+                                act_par ^= 3u;
+                            }
+                            a_lo = hin_lo + (kb + 2) * 1024; q = kb + 2;
+                        } else { a_lo = hin_lo + kb * 1024; q = kb; }
+                        if (q >= 0) {
+                            ptx::mbar_wait_a(act_a + 8 * q, (act_par >> q) & 1u);
+                            act_par ^= 1u << q;
+                        }
+                        if (tile == 0 && lane == 0) trace_ev(a.trace, g * 16 + kb);                 // operand ready, about to issue
+                        const bool last_kb = (kb == KB - 1);
+                        for (int nh = 0; nh < NH; ++nh) {
+                            ptx::mbar_wait_a(full_a + 8 * s, ph);
                             ptx::tc_fence_after_sync();
-                            const uint32_t wb = wa + s * kStageBytes;
-#pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                ptx::umma_bf16(tmem + nh * 128, ptx::umma_desc_sw128(abase + k * 32, 16, 1024),
-                                               ptx::umma_desc_sw128(wb + k * 32, 16, 1024), idesc, (kb | k) != 0);
-                            ptx::umma_commit(&bar_empty[s]);
+                            if (ptx::elect_one()) {
+                                const uint32_t b_lo = w_lo + s * 1024;
+                                const uint32_t d = dcol + nh * 128;
+                                ptx::umma_bf16_lo(d, a_lo, b_lo, idesc, kb != 0);
+                                ptx::umma_bf16_lo(d, a_lo + 2, b_lo + 2, idesc, 1);
+                                ptx::umma_bf16_lo(d, a_lo + 4, b_lo + 4, idesc, 1);
+                                ptx::umma_bf16_lo(d, a_lo + 6, b_lo + 6, idesc, 1);
+                                ptx::umma_commit_a(empty_a + 8 * s);
+                                if (last_kb) {
+                                    ptx::umma_commit_a(acc_a + 8 * nh);               // this N half is complete
+                                    if (NH == 1) ptx::umma_commit_a(acc_a + 8);        // keep both barriers in step
+                                }
+                            }
+                            __syncwarp();
+                            if (++s == kNumStages) { s = 0; ph ^= 1u; }
+                            if (tile == 0 && nh == NH - 1 && lane == 0) trace_ev(a.trace, g * 16 + 5 + kb);   // issued
                         }
                     }
-                    ptx::umma_commit(bar_acc);
                 }
             }
         }
+    } else if (warp == 2) {
+        // ============================ activation storer (NWB_MLP_SAVE) ===========================
+        if (lane == 0 && save) {
+            const SaveLayout sl{fs.kx, transient};
+            uint32_t stc[5] = {0, 0, 0, 0, 0};
+            bool first = true;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                uint8_t* save_tile = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
+                ptx::mbar_wait_sleepy(&bar_st[4], stc[4] & 1u); ++stc[4];
+                ptx::bulk_s2g(save_tile + sl.x_off(), sX, 16384);
+                ptx::bulk_commit();
+                if (!first) {                           // the previous tile's last layer has been read by now
+                    ptx::bulk_wait_read<1>();
+                    ptx::mbar_arrive(&bar_done[(nl - 1) & 1]);
+                }
+                first = false;
+                for (int g = 0; g < nl; ++g) {
+                    const int nq = layer_quarters(g, transient);
+                    const uint8_t* src = sH + (g & 1) * 65536;
+                    uint8_t* dst = save_tile + sl.act_off(g);
+                    for (int q = 0; q < nq; ++q) {
+                        ptx::mbar_wait_sleepy(&bar_st[q], stc[q] & 1u); ++stc[q];
+                        ptx::bulk_s2g(dst + q * 16384, src + q * 16384, 16384);
+                        ptx::bulk_commit();
+                    }
+                    // everything older than this layer's groups has been read out of shared memory
+                    if (nq == 4) ptx::bulk_wait_read<4>(); else ptx::bulk_wait_read<2>();
+                    if (g == 0) ptx::mbar_arrive(&bar_done[2]);                   // X
+                    else ptx::mbar_arrive(&bar_done[(g - 1) & 1]);
+                }
+            }
+            ptx::bulk_wait_all<0>();
+        }
         __syncwarp();
     } else {
-        // ============================ epilogue warps (thread == point) ===========================
+        // ============================ epilogue warps (four threads per point) ====================
+        const int ew = warp - kEpiWarp0;                   // 0..15
         const int quad = warp & 3;                         // TMEM lane quadrant this warp may read
+        const int sub = ew >> 2;                           // 16-column slice of every 64-column quarter
         const int row = quad * 32 + lane;
         const uint32_t tlane = tmem + (static_cast<uint32_t>(quad * 32) << 16);
-        const bool leader = (threadIdx.x == 64);
-        const float* cst = reinterpret_cast<const float*>(a.packed + fs.w_bytes());
-        uint32_t acc_ev = 0;
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        const float* cst = reinterpret_cast<const float*>(smem + kOffC);
+        const SaveLayout sl{fs.kx, transient};
+        uint32_t acc_ev = 0;                               // layers consumed (parity of bar_acc)
+        uint32_t wcnt[2] = {0, 0};                         // writes so far into H0, H1 (save mode hand-back)
+        uint32_t tcount = 0;                               // tiles done by this CTA
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tcount) {
             const long long p = static_cast<long long>(tile) * kTileM + row;
             const bool valid = p < a.n_points;
             const long long ray = valid ? p / a.S : 0;
             uint8_t* save_tile = save ? a.saved + static_cast<size_t>(tile) * a.save_tile_bytes : nullptr;
-            const SaveLayout sl{fs.kx, transient};
 
-            // ---- encoded-xyz operand tile ------------------------------------------------------
+            // ---- encoded-xyz operand tile: this thread packs columns [16*sub, 16*sub+16) of its row ----
             {
                 float e[64];
 #pragma unroll
@@ -217,7 +337,7 @@ field_fwd_kernel(const FwdArgs a) {
                         const float* xr = a.x_enc + p * fs.in_xyz;
 #pragma unroll
                         for (int c = 0; c < 64; ++c)
-                            if (c < fs.in_xyz) e[c] = __ldg(xr + c);
+                            if (c < fs.in_xyz && (c >> 4) == sub) e[c] = __ldg(xr + c);
                     } else {
                         const float* rr = a.rays + ray * a.ray_stride;
                         const float zz = __ldg(a.z + p);
@@ -244,89 +364,102 @@ field_fwd_kernel(const FwdArgs a) {
                         }
                     }
                 }
-                if (save) {                                 // previous tile's last bulk store must have read sH/sX
-                    if (leader) ptx::bulk_wait_read<0>();
-                    epi_bar();
-                }
+                uint32_t pk[8];
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    uint4 pk;
-                    pk.x = pack_bf16(e[8 * q], e[8 * q + 1]);
-                    pk.y = pack_bf16(e[8 * q + 2], e[8 * q + 3]);
-                    pk.z = pack_bf16(e[8 * q + 4], e[8 * q + 5]);
-                    pk.w = pack_bf16(e[8 * q + 6], e[8 * q + 7]);
-                    *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, q)) = pk;
+                for (int s4 = 0; s4 < 4; ++s4) {
+                    if (s4 == sub) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(e[16 * s4 + 2 * j], e[16 * s4 + 2 * j + 1]);
+                    }
                 }
+                // sX doubles as the head scratch of the previous tile and (save) is read by the storer: both are
+                // finished -- the last head combine ended with a barrier, the X hand-back was consumed at layer 7
+                *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 ptx::fence_proxy_async_smem();
-                if (save) {
-                    epi_bar();
-                    if (leader) { ptx::bulk_s2g(save_tile + sl.x_off(), sX, 16384); ptx::bulk_commit(); }
-                }
                 ptx::tc_fence_before_sync();
-                ptx::mbar_arrive(bar_act);
+                __syncwarp();
+                if (lane == 0) {
+                    ptx::mbar_arrive(&bar_act[0]);
+                    if (save) ptx::mbar_arrive(&bar_st[4]);
+                }
             }
 
             float sigma = 0.0f, rgb[3] = {0, 0, 0};
             const float* rb = (a.ray_bias != nullptr) ? a.ray_bias + ray * 256 : nullptr;
             for (int g = 0; g < nl; ++g) {
-                ptx::mbar_wait(bar_acc, acc_ev & 1u);
+                const uint32_t par = acc_ev & 1u;
                 ++acc_ev;
+                const int b = g & 1;
+                uint8_t* hout = sH + b * 65536;
+                const uint32_t tacc = tlane + b * 256 + sub * 16;
+                const bool last = (g == nl - 1);
+                ptx::mbar_wait_sleepy(&bar_acc[0], par);
                 ptx::tc_fence_after_sync();
-                if (save) {                                 // the bulk store of layer g-1 must have read sH
-                    if (leader) ptx::bulk_wait_read<0>();
-                    epi_bar();
+                if (tile == 0 && warp == kEpiWarp0 && lane == 0) trace_ev(a.trace, g * 16 + 10);          // acc half 0 seen
+                if (save) {                                 // the storer must have read this buffer's previous contents
+                    if (wcnt[b] > 0) ptx::mbar_wait_sleepy(&bar_done[b], (wcnt[b] - 1) & 1u);
+                    ++wcnt[b];
                 }
                 float hacc[5] = {0, 0, 0, 0, 0};
-                uint32_t* mrow = save ? reinterpret_cast<uint32_t*>(save_tile + sl.mask_off(g, nl)) + row * 8 : nullptr;
-                if (g < 7) {
+                // sign masks: per layer and row 8 x uint32, word w = columns 32w..32w+31, bit (31-j) = column 32w+j;
+                // this thread's 16 columns are the high (even sub) or low (odd sub) half of word 2q + sub/2
+                uint16_t* mrow = save ? reinterpret_cast<uint16_t*>(save_tile + sl.mask_off(g, nl)) + row * 16 + (sub >> 1) * 2 + (1 - (sub & 1))
+                                      : nullptr;
+                const int nq = layer_quarters(g, transient);
 #pragma unroll 1
-                    for (int c0 = 0; c0 < 256; c0 += 32)
-                        epi_slice<true, 0>(tlane + c0, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
-                } else if (g == 7) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 256; c0 += 32)
-                        epi_slice<true, 1>(tlane + c0, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                           hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
-                    sigma = softplus_f(hacc[0] + __ldg(cst + ConstOff::head_b));                // nerf.py:190
-                } else if (g == 8) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 256; c0 += 32)
-                        epi_slice<false, 0>(tlane + c0, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
-                } else if (g == 9) {
-                    // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 128; c0 += 32)
-                        epi_slice<true, 3>(tlane + c0, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
-#pragma unroll
-                    for (int i = 0; i < 3; ++i) rgb[i] = sigmoid_f(hacc[i] + __ldg(cst + ConstOff::head_b + 1 + i));   // nerf.py:197
-                    if (transient) {
-#pragma unroll 1
-                        for (int c0 = 128; c0 < 256; c0 += 32)
-                            epi_slice<true, 0>(tlane + c0, nullptr, rb + c0, nullptr, 0, hacc, sH, row, c0, mrow ? mrow + (c0 >> 5) : nullptr);
+                for (int q = 0; q < nq; ++q) {
+                    if (q == 2) { ptx::mbar_wait_sleepy(&bar_acc[1], par); ptx::tc_fence_after_sync(); }
+                    const int c0 = q * 64 + sub * 16;       // this thread's 16 columns of quarter q
+                    uint16_t* md = save ? mrow + 4 * q : nullptr;
+                    if (g < 7) {
+                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, hout, row, c0, md);
+                    } else if (g == 7) {
+                        epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
+                                                    hacc, hout, row, c0, md);
+                    } else if (g == 8) {
+                        epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, hout, row, c0, md);
+                    } else if (g == 9) {
+                        // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
+                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, hout, row, c0, md);
+                        else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, hout, row, c0, md);
+                    } else if (g < 12) {
+                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, hout, row, c0, md);
+                    } else {
+                        // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
+                        epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
+                                                    hacc, hout, row, c0, md);
                     }
-                } else if (g < 12) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 128; c0 += 32)
-                        epi_slice<true, 0>(tlane + c0, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, sH, row, 128 + c0, mrow ? mrow + (c0 >> 5) : nullptr);
-                } else {
-                    // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 128; c0 += 32)
-                        epi_slice<true, 5>(tlane + c0, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                           hacc, sH, row, 128 + c0, mrow ? mrow + (c0 >> 5) : nullptr);
+                    ptx::fence_proxy_async_smem();
+                    ptx::tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (!last) ptx::mbar_arrive(&bar_act[q]);
+                        if (save) ptx::mbar_arrive(&bar_st[q]);
+                        if (tile == 0 && warp == kEpiWarp0) trace_ev(a.trace, g * 16 + 11 + q);          // quarter q handed over
+                    }
                 }
-                ptx::fence_proxy_async_smem();
-                if (save) {
-                    epi_bar();
-                    if (leader) {
-                        const uint32_t bytes = (g <= 8) ? 65536u : (g == 9 ? (transient ? 65536u : 32768u) : 32768u);
-                        const uint8_t* src = (g >= 10) ? sH + 32768 : sH;
-                        ptx::bulk_s2g(save_tile + sl.act_off(g), src, bytes);
-                        ptx::bulk_commit();
+                // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
+                const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
+                if (nh_heads > 0) {
+                    if (save && g == 7) ptx::mbar_wait_sleepy(&bar_done[2], tcount & 1u);    // the storer has read this tile's X
+                    if (sub > 0) {
+                        for (int h = 0; h < nh_heads; ++h) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
                     }
+                    epi_bar_all();
+                    if (sub == 0) {
+                        for (int h = 0; h < nh_heads; ++h)
+                            hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
+                        if (g == 7) sigma = softplus_f(hacc[0] + cst[ConstOff::head_b]);                // nerf.py:190
+                        if (g == 9) {
+#pragma unroll
+                            for (int i = 0; i < 3; ++i) rgb[i] = sigmoid_f(hacc[i] + cst[ConstOff::head_b + 1 + i]);   // nerf.py:197
+                        }
+                    }
+                    if (last) epi_bar_all();                // scratch is read before the next tile's X overwrites it
                 }
                 // ---- tile outputs ---------------------------------------------------------------
-                if (g == nl - 1 && valid) {
+                if (last && valid && sub == 0) {
                     if (sigma_only) {
                         a.raw_out[p] = sigma;
                     } else {
@@ -334,30 +467,29 @@ field_fwd_kernel(const FwdArgs a) {
                         o[0] = rgb[0]; o[1] = rgb[1]; o[2] = rgb[2]; o[3] = sigma;               // nerf.py:198
                         if (transient) {
                             const float* hb = cst + ConstOff::head_b;
-                            o[4] = sigmoid_f(hacc[1] + __ldg(hb + 5));                           // nerf.py:206
-                            o[5] = sigmoid_f(hacc[2] + __ldg(hb + 6));
-                            o[6] = sigmoid_f(hacc[3] + __ldg(hb + 7));
-                            o[7] = softplus_f(hacc[0] + __ldg(hb + 4));                          // nerf.py:205
-                            o[8] = softplus_f(hacc[4] + __ldg(hb + 8));                          // nerf.py:207
+                            o[4] = sigmoid_f(hacc[1] + hb[5]);                           // nerf.py:206
+                            o[5] = sigmoid_f(hacc[2] + hb[6]);
+                            o[6] = sigmoid_f(hacc[3] + hb[7]);
+                            o[7] = softplus_f(hacc[0] + hb[4]);                          // nerf.py:205
+                            o[8] = softplus_f(hacc[4] + hb[8]);                          // nerf.py:207
                         }
                     }
                 }
-                if (g < nl - 1) {
-                    ptx::tc_fence_before_sync();
-                    ptx::mbar_arrive(bar_act);
-                }
             }
         }
-        if (save && leader) ptx::bulk_wait_all<0>();
     }
     ptx::tc_fence_before_sync();
     __syncthreads();
-    if (warp == 1) ptx::tmem_dealloc<256>(tmem);
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem);
 }
 
 }  // namespace nwb
 
 using namespace nwb;
+
+static long long* g_fwd_trace = nullptr;
+// debug hook (tools/trace_fwd.py): device buffer of >= 16*13 int64 that block 0 fills with clock64() stamps
+extern "C" void nwb_debug_set_fwd_trace(void* buf) { g_fwd_trace = static_cast<long long*>(buf); }
 
 extern "C" size_t nwb_mlp_save_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode) {
     FieldShape fs;
@@ -396,15 +528,17 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
     a.mode = mode; a.raw_out = raw_out; a.saved = static_cast<uint8_t*>(saved);
     const SaveLayout sl{fs.kx, transient};
     a.save_tile_bytes = sl.tile_bytes(fs.n_layers(mode));
+    a.trace = g_fwd_trace;
 
     static bool configured = false;
     if (!configured) {
-        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
-        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
         configured = true;
     }
-    const int grid = std::min(a.n_tiles, 2 * kNumSMs);
-    field_fwd_kernel<<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+    const int grid = std::min(a.n_tiles, kNumSMs);
+    if (mode & NWB_MLP_SAVE) field_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+    else field_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }

@@ -30,6 +30,9 @@ def bench(n_rays, S, transient, save, iters=10):
     print(f"rays={n_rays} S={S} transient={transient} save={save}: {ms:.3f} ms  {tf:.1f} TFLOP/s  {n_rays*S/ms/1e3:.2f} Mpts/s")
 
 if __name__ == "__main__":
-    for n, S in [(1024, 128), (8192, 128), (32768, 128)]:
-        for save in (False, True):
-            bench(n, S, True, save)
+    if len(sys.argv) > 1:          # python tools/perf_fwd.py <n_rays> <save 0|1> [iters]   (profiling runs)
+        bench(int(sys.argv[1]), 128, True, bool(int(sys.argv[2])), iters=int(sys.argv[3]) if len(sys.argv) > 3 else 2)
+    else:
+        for n, S in [(1024, 128), (8192, 128), (32768, 128)]:
+            for save in (False, True):
+                bench(n, S, True, save)
