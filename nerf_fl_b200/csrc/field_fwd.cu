@@ -26,19 +26,23 @@
 
 namespace nwb {
 
-constexpr int kFwdThreads = 608;              // 19 warps
-constexpr int kEpiWarp0 = 3;                  // first epilogue warp
+constexpr int kMmaWarps = 2;                  // MMA-issuing warps, each owns 1/kMmaWarps of a layer's output columns
+constexpr int kStoreWarp = 1 + kMmaWarps;
+constexpr int kEpiWarp0 = 2 + kMmaWarps;      // first epilogue warp
 constexpr int kEpiWarps = 16;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kStageBytes = 16384;            // 128 weight rows x 64 k (one SW128 K-block)
-constexpr int kNumStages = 4;
+constexpr int kFwdThreads = (kEpiWarp0 + kEpiWarps) * 32;
+constexpr int kStageBytes = 32768;            // 256 weight rows x 64 k (one SW128 K-block of a whole layer)
+constexpr int kNumStages = 3;
+constexpr int kHSlots = 6;                    // activation K-block slots (128 rows x 64 columns, 16 KB each)
+constexpr int kSlotX = 6;                     // barrier index of the encoded-xyz tile
 constexpr int kOffX = 0;                      // 16 KB  encoded xyz, 128 x 64
-constexpr int kOffH = 16384;                  // 2 x 64 KB  activations, 128 x 256 (4 K-blocks) each
-constexpr int kOffW = kOffH + 2 * 65536;      // ring
+constexpr int kOffH = 16384;                  // 6 x 16 KB activation K-block slots, used round-robin
+constexpr int kOffW = kOffH + kHSlots * 16384;               // weight ring
 constexpr int kOffC = kOffW + kNumStages * kStageBytes;      // 16 KB  fp32 biases + head weights (ConstOff block)
 constexpr int kOffBar = kOffC + 16384;
-static_assert(ConstOff::count * 4 <= 16384, "constant block does not fit its shared-memory slot");
 constexpr int kFwdSmem = kOffBar + 320;
+static_assert(ConstOff::count * 4 <= 16384, "constant block does not fit its shared-memory slot");
 static_assert(kFwdSmem <= 232448, "forward kernel exceeds the 227 KB shared-memory limit");
 
 struct FwdArgs {
@@ -57,7 +61,7 @@ struct FwdArgs {
     float* raw_out;
     uint8_t* saved;
     size_t save_tile_bytes;
-    long long* trace;      // debug: block 0 timestamps (tools/trace_fwd.py), else nullptr
+    long long* trace;      // debug (-DNWB_FWD_TRACE): block 0 timestamps for tools/trace_fwd.py, else unused
 };
 
 // named barrier of the epilogue threads (barrier 0 is __syncthreads)
@@ -66,12 +70,12 @@ __device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, %0;" :
 // One 16-column slice of a layer epilogue for this thread's row.
 //   x = acc + bias[c] (+ rbias[c]);  optional head dot products (fp32, unrounded x, after ReLU);
 //   bf16 pack, ReLU on the packed pairs (rounding is monotonic and keeps the sign, so max(rn(x), 0) ==
-//   rn(max(x, 0))) -> 2 x 16 B chunks of the output image at column c_out (same row).
+//   rn(max(x, 0))) -> chunks chunk0, chunk0+1 (16 B each) of this row in the K-block image blk.
 //   kSave: the sign bits of the 16 pre-activations go to *mask_dst, bit (15-j) = column j.
 template <bool kRelu, int kHeads, bool kSave>
 __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restrict__ bias,
                                             const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
-                                            float* hacc, uint8_t* sH, int row, int c_out, uint16_t* mask_dst) {
+                                            float* hacc, uint8_t* blk, int row, int chunk0, uint16_t* mask_dst) {
     uint32_t v[16];
     ptx::tmem_ld16(taddr, v);
     float b[16];
@@ -125,39 +129,47 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
             hacc[h] = a;
         }
     }
-    uint8_t* blk = sH + (c_out >> 6) * 16384;
-    const int chunk0 = (c_out & 63) >> 3;
     *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
     *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0 + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
 }
 
+#ifdef NWB_FWD_TRACE      // tools/trace_fwd.py: build with -DNWB_FWD_TRACE to get block 0's timeline
 __device__ __forceinline__ void trace_ev(long long* tr, int slot) {
     if (tr != nullptr && blockIdx.x == 0) tr[slot] = clock64();
 }
+#define NWB_TRACE(cond, slot) do { if (cond) trace_ev(a.trace, slot); } while (0)
+#else
+#define NWB_TRACE(cond, slot) do { } while (0)
+#endif
 
-// quarters (64-column blocks) of layer g's output
+// ---- activation slot schedule --------------------------------------------------------------------------
+// Output quarters (64 columns = one K-block of the next layer's A operand) are written to the six 16 KB slots
+// round-robin, counted from the start of the tile: quarter q of layer g lives in slot (first_quarter(g)+q) % 6.
+// A layer's epilogue starts only when ALL of its MMAs are complete, so its input slots are dead by then, and
+// its outputs (<= 4 slots) never collide with the next layer's inputs (they ARE its inputs).
 __device__ __forceinline__ int layer_quarters(int g, bool transient) {
     if (g <= 8) return 4;
     if (g == 9) return transient ? 4 : 2;
     return 2;
 }
-
+__device__ __forceinline__ int first_quarter(int g) { return g <= 10 ? 4 * g : 42 + 2 * (g - 11); }   // transient chain: 40, 42, 44
+__device__ __forceinline__ int out_slot(int g, int q) { return (first_quarter(g) + q) % kHSlots; }
 template <bool kSave>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 field_fwd_kernel(const FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sX = smem + kOffX;
-    uint8_t* sH = smem + kOffH;                                          // two 64 KB images
+    uint8_t* sH = smem + kOffH;                                          // six 16 KB K-block slots
     uint8_t* sW = smem + kOffW;
     float* s_part = reinterpret_cast<float*>(smem + kOffX);             // [3][5][128] head partial sums: sX is dead
                                                                         // once layer 4's MMAs are done
     uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kOffBar);   // [kNumStages] producer -> MMA
     uint64_t* bar_empty = bar_full + kNumStages;                        // [kNumStages] MMA -> producer
-    uint64_t* bar_acc = bar_empty + kNumStages;                         // [2] MMA -> epilogue (N half 0 / 1 done)
-    uint64_t* bar_act = bar_acc + 2;                                    // [4] epilogue -> MMA, per quarter
-    uint64_t* bar_st = bar_act + 4;                                     // [5] epilogue -> storer (4 quarters, X)
-    uint64_t* bar_done = bar_st + 5;                                    // [3] storer -> epilogue (H0, H1, X)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 3);
+    uint64_t* bar_acc = bar_empty + kNumStages;                         // [1] MMA -> epilogue (layer accumulator complete)
+    uint64_t* bar_act = bar_acc + 1;                                    // [7] epilogue -> MMA, per slot (+X)
+    uint64_t* bar_st = bar_act + 7;                                     // [7] epilogue -> storer, per slot (+X)
+    uint64_t* bar_done = bar_st + 7;                                    // [7] storer -> epilogue: slot read out, reusable
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 7);
     uint32_t* s_woff = tmem_slot + 2;                                   // [kMaxG] slab offsets
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -172,12 +184,13 @@ field_fwd_kernel(const FwdArgs a) {
             printf("nwb: dynamic shared memory is not 1 KB aligned\n");
             __trap();
         }
-        for (int s = 0; s < kNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], 1); }
-        ptx::mbar_init(&bar_acc[0], 1);
-        ptx::mbar_init(&bar_acc[1], 1);
-        for (int q = 0; q < 4; ++q) ptx::mbar_init(&bar_act[q], kEpiWarps);   // one arrival per epilogue warp
-        for (int q = 0; q < 5; ++q) ptx::mbar_init(&bar_st[q], kEpiWarps);
-        for (int q = 0; q < 3; ++q) ptx::mbar_init(&bar_done[q], 1);
+        for (int s = 0; s < kNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], kMmaWarps); }
+        ptx::mbar_init(bar_acc, kMmaWarps);
+        for (int q = 0; q < 7; ++q) {
+            ptx::mbar_init(&bar_act[q], kEpiWarps);                     // one arrival per epilogue warp
+            ptx::mbar_init(&bar_st[q], kEpiWarps);
+            ptx::mbar_init(&bar_done[q], 1);
+        }
         ptx::fence_mbar_init();
         for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
     }
@@ -194,116 +207,110 @@ field_fwd_kernel(const FwdArgs a) {
 
     if (warp == 0) {
         // ============================ weight producer ============================================
+        // one stage = one 64-wide K-block of a whole layer: N x 64 bf16 = 32 KB (N = 256) or 16 KB (N = 128),
+        // contiguous in the packed image (field_pack.cu), one bulk copy
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t s = 0, ph = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 for (int g = 0; g < nl; ++g) {
                     const uint8_t* wsrc = a.packed + s_woff[g];
-                    const int KB = fs.layer_kb(g), NH = fs.layer_n(g, a.mode) >> 7, PN = fs.packed_n(g);
+                    const int KB = fs.layer_kb(g), PN = fs.packed_n(g);
+                    const uint32_t bytes = static_cast<uint32_t>(fs.layer_n(g, a.mode)) * 128u;
                     for (int kb = 0; kb < KB; ++kb) {
-                        for (int nh = 0; nh < NH; ++nh, ++it) {
-                            const uint32_t s = it % kNumStages;
-                            ptx::mbar_wait_sleepy(&bar_empty[s], ((it / kNumStages) & 1u) ^ 1u);
-                            ptx::mbar_arrive_expect_tx(&bar_full[s], kStageBytes);
-                            ptx::bulk_g2s(sW + s * kStageBytes, wsrc + static_cast<size_t>(kb) * PN * 128 + nh * kStageBytes,
-                                          kStageBytes, &bar_full[s]);
-                        }
+                        ptx::mbar_wait_sleepy(&bar_empty[s], ph ^ 1u);
+                        ptx::mbar_arrive_expect_tx(&bar_full[s], bytes);
+                        ptx::bulk_g2s(sW + s * kStageBytes, wsrc + static_cast<size_t>(kb) * PN * 128, bytes, &bar_full[s]);
+                        if (++s == kNumStages) { s = 0; ph ^= 1u; }
                     }
                 }
             }
         }
         __syncwarp();
-    } else if (warp == 1) {
-        // ============================ MMA issuer =================================================
-        // The whole warp walks the schedule (uniform control flow); one elected lane issues.  Per 16 KB stage:
-        // 4 x tcgen05.mma (K = 16 each) + the commits.  Everything the loop touches is a 32-bit shared-memory
-        // address or a descriptor low word, kept in registers (the loop has ~64 tensor cycles per MMA to spare).
+    } else if (warp <= kMmaWarps) {
+        // ============================ MMA issuers ================================================
+        // kMmaWarps warps, each owning a column range of the layer's output (its own TMEM columns and its own
+        // rows of every weight stage), so they need no ordering between them.  A single issuing thread spends
+        // ~10 cycles per instruction on waits, descriptor setup and commits -- several hundred cycles per
+        // K-block -- during which only the MMAs it has already queued keep the tensor pipe busy; two issuers
+        // fill each other's gaps.  The whole warp walks the schedule (uniform control flow), one elected lane
+        // issues.  Per stage and warp: 4 x tcgen05.mma M=128 N=(256|128)/kMmaWarps K=16 + the commits.
         {
-            constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, 128, false, false);
+            const int mw = warp - 1;
+            constexpr int n256 = 256 / kMmaWarps, n128 = 128 / kMmaWarps;
+            constexpr uint32_t idesc256 = ptx::umma_idesc_bf16(128, n256, false, false);
+            constexpr uint32_t idesc128 = ptx::umma_idesc_bf16(128, n128, false, false);
             const uint32_t x_lo = ptx::umma_desc_lo(ptx::smem_u32(sX)), h_lo = ptx::umma_desc_lo(ptx::smem_u32(sH));
             const uint32_t w_lo = ptx::umma_desc_lo(ptx::smem_u32(sW));
             const uint32_t full_a = ptx::smem_u32(bar_full), empty_a = ptx::smem_u32(bar_empty);
             const uint32_t acc_a = ptx::smem_u32(bar_acc), act_a = ptx::smem_u32(bar_act);
-            uint32_t s = 0, ph = 0;                          // ring slot and its phase
-            uint32_t act_par = 0;                            // bit q = parity of the next phase of bar_act[q]
+            uint32_t s = 0, ph = 0;                          // ring stage and its phase
+            uint32_t act_par = 0;                            // bit i = parity of the next phase of bar_act[i]
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                int isl = 0;                                 // slot of the next activation K-block (round-robin, per tile)
                 for (int g = 0; g < nl; ++g) {
-                    const int KB = fs.layer_kb(g), NH = fs.layer_n(g, a.mode) >> 7;
-                    const uint32_t hin_lo = h_lo + ((g - 1) & 1) * 4096;       // input image of layer g (64 KB >> 4)
-                    const uint32_t dcol = tmem + (g & 1) * 256;
+                    const int KB = fs.layer_kb(g);
+                    const bool wide = fs.layer_n(g, a.mode) == 256;
+                    const uint32_t idesc = wide ? idesc256 : idesc128;
+                    const int ncols = wide ? n256 : n128;                                // this warp's output columns
+                    const uint32_t dcol = tmem + (g & 1) * 256 + mw * ncols;
+                    const uint32_t wrow_lo = (mw * ncols * 128) >> 4;                    // this warp's rows of a weight stage
+                    if (g == 10) { isl += 2; if (isl >= kHSlots) isl -= kHSlots; }       // layer 9's dir quarters feed no MMA
                     for (int kb = 0; kb < KB; ++kb) {
-                        // ---- which quarter of the previous epilogue feeds this K-block (16 KB >> 4 = 1024) --------
-                        uint32_t a_lo;
-                        int q;
-                        if (g == 0) { a_lo = x_lo; q = 0; }                                   // X-ready rides on act[0]
-                        else if (g == 4) { a_lo = (kb == 0) ? x_lo : hin_lo + (kb - 1) * 1024; q = kb - 1; }
-                        else if (g == 10) {
-                            if (kb == 0) {                    // layer 9's dir quarters feed no MMA: consume their phases
-                                ptx::mbar_wait_a(act_a, act_par & 1u);
-                                ptx::mbar_wait_a(act_a + 8, (act_par >> 1) & 1u);
-                                act_par ^= 3u;
-                            }
-                            a_lo = hin_lo + (kb + 2) * 1024; q = kb + 2;
-                        } else { a_lo = hin_lo + kb * 1024; q = kb; }
-                        if (q >= 0) {
-                            ptx::mbar_wait_a(act_a + 8 * q, (act_par >> q) & 1u);
-                            act_par ^= 1u << q;
+                        const bool is_x = (g == 0) || (g == 4 && kb == 0);
+                        const int sl = is_x ? kSlotX : isl;
+                        const uint32_t a_lo = is_x ? x_lo : h_lo + isl * 1024;           // 16 KB >> 4
+                        if (!is_x && ++isl == kHSlots) isl = 0;
+                        if (!(g == 4 && kb == 0)) {                                       // X was awaited by layer 0
+                            ptx::mbar_wait_a(act_a + 8 * sl, (act_par >> sl) & 1u);
+                            act_par ^= 1u << sl;
                         }
-                        if (tile == 0 && lane == 0) trace_ev(a.trace, g * 16 + kb);                 // operand ready, about to issue
-                        const bool last_kb = (kb == KB - 1);
-                        for (int nh = 0; nh < NH; ++nh) {
-                            ptx::mbar_wait_a(full_a + 8 * s, ph);
-                            ptx::tc_fence_after_sync();
-                            if (ptx::elect_one()) {
-                                const uint32_t b_lo = w_lo + s * 1024;
-                                const uint32_t d = dcol + nh * 128;
-                                ptx::umma_bf16_lo(d, a_lo, b_lo, idesc, kb != 0);
-                                ptx::umma_bf16_lo(d, a_lo + 2, b_lo + 2, idesc, 1);
-                                ptx::umma_bf16_lo(d, a_lo + 4, b_lo + 4, idesc, 1);
-                                ptx::umma_bf16_lo(d, a_lo + 6, b_lo + 6, idesc, 1);
-                                ptx::umma_commit_a(empty_a + 8 * s);
-                                if (last_kb) {
-                                    ptx::umma_commit_a(acc_a + 8 * nh);               // this N half is complete
-                                    if (NH == 1) ptx::umma_commit_a(acc_a + 8);        // keep both barriers in step
-                                }
-                            }
-                            __syncwarp();
-                            if (++s == kNumStages) { s = 0; ph ^= 1u; }
-                            if (tile == 0 && nh == NH - 1 && lane == 0) trace_ev(a.trace, g * 16 + 5 + kb);   // issued
+                        NWB_TRACE(tile == 0 && lane == 0 && mw == 0, g * 16 + kb);        // operand ready, about to issue
+                        ptx::mbar_wait_a(full_a + 8 * s, ph);
+                        ptx::tc_fence_after_sync();
+                        if (ptx::elect_one()) {
+                            const uint32_t b_lo = w_lo + s * (kStageBytes >> 4) + wrow_lo;
+                            ptx::umma_bf16_lo(dcol, a_lo, b_lo, idesc, kb != 0);
+                            ptx::umma_bf16_lo(dcol, a_lo + 2, b_lo + 2, idesc, 1);
+                            ptx::umma_bf16_lo(dcol, a_lo + 4, b_lo + 4, idesc, 1);
+                            ptx::umma_bf16_lo(dcol, a_lo + 6, b_lo + 6, idesc, 1);
+                            ptx::umma_commit_a(empty_a + 8 * s);
+                            if (kb == KB - 1) ptx::umma_commit_a(acc_a);                 // this warp's columns of the layer are complete
                         }
+                        __syncwarp();
+                        if (++s == kNumStages) { s = 0; ph ^= 1u; }
+                        NWB_TRACE(tile == 0 && lane == 0 && mw == 0, g * 16 + 5 + kb);    // issued
                     }
                 }
             }
         }
-    } else if (warp == 2) {
+    } else if (warp == kStoreWarp) {
         // ============================ activation storer (NWB_MLP_SAVE) ===========================
+        // Quarters are stored in the order they are produced.  After issuing store n, every group but the two
+        // newest has been read out of shared memory, so the slot of store n-2 goes back to the epilogue.
         if (lane == 0 && save) {
             const SaveLayout sl{fs.kx, transient};
-            uint32_t stc[5] = {0, 0, 0, 0, 0};
-            bool first = true;
+            uint32_t st_par = 0;                             // bit i = parity of the next phase of bar_st[i]
+            int prev1 = -1, prev2 = -1;                      // slots of the two newest stores
+            auto store = [&](int slot, const uint8_t* src, uint8_t* dst) {
+                ptx::mbar_wait_sleepy(&bar_st[slot], (st_par >> slot) & 1u);
+                st_par ^= 1u << slot;
+                ptx::bulk_s2g(dst, src, 16384);
+                ptx::bulk_commit();
+                ptx::bulk_wait_read<2>();
+                if (prev2 >= 0) ptx::mbar_arrive(&bar_done[prev2]);
+                prev2 = prev1;
+                prev1 = slot;
+            };
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 uint8_t* save_tile = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
-                ptx::mbar_wait_sleepy(&bar_st[4], stc[4] & 1u); ++stc[4];
-                ptx::bulk_s2g(save_tile + sl.x_off(), sX, 16384);
-                ptx::bulk_commit();
-                if (!first) {                           // the previous tile's last layer has been read by now
-                    ptx::bulk_wait_read<1>();
-                    ptx::mbar_arrive(&bar_done[(nl - 1) & 1]);
-                }
-                first = false;
+                store(kSlotX, sX, save_tile + sl.x_off());
                 for (int g = 0; g < nl; ++g) {
                     const int nq = layer_quarters(g, transient);
-                    const uint8_t* src = sH + (g & 1) * 65536;
                     uint8_t* dst = save_tile + sl.act_off(g);
                     for (int q = 0; q < nq; ++q) {
-                        ptx::mbar_wait_sleepy(&bar_st[q], stc[q] & 1u); ++stc[q];
-                        ptx::bulk_s2g(dst + q * 16384, src + q * 16384, 16384);
-                        ptx::bulk_commit();
+                        const int slot = out_slot(g, q);
+                        store(slot, sH + slot * 16384, dst + q * 16384);
                     }
-                    // everything older than this layer's groups has been read out of shared memory
-                    if (nq == 4) ptx::bulk_wait_read<4>(); else ptx::bulk_wait_read<2>();
-                    if (g == 0) ptx::mbar_arrive(&bar_done[2]);                   // X
-                    else ptx::mbar_arrive(&bar_done[(g - 1) & 1]);
                 }
             }
             ptx::bulk_wait_all<0>();
@@ -319,7 +326,7 @@ field_fwd_kernel(const FwdArgs a) {
         const float* cst = reinterpret_cast<const float*>(smem + kOffC);
         const SaveLayout sl{fs.kx, transient};
         uint32_t acc_ev = 0;                               // layers consumed (parity of bar_acc)
-        uint32_t wcnt[2] = {0, 0};                         // writes so far into H0, H1 (save mode hand-back)
+        uint32_t seen = 0, done_par = 0;                   // save mode: slots written before / parity of their next hand-back
         uint32_t tcount = 0;                               // tiles done by this CTA
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tcount) {
             const long long p = static_cast<long long>(tile) * kTileM + row;
@@ -380,8 +387,8 @@ field_fwd_kernel(const FwdArgs a) {
                 ptx::tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) {
-                    ptx::mbar_arrive(&bar_act[0]);
-                    if (save) ptx::mbar_arrive(&bar_st[4]);
+                    ptx::mbar_arrive(&bar_act[kSlotX]);
+                    if (save) ptx::mbar_arrive(&bar_st[kSlotX]);
                 }
             }
 
@@ -390,17 +397,11 @@ field_fwd_kernel(const FwdArgs a) {
             for (int g = 0; g < nl; ++g) {
                 const uint32_t par = acc_ev & 1u;
                 ++acc_ev;
-                const int b = g & 1;
-                uint8_t* hout = sH + b * 65536;
-                const uint32_t tacc = tlane + b * 256 + sub * 16;
+                const uint32_t tacc = tlane + (g & 1) * 256 + sub * 16;
                 const bool last = (g == nl - 1);
-                ptx::mbar_wait_sleepy(&bar_acc[0], par);
+                ptx::mbar_wait_sleepy(bar_acc, par);
                 ptx::tc_fence_after_sync();
-                if (tile == 0 && warp == kEpiWarp0 && lane == 0) trace_ev(a.trace, g * 16 + 10);          // acc half 0 seen
-                if (save) {                                 // the storer must have read this buffer's previous contents
-                    if (wcnt[b] > 0) ptx::mbar_wait_sleepy(&bar_done[b], (wcnt[b] - 1) & 1u);
-                    ++wcnt[b];
-                }
+                NWB_TRACE(tile == 0 && warp == kEpiWarp0 && lane == 0, g * 16 + 10);          // accumulator seen
                 float hacc[5] = {0, 0, 0, 0, 0};
                 // sign masks: per layer and row 8 x uint32, word w = columns 32w..32w+31, bit (31-j) = column 32w+j;
                 // this thread's 16 columns are the high (even sub) or low (odd sub) half of word 2q + sub/2
@@ -409,40 +410,50 @@ field_fwd_kernel(const FwdArgs a) {
                 const int nq = layer_quarters(g, transient);
 #pragma unroll 1
                 for (int q = 0; q < nq; ++q) {
-                    if (q == 2) { ptx::mbar_wait_sleepy(&bar_acc[1], par); ptx::tc_fence_after_sync(); }
                     const int c0 = q * 64 + sub * 16;       // this thread's 16 columns of quarter q
+                    const int slot = out_slot(g, q);
+                    uint8_t* blk = sH + slot * 16384;
+                    if (save) {                             // the storer must have read the slot's previous contents
+                        if ((seen >> slot) & 1u) {
+                            ptx::mbar_wait_sleepy(&bar_done[slot], (done_par >> slot) & 1u);
+                            done_par ^= 1u << slot;
+                        }
+                        seen |= 1u << slot;
+                    }
                     uint16_t* md = save ? mrow + 4 * q : nullptr;
                     if (g < 7) {
-                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, hout, row, c0, md);
+                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
                     } else if (g == 7) {
                         epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                                    hacc, hout, row, c0, md);
+                                                    hacc, blk, row, 2 * sub, md);
                     } else if (g == 8) {
-                        epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, hout, row, c0, md);
+                        epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
                     } else if (g == 9) {
                         // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, hout, row, c0, md);
-                        else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, hout, row, c0, md);
+                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md);
+                        else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md);
                     } else if (g < 12) {
-                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, hout, row, c0, md);
+                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
                     } else {
                         // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
                         epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                                    hacc, hout, row, c0, md);
+                                                    hacc, blk, row, 2 * sub, md);
                     }
                     ptx::fence_proxy_async_smem();
                     ptx::tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) {
-                        if (!last) ptx::mbar_arrive(&bar_act[q]);
-                        if (save) ptx::mbar_arrive(&bar_st[q]);
-                        if (tile == 0 && warp == kEpiWarp0) trace_ev(a.trace, g * 16 + 11 + q);          // quarter q handed over
+                        // the dir half of layer 9 (transient mode) and the last layer feed no MMA
+                        const bool feeds_mma = !last && !(g == 9 && transient && q < 2);
+                        if (feeds_mma) ptx::mbar_arrive(&bar_act[slot]);
+                        if (save) ptx::mbar_arrive(&bar_st[slot]);
+                        NWB_TRACE(tile == 0 && warp == kEpiWarp0, g * 16 + 11 + q);          // quarter q handed over
                     }
                 }
                 // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                 const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                 if (nh_heads > 0) {
-                    if (save && g == 7) ptx::mbar_wait_sleepy(&bar_done[2], tcount & 1u);    // the storer has read this tile's X
+                    if (save && g == 7) ptx::mbar_wait_sleepy(&bar_done[kSlotX], tcount & 1u);   // the storer has read this tile's X
                     if (sub > 0) {
                         for (int h = 0; h < nh_heads; ++h) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
                     }
