@@ -83,8 +83,8 @@ inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
 
 // saved-activation layout per tile (forward NWB_MLP_SAVE): bf16 tile images followed by ReLU sign masks
 //   [X: kx*16K][h1..h8: 8 x 64K][feat: 64K][dir|t0: 32K or 64K][t2,t4,t6: 3 x 32K][masks: 13 x 4K]
-// masks: per layer g, per row 8 x uint32; word w covers columns 32w..32w+31, bit (31-j) = 1 iff the
-// pre-activation of column 32w+j was negative (ReLU gate closed).
+// masks: per layer g, per row 16 x uint16 laid out [sub][quarter]: bit (15-j) of entry (sub, q) = 1 iff the
+// pre-activation of column 64q + 16sub + j was negative (ReLU gate closed).
 struct SaveLayout {
     int kx; bool transient;
     __host__ __device__ size_t x_off() const { return 0; }

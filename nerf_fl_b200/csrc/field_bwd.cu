@@ -230,10 +230,18 @@ field_dgrad_kernel(const BwdArgs a) {
                 // ReLU gates of layer g (prefetched before waiting for the accumulator)
                 uint32_t mw[8];
                 if (g != 8) {
+                    // forward layout: 16 x uint16 per row, entry (sub, q) at sub*4 + q, bit (15-j) = column 64q+16sub+j
                     const uint4* mp = reinterpret_cast<const uint4*>(save_tile + sl.mask_off(g, nl) + row * 32);
                     const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
-                    mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w;
-                    mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
+                    const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+                    for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31, bit (31-j) = column 32w+j
+                        const int q = w >> 1, s0 = (w & 1) * 2;
+                        const int ihi = s0 * 4 + q, ilo = (s0 + 1) * 4 + q;
+                        const uint32_t hi = (m[ihi >> 1] >> ((ihi & 1) * 16)) & 0xFFFFu;
+                        const uint32_t lo = (m[ilo >> 1] >> ((ilo & 1) * 16)) & 0xFFFFu;
+                        mw[w] = (hi << 16) | lo;
+                    }
                 }
                 if (g < nl - 1) {
                     ptx::mbar_wait(bar_acc, acc_ev & 1u);

@@ -71,11 +71,11 @@ __device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, %0;" :
 //   x = acc + bias[c] (+ rbias[c]);  optional head dot products (fp32, unrounded x, after ReLU);
 //   bf16 pack, ReLU on the packed pairs (rounding is monotonic and keeps the sign, so max(rn(x), 0) ==
 //   rn(max(x, 0))) -> chunks chunk0, chunk0+1 (16 B each) of this row in the K-block image blk.
-//   kSave: the sign bits of the 16 pre-activations go to *mask_dst, bit (15-j) = column j.
+//   kSave: the sign bits of the 16 pre-activations are returned in neg_out, bit (15-j) = column j.
 template <bool kRelu, int kHeads, bool kSave>
 __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restrict__ bias,
                                             const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
-                                            float* hacc, uint8_t* blk, int row, int chunk0, uint16_t* mask_dst) {
+                                            float* hacc, uint8_t* blk, int row, int chunk0, uint32_t& neg_out) {
     uint32_t v[16];
     ptx::tmem_ld16(taddr, v);
     float b[16];
@@ -104,7 +104,7 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
 #pragma unroll
         for (int j = 0; j < 8; ++j)
             neg |= (((pk[j] >> 15) & 1u) << (15 - 2 * j)) | ((pk[j] >> 31) << (14 - 2 * j));
-        *mask_dst = static_cast<uint16_t>(neg);
+        neg_out = neg;
     }
     if (kRelu) {
 #pragma unroll
@@ -403,10 +403,11 @@ field_fwd_kernel(const FwdArgs a) {
                 ptx::tc_fence_after_sync();
                 NWB_TRACE(tile == 0 && warp == kEpiWarp0 && lane == 0, g * 16 + 10);          // accumulator seen
                 float hacc[5] = {0, 0, 0, 0, 0};
-                // sign masks: per layer and row 8 x uint32, word w = columns 32w..32w+31, bit (31-j) = column 32w+j;
-                // this thread's 16 columns are the high (even sub) or low (odd sub) half of word 2q + sub/2
-                uint16_t* mrow = save ? reinterpret_cast<uint16_t*>(save_tile + sl.mask_off(g, nl)) + row * 16 + (sub >> 1) * 2 + (1 - (sub & 1))
-                                      : nullptr;
+                // sign masks: per layer and row 16 x uint16 laid out [sub][quarter]; bit (15-j) of entry (sub, q) =
+                // sign of the pre-activation of column 64q + 16sub + j.  A thread owns the four entries of its sub
+                // and writes them as ONE 8-byte store after the quarter loop (a global store ahead of the per-
+                // quarter proxy fence would stall the handoff).
+                unsigned long long mbits = 0ull;
                 const int nq = layer_quarters(g, transient);
 #pragma unroll 1
                 for (int q = 0; q < nq; ++q) {
@@ -420,7 +421,7 @@ field_fwd_kernel(const FwdArgs a) {
                         }
                         seen |= 1u << slot;
                     }
-                    uint16_t* md = save ? mrow + 4 * q : nullptr;
+                    uint32_t md = 0;
                     if (g < 7) {
                         epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
                     } else if (g == 7) {
@@ -439,6 +440,7 @@ field_fwd_kernel(const FwdArgs a) {
                         epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
                                                     hacc, blk, row, 2 * sub, md);
                     }
+                    if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
                     ptx::fence_proxy_async_smem();
                     ptx::tc_fence_before_sync();
                     __syncwarp();
@@ -450,6 +452,8 @@ field_fwd_kernel(const FwdArgs a) {
                         NWB_TRACE(tile == 0 && warp == kEpiWarp0, g * 16 + 11 + q);          // quarter q handed over
                     }
                 }
+                if (save && g != 8)
+                    *reinterpret_cast<unsigned long long*>(save_tile + sl.mask_off(g, nl) + row * 32 + sub * 8) = mbits;
                 // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                 const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                 if (nh_heads > 0) {
