@@ -26,7 +26,7 @@
 
 namespace nwb {
 
-constexpr int kMmaWarps = 2;                  // MMA-issuing warps, each owns 1/kMmaWarps of a layer's output columns
+constexpr int kMmaWarps = 1;                  // MMA-issuing warps, each owns 1/kMmaWarps of a layer's output columns
 constexpr int kStoreWarp = 1 + kMmaWarps;
 constexpr int kEpiWarp0 = 2 + kMmaWarps;      // first epilogue warp
 constexpr int kEpiWarps = 16;
@@ -245,6 +245,11 @@ field_fwd_kernel(const FwdArgs a) {
             const uint32_t acc_a = ptx::smem_u32(bar_acc), act_a = ptx::smem_u32(bar_act);
             uint32_t s = 0, ph = 0;                          // ring stage and its phase
             uint32_t act_par = 0;                            // bit i = parity of the next phase of bar_act[i]
+            // tcgen05.mma issue is asynchronous but the queue behind it is shallow, and the waits + fence that open
+            // a K-block cost a few hundred cycles on one thread (tools/probe_umma.py).  So the waits for K-block
+            // kb+1 of the SAME layer are taken between the 2nd and 3rd MMA of K-block kb: two queued MMAs keep the
+            // tensor pipe busy meanwhile.  (Never across a layer boundary: the next layer's first K-block is
+            // produced by an epilogue that itself waits for this layer's last MMAs.)
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 int isl = 0;                                 // slot of the next activation K-block (round-robin, per tile)
                 for (int g = 0; g < nl; ++g) {
@@ -255,30 +260,43 @@ field_fwd_kernel(const FwdArgs a) {
                     const uint32_t dcol = tmem + (g & 1) * 256 + mw * ncols;
                     const uint32_t wrow_lo = (mw * ncols * 128) >> 4;                    // this warp's rows of a weight stage
                     if (g == 10) { isl += 2; if (isl >= kHSlots) isl -= kHSlots; }       // layer 9's dir quarters feed no MMA
-                    for (int kb = 0; kb < KB; ++kb) {
+                    uint32_t a_lo = 0, b_lo = 0, empty_cur = 0;
+                    // opens K-block kb: waits for its activation quarter and its weight stage, returns the descriptors
+                    auto open_kb = [&](int kb, uint32_t& a_out, uint32_t& b_out, uint32_t& empty_out) {
                         const bool is_x = (g == 0) || (g == 4 && kb == 0);
                         const int sl = is_x ? kSlotX : isl;
-                        const uint32_t a_lo = is_x ? x_lo : h_lo + isl * 1024;           // 16 KB >> 4
+                        a_out = is_x ? x_lo : h_lo + isl * 1024;                          // 16 KB >> 4
                         if (!is_x && ++isl == kHSlots) isl = 0;
                         if (!(g == 4 && kb == 0)) {                                       // X was awaited by layer 0
                             ptx::mbar_wait_a(act_a + 8 * sl, (act_par >> sl) & 1u);
                             act_par ^= 1u << sl;
                         }
-                        NWB_TRACE(tile == 0 && lane == 0 && mw == 0, g * 16 + kb);        // operand ready, about to issue
                         ptx::mbar_wait_a(full_a + 8 * s, ph);
                         ptx::tc_fence_after_sync();
-                        if (ptx::elect_one()) {
-                            const uint32_t b_lo = w_lo + s * (kStageBytes >> 4) + wrow_lo;
+                        b_out = w_lo + s * (kStageBytes >> 4) + wrow_lo;
+                        empty_out = empty_a + 8 * s;
+                        if (++s == kNumStages) { s = 0; ph ^= 1u; }
+                    };
+                    open_kb(0, a_lo, b_lo, empty_cur);
+                    NWB_TRACE(tile == 0 && lane == 0 && mw == 0, g * 16);                 // first operand ready
+                    for (int kb = 0; kb < KB; ++kb) {
+                        const bool issuer = ptx::elect_one();
+                        if (issuer) {
                             ptx::umma_bf16_lo(dcol, a_lo, b_lo, idesc, kb != 0);
                             ptx::umma_bf16_lo(dcol, a_lo + 2, b_lo + 2, idesc, 1);
+                        }
+                        __syncwarp();
+                        uint32_t a_nx = 0, b_nx = 0, empty_nx = 0;
+                        if (kb + 1 < KB) open_kb(kb + 1, a_nx, b_nx, empty_nx);
+                        if (issuer) {
                             ptx::umma_bf16_lo(dcol, a_lo + 4, b_lo + 4, idesc, 1);
                             ptx::umma_bf16_lo(dcol, a_lo + 6, b_lo + 6, idesc, 1);
-                            ptx::umma_commit_a(empty_a + 8 * s);
+                            ptx::umma_commit_a(empty_cur);
                             if (kb == KB - 1) ptx::umma_commit_a(acc_a);                 // this warp's columns of the layer are complete
                         }
                         __syncwarp();
-                        if (++s == kNumStages) { s = 0; ph ^= 1u; }
                         NWB_TRACE(tile == 0 && lane == 0 && mw == 0, g * 16 + 5 + kb);    // issued
+                        a_lo = a_nx; b_lo = b_nx; empty_cur = empty_nx;
                     }
                 }
             }
