@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=BATCH, help="rays per rank per step (train)")
     ap.add_argument("--samples", type=int, default=N_SAMPLES, help="coarse samples (= fine importance samples)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch the training step eagerly instead of replaying its CUDA graph")
     return ap.parse_args()
 
 
@@ -259,6 +260,7 @@ def workload_config(args, n_rays_step=None):
                 f"ray-sharded across ranks, rgb+depth gathered")
     cfg = {"workload": name, "rays_per_step_per_rank": n_rays_step if n_rays_step is not None else args.batch,
            "n_samples": ns, "n_importance": ns,
+           "launch": "eager" if (args.no_graph or args.workload != "train") else "CUDA graph replay of the whole iteration",
            "l2": f"{N_ROTATE} distinct resident ray batches rotate; per-step working set (saved activations + dZ workspace, "
                  f"~2 GB at batch 1024) exceeds the 126 MB L2"}
     return cfg
@@ -349,14 +351,14 @@ def run_product(args):
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
 
     if args.workload == "train":
+        from nerf_fl_b200.train_step import TrainStep
         state = FlatTrainState(list(models.values()) + [emb["a"], emb["t"]], lr=5e-4)
-
-        def step(rays, ts, tgt):
-            out = render_rays(models, emb, rays, ts, ns, False, 1.0, 0.0, ni, 32768, True)
-            loss = sum(lossfn(out, tgt).values())
-            loss.backward()
-            state.step()                    # NCCL all-reduce of the flat gradient buffer + Adam + zero_grad
-            return loss
+        # the public training-step API: forward, NerfWLoss, backward, NCCL all-reduce of the flat gradient buffer,
+        # Adam, zero_grad -- captured once and replayed as a CUDA graph unless --no-graph
+        step = TrainStep(models, emb, state, lossfn, batch=args.batch, N_samples=ns, N_importance=ni, perturb=1.0,
+                         noise_std=0.0, white_back=True, graph=not args.no_graph)
+        eager_step = TrainStep(models, emb, state, lossfn, batch=args.batch, N_samples=ns, N_importance=ni, perturb=1.0,
+                               noise_std=0.0, white_back=True, graph=False)
         rays_per_step = args.batch
         h2d = sum(t.numel() * t.element_size() for t in hb[0])
         d2h = 4
@@ -382,6 +384,7 @@ def run_product(args):
         rays_per_step = (hi - lo)
         h2d = img.numel() * 4 + img_ts.numel() * 8
         d2h = H * W * 16
+        eager_step = step
 
     def sync_all():
         if world > 1:
@@ -424,6 +427,9 @@ def run_product(args):
     l0 = K.launch_count
     ms, wall = timed(args.steps, False)
     launches = K.launch_count - l0
+    graphed = args.workload == "train" and getattr(step, "graph", None) is not None
+    if graphed:                                  # replays run no Python: count what the captured iteration launched
+        launches = step.launches_per_step * args.steps
     clocks = sampler.stop() if rank == 0 else None
     total_rays = rays_per_step * args.steps
     if world > 1:
@@ -440,7 +446,7 @@ def run_product(args):
     # ---- per-kernel device times (CUDA events around every C-ABI call, separate pass of the same steps) --
     K.timing_start()
     for i in range(min(args.steps, 10)):
-        step(*resident[i % len(resident)])
+        eager_step(*resident[i % len(resident)])
     rec = K.timing_stop()
     check_errors()
     table = kernel_table(rec, ns, ni, args.workload)
@@ -451,7 +457,7 @@ def run_product(args):
     roofline = {"kernel": f"{dom['kernel']} (mode {dom['mode']})", "bound": dom["bound"], "achieved": dom["achieved"],
                 "peak": dom["peak"], "unit": dom["unit"], "frac": dom["frac"], "traffic": None,
                 "work_per_launch": dom["work"], "avg_launch_ms": dom["avg_ms"], "peak_source": peaks()["source"] + " (sustained)",
-                "timing": "CUDA events around each C-ABI call on the launching stream, separate pass of the same steps"}
+                "timing": "CUDA events around each C-ABI call on the launching stream, separate eager pass of the same steps"}
     fl = (train_flops_per_ray if args.workload == "train" else infer_flops_per_ray)(ns, ni)
     step_roofline = {"flops_per_ray": fl, "achieved_tflops_per_gpu": round(value / world * fl / 1e12, 2),
                      "frac_of_bf16_sustained": round(value / world * fl / 1e12 / peaks()["bf16_sustained"], 4),

@@ -238,6 +238,13 @@ int nwb_ray_consts_bwd(const nwb_field_desc* d, const nwb_field_params* p, const
 int nwb_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                   float eps, float weight_decay, int step, float grad_scale, int zero_grad, void* stream);
 
+/* same update with the step state resident on the device, so that a captured CUDA graph of the training step
+ * can be replayed: state = 16 B {int32 step; float lr; float lr/(1-beta1^step); float 1/sqrt(1-beta2^step)};
+ * the call first advances step (and refreshes the two derived scalars), then applies the update.  The host
+ * writes lr (schedulers, utils/__init__.py:44-61) and may zero step. */
+int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                      float weight_decay, float* state, float grad_scale, int zero_grad, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T
  * from bf16 tile images, through the same smem layouts / descriptors the field kernels use.

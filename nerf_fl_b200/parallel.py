@@ -89,9 +89,25 @@ class FlatTrainState:
             p.data = self.flat_p[o:o + n].view(p.shape)
             p.grad = self.flat_g[o:o + n].view(p.shape)
             p._nwb_direct_grad = True
-        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.betas, self.eps, self.weight_decay = betas, eps, weight_decay
         self.step_count = 0
+        # step state of the CUDA optimizer kernel lives on the device ({int32 step, lr, lr/bc1, 1/sqrt(bc2)}), so a
+        # captured CUDA graph of the whole iteration can be replayed (nwb_adam_step_dev)
+        self.hyper = torch.zeros(4, dtype=torch.float32, device=dev) if dev.type == "cuda" else None
+        self._lr = float(lr)
+        self.lr = lr
         self.n_params = sum(p.numel() for p in params)
+
+    @property
+    def lr(self) -> float:
+        return self._lr
+
+    @lr.setter
+    def lr(self, value: float) -> None:
+        """Schedulers (utils/__init__.py:44-61) set this between steps; stream-ordered device write."""
+        self._lr = float(value)
+        if self.hyper is not None:
+            self.hyper[1:2].fill_(self._lr)
 
     # ---- collective -------------------------------------------------------------------------
     def allreduce_grads(self, group=None):
@@ -115,11 +131,12 @@ class FlatTrainState:
             from . import _lib as L
             from . import kernels as K
             K.launch_count += 1
-            fn = L.bind("nwb_adam_step", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 5 + [C.c_int, C.c_float, C.c_int,
-                                                                                           C.c_void_p])
+            K.launch_count += 1              # tick + update kernels
+            fn = L.bind("nwb_adam_step_dev", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 4 + [C.c_void_p, C.c_float, C.c_int,
+                                                                                               C.c_void_p])
             L.check(fn(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
-                       self.exp_avg_sq.data_ptr(), self.numel, self.lr, b1, b2, self.eps, self.weight_decay,
-                       self.step_count, 1.0 / world, int(zero_grad), L.stream_ptr(self.flat_p.device)), "nwb_adam_step")
+                       self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay, self.hyper.data_ptr(),
+                       1.0 / world, int(zero_grad), L.stream_ptr(self.flat_p.device)), "nwb_adam_step_dev")
         else:
             g = self.flat_g / world + self.weight_decay * self.flat_p
             self.exp_avg.mul_(b1).add_(g, alpha=1 - b1)

@@ -1,0 +1,100 @@
+"""One training iteration of the reference's ``NeRFSystem.training_step`` (train.py:158-174) plus what
+Lightning runs around it -- ``loss.backward()``, the DDP gradient all-reduce and ``Adam.step`` -- as ONE
+replayable CUDA graph.
+
+At the reference's batch size (1024 rays) an iteration is ~60 kernels of 2-400 us each; launched one by
+one from Python the host cannot keep the GPU fed.  ``TrainStep`` runs the iteration eagerly a few times,
+captures it (``torch.cuda.graph``) on static input buffers and replays it afterwards: no Python, no
+allocator, no launch gaps in the steady state.  Everything inside is stream-ordered device work, so
+the capture needs nothing special: random draws come from torch's graph-safe Philox generator, the
+optimizer's step counter lives on the device (``nwb_adam_step_dev``), the bf16 operand caches are
+refreshed by the captured pack kernels at the start of every replay.
+"""
+from __future__ import annotations
+
+import torch
+
+from .parallel import FlatTrainState, dist_info
+from .rendering import render_rays
+
+__all__ = ["TrainStep"]
+
+
+class TrainStep:
+    """``step(rays, ts, rgbs) -> loss``: render_rays forward, loss, backward, all-reduce, Adam.
+
+    ``models`` / ``embeddings`` as for ``render_rays``; ``state`` a ``FlatTrainState`` over them;
+    ``loss_fn(results, rgbs) -> dict`` (``NerfWLoss``).  ``batch`` fixes the ray count of the captured
+    graph; other batch sizes (or ``graph=False``) run eagerly.  The returned loss is a 0-dim device
+    tensor (a static buffer in graph mode: read it before the next call)."""
+
+    def __init__(self, models, embeddings, state: FlatTrainState, loss_fn, *, batch: int, N_samples=64,
+                 N_importance=64, use_disp=False, perturb=1.0, noise_std=0.0, white_back=True, chunk=32 * 1024,
+                 graph=True, warmup=3):
+        self.models, self.embeddings, self.state, self.loss_fn = models, embeddings, state, loss_fn
+        self.batch = int(batch)
+        self.args = (int(N_samples), bool(use_disp), float(perturb), float(noise_std), int(N_importance), int(chunk),
+                     bool(white_back))
+        self.dev = state.flat_p.device
+        self.graph = None
+        self.launches_per_step = None
+        self._warmup = warmup
+        self._want_graph = bool(graph) and self.dev.type == "cuda"
+        self.terms = None            # loss terms of the last call (dict of 0-dim tensors)
+
+    # ---- the iteration itself ---------------------------------------------------------------------
+    def _iteration(self, rays, ts, rgbs, graph_safe_rng: bool):
+        Ns, use_disp, perturb, noise_std, Ni, chunk, white_back = self.args
+        kw = {}
+        if graph_safe_rng:
+            n = rays.shape[0]
+            rng = {}
+            if perturb > 0:
+                rng["perturb_rand"] = torch.rand(n, Ns, device=rays.device)
+                if Ni > 0:
+                    rng["u"] = torch.rand(n, Ni, device=rays.device)
+            kw["rng"] = rng
+        res = render_rays(self.models, self.embeddings, rays, ts, Ns, use_disp, perturb, noise_std, Ni, chunk,
+                          white_back, **kw)
+        terms = self.loss_fn(res, rgbs)
+        loss = sum(terms.values())
+        loss.backward()
+        self.state.step()
+        return loss.detach(), {k: v.detach() for k, v in terms.items()}
+
+    def _capture(self, rays, ts, rgbs):
+        from . import kernels as K
+        self.s_rays = rays.clone()
+        self.s_ts = ts.clone()
+        self.s_rgbs = rgbs.clone()
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            for _ in range(self._warmup):
+                self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True)
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        for m in self.models.values():
+            m._nwb_dirty = True                        # the captured iteration must contain the operand-cache refresh
+        g = torch.cuda.CUDAGraph()
+        l0 = K.launch_count
+        with torch.cuda.graph(g):
+            self.s_loss, self.s_terms = self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True)
+        self.launches_per_step = K.launch_count - l0
+        self.graph = g
+
+    def __call__(self, rays, ts, rgbs):
+        if self._want_graph and rays.shape[0] == self.batch:
+            if self.graph is None:
+                self._capture(rays, ts, rgbs)          # warm-up iterations + capture (the capture itself does not run)
+            self.s_rays.copy_(rays, non_blocking=True)
+            self.s_ts.copy_(ts, non_blocking=True)
+            self.s_rgbs.copy_(rgbs, non_blocking=True)
+            self.graph.replay()
+            self.state.step_count += 1
+            for m in self.models.values():
+                m._nwb_dirty = True                    # parameters moved: eager callers must repack
+            self.terms = self.s_terms
+            return self.s_loss
+        loss, self.terms = self._iteration(rays, ts, rgbs, False)
+        return loss
