@@ -15,10 +15,12 @@
 namespace nwb {
 
 constexpr int kBwdThreads = 192;
-constexpr int kBStageBytes = 16384;
-constexpr int kBNumStages = 2;
-constexpr int kBOffP = 0;                       // 16 KB  dpre block image
-constexpr int kBOffD = 16384;                   // 64 KB  dZ image (A operand)
+constexpr int kBStageBytes = 16384;                // 4 k-blocks x 32 n-rows x 128 B
+constexpr int kBChunkBytes = 4096;                 // one k-block's 32 rows
+constexpr int kBNumStages = 3;                  // the kernel is bound by the latency of the weight stream: depth matters
+constexpr int kBOffD = 0;                       // 64 KB  dZ image (A operand)
+constexpr int kBOffP = kBOffD;                  // 16 KB  dpre block image: aliases the dZ image (stored and read out
+                                                //        before layer nl-1 writes its dZ; same bulk_wait_read guard)
 constexpr int kBOffW = kBOffD + 65536;
 constexpr int kBOffBar = kBOffW + kBNumStages * kBStageBytes;
 constexpr int kBwdSmem = kBOffBar + 256;
@@ -38,7 +40,14 @@ struct BwdArgs {
     long long n_points;
     int n_tiles;
     uint32_t mode;
+    long long* trace;        // debug (-DNWB_BWD_TRACE): block 0 / first tile clock64 stamps, else unused
 };
+
+#ifdef NWB_BWD_TRACE
+#define NWB_BTRACE(cond, slot) do { if ((cond) && a.trace != nullptr && blockIdx.x == 0) a.trace[slot] = clock64(); } while (0)
+#else
+#define NWB_BTRACE(cond, slot) do { } while (0)
+#endif
 
 // one 32-column slice of dZ for this thread's row
 //   kAcc: take dA from TMEM;  kHeads > 0: add sum_h dp[h] * hw[h][c];  negmask bit (31-j): gate closed
@@ -116,21 +125,24 @@ field_dgrad_kernel(const BwdArgs a) {
     if (warp == 0) {
         // ============================ weight producer ============================================
         if (lane == 0) {
+            // one stage = a 32-row chunk of the contraction index n across ALL output k-blocks of the layer:
+            // KBO pieces of 32 rows x 128 B (4 KB, contiguous in the slab image), laid [kbo][32 rows] in the stage,
+            // so one tcgen05.mma covers the layer's whole output width (N = 64*KBO) and the dZ operand is read once
+            // per K-step instead of once per 64-column output block
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 for (int g = nl - 1; g >= 1; --g) {
                     const uint8_t* wsrc = a.packed + s_woff[g];
-                    const int KBO = (g >= 10) ? 2 : 4, NH = fs.layer_n(g, a.mode) >> 7, PN = fs.packed_n(g);
+                    const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> 5, PN = fs.packed_n(g);
                     const int kshift = (g == 4) ? fs.kx : 0;       // skip the encoded-xyz slab: no d/dx needed
-                    for (int kbo = 0; kbo < KBO; ++kbo) {
-                        for (int nh = 0; nh < NH; ++nh, ++it) {
-                            const uint32_t s = it % kBNumStages;
-                            ptx::mbar_wait(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
-                            ptx::mbar_arrive_expect_tx(&bar_full[s], kBStageBytes);
-                            ptx::bulk_g2s(sW + s * kBStageBytes,
-                                          wsrc + static_cast<size_t>(kbo + kshift) * PN * 128 + nh * kBStageBytes, kBStageBytes,
+                    for (int c = 0; c < NC; ++c, ++it) {
+                        const uint32_t s = it % kBNumStages;
+                        ptx::mbar_wait(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
+                        ptx::mbar_arrive_expect_tx(&bar_full[s], static_cast<uint32_t>(KBO) * kBChunkBytes);
+                        for (int kbo = 0; kbo < KBO; ++kbo)
+                            ptx::bulk_g2s(sW + s * kBStageBytes + kbo * kBChunkBytes,
+                                          wsrc + static_cast<size_t>(kbo + kshift) * PN * 128 + c * kBChunkBytes, kBChunkBytes,
                                           &bar_full[s]);
-                        }
                     }
                 }
             }
@@ -139,8 +151,8 @@ field_dgrad_kernel(const BwdArgs a) {
     } else if (warp == 1) {
         // ============================ MMA issuer =================================================
         if (lane == 0) {
-            // D(128 x 64) += dZ(128 x 16, K-major) . W(16 n-rows x 64 k-cols, MN-major)
-            constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, 64, false, true);
+            // D(128 x 64*KBO) += dZ(128 x 16 n, K-major) . W(16 n-rows x 64*KBO k-cols, MN-major: 8-row groups 1 KB
+            // apart, 64-column k-blocks kBChunkBytes apart inside the stage)
             const uint32_t da = ptx::smem_u32(sD), wa = ptx::smem_u32(sW);
             uint32_t it = 0, ev = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
@@ -148,23 +160,24 @@ field_dgrad_kernel(const BwdArgs a) {
                     ptx::mbar_wait(bar_act, ev & 1u);
                     ++ev;
                     ptx::tc_fence_after_sync();
-                    const int KBO = (g >= 10) ? 2 : 4, NH = fs.layer_n(g, a.mode) >> 7;
+                    NWB_BTRACE(tile == static_cast<int>(blockIdx.x), g * 8 + 0);      // dZ_g seen by the MMA thread
+                    const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> 5;
+                    const uint32_t idesc = ptx::umma_idesc_bf16(128, 64 * KBO, false, true);
                     const uint32_t dcol = (g == 10) ? 128u : 0u;
-                    for (int kbo = 0; kbo < KBO; ++kbo) {
-                        for (int nh = 0; nh < NH; ++nh, ++it) {
-                            const uint32_t s = it % kBNumStages;
-                            ptx::mbar_wait(&bar_full[s], (it / kBNumStages) & 1u);
-                            ptx::tc_fence_after_sync();
-                            const uint32_t wb = wa + s * kBStageBytes;
+                    for (int c = 0; c < NC; ++c, ++it) {
+                        const uint32_t s = it % kBNumStages;
+                        ptx::mbar_wait(&bar_full[s], (it / kBNumStages) & 1u);
+                        ptx::tc_fence_after_sync();
+                        const uint32_t wb = wa + s * kBStageBytes;
+                        const uint32_t ab = da + (c >> 1) * 16384 + (c & 1) * 64;
 #pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                ptx::umma_bf16(tmem + dcol + kbo * 64,
-                                               ptx::umma_desc_sw128(da + (2 * nh + (j >> 2)) * 16384 + (j & 3) * 32, 16, 1024),
-                                               ptx::umma_desc_sw128(wb + j * 2048, 16384, 1024), idesc, (nh | j) != 0);
-                            ptx::umma_commit(&bar_empty[s]);
-                        }
+                        for (int j = 0; j < 2; ++j)
+                            ptx::umma_bf16(tmem + dcol, ptx::umma_desc_sw128(ab + j * 32, 16, 1024),
+                                           ptx::umma_desc_sw128(wb + j * 2048, kBChunkBytes, 1024), idesc, (c | j) != 0);
+                        ptx::umma_commit(&bar_empty[s]);
                     }
                     ptx::umma_commit(bar_acc);
+                    NWB_BTRACE(tile == static_cast<int>(blockIdx.x), g * 8 + 1);      // all MMAs of layer g issued
                 }
             }
         }
@@ -248,8 +261,10 @@ field_dgrad_kernel(const BwdArgs a) {
                     ++acc_ev;
                     ptx::tc_fence_after_sync();
                 }
+                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 2);    // accumulator seen
                 if (leader) ptx::bulk_wait_read<0>();       // the previous image's bulk store has read sD
                 epi_bar();
+                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 3);    // sD free
                 uint32_t dz_bytes = 65536;
                 if (g >= 10) {
                     dz_bytes = 32768;
@@ -310,8 +325,10 @@ field_dgrad_kernel(const BwdArgs a) {
                     for (int c0 = 0; c0 < 256; c0 += 32)
                         bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
                 }
+                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 4);    // leader's slices written
                 ptx::fence_proxy_async_smem();
                 epi_bar();
+                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 5);    // all slices written
                 if (leader) { ptx::bulk_s2g(dz_tile + dl.dz_off(g), sD, dz_bytes); ptx::bulk_commit(); }
                 if (g >= 1) {
                     ptx::tc_fence_before_sync();
@@ -335,6 +352,10 @@ field_dgrad_kernel(const BwdArgs a) {
 }  // namespace nwb
 
 using namespace nwb;
+
+static long long* g_bwd_trace = nullptr;
+// debug hook (tools/trace_bwd.py): device buffer of >= 8*13 int64 that block 0 fills with clock64() stamps
+extern "C" void nwb_debug_set_bwd_trace(void* buf) { g_bwd_trace = static_cast<long long*>(buf); }
 
 int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* grads, const uint8_t* saved, size_t save_tile_bytes,
                      const uint8_t* dz, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st);
@@ -385,7 +406,7 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
     a.d_ray_bias = d_ray_bias;
     a.g_head_b[0] = grads->sigma_b; a.g_head_b[1] = grads->rgb_b; a.g_head_b[2] = grads->tsigma_b;
     a.g_head_b[3] = grads->trgb_b; a.g_head_b[4] = grads->tbeta_b;
-    a.S = S; a.mode = mode;
+    a.S = S; a.mode = mode; a.trace = g_bwd_trace;
 
     if (run_dgrad) {
         static bool configured = false;

@@ -23,6 +23,7 @@
 // Activations never leave the SM unless NWB_MLP_SAVE asks for them (bf16 tile images for backward).
 #include "field_dev.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 namespace nwb {
 
@@ -569,7 +570,8 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
         configured = true;
     }
-    const int grid = std::min(a.n_tiles, kNumSMs);
+    int grid = std::min(a.n_tiles, kNumSMs);
+    if (const char* e = getenv("NWB_DEBUG_GRID")) grid = std::max(1, std::min(grid, atoi(e)));   // bottleneck experiments only
     if (mode & NWB_MLP_SAVE) field_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
     else field_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
     NWB_LAUNCH_CHECK();
