@@ -10,13 +10,52 @@ namespace nwb {
 
 constexpr int kCompWarps = 4;
 
-__device__ __forceinline__ void stage_rows(float* slab, const float* __restrict__ src, int nfl, int lane) {
-    // nfl floats, contiguous; float4 path when the source is 16B aligned
-    if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (nfl & 3) == 0) {
+// Software prefetch of one 32-sample chunk: the chunk's AoS rows (<= 32*C floats, <= 3 float4 per lane) and this
+// lane's z / z_next are pulled into REGISTERS one chunk ahead of their use, so every warp keeps two chunks of HBM
+// traffic in flight instead of one (the kernels are latency-bound, not instruction-bound: ncu r01b, 37 % of HBM peak
+// with a single chunk in flight).
+template <int C>
+struct ChunkRegs {
+    static constexpr int kV4 = (32 * C / 4 + 31) / 32;     // float4 per lane (C=9: 3, C=4: 1, C=1: 1)
+    float4 v[kV4];
+    float s[(C == 1) ? 1 : 2];                             // unaligned fallback keeps a scalar tail only for tiny C
+    float zi, zn;
+    bool vec;
+};
+template <int C>
+__device__ __forceinline__ void chunk_load(ChunkRegs<C>& r, const float* __restrict__ raw, const float* __restrict__ z,
+                                           int64_t row, int base, int S, int lane) {
+    const int cnt = min(32, S - base);
+    const float* src = raw + (row + base) * C;
+    const int nfl = cnt * C;
+    r.vec = (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (nfl & 3) == 0;
+    if (r.vec) {
         const float4* s4 = reinterpret_cast<const float4*>(src);
+#pragma unroll
+        for (int k = 0; k < ChunkRegs<C>::kV4; ++k) {
+            const int i = lane + 32 * k;
+            if (i < (nfl >> 2)) r.v[k] = __ldg(s4 + i);
+        }
+    }
+    const int i = base + lane;
+    r.zi = (lane < cnt) ? __ldg(z + row + i) : 0.0f;
+    r.zn = (lane < cnt && i + 1 < S) ? __ldg(z + row + i + 1) : 0.0f;
+}
+// registers -> the warp's shared-memory slab (falls back to a direct staged copy for unaligned / ragged chunks)
+template <int C>
+__device__ __forceinline__ void chunk_commit(const ChunkRegs<C>& r, float* slab, const float* __restrict__ raw,
+                                             int64_t row, int base, int S, int lane) {
+    const int cnt = min(32, S - base);
+    const int nfl = cnt * C;
+    if (r.vec) {
         float4* d4 = reinterpret_cast<float4*>(slab);
-        for (int i = lane; i < (nfl >> 2); i += 32) d4[i] = __ldg(s4 + i);
+#pragma unroll
+        for (int k = 0; k < ChunkRegs<C>::kV4; ++k) {
+            const int i = lane + 32 * k;
+            if (i < (nfl >> 2)) d4[i] = r.v[k];
+        }
     } else {
+        const float* src = raw + (row + base) * C;
         for (int i = lane; i < nfl; i += 32) slab[i] = __ldg(src + i);
     }
     __syncwarp();
@@ -49,21 +88,30 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     const bool white = flags & NWB_COMP_WHITE_BACK;
     const bool test_time = flags & NWB_COMP_TEST_TIME;
     const bool weights_only = (C == 1) || (test_time && (flags & NWB_COMP_COARSE));
+    ChunkRegs<C> cur;
+    bool primed = false;
 
     for (int ray = blockIdx.x * kCompWarps + warp; ray < n_rays; ray += gridDim.x * kCompWarps) {
         const int64_t row = static_cast<int64_t>(ray) * S;
         float cT = 1.0f, cTs = 1.0f, cTt = 1.0f;
         float opac = 0, depth = 0, beta = 0, sr = 0, sg = 0, sb = 0, tr = 0, tg = 0, tb = 0;
         float xsr = 0, xsg = 0, xsb = 0, xsd = 0, xtr = 0, xtg = 0, xtb = 0, xtd = 0;
+        if (!primed) { chunk_load<C>(cur, raw, z, row, 0, S, lane); primed = true; }
         for (int base = 0; base < S; base += 32) {
             const int cnt = min(32, S - base);
-            stage_rows(slab, raw + (row + base) * C, cnt * C, lane);
+            chunk_commit<C>(cur, slab, raw, row, base, S, lane);
+            const float zi_r = cur.zi, zn_r = cur.zn;
+            {   // next chunk of this ray, else the first chunk of this warp's next ray
+                const int nray = ray + gridDim.x * kCompWarps;
+                if (base + 32 < S) chunk_load<C>(cur, raw, z, row, base + 32, S, lane);
+                else if (nray < n_rays) chunk_load<C>(cur, raw, z, static_cast<int64_t>(nray) * S, 0, S, lane);
+            }
             const int i = base + lane;
             const bool live = lane < cnt;
             float zi = 0, delta = 0, sig_s = 0, sig_t = 0, cr = 0, cg = 0, cb = 0, qr = 0, qg = 0, qb = 0, bt = 0;
             if (live) {
-                zi = __ldg(z + row + i);
-                delta = (i + 1 < S) ? __fsub_rn(__ldg(z + row + i + 1), zi) : 1e2f;
+                zi = zi_r;
+                delta = (i + 1 < S) ? __fsub_rn(zn_r, zi) : 1e2f;
                 const float* v = slab + lane * C;
                 if (C == 1) {
                     sig_s = v[0];
@@ -179,21 +227,35 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         }
         const float g_bg = white ? -(Gs[0] + Gs[1] + Gs[2]) : 0.0f;   // d(1 - sum w)/dw
 
-        // pass 1: transmittance
+        // pass 1: transmittance (this lane's loads for chunk k+1 are issued before chunk k's exp + scan)
+        const int last_base = ((S - 1) / 32) * 32;
+        ChunkRegs<C> cur;
+        chunk_load<C>(cur, raw, z, row, last_base, S, lane);       // pass 2 starts at the ray's last chunk
         float cT = 1.0f;
+        float p_zi = 0, p_zn = 0, p_s = 0, p_t = 0, p_n = 0;
+        auto p1_load = [&](int base) {
+            const int i = base + lane;
+            if (i < S) {
+                p_zi = __ldg(z + row + i);
+                p_zn = (i + 1 < S) ? __ldg(z + row + i + 1) : 0.0f;
+                p_s = (C == 1) ? __ldg(raw + row + i) : __ldg(raw + (row + i) * C + 3);
+                if (transient) p_t = __ldg(raw + (row + i) * C + 7);
+                else if (noise != nullptr) p_n = __ldg(noise + row + i);
+            }
+        };
+        p1_load(0);
         for (int base = 0; base < S; base += 32) {
             const int i = base + lane;
             const bool live = i < S;
+            const float zi = p_zi, zn = p_zn, s0 = p_s, t0 = p_t, n0 = p_n;
+            if (base + 32 < S) p1_load(base + 32);
             float alpha = 0.0f;
             if (live) {
-                const float zi = __ldg(z + row + i);
-                const float delta = (i + 1 < S) ? __fsub_rn(__ldg(z + row + i + 1), zi) : 1e2f;
-                float s;
-                if (C == 1) s = __ldg(raw + row + i);
-                else s = __ldg(raw + (row + i) * C + 3);
-                if (transient) s = __fadd_rn(s, __ldg(raw + (row + i) * C + 7));
+                const float delta = (i + 1 < S) ? __fsub_rn(zn, zi) : 1e2f;
+                float s = s0;
+                if (transient) s = __fadd_rn(s, t0);
                 else {
-                    if (noise != nullptr) s = __fadd_rn(s, __fmul_rn(__ldg(noise + row + i), noise_std));
+                    if (noise != nullptr) s = __fadd_rn(s, __fmul_rn(n0, noise_std));
                     s = fmaxf(s, 0.0f);
                 }
                 alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, s)));
@@ -205,10 +267,11 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 
         // pass 2: reverse chunks, suffix sums of q
         float suffix = 0.0f;   // sum of q over all samples after the current chunk
-        const int last_base = ((S - 1) / 32) * 32;
         for (int base = last_base; base >= 0; base -= 32) {
             const int cnt = min(32, S - base);
-            stage_rows(slab, raw + (row + base) * C, cnt * C, lane);
+            chunk_commit<C>(cur, slab, raw, row, base, S, lane);
+            const float zi_r = cur.zi, zn_r = cur.zn;
+            if (base >= 32) chunk_load<C>(cur, raw, z, row, base - 32, S, lane);
             const int i = base + lane;
             const bool live = lane < cnt;
             float q = 0.0f, dsig_s = 0.0f, dsig_t = 0.0f, dcs[3] = {0, 0, 0}, dct[3] = {0, 0, 0}, dbeta = 0.0f;
@@ -216,8 +279,8 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
             bool pass_s = true;
             if (live) {
                 const float* v = slab + lane * C;
-                const float zi = __ldg(z + row + i);
-                delta = (i + 1 < S) ? __fsub_rn(__ldg(z + row + i + 1), zi) : 1e2f;
+                const float zi = zi_r;
+                delta = (i + 1 < S) ? __fsub_rn(zn_r, zi) : 1e2f;
                 T = Tbuf[i];
                 float Gw = g_op + g_dp * zi + g_bg + (g.d_weights ? __ldg(g.d_weights + row + i) : 0.0f);
                 if (transient) {

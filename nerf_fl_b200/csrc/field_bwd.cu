@@ -51,9 +51,12 @@ struct BwdArgs {
 
 // one 32-column slice of dZ for this thread's row
 //   kAcc: take dA from TMEM;  kHeads > 0: add sum_h dp[h] * hw[h][c];  negmask bit (31-j): gate closed
+//   Head weights arrive lane-distributed (lane l holds hw[h][c_out + l], one coalesced load per warp issued ahead of
+//   the accumulator wait) and are broadcast with shuffles: every thread of the warp needs the same 32 values, and a
+//   warp-uniform global load per value costs an L2 round trip each (shared memory is full, L1 is carved away).
 template <bool kAcc, int kHeads, bool kMask>
-__device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* __restrict__ hw, int hw_ld, const float* dp,
-                                          uint32_t negmask, uint8_t* sD, int row, int c_out) {
+__device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, const float* dp, uint32_t negmask,
+                                          uint8_t* sD, int row, int c_out) {
     float x[32];
     if (kAcc) {
         uint32_t v[32];
@@ -68,13 +71,9 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* __restric
     if (kHeads > 0) {
 #pragma unroll
         for (int h = 0; h < kHeads; ++h) {
-            const float d = dp[h];
+            const float d = dp[h], wl = hwl[h];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(hw + h * hw_ld) + q);
-                x[4 * q] = fmaf(d, t.x, x[4 * q]); x[4 * q + 1] = fmaf(d, t.y, x[4 * q + 1]);
-                x[4 * q + 2] = fmaf(d, t.z, x[4 * q + 2]); x[4 * q + 3] = fmaf(d, t.w, x[4 * q + 3]);
-            }
+            for (int j = 0; j < 32; ++j) x[j] = fmaf(d, __shfl_sync(0xffffffffu, wl, j), x[j]);
         }
     }
     if (kMask) {
@@ -256,6 +255,18 @@ field_dgrad_kernel(const BwdArgs a) {
                         mw[w] = (hi << 16) | lo;
                     }
                 }
+                // head weights of this layer's head term, lane-distributed: hwl[slice][head] = hw[head][32*slice + lane]
+                float hwl[20];
+                if (g == 12) {
+#pragma unroll
+                    for (int i = 0; i < 20; ++i) hwl[i] = __ldg(cst + ConstOff::tsigma_w + (i % 5) * 128 + (i / 5) * 32 + lane);
+                } else if (g == 9) {
+#pragma unroll
+                    for (int i = 0; i < 12; ++i) hwl[i] = __ldg(cst + ConstOff::rgb_w + (i % 3) * 128 + (i / 3) * 32 + lane);
+                } else if (g == 7) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) hwl[i] = __ldg(cst + ConstOff::sigma_w + i * 32 + lane);
+                }
                 if (g < nl - 1) {
                     ptx::mbar_wait(bar_acc, acc_ev & 1u);
                     ++acc_ev;
@@ -269,61 +280,37 @@ field_dgrad_kernel(const BwdArgs a) {
                 if (g >= 10) {
                     dz_bytes = 32768;
                     if (g == 12) {
-#pragma unroll 1
-                        for (int c0 = 0; c0 < 128; c0 += 32)
-                            bwd_slice<false, 5, true>(0, cst + ConstOff::tsigma_w + c0, 128, dp + 4, mw[c0 >> 5], sD, row, c0);
+#pragma unroll
+                        for (int sl4 = 0; sl4 < 4; ++sl4)
+                            bwd_slice<false, 5, true>(0, hwl + 5 * sl4, dp + 4, mw[sl4], sD, row, 32 * sl4);
                     } else {
 #pragma unroll 1
                         for (int c0 = 0; c0 < 128; c0 += 32)
-                            bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
+                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
                     }
                 } else if (g == 9) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 128; c0 += 32)
-                        bwd_slice<false, 3, true>(0, cst + ConstOff::rgb_w + c0, 128, dp + 1, mw[c0 >> 5], sD, row, c0);
+#pragma unroll
+                    for (int sl4 = 0; sl4 < 4; ++sl4)
+                        bwd_slice<false, 3, true>(0, hwl + 3 * sl4, dp + 1, mw[sl4], sD, row, 32 * sl4);
                     if (transient) {
 #pragma unroll 1
                         for (int c0 = 128; c0 < 256; c0 += 32)
-                            bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
+                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
                     } else {
                         dz_bytes = 32768;
-                    }
-                    // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples
-                    epi_bar();
-                    {
-                        const int ncols = transient ? 256 : 128;
-                        const int c = 2 * et;
-                        if (c < ncols) {
-                            const uint8_t* colp = sD + (c >> 6) * 16384 + (c & 7) * 2;
-                            const int chunk = (c & 63) >> 3;
-                            long long ray = p0 / a.S;
-                            int in_ray = static_cast<int>(p0 - ray * a.S);
-                            float s0 = 0.0f, s1 = 0.0f;
-                            const int nrow = static_cast<int>(min(static_cast<long long>(kTileM), a.n_points - p0));
-                            for (int r = 0; r < nrow; ++r) {
-                                const uint32_t w = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r, chunk));
-                                s0 += __uint_as_float(w << 16);
-                                s1 += __uint_as_float(w & 0xFFFF0000u);
-                                if (++in_ray == a.S || r == nrow - 1) {
-                                    atomicAdd(a.d_ray_bias + ray * 256 + c, s0);
-                                    atomicAdd(a.d_ray_bias + ray * 256 + c + 1, s1);
-                                    s0 = s1 = 0.0f; in_ray = 0; ++ray;
-                                }
-                            }
-                        }
                     }
                 } else if (g == 8) {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 0, false>(tlane + c0, nullptr, 0, nullptr, 0u, sD, row, c0);
+                        bwd_slice<true, 0, false>(tlane + c0, nullptr, nullptr, 0u, sD, row, c0);
                 } else if (g == 7) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 1, true>(tlane + c0, cst + ConstOff::sigma_w + c0, 0, dp, mw[c0 >> 5], sD, row, c0);
+#pragma unroll
+                    for (int sl8 = 0; sl8 < 8; ++sl8)
+                        bwd_slice<true, 1, true>(tlane + 32 * sl8, hwl + sl8, dp, mw[sl8], sD, row, 32 * sl8);
                 } else {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 0, true>(tlane + c0, nullptr, 0, nullptr, mw[c0 >> 5], sD, row, c0);
+                        bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
                 }
                 NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 4);    // leader's slices written
                 ptx::fence_proxy_async_smem();
@@ -333,6 +320,42 @@ field_dgrad_kernel(const BwdArgs a) {
                 if (g >= 1) {
                     ptx::tc_fence_before_sync();
                     ptx::mbar_arrive(bar_act);
+                }
+                if (g == 9) {
+                    // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples.  Runs
+                    // AFTER the handoff, next to layer 9's MMAs and the bulk store (all three only read the image);
+                    // the next layer's epilogue rewrites it only behind its barrier.
+                    const int ncols = transient ? 256 : 128;
+                    const int c = 2 * et;
+                    if (c < ncols) {
+                        const uint8_t* colp = sD + (c >> 6) * 16384 + (c & 7) * 2;
+                        const int chunk = (c & 63) >> 3;
+                        long long ray = p0 / a.S;
+                        const int nrow = static_cast<int>(min(static_cast<long long>(kTileM), a.n_points - p0));
+                        int r = 0;
+                        int seg_end = static_cast<int>(min(static_cast<long long>(nrow), (ray + 1) * a.S - p0));
+                        while (r < nrow) {                      // one segment = the rows of one ray inside this tile
+                            float s0 = 0.0f, s1 = 0.0f, u0 = 0.0f, u1 = 0.0f;
+                            for (; r + 8 <= seg_end; r += 8) {
+                                uint32_t w[8];
+#pragma unroll
+                                for (int k = 0; k < 8; ++k) w[k] = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r + k, chunk));
+#pragma unroll
+                                for (int k = 0; k < 8; k += 2) {
+                                    s0 += __uint_as_float(w[k] << 16); s1 += __uint_as_float(w[k] & 0xFFFF0000u);
+                                    u0 += __uint_as_float(w[k + 1] << 16); u1 += __uint_as_float(w[k + 1] & 0xFFFF0000u);
+                                }
+                            }
+                            for (; r < seg_end; ++r) {
+                                const uint32_t w = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r, chunk));
+                                s0 += __uint_as_float(w << 16); s1 += __uint_as_float(w & 0xFFFF0000u);
+                            }
+                            atomicAdd(a.d_ray_bias + ray * 256 + c, s0 + u0);
+                            atomicAdd(a.d_ray_bias + ray * 256 + c + 1, s1 + u1);
+                            ++ray;
+                            seg_end = min(nrow, seg_end + a.S);
+                        }
+                    }
                 }
             }
         }

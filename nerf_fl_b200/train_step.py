@@ -43,7 +43,7 @@ class TrainStep:
         self.terms = None            # loss terms of the last call (dict of 0-dim tensors)
 
     # ---- the iteration itself ---------------------------------------------------------------------
-    def _iteration(self, rays, ts, rgbs, graph_safe_rng: bool):
+    def _iteration(self, rays, ts, rgbs, graph_safe_rng: bool, do_step: bool = True):
         Ns, use_disp, perturb, noise_std, Ni, chunk, white_back = self.args
         kw = {}
         if graph_safe_rng:
@@ -59,7 +59,8 @@ class TrainStep:
         terms = self.loss_fn(res, rgbs)
         loss = sum(terms.values())
         loss.backward()
-        self.state.step()
+        if do_step:
+            self.state.step()
         return loss.detach(), {k: v.detach() for k, v in terms.items()}
 
     def _capture(self, rays, ts, rgbs):
@@ -67,6 +68,12 @@ class TrainStep:
         self.s_rays = rays.clone()
         self.s_ts = ts.clone()
         self.s_rgbs = rgbs.clone()
+        # One process per GPU with world > 1: the gradient all-reduce stays OUTSIDE the graph.  The captured part is
+        # forward + loss + backward (everything up to the flat gradient buffer); the NCCL all-reduce and the two
+        # Adam kernels are enqueued behind the replay on the same stream (3 host calls per iteration instead of
+        # ~60).  A collective inside a capture ties the graph to the communicator's internal streams and to the
+        # process group's watchdog thread, and a hang there takes the whole job down.
+        self._split = dist_info()[1] > 1
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(side):
@@ -78,9 +85,10 @@ class TrainStep:
             m._nwb_dirty = True                        # the captured iteration must contain the operand-cache refresh
         g = torch.cuda.CUDAGraph()
         l0 = K.launch_count
-        with torch.cuda.graph(g):
-            self.s_loss, self.s_terms = self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True)
-        self.launches_per_step = K.launch_count - l0
+        # thread_local: other threads of the process (NCCL watchdog, clock sampler) may touch CUDA during the capture
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            self.s_loss, self.s_terms = self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True, do_step=not self._split)
+        self.launches_per_step = K.launch_count - l0 + (2 if self._split else 0)
         self.graph = g
 
     def __call__(self, rays, ts, rgbs):
@@ -91,7 +99,10 @@ class TrainStep:
             self.s_ts.copy_(ts, non_blocking=True)
             self.s_rgbs.copy_(rgbs, non_blocking=True)
             self.graph.replay()
-            self.state.step_count += 1
+            if self._split:
+                self.state.step()                      # all-reduce + Adam, stream-ordered behind the replay
+            else:
+                self.state.step_count += 1
             for m in self.models.values():
                 m._nwb_dirty = True                    # parameters moved: eager callers must repack
             self.terms = self.s_terms
