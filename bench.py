@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--workload", default="train", choices=["train", "infer"])
     ap.add_argument("--batch", type=int, default=BATCH, help="rays per rank per step (train)")
     ap.add_argument("--samples", type=int, default=N_SAMPLES, help="coarse samples (= fine importance samples)")
+    ap.add_argument("--vocab", type=int, default=N_VOCAB, help="embedding rows (configs[2], Phototourism-shaped: 1500)")
+    ap.add_argument("--beta-min", type=float, default=BETA_MIN, help="configs[2]: 0.03")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch the training step eagerly instead of replaying its CUDA graph")
     return ap.parse_args()
@@ -247,6 +249,19 @@ def run_reference(args):
             "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
+
+
+def ncu_traffic(dom, args):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this same command (profiles/ncu_traffic.json, written by tools/ncu_table.py);
+    None when no capture exists for this kernel / workload size."""
+    try:
+        tab = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except (OSError, ValueError):
+        return None
+    key = f"{dom['kernel']}|mode{dom['mode']}|batch{args.batch}|samples{args.samples}|{args.workload}"
+    ent = tab.get(key)
+    return None if ent is None else ent["bytes"]          # bytes per launch
 
 
 def workload_config(args, n_rays_step=None):
@@ -455,7 +470,8 @@ def run_product(args):
         r["share_of_kernel_time"] = round(r["total_ms"] / min(args.steps, 10) / sum_ms, 4)
     dom = next(r for r in table if "bound" in r)             # table is sorted by total time
     roofline = {"kernel": f"{dom['kernel']} (mode {dom['mode']})", "bound": dom["bound"], "achieved": dom["achieved"],
-                "peak": dom["peak"], "unit": dom["unit"], "frac": dom["frac"], "traffic": None,
+                "peak": dom["peak"], "unit": dom["unit"], "frac": dom["frac"], "traffic": ncu_traffic(dom, args),
+                "traffic_unit": "B per launch (dram read+write, ncu --set full, profiles/ncu_traffic.json)",
                 "work_per_launch": dom["work"], "avg_launch_ms": dom["avg_ms"], "peak_source": peaks()["source"] + " (sustained)",
                 "timing": "CUDA events around each C-ABI call on the launching stream, separate eager pass of the same steps"}
     fl = (train_flops_per_ray if args.workload == "train" else infer_flops_per_ray)(ns, ni)
@@ -496,8 +512,9 @@ def emit(line: dict):
 
 
 def main():
-    global _JSON_FD
+    global _JSON_FD, N_VOCAB, BETA_MIN
     args = parse_args()
+    N_VOCAB, BETA_MIN = args.vocab, args.beta_min
     # native libraries print to fd 1 behind Python's back (NCCL's "NCCL version ..." banner): keep the real stdout
     # for the JSON line only and send everything else to stderr
     sys.stdout.flush()

@@ -79,8 +79,11 @@ posenc_kernel(const float* __restrict__ x, int64_t n, int n_freqs, float* __rest
 // ------------------------------------------------------------------------------------------------
 // (a6) models/rendering.py:7-46 + :267-272.  One warp per ray:
 //   stage z / w rows in smem (coalesced), warp-scan the CDF, per-lane binary search
-//   (searchsorted right=True), inverse-CDF lerp, then a warp bitonic sort of [z_coarse | z_new].
-// smem per warp: cdf[Ns-1], bins[Ns-1], keys[P] with P = next_pow2(Ns+Ni).
+//   (searchsorted right=True), inverse-CDF lerp.  sort(cat[z, z_new]) is a MERGE: z_coarse is sorted, z_new is
+//   sorted whenever u is (det, or a sorted u_in) -- checked with a warp vote, otherwise z_new alone goes through a
+//   bitonic network -- and every element then finds its output slot by one binary search in the other list
+//   (rank of a coarse z = i + #{z_new < z}, rank of a new z = j + #{z_coarse <= z}: a stable merge, no collisions).
+// smem per warp: cdf[Ns-1], bins[Ns-1], zc[Ns], zn[P] with P = next_pow2(Ni), out[Ns+Ni].
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse,
@@ -91,10 +94,12 @@ sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restr
     const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int M = Ns - 2;        // number of pdf bins (weights[:,1:-1])
     const int nb = Ns - 1;       // number of bin edges == cdf entries
-    const int per_warp = 2 * nb + P;
+    const int per_warp = 2 * nb + Ns + P + Ns + Ni;
     float* cdf = smem + warp * per_warp;
     float* bins = cdf + nb;
-    float* keys = bins + nb;
+    float* keys = bins + nb;          // zc[Ns] followed by zn[P]
+    float* zn = keys + Ns;
+    float* outb = zn + P;
     const float eps = 1e-5f;
 
     for (int ray = blockIdx.x * warps + warp; ray < n_rays; ray += gridDim.x * warps) {
@@ -159,23 +164,48 @@ sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restr
             if (z_new_out != nullptr) z_new_out[static_cast<int64_t>(ray) * Ni + j] = s;
             if (inds_out != nullptr) inds_out[static_cast<int64_t>(ray) * Ni + j] = lo;
         }
-        for (int i = Ns + Ni + lane; i < P; i += 32) keys[i] = INFINITY;
+        for (int i = Ni + lane; i < P; i += 32) zn[i] = INFINITY;
         __syncwarp();
-        // warp bitonic sort of P keys in smem
-        for (int k = 2; k <= P; k <<= 1) {
-            for (int j = k >> 1; j > 0; j >>= 1) {
-                for (int t = lane; t < (P >> 1); t += 32) {
-                    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));   // index with bit j clear
-                    const int l = i | j;
-                    const bool up = ((i & k) == 0);
-                    const float a = keys[i], b = keys[l];
-                    if ((a > b) == up) { keys[i] = b; keys[l] = a; }
+        // is z_new already ascending?
+        bool ok = true;
+        for (int j = lane; j + 1 < Ni; j += 32) ok = ok && (zn[j] <= zn[j + 1]);
+        if (!__all_sync(0xffffffffu, ok)) {
+            // warp bitonic sort of the P new keys in smem
+            for (int k = 2; k <= P; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int t = lane; t < (P >> 1); t += 32) {
+                        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));   // index with bit j clear
+                        const int l = i | j;
+                        const bool up = ((i & k) == 0);
+                        const float a = zn[i], b = zn[l];
+                        if ((a > b) == up) { zn[i] = b; zn[l] = a; }
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
             }
         }
+        // merge by rank
+        for (int i = lane; i < Ns; i += 32) {
+            const float a = keys[i];
+            int lo = 0, hi = Ni;                       // #{z_new < a}
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (zn[mid] < a) lo = mid + 1; else hi = mid;
+            }
+            outb[i + lo] = a;
+        }
+        for (int j = lane; j < Ni; j += 32) {
+            const float b = zn[j];
+            int lo = 0, hi = Ns;                       // #{z_coarse <= b}
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (keys[mid] <= b) lo = mid + 1; else hi = mid;
+            }
+            outb[j + lo] = b;
+        }
+        __syncwarp();
         float* zo = z_out + static_cast<int64_t>(ray) * (Ns + Ni);
-        for (int i = lane; i < Ns + Ni; i += 32) zo[i] = keys[i];
+        for (int i = lane; i < Ns + Ni; i += 32) zo[i] = outb[i];
         __syncwarp();
     }
 }
@@ -219,9 +249,9 @@ extern "C" int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse
     NWB_REQUIRE(n_samples + n_importance <= 4096, "nwb_sample_pdf_merge: too many samples per ray");
     if (n_rays == 0) return NWB_OK;
     int P = 1;
-    while (P < n_samples + n_importance) P <<= 1;
+    while (P < n_importance) P <<= 1;
     const int warps = 4;
-    const size_t smem = static_cast<size_t>(warps) * (2 * (n_samples - 1) + P) * sizeof(float);
+    const size_t smem = static_cast<size_t>(warps) * (2 * (n_samples - 1) + P + 2 * n_samples + n_importance) * sizeof(float);
     if (smem > 48 * 1024)
         NWB_CUDA(cudaFuncSetAttribute(sample_pdf_merge_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
