@@ -246,6 +246,23 @@ int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t n, float b
                       float weight_decay, float* state, float grad_scale, int zero_grad, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * (f1) NerfWLoss -- losses.py:19-50 -- the objective over the maps render_rays returns, forward and
+ * backward as one launch each.  terms[5] = {c_l, f_l, b_l, s_l, their sum} (device); rgb_fine / beta /
+ * transient_sigmas may be NULL (coarse-only and no-transient variants, losses.py:37-45).  scratch:
+ * nwb_nerfw_loss_scratch_bytes() bytes, zeroed ONCE by the caller, reused by every call (the kernel resets
+ * its ticket; grid-wide reduction in block order, deterministic).  g_terms: host array of 5 DEVICE pointers to
+ * the cotangents of terms[0..4] (any may be NULL = 0).
+ * ---------------------------------------------------------------------------------------- */
+size_t nwb_nerfw_loss_scratch_bytes(void);
+int nwb_nerfw_loss_fwd(const float* rgb_coarse, const float* rgb_fine, const float* beta,
+                       const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
+                       float lambda_u, float coef, void* scratch, float* terms, void* stream);
+int nwb_nerfw_loss_bwd(const float* rgb_coarse, const float* rgb_fine, const float* beta,
+                       const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
+                       float lambda_u, float coef, const float* const* g_terms, float* d_rgb_coarse,
+                       float* d_rgb_fine, float* d_beta, float* d_transient_sigmas, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T
  * from bf16 tile images, through the same smem layouts / descriptors the field kernels use.
  * ---------------------------------------------------------------------------------------- */

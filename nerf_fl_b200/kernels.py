@@ -353,3 +353,45 @@ def ray_consts_bwd(desc, sd, ray_feat, d_ray_bias, *, ts=None, n_vocab=0, transi
         L.check(fn(C.byref(desc), C.byref(st), L.ptr(ray_feat), L.ptr(d_ray_bias), L.ptr(ts), n_vocab, ray_feat.shape[0],
                    mode, C.byref(gt), L.ptr(d_emb_a), L.ptr(d_emb_t), L.ptr(d_a_rows), L.ptr(d_t_rows),
                    L.stream_ptr(dev)), "nwb_ray_consts_bwd")
+
+
+# ---- objective (f1): NerfWLoss forward / backward -------------------------------------------------
+_loss_scratch = {}
+
+
+def _loss_scratch_for(dev) -> torch.Tensor:
+    key = (dev.type, dev.index)
+    if key not in _loss_scratch:
+        n = _fn("nwb_nerfw_loss_scratch_bytes", [], _sz)()
+        _loss_scratch[key] = torch.zeros(n, dtype=torch.uint8, device=dev)     # zeroed once; the kernel resets its ticket
+    return _loss_scratch[key]
+
+
+def nerfw_loss_fwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda_u: float, coef: float) -> torch.Tensor:
+    """-> terms (5,) = [c_l, f_l, b_l, s_l, total] on the device (one launch)."""
+    dev = rgb_coarse.device
+    terms = torch.empty(5, device=dev, dtype=torch.float32)
+    n_ts = transient_sigmas.numel() if transient_sigmas is not None else 0
+    fn = _fn("nwb_nerfw_loss_fwd", [_vp] * 5 + [_i, _i64, C.c_float, C.c_float, _vp, _vp, _vp])
+    with _timed("nwb_nerfw_loss_fwd", rgb_coarse.shape[0]):
+        L.check(fn(L.ptr(rgb_coarse), L.ptr(rgb_fine), L.ptr(beta), L.ptr(transient_sigmas), L.ptr(targets),
+                   rgb_coarse.shape[0], n_ts, lambda_u, coef, L.ptr(_loss_scratch_for(dev)), L.ptr(terms),
+                   L.stream_ptr(dev)), "nwb_nerfw_loss_fwd")
+    return terms
+
+
+def nerfw_loss_bwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda_u: float, coef: float, g_terms):
+    """g_terms: 5 device scalars or None -> (d_rgb_coarse, d_rgb_fine, d_beta, d_transient_sigmas) (one launch)."""
+    dev = rgb_coarse.device
+    d_c = torch.empty_like(rgb_coarse)
+    d_f = torch.empty_like(rgb_fine) if rgb_fine is not None else None
+    d_b = torch.empty_like(beta) if beta is not None else None
+    d_s = torch.empty_like(transient_sigmas) if (transient_sigmas is not None and beta is not None) else None
+    n_ts = transient_sigmas.numel() if transient_sigmas is not None else 0
+    gp = (_vp * 5)(*[(g.data_ptr() if g is not None else None) for g in g_terms])
+    fn = _fn("nwb_nerfw_loss_bwd", [_vp] * 5 + [_i, _i64, C.c_float, C.c_float, C.POINTER(_vp * 5), _vp, _vp, _vp, _vp, _vp])
+    with _timed("nwb_nerfw_loss_bwd", rgb_coarse.shape[0]):
+        L.check(fn(L.ptr(rgb_coarse), L.ptr(rgb_fine), L.ptr(beta), L.ptr(transient_sigmas), L.ptr(targets),
+                   rgb_coarse.shape[0], n_ts, lambda_u, coef, C.byref(gp), L.ptr(d_c), L.ptr(d_f), L.ptr(d_b), L.ptr(d_s),
+                   L.stream_ptr(dev)), "nwb_nerfw_loss_bwd")
+    return d_c, d_f, d_b, d_s

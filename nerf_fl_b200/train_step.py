@@ -57,7 +57,9 @@ class TrainStep:
         res = render_rays(self.models, self.embeddings, rays, ts, Ns, use_disp, perturb, noise_std, Ni, chunk,
                           white_back, **kw)
         terms = self.loss_fn(res, rgbs)
-        loss = sum(terms.values())
+        loss = getattr(terms, "total", None)
+        if loss is None:
+            loss = sum(terms.values())               # train.py:166
         loss.backward()
         if do_step:
             self.state.step()
