@@ -15,6 +15,7 @@ namespace nwb {
 
 constexpr int kObjThreads = 256;
 constexpr int kObjMaxBlocks = 148;
+static_assert(kObjMaxBlocks <= kObjThreads, "the last block reduces one partial per thread");
 
 struct ObjArgs {
     const float* rgb_c; const float* rgb_f; const float* beta; const float* ts; const float* tgt;
@@ -37,7 +38,7 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 }
 
 // scratch: [kObjMaxBlocks][4] partial sums followed by one uint32 ticket; the last block to finish adds the
-// partials in block order (deterministic) and writes terms[0..4]
+// partials in a fixed tree order (deterministic) and writes terms[0..4]
 __global__ void __launch_bounds__(kObjThreads)
 nerfw_loss_fwd_kernel(const ObjArgs a, float* __restrict__ scratch, float* __restrict__ terms) {
     __shared__ float red[kObjThreads / 32];
@@ -74,23 +75,26 @@ nerfw_loss_fwd_kernel(const ObjArgs a, float* __restrict__ scratch, float* __res
         is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
     }
     __syncthreads();
-    if (is_last && threadIdx.x == 0) {
+    if (is_last) {                               // whole block: partials of block b go to thread b, fixed tree order
         __threadfence();
-        float t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-        for (unsigned b = 0; b < gridDim.x; ++b) {
-            const volatile float* p = scratch + 4 * b;
-            t0 += p[0]; t1 += p[1]; t2 += p[2]; t3 += p[3];
+        float q0 = 0, q1 = 0, q2 = 0, q3 = 0;
+        if (threadIdx.x < gridDim.x) {
+            const volatile float* p = scratch + 4 * threadIdx.x;
+            q0 = p[0]; q1 = p[1]; q2 = p[2]; q3 = p[3];
         }
-        const float inv3 = 1.0f / static_cast<float>(n3), invn = 1.0f / static_cast<float>(a.n);
-        const float c_l = a.coef * 0.5f * t0 * inv3;
-        float f_l = 0.0f, b_l = 0.0f, s_l = 0.0f;
-        if (a.rgb_f != nullptr) f_l = a.coef * (a.beta != nullptr ? t1 * inv3 : 0.5f * t1 * inv3);
-        if (a.beta != nullptr) {
-            b_l = a.coef * (t2 * invn + 3.0f);
-            if (a.ts != nullptr) s_l = a.coef * a.lambda_u * t3 / static_cast<float>(a.n_ts);
+        const float t0 = block_sum(q0, red), t1 = block_sum(q1, red), t2 = block_sum(q2, red), t3 = block_sum(q3, red);
+        if (threadIdx.x == 0) {
+            const float inv3 = 1.0f / static_cast<float>(n3), invn = 1.0f / static_cast<float>(a.n);
+            const float c_l = a.coef * 0.5f * t0 * inv3;
+            float f_l = 0.0f, b_l = 0.0f, s_l = 0.0f;
+            if (a.rgb_f != nullptr) f_l = a.coef * (a.beta != nullptr ? t1 * inv3 : 0.5f * t1 * inv3);
+            if (a.beta != nullptr) {
+                b_l = a.coef * (t2 * invn + 3.0f);
+                if (a.ts != nullptr) s_l = a.coef * a.lambda_u * t3 / static_cast<float>(a.n_ts);
+            }
+            terms[0] = c_l; terms[1] = f_l; terms[2] = b_l; terms[3] = s_l; terms[4] = ((c_l + f_l) + b_l) + s_l;
+            *ticket = 0u;                        // ready for the next call (graph replays reuse the scratch)
         }
-        terms[0] = c_l; terms[1] = f_l; terms[2] = b_l; terms[3] = s_l; terms[4] = ((c_l + f_l) + b_l) + s_l;
-        *ticket = 0u;                            // ready for the next call (graph replays reuse the scratch)
     }
 }
 

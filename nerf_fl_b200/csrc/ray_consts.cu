@@ -9,73 +9,110 @@
 
 namespace nwb {
 
-constexpr int kRcWarps = 4;
+constexpr int kRcRays = 16;            // rays per block pass
+constexpr int kRcThreads = 256;        // thread j = output feature j (0..127 dir_encoding, 128..255 transient_encoding.0)
 constexpr int kMaxFeat = 768;
 
-__global__ void __launch_bounds__(kRcWarps * 32)
+// Forward.  Phase 1: the block builds the feature rows [PosEmbedding(dir) | a | t] of kRcRays rays in shared memory
+// (and writes them out for the backward).  Phase 2: thread j keeps 32 weights of its row W[j, 256 + k0 .. +32) in
+// REGISTERS and sweeps the block's rays against them (features read as warp-uniform float4 broadcasts), so the
+// fp32 weight columns are read from L2 once per block instead of once per ray, and never uncoalesced per FMA.
+__global__ void __launch_bounds__(kRcThreads)
 ray_consts_fwd_kernel(FieldShape fs, nwb_field_params p, const float* __restrict__ dirs, int dir_stride,
                       int dir_is_encoded, int n_freq_dir, const int64_t* __restrict__ ts,
                       const float* __restrict__ emb_a, const float* __restrict__ emb_t, int n_vocab,
                       const float* __restrict__ a_rows, const float* __restrict__ t_rows, int n_rays,
                       uint32_t mode, float* __restrict__ ray_feat, float* __restrict__ ray_bias,
                       int* __restrict__ err_flag) {
-    extern __shared__ float sm[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    extern __shared__ __align__(16) float sm[];
     const bool use_t = (mode & NWB_MLP_TRANSIENT) != 0;
     const int nd = fs.in_dir, na = fs.in_a, nt = use_t ? fs.in_t : 0;
     const int nf = nd + na + nt;
+    const int ka = nd + na;                                  // contraction length of the dir_encoding half
+    const int ka_p = (ka + 3) & ~3, kt_p = (nt + 3) & ~3;   // padded row lengths (float4 reads)
     const int feat_ld = fs.in_dir + fs.in_a + fs.in_t;
-    float* feat = sm + warp * kMaxFeat;
-    for (int ray = blockIdx.x * kRcWarps + warp; ray < n_rays; ray += gridDim.x * kRcWarps) {
-        int64_t t_idx = 0;
-        if ((na > 0 && a_rows == nullptr) || (nt > 0 && t_rows == nullptr)) {
-            t_idx = ts[ray];
-            if (t_idx < 0 || t_idx >= n_vocab) {
-                if (lane == 0) atomicExch(err_flag, 1);
-                t_idx = 0;
+    float* sfa = sm;                                         // [kRcRays][ka_p]  dir | a
+    float* sft = sfa + kRcRays * ka_p;                       // [kRcRays][kt_p]  t
+    const int j = threadIdx.x;
+    const bool is_t = j >= kHalf;
+    const int jj = is_t ? j - kHalf : j;
+    const int K = is_t ? nt : ka;
+    const float* wrow = is_t ? (use_t ? p.tenc_w[0] + static_cast<int64_t>(jj) * (kW + fs.in_t) + kW : nullptr)
+                             : p.dir_w + static_cast<int64_t>(jj) * (kW + fs.in_dir + fs.in_a) + kW;
+    const float bias = is_t ? (use_t ? p.tenc_b[0][jj] : 0.0f) : p.dir_b[jj];
+    const float* sf = is_t ? sft : sfa;
+    const int sf_ld = is_t ? kt_p : ka_p;
+
+    for (int r0 = blockIdx.x * kRcRays; r0 < n_rays; r0 += gridDim.x * kRcRays) {
+        const int nr = min(kRcRays, n_rays - r0);
+        // ---- phase 1: feature rows ----
+        for (int idx = threadIdx.x; idx < nr * nf; idx += kRcThreads) {
+            const int r = idx / nf, e = idx - r * nf;
+            const int ray = r0 + r;
+            int64_t t_idx = 0;
+            if (e >= nd && ((e < ka && a_rows == nullptr) || (e >= ka && t_rows == nullptr))) {
+                t_idx = ts[ray];
+                if (t_idx < 0 || t_idx >= n_vocab) {
+                    atomicExch(err_flag, 1);
+                    t_idx = 0;
+                }
             }
-        }
-        for (int e = lane; e < nf; e += 32) {
             float v;
             if (e < nd) {
-                if (dir_is_encoded) {
-                    v = dirs[static_cast<int64_t>(ray) * dir_stride + e];
-                } else if (e < 3) {
+                if (dir_is_encoded || e < 3) {
                     v = dirs[static_cast<int64_t>(ray) * dir_stride + e];
                 } else {
-                    const int k = (e - 3) / 6, r = (e - 3) % 6;
-                    const float arg = __fmul_rn(dirs[static_cast<int64_t>(ray) * dir_stride + (r % 3)],
+                    const int k = (e - 3) / 6, rr = (e - 3) % 6;
+                    const float arg = __fmul_rn(dirs[static_cast<int64_t>(ray) * dir_stride + (rr % 3)],
                                                 exp2f(static_cast<float>(k)));
-                    v = (r < 3) ? sinf(arg) : cosf(arg);
+                    v = (rr < 3) ? sinf(arg) : cosf(arg);
                 }
-            } else if (e < nd + na) {
-                const int j = e - nd;
-                v = a_rows ? a_rows[static_cast<int64_t>(ray) * na + j] : emb_a[t_idx * na + j];
+                sfa[r * ka_p + e] = v;
+            } else if (e < ka) {
+                const int q = e - nd;
+                v = a_rows ? a_rows[static_cast<int64_t>(ray) * na + q] : emb_a[t_idx * na + q];
+                sfa[r * ka_p + e] = v;
             } else {
-                const int j = e - nd - na;
-                v = t_rows ? t_rows[static_cast<int64_t>(ray) * nt + j] : emb_t[t_idx * nt + j];
+                const int q = e - ka;
+                v = t_rows ? t_rows[static_cast<int64_t>(ray) * nt + q] : emb_t[t_idx * nt + q];
+                sft[r * kt_p + q] = v;
             }
-            feat[e] = v;
             if (ray_feat) ray_feat[static_cast<int64_t>(ray) * feat_ld + e] = v;
         }
-        __syncwarp();
-        const int ld_dir = kW + fs.in_dir + fs.in_a;
-        const int ld_t = kW + fs.in_t;
-        for (int j = lane; j < 2 * kHalf; j += 32) {
-            float acc = 0.0f;
-            if (j < kHalf) {
-                const float* w = p.dir_w + static_cast<int64_t>(j) * ld_dir + kW;
-                acc = p.dir_b[j];
-                for (int k = 0; k < nd + na; ++k) acc = fmaf(w[k], feat[k], acc);
-            } else if (use_t) {
-                const int jj = j - kHalf;
-                const float* w = p.tenc_w[0] + static_cast<int64_t>(jj) * ld_t + kW;
-                acc = p.tenc_b[0][jj];
-                for (int k = 0; k < nt; ++k) acc = fmaf(w[k], feat[nd + na + k], acc);
+        for (int idx = threadIdx.x; idx < nr * (ka_p - ka); idx += kRcThreads) sfa[(idx / (ka_p - ka)) * ka_p + ka + idx % (ka_p - ka)] = 0.0f;
+        if (kt_p > nt)
+            for (int idx = threadIdx.x; idx < nr * (kt_p - nt); idx += kRcThreads) sft[(idx / (kt_p - nt)) * kt_p + nt + idx % (kt_p - nt)] = 0.0f;
+        __syncthreads();
+        // ---- phase 2: ray_bias[ray, j] = b[j] + sum_k W[j, 256 + k] feat[ray, k] ----
+        float acc[kRcRays];
+#pragma unroll
+        for (int r = 0; r < kRcRays; ++r) acc[r] = bias;
+        for (int k0 = 0; k0 < K; k0 += 32) {
+            float w[32];
+#pragma unroll
+            for (int q = 0; q < 32; ++q) w[q] = (k0 + q < K) ? __ldg(wrow + k0 + q) : 0.0f;
+            const int nq4 = min(8, (sf_ld - k0) >> 2);                      // float4 groups left in the padded row
+#pragma unroll
+            for (int r = 0; r < kRcRays; ++r) {
+                if (r < nr) {
+                    const float4* fr = reinterpret_cast<const float4*>(sf + r * sf_ld + k0);
+                    float a = acc[r];
+#pragma unroll
+                    for (int q4 = 0; q4 < 8; ++q4) {
+                        if (q4 < nq4) {
+                            const float4 f = fr[q4];
+                            a = fmaf(w[4 * q4], f.x, a); a = fmaf(w[4 * q4 + 1], f.y, a);
+                            a = fmaf(w[4 * q4 + 2], f.z, a); a = fmaf(w[4 * q4 + 3], f.w, a);
+                        }
+                    }
+                    acc[r] = a;
+                }
             }
-            ray_bias[static_cast<int64_t>(ray) * 256 + j] = acc;
         }
-        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < kRcRays; ++r)
+            if (r < nr) ray_bias[static_cast<int64_t>(r0 + r) * 256 + j] = (is_t && !use_t) ? 0.0f : acc[r];
+        __syncthreads();
     }
 }
 
@@ -85,7 +122,7 @@ ray_consts_fwd_kernel(FieldShape fs, nwb_field_params p, const float* __restrict
 // dW[j, 256+k] in registers, so each block issues ONE atomic per weight element (n_rays/kRcbRays-way
 // contention instead of one atomic per ray group and element).  Embedding-row cotangents
 // W[:, 256+nd:]^T g are taken against a shared-memory copy of the weight columns.
-constexpr int kRcbRays = 32;
+constexpr int kRcbRays = 16;
 constexpr int kRcbThreads = 256;
 
 __global__ void __launch_bounds__(kRcbThreads)
@@ -182,9 +219,9 @@ extern "C" int nwb_ray_consts_fwd(const nwb_field_desc* d, const nwb_field_param
     NWB_REQUIRE(fs.in_a == 0 || a_rows || (emb_a && ts), "nwb_ray_consts_fwd: appearance needs a_rows or (emb_a, ts)");
     NWB_REQUIRE(!use_t || t_rows || (emb_t && ts), "nwb_ray_consts_fwd: transient needs t_rows or (emb_t, ts)");
     NWB_REQUIRE(fs.in_dir + fs.in_a + fs.in_t <= kMaxFeat, "nwb_ray_consts_fwd: feature row too wide");
-    const int blocks = std::min((n_rays + kRcWarps - 1) / kRcWarps, kNumSMs * 8);
-    const size_t smem = kRcWarps * kMaxFeat * sizeof(float);
-    ray_consts_fwd_kernel<<<blocks, kRcWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+    const int blocks = std::min((n_rays + kRcRays - 1) / kRcRays, kNumSMs * 4);
+    const size_t smem = static_cast<size_t>(kRcRays) * (((fs.in_dir + fs.in_a + 3) & ~3) + ((fs.in_t + 3) & ~3)) * sizeof(float);
+    ray_consts_fwd_kernel<<<blocks, kRcThreads, smem, static_cast<cudaStream_t>(stream)>>>(
         fs, *p, dirs, dir_stride, dir_is_encoded, n_freq_dir, ts, emb_a, emb_t, n_vocab, a_rows, t_rows, n_rays,
         mode, ray_feat, ray_bias, err_flag);
     NWB_LAUNCH_CHECK();

@@ -14,7 +14,8 @@ constexpr int kP2OffR = 49152 + 65536;     // 3 x 32 KB ring for bulk copies
 constexpr int kP2Smem = kP2OffR + 3 * 32768;
 
 // mode bits: 1 = st.shared.v4 (16 B/thread/iter), 2 = + fence.proxy.async per iter, 4 = bulk g2s stream (warp 1),
-//            8 = tcgen05.ld x16 per iter, 16 = pace the interfering threads (~epilogue rate: one iter per ~40 cycles)
+//            8 = tcgen05.ld x16 per iter, 16 = pace the interfering threads (~epilogue rate: one iter per ~40 cycles),
+//            32 / 64 = issue every 32 KB ring stage as 8 x 4 KB / 2 x 16 KB bulk copies
 __global__ void __launch_bounds__(kP2Threads, 1)
 umma_probe2_kernel(int rounds, int mode, const uint8_t* gsrc, long long* out) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -57,7 +58,10 @@ umma_probe2_kernel(int rounds, int mode, const uint8_t* gsrc, long long* out) {
                 const uint32_t s = it % 3;
                 if (it >= 3) ptx::mbar_wait(&bar[1 + s], ((it / 3) - 1) & 1u);
                 ptx::mbar_arrive_expect_tx(&bar[1 + s], 32768);
-                ptx::bulk_g2s(smem + kP2OffR + s * 32768, gsrc + (static_cast<size_t>(it) % 40) * 32768, 32768, &bar[1 + s]);
+                const int pieces = (mode & 32) ? 8 : ((mode & 64) ? 2 : 1);      // 32 KB as 1 x 32 KB, 2 x 16 KB or 8 x 4 KB copies
+                const uint32_t pb = 32768u / pieces;
+                for (int pc = 0; pc < pieces; ++pc)
+                    ptx::bulk_g2s(smem + kP2OffR + s * 32768 + pc * pb, gsrc + (static_cast<size_t>(it) % 40) * 32768 + pc * pb, pb, &bar[1 + s]);
                 ++it;
                 bytes += 32768;
             }

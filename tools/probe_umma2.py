@@ -1,6 +1,6 @@
 """Interference probe: cycles per tcgen05.mma (M=128 N=256 K=16, floor 128) while other warps write shared memory,
 fence, read TMEM, or stream bulk copies from L2.  mode bits: 1 st.shared, 2 fence.proxy.async, 4 bulk g2s stream,
-8 tcgen05.ld, 16 paced."""
+8 tcgen05.ld, 16 paced, 32 / 64: each 32 KB stage as 8 x 4 KB / 2 x 16 KB copies."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -11,7 +11,7 @@ src = torch.zeros(40 * 32768, dtype=torch.uint8, device="cuda")
 rounds = 256
 for grid in (1, 148):
     out = torch.zeros(2 * grid, dtype=torch.int64, device="cuda")
-    for mode in (0, 1, 3, 1 | 16, 3 | 16, 8, 8 | 16, 4, 4 | 1, 4 | 3 | 8, 4 | 3 | 8 | 16):
+    for mode in (0, 1, 3, 1 | 16, 3 | 16, 8, 8 | 16, 4, 4 | 64, 4 | 32, 4 | 1, 4 | 3 | 8, 4 | 3 | 8 | 16, 4 | 3 | 8 | 16 | 32):
         for rep in range(2):
             out.zero_()
             L.check(fn(grid, rounds, mode, src.data_ptr(), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
