@@ -313,6 +313,15 @@ def kernel_table(rec, ns, ni, workload):
             ach = fl / (avg_ms * 1e-3) / 1e12
             row.update(bound="tensor", achieved=round(ach, 2), peak=pk["bf16_sustained"], unit="TFLOP/s",
                        frac=round(ach / pk["bf16_sustained"], 4), work=f"{typ} {kind}: {field_flops_per_point(kind, typ):.0f} FLOP/point x {per_launch_units:.0f} points")
+            if kind == "wgrad":
+                # dW = dZ^T . A reads every dZ image and every saved activation image exactly once (DESIGN.md section 3:
+                # fine 770 048 + 770 048 B, coarse 638 976 + 638 976 B per 128-point tile) and keeps the products in
+                # TMEM: 49 FLOP per byte -- the HBM roofline binds long before the tensor one
+                bpp = 12032 if fine else 9984
+                gbs = bpp * per_launch_units / (avg_ms * 1e-3) / 1e9
+                row.update(bound="hbm", achieved=round(gbs, 1), peak=pk["hbm_gbs"], unit="GB/s", frac=round(gbs / pk["hbm_gbs"], 4),
+                           tensor_tflops=round(ach, 2), tensor_frac=round(ach / pk["bf16_sustained"], 4),
+                           work=f"{typ} wgrad: {bpp} B/point (dZ + saved activation images, read once) x {per_launch_units:.0f} points")
         elif name in ("nwb_composite_fwd", "nwb_composite_bwd"):
             Cc, S = mode // 1000, mode % 1000
             if name.endswith("fwd"):
@@ -472,7 +481,7 @@ def run_product(args):
     roofline = {"kernel": f"{dom['kernel']} (mode {dom['mode']})", "bound": dom["bound"], "achieved": dom["achieved"],
                 "peak": dom["peak"], "unit": dom["unit"], "frac": dom["frac"], "traffic": ncu_traffic(dom, args),
                 "traffic_unit": "B per launch (dram read+write, ncu --set full, profiles/ncu_traffic.json)",
-                "work_per_launch": dom["work"], "avg_launch_ms": dom["avg_ms"], "peak_source": peaks()["source"] + " (sustained)",
+                "work_per_launch": dom["work"], "avg_launch_ms": dom["avg_ms"], "peak_source": peaks()["source"] + (" (bf16_tflops_sustained)" if dom["bound"] == "tensor" else " (hbm_gbs, copy read+write)"),
                 "timing": "CUDA events around each C-ABI call on the launching stream, separate eager pass of the same steps"}
     fl = (train_flops_per_ray if args.workload == "train" else infer_flops_per_ray)(ns, ni)
     step_roofline = {"flops_per_ray": fl, "achieved_tflops_per_gpu": round(value / world * fl / 1e12, 2),
