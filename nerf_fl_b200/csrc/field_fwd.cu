@@ -519,6 +519,8 @@ field_fwd_kernel(const FwdArgs a) {
 
 }  // namespace nwb
 
+#include "field_fwd_dual.cuh"
+
 using namespace nwb;
 
 static long long* g_fwd_trace = nullptr;
@@ -569,6 +571,21 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
         configured = true;
+    }
+    // second-generation kernel (CTA pairs, two tiles in flight per CTA); NWB_FWD_GEN=1 selects the first one
+    static const bool dual = [] { const char* e = getenv("NWB_FWD_GEN"); return e == nullptr || e[0] != '1'; }();
+    if (dual) {
+        static bool configured2 = false;
+        if (!configured2) {
+            NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
+            NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
+            configured2 = true;
+        }
+        const int grid2 = 2 * std::min((a.n_tiles + 3) / 4, kNumSMs / 2);
+        if (mode & NWB_MLP_SAVE) field_fwd_dual_kernel<true><<<grid2, kFwdThreads, kDSmem, static_cast<cudaStream_t>(stream)>>>(a);
+        else field_fwd_dual_kernel<false><<<grid2, kFwdThreads, kDSmem, static_cast<cudaStream_t>(stream)>>>(a);
+        NWB_LAUNCH_CHECK();
+        return NWB_OK;
     }
     int grid = std::min(a.n_tiles, kNumSMs);
     if (const char* e = getenv("NWB_DEBUG_GRID")) grid = std::max(1, std::min(grid, atoi(e)));   // bottleneck experiments only

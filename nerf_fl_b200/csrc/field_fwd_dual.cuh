@@ -1,0 +1,384 @@
+// Fused field forward, second generation: CTA PAIRS with TWO TILES IN FLIGHT per CTA.  Included by field_fwd.cu
+// (shares FwdArgs, epi_slice16, layer_quarters with the first-generation kernel, which stays as the reference).
+//
+// Why: in the one-tile kernel the epilogue is the critical resource -- the MMA warp spends
+// 50-60 % of its time waiting for activation quarters, because a layer's MMAs cannot start before the previous
+// layer's epilogue has produced their operand, and that epilogue cannot start before the previous MMAs are done.
+// Here every CTA works on two independent 128-point tiles (slots 0 and 1).  The 16 epilogue warps alternate between
+// them -- epilogue(slot 0, layer g), epilogue(slot 1, layer g), epilogue(slot 0, layer g+1), ... -- and while they
+// are busy with one slot the tensor pipe runs the other slot's next layer, whose operand is already complete.
+//   TMEM     512 columns = 2 slots x 256 fp32 accumulator columns (no ping-pong inside a tile any more)
+//   smem     2 x 16 KB encoded xyz, 2 x 64 KB activations (a layer's output overwrites its input IN PLACE: the
+//            input is dead once the layer's MMAs have completed), 3 x 16 KB weight ring, 16 KB constants
+//   weights  48 KB of ring only feeds two tiles because the kernel runs as CTA pairs: tcgen05.mma.cta_group::2,
+//            M = 256 = slot t of both CTAs, each CTA staging HALF of every weight K-block (its N/2 rows).
+//            Rank 0 issues; rank 1's MMA warp relays "my half has landed"; completions are multicast.
+// One handoff per (slot, layer) in each direction: bar_act[t] (epilogue -> MMA: the slot's operand image is
+// complete, arrivals from the epilogue warps of BOTH CTAs on rank 0's barrier) and bar_acc[t] (MMA -> epilogue).
+// NWB_MLP_SAVE: the storer warp bulk-stores each finished image; the epilogue waits for the copy engine to have
+// read a slot's previous image before it overwrites it (bar_done[t]).
+#pragma once
+
+namespace nwb {
+
+constexpr int kDOffX = 0;                         // 2 x 16 KB
+constexpr int kDOffH = 32768;                     // 2 x 64 KB
+constexpr int kDStageBytes = 16384;               // this CTA's half of a weight K-block
+constexpr int kDNumStages = 3;
+constexpr int kDOffW = kDOffH + 2 * 65536;
+constexpr int kDOffC = kDOffW + kDNumStages * kDStageBytes;
+constexpr int kDOffBar = kDOffC + 16384;
+constexpr int kDSmem = kDOffBar + 256;
+static_assert(kDSmem <= 232448, "dual-tile forward exceeds the 227 KB shared-memory limit");
+
+// first activation K-block (16 KB slot of the slot's H image) layer g reads, after the optional X block
+__device__ __forceinline__ int dual_in_slot0(int g) { return g == 10 ? 2 : 0; }
+
+template <bool kSave>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
+field_fwd_dual_kernel(const FwdArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sW = smem + kDOffW;
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kDOffBar);  // [3] producer (+ partner relay) -> MMA
+    uint64_t* bar_empty = bar_full + kDNumStages;                       // [3] MMA -> producers of both CTAs
+    uint64_t* bar_acc = bar_empty + kDNumStages;                        // [2] MMA -> epilogue, per slot
+    uint64_t* bar_act = bar_acc + 2;                                    // [2] epilogues of both CTAs -> MMA, per slot
+    uint64_t* bar_st = bar_act + 2;                                     // [2] epilogue -> storer, per slot
+    uint64_t* bar_done = bar_st + 2;                                    // [2] storer -> epilogue, per slot
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 2);
+    uint32_t* s_woff = tmem_slot + 2;                                   // [kMaxG]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int quad0 = static_cast<int>(ptx::cluster_id_x()), quad_step = static_cast<int>(ptx::cluster_count_x());
+    const int n_quads = (a.n_tiles + 3) >> 2;          // a cluster step covers 4 tiles: tile = 4*quad + 2*slot + rank
+    const FieldShape& fs = a.fs;
+    const int nl = fs.n_layers(a.mode);
+    const bool transient = (a.mode & NWB_MLP_TRANSIENT) != 0;
+    const bool sigma_only = (a.mode & NWB_MLP_SIGMA_ONLY) != 0;
+    constexpr bool save = kSave;
+
+    if (threadIdx.x == 0) {
+        if ((ptx::smem_u32(smem) & 1023u) != 0) {
+            printf("nwb: dynamic shared memory is not 1 KB aligned\n");
+            __trap();
+        }
+        for (int s = 0; s < kDNumStages; ++s) { ptx::mbar_init(&bar_full[s], rank == 0 ? 2 : 1); ptx::mbar_init(&bar_empty[s], 1); }
+        for (int t = 0; t < 2; ++t) {
+            ptx::mbar_init(&bar_acc[t], 1);
+            ptx::mbar_init(&bar_act[t], 2 * kEpiWarps);
+            ptx::mbar_init(&bar_st[t], kEpiWarps);
+            ptx::mbar_init(&bar_done[t], 1);
+        }
+        ptx::fence_mbar_init();
+        for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
+    }
+    {
+        const float4* src = reinterpret_cast<const float4*>(a.packed + fs.w_bytes());
+        float4* dst = reinterpret_cast<float4*>(smem + kDOffC);
+        for (int i = threadIdx.x; i < ConstOff::count / 4; i += kFwdThreads) dst[i] = __ldg(src + i);
+    }
+    if (warp == 1) ptx::tmem_alloc_pair<512>(tmem_slot);
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::cluster_sync_all();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ============================ weight producer ============================================
+        // per (layer, slot, K-block): my N/2 rows x 64 k of the packed slab image, one bulk copy
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (int quad = quad0; quad < n_quads; quad += quad_step) {
+                for (int g = 0; g < nl; ++g) {
+                    const int KB = fs.layer_kb(g), PN = fs.packed_n(g);
+                    const uint32_t bytes = static_cast<uint32_t>(fs.layer_n(g, a.mode)) * 64u;
+                    const uint8_t* wsrc = a.packed + s_woff[g] + rank * bytes;
+                    for (int t = 0; t < 2; ++t) {
+                        for (int kb = 0; kb < KB; ++kb) {
+                            ptx::mbar_wait_sleepy(&bar_empty[s], ph ^ 1u);
+                            ptx::mbar_arrive_expect_tx(&bar_full[s], bytes);
+                            ptx::bulk_g2s(sW + s * kDStageBytes, wsrc + static_cast<size_t>(kb) * PN * 128, bytes, &bar_full[s]);
+                            if (++s == kDNumStages) { s = 0; ph ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ============================ MMA issuer (rank 0) / weight relay (rank 1) ==================
+        if (rank == 0) {
+            constexpr uint32_t idesc256 = ptx::umma_idesc_bf16(256, 256, false, false);
+            constexpr uint32_t idesc128 = ptx::umma_idesc_bf16(256, 128, false, false);
+            const uint32_t w_lo = ptx::umma_desc_lo(ptx::smem_u32(sW));
+            const uint32_t full_a = ptx::smem_u32(bar_full), empty_a = ptx::smem_u32(bar_empty);
+            const uint32_t acc_a = ptx::smem_u32(bar_acc), act_a = ptx::smem_u32(bar_act);
+            uint32_t s = 0, ph = 0;
+            uint32_t act_par = 0;                            // bit t = parity of the next phase of bar_act[t]
+            for (int quad = quad0; quad < n_quads; quad += quad_step) {
+                for (int g = 0; g < nl; ++g) {
+                    const int KB = fs.layer_kb(g);
+                    const uint32_t idesc = (fs.layer_n(g, a.mode) == 256) ? idesc256 : idesc128;
+                    for (int t = 0; t < 2; ++t) {
+                        const uint32_t x_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + kDOffX + t * 16384));
+                        const uint32_t h_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + kDOffH + t * 65536));
+                        const uint32_t dcol = tmem + t * 256;
+                        // the slot's operand image (X for layer 0, the previous layer's output otherwise) is complete in
+                        // both CTAs, and its previous accumulator has been read out
+                        ptx::mbar_wait_a(act_a + 8 * t, (act_par >> t) & 1u);
+                        act_par ^= 1u << t;
+                        ptx::tc_fence_after_sync();
+                        int hs = dual_in_slot0(g);
+                        for (int kb = 0; kb < KB; ++kb) {
+                            const bool is_x = (g == 0) || (g == 4 && kb == 0);
+                            const uint32_t a_lo = is_x ? x_lo : h_lo + (hs++) * 1024;
+                            ptx::mbar_wait_a(full_a + 8 * s, ph);
+                            ptx::tc_fence_after_sync();
+                            const uint32_t b_lo = w_lo + s * (kDStageBytes >> 4);
+                            if (ptx::elect_one()) {
+                                ptx::umma2_bf16_lo(dcol, a_lo, b_lo, idesc, kb != 0);
+                                ptx::umma2_bf16_lo(dcol, a_lo + 2, b_lo + 2, idesc, 1);
+                                ptx::umma2_bf16_lo(dcol, a_lo + 4, b_lo + 4, idesc, 1);
+                                ptx::umma2_bf16_lo(dcol, a_lo + 6, b_lo + 6, idesc, 1);
+                                ptx::umma2_commit_both(empty_a + 8 * s);
+                                if (kb == KB - 1) ptx::umma2_commit_both(acc_a + 8 * t);
+                            }
+                            __syncwarp();
+                            if (++s == kDNumStages) { s = 0; ph ^= 1u; }
+                        }
+                    }
+                }
+            }
+        } else if (lane == 0) {
+            const uint32_t full_a = ptx::smem_u32(bar_full);
+            const uint32_t full_leader = ptx::mapa(full_a, 0);
+            uint32_t s = 0, ph = 0;
+            for (int quad = quad0; quad < n_quads; quad += quad_step) {
+                for (int g = 0; g < nl; ++g) {
+                    const int n = 2 * fs.layer_kb(g);
+                    for (int i = 0; i < n; ++i) {
+                        ptx::mbar_wait_a(full_a + 8 * s, ph);
+                        ptx::mbar_arrive_cluster(full_leader + 8 * s);
+                        if (++s == kDNumStages) { s = 0; ph ^= 1u; }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == kStoreWarp) {
+        // ============================ activation storer (NWB_MLP_SAVE) ===========================
+        // images are stored in the order the epilogue finishes them: X of slot 0, X of slot 1, then (layer, slot);
+        // a slot is handed back as soon as the copy engine has read the image out of shared memory
+        if (lane == 0 && save) {
+            const SaveLayout sl{fs.kx, transient};
+            uint32_t st_par = 0;
+            auto store = [&](int t, bool ghost, const uint8_t* src, uint8_t* dst, uint32_t bytes) {
+                ptx::mbar_wait_sleepy(&bar_st[t], (st_par >> t) & 1u);
+                st_par ^= 1u << t;
+                if (!ghost) ptx::bulk_s2g(dst, src, bytes);
+                ptx::bulk_commit();
+                ptx::bulk_wait_read<0>();
+                ptx::mbar_arrive(&bar_done[t]);
+            };
+            for (int quad = quad0; quad < n_quads; quad += quad_step) {
+                uint8_t* save_tile[2];
+                bool ghost[2];
+                for (int t = 0; t < 2; ++t) {
+                    const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
+                    ghost[t] = tile >= a.n_tiles;
+                    save_tile[t] = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
+                }
+                for (int t = 0; t < 2; ++t) store(t, ghost[t], smem + kDOffX + t * 16384, save_tile[t] + sl.x_off(), 16384);
+                for (int g = 0; g < nl; ++g)
+                    for (int t = 0; t < 2; ++t)
+                        store(t, ghost[t], smem + kDOffH + t * 65536, save_tile[t] + sl.act_off(g),
+                              static_cast<uint32_t>(layer_quarters(g, transient)) * 16384u);
+            }
+            ptx::bulk_wait_all<0>();
+        }
+        __syncwarp();
+    } else {
+        // ============================ epilogue warps (four threads per point) ====================
+        const int ew = warp - kEpiWarp0;                   // 0..15
+        const int quad_l = warp & 3;                       // TMEM lane quadrant this warp may read
+        const int sub = ew >> 2;                           // 16-column slice of every 64-column quarter
+        const int row = quad_l * 32 + lane;
+        const uint32_t tlane = tmem + (static_cast<uint32_t>(quad_l * 32) << 16);
+        const float* cst = reinterpret_cast<const float*>(smem + kDOffC);
+        const SaveLayout sl{fs.kx, transient};
+        const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
+        uint32_t acc_par = 0;                              // bit t = parity of the next phase of bar_acc[t]
+        uint32_t n_writes[2] = {0, 0};                     // images written into slot t so far (save: each waits for the
+                                                           // previous one's store to have been read)
+        auto wait_slot_free = [&](int t) {
+            if (save && n_writes[t] > 0) ptx::mbar_wait_sleepy(&bar_done[t], (n_writes[t] - 1) & 1u);
+            ++n_writes[t];
+        };
+        auto hand_over = [&](int t, bool feeds_mma) {      // after this thread's shared-memory writes of the image
+            ptx::fence_proxy_async_smem();
+            ptx::tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) {
+                if (feeds_mma) { if (rank == 0) ptx::mbar_arrive(&bar_act[t]); else ptx::mbar_arrive_cluster(act_leader + 8 * t); }
+                if (save) ptx::mbar_arrive(&bar_st[t]);
+            }
+        };
+        for (int quad = quad0; quad < n_quads; quad += quad_step) {
+            long long p[2];
+            bool valid[2], ghost[2];
+            long long ray[2];
+            uint8_t* save_tile[2];
+            // ---- encoded-xyz operand tiles of both slots: this thread packs columns [16*sub, 16*sub+16) of its row ----
+#pragma unroll 1
+            for (int t = 0; t < 2; ++t) {
+                const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
+                ghost[t] = tile >= a.n_tiles;
+                p[t] = static_cast<long long>(tile) * kTileM + row;
+                valid[t] = p[t] < a.n_points;
+                ray[t] = valid[t] ? p[t] / a.S : 0;
+                save_tile[t] = save ? a.saved + static_cast<size_t>(tile) * a.save_tile_bytes : nullptr;
+                uint8_t* sX = smem + kDOffX + t * 16384;
+                float e[64];
+#pragma unroll
+                for (int c = 0; c < 64; ++c) e[c] = 0.0f;
+                if (valid[t]) {
+                    if (a.x_enc != nullptr) {
+                        const float* xr = a.x_enc + p[t] * fs.in_xyz;
+#pragma unroll
+                        for (int c = 0; c < 64; ++c)
+                            if (c < fs.in_xyz && (c >> 4) == sub) e[c] = __ldg(xr + c);
+                    } else {
+                        const float* rr = a.rays + ray[t] * a.ray_stride;
+                        const float zz = __ldg(a.z + p[t]);
+                        float sn[3], cs[3];
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) {
+                            e[i] = __fadd_rn(__ldg(rr + i), __fmul_rn(__ldg(rr + 3 + i), zz));   // rendering.py:261
+                            sincosf(e[i], &sn[i], &cs[i]);
+                        }
+                        // octave k+1 from octave k by the double-angle identities (see the first-generation kernel)
+#pragma unroll
+                        for (int k = 0; k < 10; ++k) {
+                            if (k < a.n_freq_xyz) {
+#pragma unroll
+                                for (int i = 0; i < 3; ++i) {
+                                    e[3 + 6 * k + i] = sn[i];
+                                    e[6 + 6 * k + i] = cs[i];
+                                    const float s2 = 2.0f * sn[i] * cs[i];
+                                    const float c2 = fmaf(-2.0f * sn[i], sn[i], 1.0f);
+                                    sn[i] = s2; cs[i] = c2;
+                                }
+                            }
+                        }
+                    }
+                }
+                uint32_t pk[8];
+#pragma unroll
+                for (int s4 = 0; s4 < 4; ++s4) {
+                    if (s4 == sub) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(e[16 * s4 + 2 * j], e[16 * s4 + 2 * j + 1]);
+                    }
+                }
+                // X_t doubles as the head scratch of the previous quad (its last combine ended with a barrier)
+                wait_slot_free(t);
+                *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                hand_over(t, true);
+            }
+
+            float sigma[2] = {0.0f, 0.0f}, rgb[2][3] = {{0, 0, 0}, {0, 0, 0}};
+            for (int g = 0; g < nl; ++g) {
+                const bool last = (g == nl - 1);
+                const int nq = layer_quarters(g, transient);
+#pragma unroll 1
+                for (int t = 0; t < 2; ++t) {
+                    uint8_t* sH = smem + kDOffH + t * 65536;
+                    float* s_part = reinterpret_cast<float*>(smem + kDOffX + t * 16384);    // [3][5][128] head partial sums:
+                                                                                             // X_t is dead once layer 4 is done
+                    const float* rb = (a.ray_bias != nullptr) ? a.ray_bias + ray[t] * 256 : nullptr;
+                    const uint32_t tacc = tlane + t * 256 + sub * 16;
+                    ptx::mbar_wait_sleepy(&bar_acc[t], (acc_par >> t) & 1u);
+                    acc_par ^= 1u << t;
+                    ptx::tc_fence_after_sync();
+                    wait_slot_free(t);                       // save: the storer has read the image this one overwrites
+                    float hacc[5] = {0, 0, 0, 0, 0};
+                    // sign masks: per layer and row 16 x uint16 laid out [sub][quarter]; bit (15-j) of entry (sub, q) =
+                    // sign of the pre-activation of column 64q + 16sub + j; one 8-byte store per thread after the handoff
+                    unsigned long long mbits = 0ull;
+#pragma unroll 1
+                    for (int q = 0; q < nq; ++q) {
+                        const int c0 = q * 64 + sub * 16;   // this thread's 16 columns of quarter q
+                        uint8_t* blk = sH + q * 16384;      // in place: quarter q = K-block q of the next layer's operand
+                        uint32_t md = 0;
+                        if (g < 7) {
+                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        } else if (g == 7) {
+                            epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
+                                                        hacc, blk, row, 2 * sub, md);
+                        } else if (g == 8) {
+                            epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        } else if (g == 9) {
+                            // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
+                            if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md);
+                            else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        } else if (g < 12) {
+                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        } else {
+                            // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
+                            epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
+                                                        hacc, blk, row, 2 * sub, md);
+                        }
+                        if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
+                    }
+                    hand_over(t, !last);
+                    if (save && g != 8 && !ghost[t])
+                        *reinterpret_cast<unsigned long long*>(save_tile[t] + sl.mask_off(g, nl) + row * 32 + sub * 8) = mbits;
+                    // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
+                    const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
+                    if (nh_heads > 0) {
+                        if (sub > 0) {
+                            for (int h = 0; h < nh_heads; ++h) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
+                        }
+                        epi_bar_all();
+                        if (sub == 0) {
+                            for (int h = 0; h < nh_heads; ++h)
+                                hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
+                            if (g == 7) sigma[t] = softplus_f(hacc[0] + cst[ConstOff::head_b]);                // nerf.py:190
+                            if (g == 9) {
+#pragma unroll
+                                for (int i = 0; i < 3; ++i) rgb[t][i] = sigmoid_f(hacc[i] + cst[ConstOff::head_b + 1 + i]);   // nerf.py:197
+                            }
+                        }
+                        epi_bar_all();                       // scratch is read before anyone rewrites it
+                    }
+                    // ---- tile outputs ---------------------------------------------------------------
+                    if (last && valid[t] && sub == 0) {
+                        if (sigma_only) {
+                            a.raw_out[p[t]] = sigma[t];
+                        } else {
+                            float* o = a.raw_out + p[t] * (transient ? 9 : 4);
+                            o[0] = rgb[t][0]; o[1] = rgb[t][1]; o[2] = rgb[t][2]; o[3] = sigma[t];   // nerf.py:198
+                            if (transient) {
+                                const float* hb = cst + ConstOff::head_b;
+                                o[4] = sigmoid_f(hacc[1] + hb[5]);                           // nerf.py:206
+                                o[5] = sigmoid_f(hacc[2] + hb[6]);
+                                o[6] = sigmoid_f(hacc[3] + hb[7]);
+                                o[7] = softplus_f(hacc[0] + hb[4]);                          // nerf.py:205
+                                o[8] = softplus_f(hacc[4] + hb[8]);                          // nerf.py:207
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::cluster_sync_all();                               // the partner has finished with my shared memory / TMEM too
+    if (warp == 1) ptx::tmem_dealloc_pair<512>(tmem);
+}
+
+}  // namespace nwb
