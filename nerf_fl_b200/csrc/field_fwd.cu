@@ -101,11 +101,16 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
 #pragma unroll
     for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(x[2 * j], x[2 * j + 1]);
     if (kRelu && kSave) {
-        uint32_t neg = 0;                                  // packed word j: bit 15 = column 2j, bit 31 = column 2j+1
+        // packed word j: bit 15 = sign of column 2j, bit 31 = sign of column 2j+1.  Two words at a time: the four
+        // sign-carrying bytes are gathered with one byte permute, reduced to 0/1 per byte, and one multiply lines the
+        // four bits up as a nibble, column 4k first (0x08040201: byte i -> bit 27-i, no carries can reach bit 24)
+        uint32_t neg = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-            neg |= (((pk[j] >> 15) & 1u) << (15 - 2 * j)) | ((pk[j] >> 31) << (14 - 2 * j));
-        neg_out = neg;
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t b = (__byte_perm(pk[2 * k], pk[2 * k + 1], 0x7531) >> 7) & 0x01010101u;
+            neg |= ((b * 0x08040201u) >> 24) << (12 - 4 * k);
+        }
+        neg_out = neg & 0xFFFFu;
     }
     if (kRelu) {
 #pragma unroll
@@ -573,7 +578,13 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
         configured = true;
     }
     // second-generation kernel (CTA pairs, two tiles in flight per CTA); NWB_FWD_GEN=1 selects the first one
-    static const bool dual = [] { const char* e = getenv("NWB_FWD_GEN"); return e == nullptr || e[0] != '1'; }();
+    // Either kernel is used where it is faster: the pair kernel needs 74 clusters x 4 tiles per round against 148
+    // CTAs x 1 tile, and a round of it costs ~1.55x (inference) / ~1.85x (saving activations) a round of the
+    // one-tile kernel [B200, tools/perf_fwd.py] -- so small launches can lose to wave quantisation.
+    static const int gen = [] { const char* e = getenv("NWB_FWD_GEN"); return e == nullptr ? 0 : atoi(e); }();   // 1 / 2 force a kernel
+    const double r1 = (a.n_tiles + kNumSMs - 1) / kNumSMs;
+    const double r2 = ((a.n_tiles + 3) / 4 + kNumSMs / 2 - 1) / (kNumSMs / 2) * ((mode & NWB_MLP_SAVE) ? 1.85 : 1.55);
+    const bool dual = gen == 2 || (gen != 1 && r2 < r1);
     if (dual) {
         static bool configured2 = false;
         if (!configured2) {
