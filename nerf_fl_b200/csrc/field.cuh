@@ -83,8 +83,9 @@ inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
 
 // saved-activation layout per tile (forward NWB_MLP_SAVE): bf16 tile images followed by ReLU sign masks
 //   [X: kx*16K][h1..h8: 8 x 64K][feat: 64K][dir|t0: 32K or 64K][t2,t4,t6: 3 x 32K][masks: 13 x 4K]
-// masks: per layer g, per row 16 x uint16 laid out [sub][quarter]: bit (15-j) of entry (sub, q) = 1 iff the
-// pre-activation of column 64q + 16sub + j was negative (ReLU gate closed).
+// masks: per layer g four 1 KB sub-blocks [sub][row] of 4 x uint16: bit (15-j) of entry q of (sub, row) = 1 iff the
+// pre-activation of column 64q + 16sub + j of that row was negative (ReLU gate closed).  A forward epilogue thread owns
+// one (sub, row) entry group: its warp writes 256 contiguous bytes.
 struct SaveLayout {
     int kx; bool transient;
     __host__ __device__ size_t x_off() const { return 0; }

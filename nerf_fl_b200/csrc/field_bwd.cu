@@ -242,9 +242,11 @@ field_dgrad_kernel(const BwdArgs a) {
                 // ReLU gates of layer g (prefetched before waiting for the accumulator)
                 uint32_t mw[8];
                 if (g != 8) {
-                    // forward layout: 16 x uint16 per row, entry (sub, q) at sub*4 + q, bit (15-j) = column 64q+16sub+j
-                    const uint4* mp = reinterpret_cast<const uint4*>(save_tile + sl.mask_off(g, nl) + row * 32);
-                    const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
+                    // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit (15-j) = column 64q+16sub+j);
+                    // gathered here into the old per-row order, entry (sub, q) at sub*4 + q
+                    const uint2* mp = reinterpret_cast<const uint2*>(save_tile + sl.mask_off(g, nl)) + row;
+                    const uint2 a0 = __ldg(mp), a1 = __ldg(mp + 128), a2 = __ldg(mp + 256), a3 = __ldg(mp + 384);
+                    const uint4 m0 = make_uint4(a0.x, a0.y, a1.x, a1.y), m1 = make_uint4(a2.x, a2.y, a3.x, a3.y);
                     const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
                     for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31, bit (31-j) = column 32w+j

@@ -427,7 +427,7 @@ field_fwd_kernel(const FwdArgs a) {
                 ptx::tc_fence_after_sync();
                 NWB_TRACE(tile == 0 && warp == kEpiWarp0 && lane == 0, g * 16 + 10);          // accumulator seen
                 float hacc[5] = {0, 0, 0, 0, 0};
-                // sign masks: per layer and row 16 x uint16 laid out [sub][quarter]; bit (15-j) of entry (sub, q) =
+                // sign masks: per layer [sub][row] x 4 uint16 (one per quarter: a warp's store is 256 contiguous bytes); bit (15-j) of entry q =
                 // sign of the pre-activation of column 64q + 16sub + j.  A thread owns the four entries of its sub
                 // and writes them as ONE 8-byte store after the quarter loop (a global store ahead of the per-
                 // quarter proxy fence would stall the handoff).
@@ -477,7 +477,7 @@ field_fwd_kernel(const FwdArgs a) {
                     }
                 }
                 if (save && g != 8)
-                    *reinterpret_cast<unsigned long long*>(save_tile + sl.mask_off(g, nl) + row * 32 + sub * 8) = mbits;
+                    *reinterpret_cast<unsigned long long*>(save_tile + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
                 // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                 const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                 if (nh_heads > 0) {

@@ -305,7 +305,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                     ptx::tc_fence_after_sync();
                     wait_slot_free(t);                       // save: the storer has read the image this one overwrites
                     float hacc[5] = {0, 0, 0, 0, 0};
-                    // sign masks: per layer and row 16 x uint16 laid out [sub][quarter]; bit (15-j) of entry (sub, q) =
+                    // sign masks: per layer [sub][row] x 4 uint16 (one per quarter: a warp's store is 256 contiguous bytes); bit (15-j) of entry q =
                     // sign of the pre-activation of column 64q + 16sub + j; one 8-byte store per thread after the handoff
                     unsigned long long mbits = 0ull;
 #pragma unroll 1
@@ -335,7 +335,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                     }
                     hand_over(t, !last);
                     if (save && g != 8 && !ghost[t])
-                        *reinterpret_cast<unsigned long long*>(save_tile[t] + sl.mask_off(g, nl) + row * 32 + sub * 8) = mbits;
+                        *reinterpret_cast<unsigned long long*>(save_tile[t] + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
                     // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                     const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                     if (nh_heads > 0) {
