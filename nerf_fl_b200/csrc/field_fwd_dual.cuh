@@ -31,6 +31,12 @@ constexpr int kDOffBar = kDOffC + 16384;
 constexpr int kDSmem = kDOffBar + 256;
 static_assert(kDSmem <= 232448, "dual-tile forward exceeds the 227 KB shared-memory limit");
 
+// Sign masks of layers >= kDMaskSmemFrom go through shared memory (the upper half of the slot's xyz buffer, dead
+// once layer 4's MMAs are done; the lower half is the head scratch) and ride in the image's bulk store; a global
+// store from the epilogue threads makes the next proxy fence (MEMBAR) wait for it -- ~10 % of the kernel.
+constexpr int kDMaskOff = 8192;
+constexpr int kDMaskSmemFrom = 5;
+
 // first activation K-block (16 KB slot of the slot's H image) layer g reads, after the optional X block
 __device__ __forceinline__ int dual_in_slot0(int g) { return g == 10 ? 2 : 0; }
 
@@ -174,10 +180,11 @@ field_fwd_dual_kernel(const FwdArgs a) {
         if (lane == 0 && save) {
             const SaveLayout sl{fs.kx, transient};
             uint32_t st_par = 0;
-            auto store = [&](int t, bool ghost, const uint8_t* src, uint8_t* dst, uint32_t bytes) {
+            auto store = [&](int t, bool ghost, const uint8_t* src, uint8_t* dst, uint32_t bytes, uint8_t* mask_dst) {
                 ptx::mbar_wait_sleepy(&bar_st[t], (st_par >> t) & 1u);
                 st_par ^= 1u << t;
                 if (!ghost) ptx::bulk_s2g(dst, src, bytes);
+                if (!ghost && mask_dst != nullptr) ptx::bulk_s2g(mask_dst, smem + kDOffX + t * 16384 + kDMaskOff, 4096);
                 ptx::bulk_commit();
                 ptx::bulk_wait_read<0>();
                 ptx::mbar_arrive(&bar_done[t]);
@@ -190,11 +197,12 @@ field_fwd_dual_kernel(const FwdArgs a) {
                     ghost[t] = tile >= a.n_tiles;
                     save_tile[t] = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
                 }
-                for (int t = 0; t < 2; ++t) store(t, ghost[t], smem + kDOffX + t * 16384, save_tile[t] + sl.x_off(), 16384);
+                for (int t = 0; t < 2; ++t) store(t, ghost[t], smem + kDOffX + t * 16384, save_tile[t] + sl.x_off(), 16384, nullptr);
                 for (int g = 0; g < nl; ++g)
                     for (int t = 0; t < 2; ++t)
                         store(t, ghost[t], smem + kDOffH + t * 65536, save_tile[t] + sl.act_off(g),
-                              static_cast<uint32_t>(layer_quarters(g, transient)) * 16384u);
+                              static_cast<uint32_t>(layer_quarters(g, transient)) * 16384u,
+                              (g >= kDMaskSmemFrom && g != 8) ? save_tile[t] + sl.mask_off(g, nl) : nullptr);
             }
             ptx::bulk_wait_all<0>();
         }
@@ -333,8 +341,10 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         }
                         if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
                     }
+                    if (save && g >= kDMaskSmemFrom && g != 8)
+                        *reinterpret_cast<unsigned long long*>(smem + kDOffX + t * 16384 + kDMaskOff + sub * 1024 + row * 8) = mbits;
                     hand_over(t, !last);
-                    if (save && g != 8 && !ghost[t])
+                    if (save && g < kDMaskSmemFrom && !ghost[t])
                         *reinterpret_cast<unsigned long long*>(save_tile[t] + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
                     // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                     const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
