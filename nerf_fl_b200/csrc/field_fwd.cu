@@ -58,6 +58,7 @@ struct FwdArgs {
     int S;
     long long n_points;
     int n_tiles;
+    int first_tile;        // one-tile kernel: tiles [first_tile, n_tiles); pair kernel: tiles [0, n_tiles)
     uint32_t mode;
     float* raw_out;
     uint8_t* saved;
@@ -217,7 +218,7 @@ field_fwd_kernel(const FwdArgs a) {
         // contiguous in the packed image (field_pack.cu), one bulk copy
         if (lane == 0) {
             uint32_t s = 0, ph = 0;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 for (int g = 0; g < nl; ++g) {
                     const uint8_t* wsrc = a.packed + s_woff[g];
                     const int KB = fs.layer_kb(g), PN = fs.packed_n(g);
@@ -256,7 +257,7 @@ field_fwd_kernel(const FwdArgs a) {
             // kb+1 of the SAME layer are taken between the 2nd and 3rd MMA of K-block kb: two queued MMAs keep the
             // tensor pipe busy meanwhile.  (Never across a layer boundary: the next layer's first K-block is
             // produced by an epilogue that itself waits for this layer's last MMAs.)
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 int isl = 0;                                 // slot of the next activation K-block (round-robin, per tile)
                 for (int g = 0; g < nl; ++g) {
                     const int KB = fs.layer_kb(g);
@@ -325,7 +326,7 @@ field_fwd_kernel(const FwdArgs a) {
                 prev2 = prev1;
                 prev1 = slot;
             };
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 uint8_t* save_tile = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
                 store(kSlotX, sX, save_tile + sl.x_off());
                 for (int g = 0; g < nl; ++g) {
@@ -352,7 +353,7 @@ field_fwd_kernel(const FwdArgs a) {
         uint32_t acc_ev = 0;                               // layers consumed (parity of bar_acc)
         uint32_t seen = 0, done_par = 0;                   // save mode: slots written before / parity of their next hand-back
         uint32_t tcount = 0;                               // tiles done by this CTA
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tcount) {
+        for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tcount) {
             const long long p = static_cast<long long>(tile) * kTileM + row;
             const bool valid = p < a.n_points;
             const long long ray = valid ? p / a.S : 0;
@@ -578,27 +579,32 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
         configured = true;
     }
     // second-generation kernel (CTA pairs, two tiles in flight per CTA); NWB_FWD_GEN=1 selects the first one
-    // Either kernel is used where it is faster: the pair kernel needs 74 clusters x 4 tiles per round against 148
-    // CTAs x 1 tile, and a round of it costs ~1.55x (inference) / ~1.85x (saving activations) a round of the
-    // one-tile kernel [B200, tools/perf_fwd.py] -- so small launches can lose to wave quantisation.
+    // Two kernels, each used where it is faster [B200, tools/perf_fwd.py]: a round of the pair kernel (74 clusters x
+    // 4 tiles) costs ~1.55x (inference) / ~1.75x (saving activations) a round of the one-tile kernel (148 CTAs x 1
+    // tile).  So: whole rounds of 296 tiles go to the pair kernel, and a remainder of <= 148 tiles -- which would
+    // cost it a full round -- goes to the one-tile kernel, launched behind it on the same stream.
     static const int gen = [] { const char* e = getenv("NWB_FWD_GEN"); return e == nullptr ? 0 : atoi(e); }();   // 1 / 2 force a kernel
-    const double r1 = (a.n_tiles + kNumSMs - 1) / kNumSMs;
-    const double r2 = ((a.n_tiles + 3) / 4 + kNumSMs / 2 - 1) / (kNumSMs / 2) * ((mode & NWB_MLP_SAVE) ? 1.85 : 1.55);
-    const bool dual = gen == 2 || (gen != 1 && r2 < r1);
-    if (dual) {
+    constexpr int kRound = 4 * (kNumSMs / 2);
+    int pair_tiles = a.n_tiles;                                     // tiles [0, pair_tiles) -> pair kernel
+    if (gen == 1) pair_tiles = 0;
+    else if (gen != 2 && a.n_tiles % kRound != 0 && a.n_tiles % kRound <= kNumSMs) pair_tiles = a.n_tiles - a.n_tiles % kRound;
+    if (pair_tiles > 0) {
         static bool configured2 = false;
         if (!configured2) {
             NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
             NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
             configured2 = true;
         }
-        const int grid2 = 2 * std::min((a.n_tiles + 3) / 4, kNumSMs / 2);
-        if (mode & NWB_MLP_SAVE) field_fwd_dual_kernel<true><<<grid2, kFwdThreads, kDSmem, static_cast<cudaStream_t>(stream)>>>(a);
-        else field_fwd_dual_kernel<false><<<grid2, kFwdThreads, kDSmem, static_cast<cudaStream_t>(stream)>>>(a);
+        FwdArgs a2 = a;
+        a2.n_tiles = pair_tiles;
+        const int grid2 = 2 * std::min((pair_tiles + 3) / 4, kNumSMs / 2);
+        if (mode & NWB_MLP_SAVE) field_fwd_dual_kernel<true><<<grid2, kFwdThreads, kDSmem, static_cast<cudaStream_t>(stream)>>>(a2);
+        else field_fwd_dual_kernel<false><<<grid2, kFwdThreads, kDSmem, static_cast<cudaStream_t>(stream)>>>(a2);
         NWB_LAUNCH_CHECK();
-        return NWB_OK;
+        if (pair_tiles == a.n_tiles) return NWB_OK;
     }
-    int grid = std::min(a.n_tiles, kNumSMs);
+    a.first_tile = pair_tiles;
+    int grid = std::min(a.n_tiles - a.first_tile, kNumSMs);
     if (const char* e = getenv("NWB_DEBUG_GRID")) grid = std::max(1, std::min(grid, atoi(e)));   // bottleneck experiments only
     if (mode & NWB_MLP_SAVE) field_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
     else field_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
