@@ -15,9 +15,9 @@
 namespace nwb {
 
 constexpr int kBwdThreads = 192;
-constexpr int kBStageBytes = 16384;                // 4 k-blocks x 32 n-rows x 128 B
+constexpr int kBStageBytes = 8192;                 // this CTA's half of a stage: 2 of the 4 k-blocks x 32 n-rows x 128 B
 constexpr int kBChunkBytes = 4096;                 // one k-block's 32 rows
-constexpr int kBNumStages = 3;                  // the kernel is bound by the latency of the weight stream: depth matters
+constexpr int kBNumStages = 6;                  // the kernel is bound by the latency of the weight stream: depth matters
 constexpr int kBOffD = 0;                       // 64 KB  dZ image (A operand)
 constexpr int kBOffP = kBOffD;                  // 16 KB  dpre block image: aliases the dZ image (stored and read out
                                                 //        before layer nl-1 writes its dZ; same bulk_wait_read guard)
@@ -84,7 +84,7 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, cons
     store_slice_bf16(sD, row, c_out, x);
 }
 
-__global__ void __launch_bounds__(kBwdThreads, 2)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 2)
 field_dgrad_kernel(const BwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sP = smem + kBOffP;
@@ -99,6 +99,12 @@ field_dgrad_kernel(const BwdArgs a) {
     float* s_hb = reinterpret_cast<float*>(s_woff + kMaxG + 1);   // [9] head-bias gradient partials
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // CTA pairs: one tcgen05.mma.cta_group::2 per K-step covers this CTA's tile and its partner's (M = 256), and
+    // each CTA stages only HALF of every weight stage (its half of the output k-blocks) -- the kernel waits for
+    // the weight stream 30 % of the time, and two CTAs per SM leave each only 48 KB of ring.
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int pair0 = static_cast<int>(ptx::cluster_id_x()), pair_step = static_cast<int>(ptx::cluster_count_x());
+    const int n_pairs = (a.n_tiles + 1) >> 1;      // an odd tail tile is paired with a ghost (protocol only)
     const FieldShape& fs = a.fs;
     const int nl = fs.n_layers(a.mode);            // 10 or 13
     const bool transient = (a.mode & NWB_MLP_TRANSIENT) != 0;
@@ -108,16 +114,18 @@ field_dgrad_kernel(const BwdArgs a) {
             printf("nwb: dynamic shared memory is not 1 KB aligned\n");
             __trap();
         }
-        for (int s = 0; s < kBNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], 1); }
+        // leader's full barrier: own producer (+ bytes) and the partner's relay; completions are multicast
+        for (int s = 0; s < kBNumStages; ++s) { ptx::mbar_init(&bar_full[s], rank == 0 ? 2 : 1); ptx::mbar_init(&bar_empty[s], 1); }
         ptx::mbar_init(bar_acc, 1);
-        ptx::mbar_init(bar_act, 128);
+        ptx::mbar_init(bar_act, 2);                 // one arrival per CTA (its epilogue leader), on the leader CTA's copy
         ptx::fence_mbar_init();
         for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
         for (int i = 0; i < 9; ++i) s_hb[i] = 0.0f;
     }
-    if (warp == 1) ptx::tmem_alloc<256>(tmem_slot);
+    if (warp == 1) ptx::tmem_alloc_pair<256>(tmem_slot);
     ptx::tc_fence_before_sync();
     __syncthreads();
+    ptx::cluster_sync_all();
     ptx::tc_fence_after_sync();
     const uint32_t tmem = *tmem_slot;
 
@@ -129,18 +137,18 @@ field_dgrad_kernel(const BwdArgs a) {
             // so one tcgen05.mma covers the layer's whole output width (N = 64*KBO) and the dZ operand is read once
             // per K-step instead of once per 64-column output block
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int pair = pair0; pair < n_pairs; pair += pair_step) {
                 for (int g = nl - 1; g >= 1; --g) {
                     const uint8_t* wsrc = a.packed + s_woff[g];
-                    const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> 5, PN = fs.packed_n(g);
-                    const int kshift = (g == 4) ? fs.kx : 0;       // skip the encoded-xyz slab: no d/dx needed
+                    const int KH = (g >= 10) ? 1 : 2, NC = fs.layer_n(g, a.mode) >> 5, PN = fs.packed_n(g);   // my k-blocks
+                    const int kshift = ((g == 4) ? fs.kx : 0) + static_cast<int>(rank) * KH;   // layer 4: skip the xyz slab
                     for (int c = 0; c < NC; ++c, ++it) {
                         const uint32_t s = it % kBNumStages;
                         ptx::mbar_wait(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
-                        ptx::mbar_arrive_expect_tx(&bar_full[s], static_cast<uint32_t>(KBO) * kBChunkBytes);
-                        for (int kbo = 0; kbo < KBO; ++kbo)
-                            ptx::bulk_g2s(sW + s * kBStageBytes + kbo * kBChunkBytes,
-                                          wsrc + static_cast<size_t>(kbo + kshift) * PN * 128 + c * kBChunkBytes, kBChunkBytes,
+                        ptx::mbar_arrive_expect_tx(&bar_full[s], static_cast<uint32_t>(KH) * kBChunkBytes);
+                        for (int kl = 0; kl < KH; ++kl)
+                            ptx::bulk_g2s(sW + s * kBStageBytes + kl * kBChunkBytes,
+                                          wsrc + static_cast<size_t>(kl + kshift) * PN * 128 + c * kBChunkBytes, kBChunkBytes,
                                           &bar_full[s]);
                     }
                 }
@@ -149,34 +157,51 @@ field_dgrad_kernel(const BwdArgs a) {
         __syncwarp();
     } else if (warp == 1) {
         // ============================ MMA issuer =================================================
-        if (lane == 0) {
-            // D(128 x 64*KBO) += dZ(128 x 16 n, K-major) . W(16 n-rows x 64*KBO k-cols, MN-major: 8-row groups 1 KB
-            // apart, 64-column k-blocks kBChunkBytes apart inside the stage)
+        if (lane == 0 && rank == 0) {
+            // D(256 x 64*KBO) += dZ(128 x 16 n per CTA, K-major) . W(16 n-rows x 64*KBO k-cols, MN-major; each CTA holds
+            // its half of the k-blocks: 8-row groups 1 KB apart, k-blocks kBChunkBytes apart inside the stage)
             const uint32_t da = ptx::smem_u32(sD), wa = ptx::smem_u32(sW);
+            const uint32_t full_a = ptx::smem_u32(bar_full), empty_a = ptx::smem_u32(bar_empty);
+            const uint32_t acc_a = ptx::smem_u32(bar_acc), act_a = ptx::smem_u32(bar_act);
             uint32_t it = 0, ev = 0;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            for (int pair = pair0; pair < n_pairs; pair += pair_step) {
                 for (int g = nl - 1; g >= 1; --g) {
-                    ptx::mbar_wait(bar_act, ev & 1u);
+                    ptx::mbar_wait_a(act_a, ev & 1u);
                     ++ev;
                     ptx::tc_fence_after_sync();
-                    NWB_BTRACE(tile == static_cast<int>(blockIdx.x), g * 8 + 0);      // dZ_g seen by the MMA thread
+                    NWB_BTRACE(pair == pair0, g * 8 + 0);      // dZ_g seen by the MMA thread
                     const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> 5;
-                    const uint32_t idesc = ptx::umma_idesc_bf16(128, 64 * KBO, false, true);
+                    const uint32_t idesc = ptx::umma_idesc_bf16(256, 64 * KBO, false, true);
                     const uint32_t dcol = (g == 10) ? 128u : 0u;
                     for (int c = 0; c < NC; ++c, ++it) {
                         const uint32_t s = it % kBNumStages;
-                        ptx::mbar_wait(&bar_full[s], (it / kBNumStages) & 1u);
+                        ptx::mbar_wait_a(full_a + 8 * s, (it / kBNumStages) & 1u);
                         ptx::tc_fence_after_sync();
                         const uint32_t wb = wa + s * kBStageBytes;
                         const uint32_t ab = da + (c >> 1) * 16384 + (c & 1) * 64;
 #pragma unroll
                         for (int j = 0; j < 2; ++j)
-                            ptx::umma_bf16(tmem + dcol, ptx::umma_desc_sw128(ab + j * 32, 16, 1024),
-                                           ptx::umma_desc_sw128(wb + j * 2048, kBChunkBytes, 1024), idesc, (c | j) != 0);
-                        ptx::umma_commit(&bar_empty[s]);
+                            ptx::umma2_bf16(tmem + dcol, ptx::umma_desc_sw128(ab + j * 32, 16, 1024),
+                                            ptx::umma_desc_sw128(wb + j * 2048, kBChunkBytes, 1024), idesc, (c | j) != 0);
+                        ptx::umma2_commit_both(empty_a + 8 * s);
                     }
-                    ptx::umma_commit(bar_acc);
-                    NWB_BTRACE(tile == static_cast<int>(blockIdx.x), g * 8 + 1);      // all MMAs of layer g issued
+                    ptx::umma2_commit_both(acc_a);
+                    NWB_BTRACE(pair == pair0, g * 8 + 1);      // all MMAs of layer g issued
+                }
+            }
+        } else if (lane == 0) {
+            // partner: tell the leader when MY half of a weight stage has landed
+            const uint32_t full_a = ptx::smem_u32(bar_full);
+            const uint32_t full_leader = ptx::mapa(full_a, 0);
+            uint32_t it = 0;
+            for (int pair = pair0; pair < n_pairs; pair += pair_step) {
+                for (int g = nl - 1; g >= 1; --g) {
+                    const int NC = fs.layer_n(g, a.mode) >> 5;
+                    for (int c = 0; c < NC; ++c, ++it) {
+                        const uint32_t s = it % kBNumStages;
+                        ptx::mbar_wait_a(full_a + 8 * s, (it / kBNumStages) & 1u);
+                        ptx::mbar_arrive_cluster(full_leader + 8 * s);
+                    }
                 }
             }
         }
@@ -193,7 +218,10 @@ field_dgrad_kernel(const BwdArgs a) {
         const DzLayout dl{transient};
         const int C = transient ? 9 : 4;
         uint32_t acc_ev = 0;
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
+        for (int pair = pair0; pair < n_pairs; pair += pair_step) {
+            const int tile = 2 * pair + static_cast<int>(rank);
+            const bool ghost = tile >= a.n_tiles;           // partner of an odd tail tile: all rows invalid, nothing stored
             const long long p0 = static_cast<long long>(tile) * kTileM;
             const long long p = p0 + row;
             const bool valid = p < a.n_points;
@@ -236,12 +264,14 @@ field_dgrad_kernel(const BwdArgs a) {
             }
             ptx::fence_proxy_async_smem();
             epi_bar();
-            if (leader) { ptx::bulk_s2g(dz_tile + dl.dpre_off(), sP, 16384); ptx::bulk_commit(); }
+            if (leader && !ghost) { ptx::bulk_s2g(dz_tile + dl.dpre_off(), sP, 16384); ptx::bulk_commit(); }
 
             for (int g = nl - 1; g >= 0; --g) {
                 // ReLU gates of layer g (prefetched before waiting for the accumulator)
                 uint32_t mw[8];
-                if (g != 8) {
+#pragma unroll
+                for (int w = 0; w < 8; ++w) mw[w] = 0u;
+                if (g != 8 && !ghost) {
                     // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit (15-j) = column 64q+16sub+j);
                     // gathered here into the old per-row order, entry (sub, q) at sub*4 + q
                     const uint2* mp = reinterpret_cast<const uint2*>(save_tile + sl.mask_off(g, nl)) + row;
@@ -274,10 +304,10 @@ field_dgrad_kernel(const BwdArgs a) {
                     ++acc_ev;
                     ptx::tc_fence_after_sync();
                 }
-                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 2);    // accumulator seen
+                NWB_BTRACE(leader && pair == pair0, g * 8 + 2);    // accumulator seen
                 if (leader) ptx::bulk_wait_read<0>();       // the previous image's bulk store has read sD
                 epi_bar();
-                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 3);    // sD free
+                NWB_BTRACE(leader && pair == pair0, g * 8 + 3);    // sD free
                 uint32_t dz_bytes = 65536;
                 if (g >= 10) {
                     dz_bytes = 32768;
@@ -314,14 +344,14 @@ field_dgrad_kernel(const BwdArgs a) {
                     for (int c0 = 0; c0 < 256; c0 += 32)
                         bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
                 }
-                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 4);    // leader's slices written
+                NWB_BTRACE(leader && pair == pair0, g * 8 + 4);    // leader's slices written
                 ptx::fence_proxy_async_smem();
+                ptx::tc_fence_before_sync();                // this thread's tcgen05.ld of the accumulator are done
                 epi_bar();
-                NWB_BTRACE(leader && tile == static_cast<int>(blockIdx.x), g * 8 + 5);    // all slices written
-                if (leader) { ptx::bulk_s2g(dz_tile + dl.dz_off(g), sD, dz_bytes); ptx::bulk_commit(); }
-                if (g >= 1) {
-                    ptx::tc_fence_before_sync();
-                    ptx::mbar_arrive(bar_act);
+                NWB_BTRACE(leader && pair == pair0, g * 8 + 5);    // all slices written
+                if (leader) {
+                    if (!ghost) { ptx::bulk_s2g(dz_tile + dl.dz_off(g), sD, dz_bytes); ptx::bulk_commit(); }
+                    if (g >= 1) { if (rank == 0) ptx::mbar_arrive(bar_act); else ptx::mbar_arrive_cluster(act_leader); }
                 }
                 if (g == 9) {
                     // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples.  Runs
@@ -365,7 +395,8 @@ field_dgrad_kernel(const BwdArgs a) {
     }
     ptx::tc_fence_before_sync();
     __syncthreads();
-    if (warp == 1) ptx::tmem_dealloc<256>(tmem);
+    ptx::cluster_sync_all();                        // the partner has finished with my shared memory / TMEM too
+    if (warp == 1) ptx::tmem_dealloc_pair<256>(tmem);
     if (threadIdx.x < 9) {
         const int i = threadIdx.x;
         float* dst = (i == 0) ? a.g_head_b[0] : (i < 4) ? a.g_head_b[1] + (i - 1) : (i == 4) ? a.g_head_b[2]
@@ -440,7 +471,7 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
             configured = true;
         }
-        const int grid = std::min(a.n_tiles, 2 * kNumSMs);
+        const int grid = 2 * std::min((a.n_tiles + 1) / 2, kNumSMs);      // CTA pairs, two CTAs per SM
         field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
         NWB_LAUNCH_CHECK();
     }

@@ -310,6 +310,17 @@ __device__ __forceinline__ void umma2_bf16_lo(uint32_t tmem_d, uint32_t a_lo, ui
         "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(kDescHiSw128)
         : "memory");
 }
+// same with full 64-bit descriptors (MN-major operands)
+__device__ __forceinline__ void umma2_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // all MMAs issued so far by this thread arrive (once complete) on the mbarrier at this shared-memory offset in
 // BOTH CTAs of the pair
 __device__ __forceinline__ void umma2_commit_both(uint32_t bar_addr) {
