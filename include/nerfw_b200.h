@@ -245,6 +245,23 @@ int nwb_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, f
 int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
                       float weight_decay, float* state, float grad_scale, int zero_grad, void* stream);
 
+/* (f2) the same update in ONE launch that also refreshes the packed operand caches of
+ * up to 4 fields whose parameters live inside the flat buffer [p, p+n): every weight-image element and constant
+ * slot maps to one parameter, which is updated in place and written to the cache in the same pass (ends the
+ * per-step nwb_field_pack launches); `rest` lists the flat offsets no cache refers to (int32, from
+ * nwb_adam_pack_cover).  state is 32 B: the 16 B of nwb_adam_step_dev followed by a uint32 ticket (zeroed by
+ * the caller once) and padding; the step advances inside the launch.  Results are identical to
+ * nwb_adam_step_dev followed by nwb_field_pack (tests/test_optim_gpu.py). */
+int nwb_adam_pack_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                           float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
+                           const nwb_field_desc* const* descs, const nwb_field_params* const* params,
+                           void* const* packed, const int32_t* rest, int64_t n_rest, void* stream);
+/* setup: cover[off] = 1 for every flat offset the caches of these fields are built from (cover: n bytes, zeroed
+ * by the caller); the complement is the `rest` list above */
+int nwb_adam_pack_cover(float* p, int64_t n, int n_fields, const nwb_field_desc* const* descs,
+                        const nwb_field_params* const* params, void* const* packed, unsigned char* cover,
+                        void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (f1) NerfWLoss -- losses.py:19-50 -- the objective over the maps render_rays returns, forward and
  * backward as one launch each.  terms[5] = {c_l, f_l, b_l, s_l, their sum} (device); rgb_fine / beta /
@@ -261,6 +278,24 @@ int nwb_nerfw_loss_bwd(const float* rgb_coarse, const float* rgb_fine, const flo
                        const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
                        float lambda_u, float coef, const float* const* g_terms, float* d_rgb_coarse,
                        float* d_rgb_fine, float* d_beta, float* d_transient_sigmas, void* stream);
+
+/* metrics.py:4-13 (mse, psnr) over n floats: out[2] = {mean((pred-gt)^2), -10 log10 of it} (device), one launch,
+ * deterministic.  clip01 != 0 clamps pred to [0,1] first (eval.py:201).  scratch: nwb_nerfw_loss_scratch_bytes()
+ * bytes, zeroed once by the caller, not shared with a concurrently running loss call. */
+int nwb_mse_psnr(const float* pred, const float* gt, int64_t n, int clip01, void* scratch, float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (f3) rays of a pixel range of one view, generated on the device -- datasets/ray_utils.py:5-55
+ * (get_ray_directions: no +0.5 centring; get_rays: directions @ c2w[:, :3]^T, normalised; origin = c2w[:, 3])
+ * and the (N,8) row [rays_o, rays_d, near, far] of datasets/blender.py:97-100.  Pixels are row-major,
+ * pixel = j * W + i; c2w is a HOST pointer to 12 floats ((3,4) row-major), passed by value to the kernel.
+ * rays: device (n_rays, 8) fp32, 16 B aligned.
+ * ---------------------------------------------------------------------------------------- */
+int nwb_gen_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w_host, float near_,
+                 float far_, int64_t first_pixel, int64_t n_rays, float* rays, void* stream);
+
+/* (f4) eval.py:201-203: out[i] = uint8(clip(x[i], 0, 1) * 255) (truncation, as numpy's astype) over n floats */
+int nwb_pack_rgb8(const float* x, int64_t n, unsigned char* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T

@@ -132,6 +132,44 @@ nerfw_loss_bwd_kernel(const ObjArgs a, const float* g0, const float* g1, const f
     }
 }
 
+
+// metrics.py:4-13: mse = mean((pred - gt)^2), psnr = -10 log10(mse); same deterministic last-block reduction.
+// clip01: eval.py:201 clips the prediction to [0,1] before it is compared (eval.py:208-210).
+__global__ void __launch_bounds__(kObjThreads)
+mse_psnr_kernel(const float* __restrict__ pred, const float* __restrict__ gt, long long n, int clip01,
+                float* __restrict__ scratch, float* __restrict__ out) {
+    __shared__ float red[kObjThreads / 32];
+    __shared__ bool is_last;
+    const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+    float s = 0.0f;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += nth) {
+        float p = __ldg(pred + i);
+        if (clip01) p = fminf(fmaxf(p, 0.0f), 1.0f);
+        const float d = p - __ldg(gt + i);
+        s += d * d;
+    }
+    const float r = block_sum(s, red);
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + 4 * kObjMaxBlocks);
+    if (threadIdx.x == 0) {
+        scratch[4 * blockIdx.x] = r;
+        __threadfence();
+        is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        float q = 0.0f;
+        if (threadIdx.x < gridDim.x) q = *reinterpret_cast<const volatile float*>(scratch + 4 * threadIdx.x);
+        const float t = block_sum(q, red);
+        if (threadIdx.x == 0) {
+            const float mse = t / static_cast<float>(n);
+            out[0] = mse;
+            out[1] = -10.0f * log10f(mse);
+            *ticket = 0u;
+        }
+    }
+}
+
 }  // namespace nwb
 
 using namespace nwb;
@@ -164,6 +202,14 @@ extern "C" int nwb_nerfw_loss_bwd(const float* rgb_coarse, const float* rgb_fine
     ObjArgs a{rgb_coarse, rgb_fine, beta, transient_sigmas, targets, n_rays, n_ts, lambda_u, coef};
     nerfw_loss_bwd_kernel<<<obj_grid(a), kObjThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         a, g_terms[0], g_terms[1], g_terms[2], g_terms[3], g_terms[4], d_rgb_coarse, d_rgb_fine, d_beta, d_transient_sigmas);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
+extern "C" int nwb_mse_psnr(const float* pred, const float* gt, int64_t n, int clip01, void* scratch, float* out, void* stream) {
+    NWB_REQUIRE(n >= 1 && pred && gt && scratch && out, "nwb_mse_psnr: null pointer / empty input");
+    const int grid = static_cast<int>(std::max<long long>(1, std::min<long long>(kObjMaxBlocks, (n + 4 * kObjThreads - 1) / (4 * kObjThreads))));
+    mse_psnr_kernel<<<grid, kObjThreads, 0, static_cast<cudaStream_t>(stream)>>>(pred, gt, n, clip01, static_cast<float*>(scratch), out);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }

@@ -2,11 +2,21 @@
 // torch.optim.Adam(lr, eps=1e-8, weight_decay) over every trainable tensor; train.py:139-142).
 // One vectorised elementwise pass over the 1.3 M parameters: reads p, g, m, v, writes p, m, v and
 // (optionally) clears g for the next step's atomic accumulation -- HBM-bound, 7 floats per element.
-#include "common.cuh"
+#include "field_pack.cuh"
 #include <algorithm>
 #include <math.h>
 
 namespace nwb {
+
+// torch.optim.Adam's update; every rounding spelled out so that the plain and the cache-refreshing kernels (and any
+// future variant) produce the same bits
+__device__ __forceinline__ void adam_update(float& pp, float gg, float& mm, float& vv, float beta1, float beta2, float eps,
+                                            float wd, float gscale, float step_size, float inv_sqrt_bc2) {
+    gg = __fmaf_rn(wd, pp, __fmul_rn(gg, gscale));
+    mm = __fmaf_rn(beta1, mm, __fmul_rn(1.0f - beta1, gg));
+    vv = __fmaf_rn(beta2, vv, __fmul_rn(__fmul_rn(1.0f - beta2, gg), gg));
+    pp = __fsub_rn(pp, __fdiv_rn(__fmul_rn(step_size, mm), __fmaf_rn(__fsqrt_rn(vv), inv_sqrt_bc2, eps)));
+}
 
 __global__ void __launch_bounds__(256)
 adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4,
@@ -18,10 +28,7 @@ adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__
         inv_sqrt_bc2 = hyper[3];
     }
     auto upd = [&](float& pp, float gg, float& mm, float& vv) {
-        gg = gg * gscale + wd * pp;
-        mm = beta1 * mm + (1.0f - beta1) * gg;
-        vv = beta2 * vv + (1.0f - beta2) * gg * gg;
-        pp -= step_size * mm / (sqrtf(vv) * inv_sqrt_bc2 + eps);
+        adam_update(pp, gg, mm, vv, beta1, beta2, eps, wd, gscale, step_size, inv_sqrt_bc2);
     };
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
@@ -48,6 +55,94 @@ __global__ void adam_tick_kernel(float* state, float beta1, float beta2) {
     const double bc1 = 1.0 - pow(static_cast<double>(beta1), t), bc2 = 1.0 - pow(static_cast<double>(beta2), t);
     state[2] = static_cast<float>(static_cast<double>(state[1]) / bc1);
     state[3] = static_cast<float>(1.0 / sqrt(bc2));
+}
+
+
+// ---- (f2) Adam that also refreshes the packed operand caches ------------------------------------------------------
+// One launch walks (1) every element of every field's bf16 weight images and (2) constant block -- each maps to exactly
+// one fp32 parameter (field_pack.cuh) which is updated in place and written straight into the cache -- and (3) `rest`,
+// the flat offsets no image or constant refers to (per-ray tail columns of dir_encoding / transient_encoding.0, their
+// biases, the embedding tables, alignment padding).  The step state advances inside the same launch: every block derives
+// the new step's scalars from state[0], the last block to finish stores them (ticket in state[4]).
+constexpr int kAdamMaxFields = 4;
+
+struct AdamPackArgs {
+    PackArgs f[kAdamMaxFields];
+    uint8_t* packed[kAdamMaxFields];
+    int y0[kAdamMaxFields + 1];          // first blockIdx.y of each field's slices (its layers, then its constants)
+    int n_fields;
+    float *p, *g, *m, *v;
+    const int32_t* rest;
+    int n_rest;
+    unsigned char* cover;                // mark mode (setup): cover[off] = 1 for every referenced parameter, no update
+    float beta1, beta2, eps, wd, gscale;
+    int zero_grad;
+    float* state;
+};
+
+__global__ void __launch_bounds__(256)
+adam_pack_kernel(const AdamPackArgs a) {
+    __shared__ float s_hyp[2];
+    const bool mark = a.cover != nullptr;
+    int t_new = 0;
+    if (threadIdx.x == 0 && !mark) {
+        t_new = *reinterpret_cast<const volatile int*>(a.state) + 1;
+        const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), t_new), bc2 = 1.0 - pow(static_cast<double>(a.beta2), t_new);
+        s_hyp[0] = static_cast<float>(static_cast<double>(a.state[1]) / bc1);
+        s_hyp[1] = static_cast<float>(1.0 / sqrt(bc2));
+    }
+    __syncthreads();
+    const float step_size = mark ? 0.0f : s_hyp[0], inv_sqrt_bc2 = mark ? 1.0f : s_hyp[1];
+    // returns the updated parameter
+    auto step_at = [&](const float* src) -> float {
+        const size_t off = static_cast<size_t>(src - a.p);
+        if (mark) { a.cover[off] = 1; return 0.0f; }
+        float pp = a.p[off], mm = a.m[off], vv = a.v[off];
+        adam_update(pp, a.g[off], mm, vv, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
+        a.p[off] = pp; a.m[off] = mm; a.v[off] = vv;
+        if (a.zero_grad) a.g[off] = 0.0f;
+        return pp;
+    };
+    const int y = blockIdx.y;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    if (y == a.y0[a.n_fields]) {
+        for (int i = tid; i < a.n_rest; i += nth) step_at(a.p + a.rest[i]);
+    } else {
+        int f = 0;
+        while (f + 1 < a.n_fields && y >= a.y0[f + 1]) ++f;
+        const PackArgs& pa = a.f[f];
+        const FieldShape& fs = pa.fs;
+        const int g = y - a.y0[f];
+        if (g < fs.n_packed_layers()) {
+            const int N = fs.packed_n(g), K = fs.layer_kb(g) * 64;
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(a.packed[f] + fs.w_off(g));
+            for (int idx = tid; idx < N * K; idx += nth) {
+                const int n = idx / K, k = idx - n * K;
+                const float* src = pack_ptr(pa, g, n, k);
+                const float w = src ? step_at(src) : 0.0f;
+                if (!mark) dst[pack_dst_off(N, n, k) >> 1] = __float2bfloat16_rn(w);
+            }
+        } else {
+            float* c = reinterpret_cast<float*>(a.packed[f] + fs.w_bytes());
+            for (int i = tid; i < ConstOff::count; i += nth) {
+                const float* src = const_ptr(pa, i);
+                const float w = src ? step_at(src) : 0.0f;
+                if (!mark) c[i] = w;
+            }
+        }
+    }
+    if (mark) return;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(a.state + 4);
+        __threadfence();
+        if (atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1) {
+            *reinterpret_cast<int*>(a.state) = t_new;
+            a.state[2] = s_hyp[0];
+            a.state[3] = s_hyp[1];
+            *ticket = 0u;
+        }
+    }
 }
 
 }  // namespace nwb
@@ -92,4 +187,60 @@ extern "C" int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t
         0.0f, beta1, beta2, 1.0f, eps, weight_decay, grad_scale, zero_grad, state);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
+}
+
+static int adam_pack_launch(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                            float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
+                            const nwb_field_desc* const* descs, const nwb_field_params* const* params,
+                            void* const* packed, const int32_t* rest, int64_t n_rest, unsigned char* cover, void* stream,
+                            const char* who) {
+    NWB_REQUIRE(n >= 1 && n < (1ll << 31) && p && n_fields >= 1 && n_fields <= kAdamMaxFields && descs && params && packed,
+                "%s: bad size / null pointer (at most %d fields)", who, kAdamMaxFields);
+    NWB_REQUIRE(n_rest >= 0 && n_rest < (1ll << 31) && (n_rest == 0 || rest), "%s: bad rest list", who);
+    AdamPackArgs a{};
+    a.n_fields = n_fields;
+    int y = 0;
+    for (int f = 0; f < n_fields; ++f) {
+        int rc = make_shape(descs[f], &a.f[f].fs);
+        if (rc != NWB_OK) return rc;
+        rc = check_pack_params(a.f[f].fs, params[f], packed[f], who);
+        if (rc != NWB_OK) return rc;
+        a.f[f].p = *params[f];
+        // every parameter the caches are built from must live inside the flat buffer
+        const float* const* slots = reinterpret_cast<const float* const*>(params[f]);
+        for (size_t i = 0; i < sizeof(nwb_field_params) / sizeof(float*); ++i)
+            NWB_REQUIRE(slots[i] == nullptr || (slots[i] >= p && slots[i] < p + n),
+                        "%s: parameter slot %d of field %d is outside the flat buffer", who, static_cast<int>(i), f);
+        a.packed[f] = static_cast<uint8_t*>(packed[f]);
+        a.y0[f] = y;
+        y += a.f[f].fs.n_packed_layers() + 1;
+    }
+    a.y0[n_fields] = y;
+    a.p = p; a.g = g; a.m = m; a.v = v;
+    a.rest = rest; a.n_rest = static_cast<int>(n_rest);
+    a.cover = cover;
+    a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay; a.gscale = grad_scale; a.zero_grad = zero_grad;
+    a.state = state;
+    dim3 grid(64, y + 1);
+    adam_pack_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
+extern "C" int nwb_adam_pack_cover(float* p, int64_t n, int n_fields, const nwb_field_desc* const* descs,
+                                   const nwb_field_params* const* params, void* const* packed, unsigned char* cover,
+                                   void* stream) {
+    NWB_REQUIRE(cover, "nwb_adam_pack_cover: cover is null");
+    return adam_pack_launch(p, nullptr, nullptr, nullptr, n, 0.f, 0.f, 0.f, 0.f, nullptr, 0.f, 0, n_fields, descs, params,
+                            packed, nullptr, 0, cover, stream, "nwb_adam_pack_cover");
+}
+
+extern "C" int nwb_adam_pack_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                                      float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
+                                      const nwb_field_desc* const* descs, const nwb_field_params* const* params,
+                                      void* const* packed, const int32_t* rest, int64_t n_rest, void* stream) {
+    NWB_REQUIRE(g && m && v && state, "nwb_adam_pack_step_dev: null pointer");
+    NWB_REQUIRE((reinterpret_cast<uintptr_t>(state) & 15u) == 0, "nwb_adam_pack_step_dev: state must be 16 B aligned (32 B long)");
+    return adam_pack_launch(p, g, m, v, n, beta1, beta2, eps, weight_decay, state, grad_scale, zero_grad, n_fields, descs,
+                            params, packed, rest, n_rest, nullptr, stream, "nwb_adam_pack_step_dev");
 }

@@ -395,3 +395,48 @@ def nerfw_loss_bwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda
                    rgb_coarse.shape[0], n_ts, lambda_u, coef, C.byref(gp), L.ptr(d_c), L.ptr(d_f), L.ptr(d_b), L.ptr(d_s),
                    L.stream_ptr(dev)), "nwb_nerfw_loss_bwd")
     return d_c, d_f, d_b, d_s
+
+
+# ---- metrics (f1), on-device ray generation (f3), eval output pack (f4) ---------------------------
+def mse_psnr(pred: torch.Tensor, gt: torch.Tensor, clip01: bool = False) -> torch.Tensor:
+    """-> (2,) = [mse, psnr] on the device (metrics.py:4-13), one launch."""
+    pred, gt = _f32(pred), _f32(gt)
+    if pred.shape != gt.shape:
+        raise ValueError(f"mse_psnr: shapes differ {tuple(pred.shape)} vs {tuple(gt.shape)}")
+    dev = pred.device
+    out = torch.empty(2, device=dev, dtype=torch.float32)
+    fn = _fn("nwb_mse_psnr", [_vp, _vp, _i64, _i, _vp, _vp, _vp])
+    with _timed("nwb_mse_psnr", pred.numel()):
+        L.check(fn(L.ptr(pred), L.ptr(gt), pred.numel(), int(clip01), L.ptr(_loss_scratch_for(dev)), L.ptr(out),
+                   L.stream_ptr(dev)), "nwb_mse_psnr")
+    return out
+
+
+def gen_rays(H: int, W: int, K, c2w, near: float, far: float, first_pixel: int = 0, n_rays: int | None = None,
+             device=None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Rays (n,8) = [o, d, near, far] of pixels [first_pixel, first_pixel+n) of one view, row-major, made on the device
+    (ray_utils.py:5-55 + blender.py:97-100).  K: (3,3) intrinsics, c2w: (3,4) pose -- small HOST arrays/tensors."""
+    Kh = torch.as_tensor(K, dtype=torch.float64).cpu()
+    pose = torch.as_tensor(c2w, dtype=torch.float32).cpu().contiguous()
+    if pose.shape != (3, 4):
+        raise ValueError(f"gen_rays: c2w must be (3,4), got {tuple(pose.shape)}")
+    n = H * W - first_pixel if n_rays is None else int(n_rays)
+    if out is None:
+        out = torch.empty(n, 8, device=device or torch.device("cuda"), dtype=torch.float32)
+    cbuf = (C.c_float * 12)(*pose.reshape(-1).tolist())
+    fn = _fn("nwb_gen_rays", [_i, _i] + [C.c_float] * 4 + [C.POINTER(C.c_float * 12), C.c_float, C.c_float, _i64, _i64, _vp, _vp])
+    with _timed("nwb_gen_rays", n):
+        L.check(fn(H, W, float(Kh[0, 0]), float(Kh[1, 1]), float(Kh[0, 2]), float(Kh[1, 2]), C.byref(cbuf), float(near),
+                   float(far), int(first_pixel), n, L.ptr(out), L.stream_ptr(out.device)), "nwb_gen_rays")
+    return out
+
+
+def pack_rgb8(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """uint8(clip(x, 0, 1) * 255), same shape (eval.py:201-203), one launch."""
+    x = _f32(x)
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=torch.uint8)
+    fn = _fn("nwb_pack_rgb8", [_vp, _i64, _vp, _vp])
+    with _timed("nwb_pack_rgb8", x.numel()):
+        L.check(fn(L.ptr(x), x.numel(), L.ptr(out), L.stream_ptr(x.device)), "nwb_pack_rgb8")
+    return out

@@ -61,7 +61,7 @@ class FlatTrainState:
     (state_dict keys and shapes are untouched, so checkpoints keep loading) and the parameters are
     tagged so the render_rays backward accumulates into ``.grad`` in place."""
 
-    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, fused_pack=True):
         self.modules = list(modules)
         params, seen = [], set()
         for m in self.modules:
@@ -93,7 +93,16 @@ class FlatTrainState:
         self.step_count = 0
         # step state of the CUDA optimizer kernel lives on the device ({int32 step, lr, lr/bc1, 1/sqrt(bc2)}), so a
         # captured CUDA graph of the whole iteration can be replayed (nwb_adam_step_dev)
-        self.hyper = torch.zeros(4, dtype=torch.float32, device=dev) if dev.type == "cuda" else None
+        # (+ the ticket word of nwb_adam_pack_step_dev)
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=dev) if dev.type == "cuda" else None
+        # (f2) fields whose packed operand caches the optimizer kernel refreshes itself: NeRF modules with every
+        # parameter inside the flat buffer
+        self._fused = None
+        self._fused_fields = []
+        if fused_pack and dev.type == "cuda":
+            mine = {id(p) for p in params}
+            self._fused_fields = [m for m in self.modules if hasattr(m, "nwb_packed")
+                                  and all(id(p) in mine for p in m.parameters())][:4]
         self._lr = float(lr)
         self.lr = lr
         self.n_params = sum(p.numel() for p in params)
@@ -127,6 +136,20 @@ class FlatTrainState:
         host logic, the same update written with torch ops."""
         self.step_count += 1
         b1, b2 = self.betas
+        if self.flat_p.is_cuda and self._fused_fields:
+            from . import _lib as L
+            from . import kernels as K
+            fz = self._fused or self._fused_setup()
+            with K._timed("nwb_adam_pack_step_dev", 0):
+                L.check(fz["fn"](self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
+                                 self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay,
+                                 self.hyper.data_ptr(), 1.0 / world, int(zero_grad), fz["n"], fz["descs"], fz["params"],
+                                 fz["packed"], fz["rest"].data_ptr(), fz["rest"].numel(),
+                                 L.stream_ptr(self.flat_p.device)), "nwb_adam_pack_step_dev")
+            for m in self.modules:                   # fields outside the fused set still repack on their own
+                if hasattr(m, "_nwb_cache") and not any(m is f for f in self._fused_fields):
+                    m._nwb_dirty = True
+            return
         if self.flat_p.is_cuda:
             from . import _lib as L
             from . import kernels as K
@@ -148,6 +171,48 @@ class FlatTrainState:
         for m in self.modules:                       # packed bf16 operand caches are stale now
             if hasattr(m, "_nwb_cache"):
                 m._nwb_dirty = True
+
+    @property
+    def refreshes_caches(self) -> bool:
+        """True when the optimizer launch itself rewrites the packed bf16 operand caches (no repack pass)."""
+        return bool(self._fused_fields)
+
+    def prepare(self) -> None:
+        """One-time setup of the cache-refreshing optimizer launch; call before capturing a CUDA graph."""
+        if self._fused_fields and self._fused is None:
+            self._fused_setup()
+
+    def _fused_setup(self):
+        """One-time: the packed caches' buffers, the C pointer tables and the `rest` offset list (flat offsets that no
+        cache element comes from) for nwb_adam_pack_step_dev."""
+        from . import _lib as L
+        from . import kernels as K
+        fields = self._fused_fields
+        n = len(fields)
+        keep = []
+        descs = (C.POINTER(L.FieldDesc) * n)()
+        params = (C.POINTER(L.FieldParams) * n)()
+        packed = (C.c_void_p * n)()
+        for i, m in enumerate(fields):
+            buf = m.nwb_packed()                       # packs once; from here on the optimizer keeps it fresh
+            d = m.nwb_desc()
+            st, ka = K.field_slots({k: v.detach() for k, v in m.nwb_params().items()})
+            keep += [buf, d, st, ka]
+            descs[i] = C.pointer(d)
+            params[i] = C.pointer(st)
+            packed[i] = buf.data_ptr()
+        dev = self.flat_p.device
+        cover = torch.zeros(self.numel, dtype=torch.uint8, device=dev)
+        tables = [C.c_int, C.POINTER(C.POINTER(L.FieldDesc)), C.POINTER(C.POINTER(L.FieldParams)), C.POINTER(C.c_void_p)]
+        cov = L.bind("nwb_adam_pack_cover", [C.c_void_p, C.c_int64] + tables + [C.c_void_p, C.c_void_p])
+        L.check(cov(self.flat_p.data_ptr(), self.numel, n, descs, params, packed, cover.data_ptr(), L.stream_ptr(dev)),
+                "nwb_adam_pack_cover")
+        rest = torch.nonzero(cover == 0).flatten().to(torch.int32).contiguous()
+        fn = L.bind("nwb_adam_pack_step_dev", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 4 +
+                    [C.c_void_p, C.c_float, C.c_int] + tables + [C.c_void_p, C.c_int64, C.c_void_p])
+        self._fused = {"fn": fn, "n": n, "descs": descs, "params": params, "packed": packed, "rest": rest, "keep": keep,
+                       "covered": int(self.numel - rest.numel())}
+        return self._fused
 
     def step(self, group=None):
         """all-reduce + Adam: everything that follows backward in one training iteration."""

@@ -83,14 +83,17 @@ class TrainStep:
                 self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True)
         torch.cuda.current_stream(self.dev).wait_stream(side)
         torch.cuda.synchronize(self.dev)
-        for m in self.models.values():
-            m._nwb_dirty = True                        # the captured iteration must contain the operand-cache refresh
+        if self.state.refreshes_caches:
+            self.state.prepare()                       # pointer tables + rest list (synchronises): not inside a capture
+        else:
+            for m in self.models.values():
+                m._nwb_dirty = True                    # the captured iteration must contain the operand-cache refresh
         g = torch.cuda.CUDAGraph()
         l0 = K.launch_count
         # thread_local: other threads of the process (NCCL watchdog, clock sampler) may touch CUDA during the capture
         with torch.cuda.graph(g, capture_error_mode="thread_local"):
             self.s_loss, self.s_terms = self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True, do_step=not self._split)
-        self.launches_per_step = K.launch_count - l0 + (2 if self._split else 0)
+        self.launches_per_step = K.launch_count - l0 + ((1 if self.state.refreshes_caches else 2) if self._split else 0)
         self.graph = g
 
     def __call__(self, rays, ts, rgbs):
@@ -105,8 +108,9 @@ class TrainStep:
                 self.state.step()                      # all-reduce + Adam, stream-ordered behind the replay
             else:
                 self.state.step_count += 1
-            for m in self.models.values():
-                m._nwb_dirty = True                    # parameters moved: eager callers must repack
+            if not self.state.refreshes_caches:
+                for m in self.models.values():
+                    m._nwb_dirty = True                # parameters moved: eager callers must repack
             self.terms = self.s_terms
             return self.s_loss
         loss, self.terms = self._iteration(rays, ts, rgbs, False)

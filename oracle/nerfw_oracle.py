@@ -374,3 +374,30 @@ def field_forward_bf16(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor | None, t
         out += [torch.sigmoid(_lin(p, "transient_rgb.0", ht)), F.softplus(_lin(p, "transient_sigma.0", ht)),
                 F.softplus(_lin(p, "transient_beta.0", ht))]
     return torch.cat(out, 1)
+
+
+# ---- data formats either side of render_rays: rays, uint8 images, PSNR -------------------------
+def ray_directions(H: int, W: int, K) -> torch.Tensor:
+    """datasets/ray_utils.py:5-26: (H, W, 3) camera-space directions; i = column, j = row, no +0.5 centring."""
+    j, i = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    fx, fy, cx, cy = float(K[0][0]), float(K[1][1]), float(K[0][2]), float(K[1][2])
+    return torch.stack([(i - cx) / fx, -(j - cy) / fy, -torch.ones_like(i)], -1)
+
+
+def rays_of_view(H: int, W: int, K, c2w: torch.Tensor, near: float, far: float) -> torch.Tensor:
+    """ray_utils.py:29-55 + blender.py:97-100: (H*W, 8) rows [rays_o, rays_d, near, far], row-major pixels."""
+    d = ray_directions(H, W, K).reshape(-1, 3) @ c2w[:, :3].T            # :46
+    d = d / torch.norm(d, dim=-1, keepdim=True)                          # :48
+    o = c2w[:, 3].expand(d.shape)                                        # :50
+    one = torch.ones_like(d[:, :1])
+    return torch.cat([o, d, near * one, far * one], 1)
+
+
+def pack_rgb8(x: torch.Tensor) -> torch.Tensor:
+    """eval.py:201-203: (np.clip(x, 0, 1) * 255).astype(np.uint8) -- fp32 product, truncation."""
+    return (x.float().clamp(0, 1) * 255).to(torch.uint8)
+
+
+def psnr(pred: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
+    """metrics.py:4-13."""
+    return -10 * torch.log10(torch.mean((pred - gt) ** 2))
