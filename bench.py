@@ -467,6 +467,35 @@ def run_product(args):
     ms_e2e, _ = timed(args.steps, True)
     e2e_value = total_rays / (ms_e2e * 1e-3)
 
+    # ---- inference only: the same image from a 48-byte pose (rays made on the device) to a uint8 image
+    # (clip + pack on the device, 8f-4): what an eval loop built on nerf_fl_b200.inference.render_image moves
+    e2e_pose = None
+    if args.workload == "infer":
+        from nerf_fl_b200.inference import render_image
+        Kc, c2w = syn.view_camera(H, W)
+        u8_host = torch.zeros(H, W, 3, dtype=torch.uint8).pin_memory()
+
+        def pose_steps(k):
+            sync_all()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(k):
+                out = render_image(models, emb, H, W, Kc, c2w, 0, ns, ni, chunk=chunk, white_back=True, device=dev)
+                u8_host.copy_(out["img_u8"], non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            e1.record()
+            sync_all()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t[0])
+        pose_steps(2)
+        ms_pose = pose_steps(args.steps)
+        e2e_pose = {"value": H * W * args.steps / (ms_pose * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": 48 + 36,
+                    "d2h_bytes_per_step": H * W * 3, "ms_per_step": ms_pose / args.steps,
+                    "what": "render_image: pose + intrinsics in (kernel arguments), rays generated on the device, "
+                            "rgb_fine clipped and packed to uint8 on the device, (H,W,3) uint8 read back"}
+
     # ---- per-kernel device times (CUDA events around every C-ABI call, separate pass of the same steps) --
     K.timing_start()
     for i in range(min(args.steps, 10)):
@@ -500,6 +529,8 @@ def run_product(args):
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "roofline": roofline, "step_roofline": step_roofline, "kernels": table,
             "wall_ms_per_step": wall / args.steps}
+    if e2e_pose is not None:
+        line["e2e_pose_in_u8_out"] = e2e_pose
     if world == 1 and not args.no_cpu_baseline:
         v, sample, cores, cms, n = cpu_leg(args.workload, ns, ni, 3, 1, 25.0, min(args.batch, 1024))
         line["cpu_baseline"] = {"value": v, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample}

@@ -54,6 +54,16 @@ def blender_rays(n_rays: int, H: int = 400, W: int = 400, n_views: int = 100, se
     return torch.cat([t, d, near[:, None], far[:, None]], dim=-1).float().contiguous()
 
 
+def view_camera(H: int, W: int, view: int = 0, seed: int = 1):
+    """(K (3,3) float64 ndarray-like tensor, c2w (3,4) fp32) of the view image_rays(H, W, view, seed) draws: blender.py:55-62
+    intrinsics (focal from FOV_X, principal point at W/2, H/2) and the seeded look-at pose."""
+    gen = torch.Generator().manual_seed(seed)
+    pose = _look_at_poses(max(view + 1, 1), 4.0, gen)[view]
+    focal = 0.5 * W / math.tan(0.5 * FOV_X)
+    K = torch.tensor([[focal, 0.0, W / 2], [0.0, focal, H / 2], [0.0, 0.0, 1.0]], dtype=torch.float64)
+    return K, pose.float().contiguous()
+
+
 def image_rays(H: int, W: int, view: int = 0, seed: int = 1) -> torch.Tensor:
     """All H*W rays of one view in row-major pixel order (the eval.py:186-194 shape)."""
     gen = torch.Generator().manual_seed(seed)
