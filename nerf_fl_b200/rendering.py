@@ -13,6 +13,7 @@ never materialised: points are generated and encoded inside the field kernel.
 """
 from __future__ import annotations
 
+import contextlib
 import itertools
 
 import os
@@ -75,8 +76,8 @@ _BWD_STREAMS = os.environ.get("NWB_BWD_STREAMS", "1") != "0"
 _side_streams = {}
 
 
-def _side_stream(dev) -> torch.cuda.Stream:
-    key = dev.index if dev.index is not None else torch.cuda.current_device()
+def _side_stream(dev, which: int = 0) -> torch.cuda.Stream:
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), which)
     if key not in _side_streams:
         _side_streams[key] = torch.cuda.Stream(device=dev)
     return _side_streams[key]
@@ -88,8 +89,21 @@ class _Pass:
                  "noise", "keys", "use_a", "a_rows", "t_rows")
 
 
+def _ray_consts(model, dirs, n_freq_dir, ts, emb_a, emb_t, a_rows, t_rows, transient):
+    """Per-ray feature rows [dir | a | t] and the per-ray bias of dir_encoding / transient_encoding.0: everything of a
+    pass that does not depend on the sample depths."""
+    use_a = bool(model.encode_appearance)
+    sd = {k: v.detach() for k, v in model.nwb_params().items()}
+    feat, rb, _ = K.ray_consts_fwd(model.nwb_desc(), sd, dirs, n_freq_dir=n_freq_dir, ts=ts,
+                                   emb_a=emb_a if (use_a and a_rows is None) else None,
+                                   emb_t=emb_t if (transient and t_rows is None) else None,
+                                   a_rows=a_rows if use_a else None, t_rows=t_rows if transient else None,
+                                   transient=transient, err_flag=_err_flag(dirs.device))
+    return feat, rb
+
+
 def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, transient, dirs, n_freq_dir,
-              n_freq_xyz, ts, emb_a, emb_t, a_rows, t_rows, save):
+              n_freq_xyz, ts, emb_a, emb_t, a_rows, t_rows, save, consts=None):
     """One inference() call: field forward over the ray samples + volume rendering."""
     n, S = z.shape
     dev = rays.device
@@ -107,12 +121,10 @@ def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, t
     P.mode = K.mlp_mode(sigma_only=sigma_only, transient=transient, save=save)
     rb = None
     P.feat = None
-    if not sigma_only:
-        P.feat, rb, _ = K.ray_consts_fwd(P.desc, sd, dirs, n_freq_dir=n_freq_dir, ts=ts,
-                                         emb_a=emb_a if (P.use_a and a_rows is None) else None,
-                                         emb_t=emb_t if (transient and t_rows is None) else None,
-                                         a_rows=a_rows if P.use_a else None, t_rows=t_rows if transient else None,
-                                         transient=transient, err_flag=_err_flag(dev))
+    if consts is not None:
+        P.feat, rb = consts
+    elif not sigma_only:
+        P.feat, rb = _ray_consts(model, dirs, n_freq_dir, ts, emb_a, emb_t, a_rows, t_rows, transient)
     P.saved = K.aligned_empty(K.mlp_save_bytes(P.desc, n * S, P.mode), dev, 16) if save else None
     P.raw = K.mlp_fwd(P.desc, P.packed, n_rays=n, S=S, mode=P.mode, ray_bias=rb, rays=rays, z=z,
                       n_freq_xyz=n_freq_xyz, saved=P.saved)
@@ -122,7 +134,7 @@ def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, t
     return P, res
 
 
-def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_w, emb_t_w, names, params):
+def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_w, emb_t_w, names, params, aux=None):
     """Backward of _run_pass -> (param sinks, direct?, d_emb_a, d_emb_t, d_a_rows, d_t_rows)."""
     n, S = P.z.shape
     dev = P.z.device
@@ -130,8 +142,15 @@ def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_
                             white_back=white_back, noise=P.noise, noise_std=noise_std)
     sinks, direct = _grad_sinks(names, params, dev)
     d_rb = torch.zeros(n, 256, device=dev, dtype=torch.float32)
+    # dgrad produces d_ray_bias and the dZ images; wgrad (dZ -> weight gradients) and the per-ray constants' backward
+    # (d_ray_bias -> tail columns, biases, embedding rows) are independent of each other: with `aux` (a stream, graph
+    # capture only) the second runs next to the first
+    ws = K.mlp_bwd(P.desc, P.packed, P.raw, d_raw.view(n * S, -1), P.saved, n_rays=n, S=S, mode=P.mode, grads=sinks,
+                   d_ray_bias=d_rb, phases=("dgrad",))
+    if aux is not None:
+        aux.wait_stream(torch.cuda.current_stream(dev))
     K.mlp_bwd(P.desc, P.packed, P.raw, d_raw.view(n * S, -1), P.saved, n_rays=n, S=S, mode=P.mode, grads=sinks,
-              d_ray_bias=d_rb)
+              d_ray_bias=d_rb, workspace=ws, phases=("wgrad",))
     sd = {k: v.detach() for k, v in zip(names, params)}
     d_a_rows = torch.empty_like(P.a_rows) if (P.use_a and P.a_rows is not None) else None
     d_t_rows = torch.empty_like(P.t_rows) if (P.transient and P.t_rows is not None) else None
@@ -144,8 +163,11 @@ def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_
         et_direct = getattr(emb_t_w, "_nwb_direct_grad", False) and emb_t_w.grad is not None
         d_et = emb_t_w.grad if et_direct else torch.zeros_like(emb_t_w)
     n_vocab = emb_a_w.shape[0] if emb_a_w is not None else (emb_t_w.shape[0] if emb_t_w is not None else 0)
-    K.ray_consts_bwd(P.desc, sd, P.feat, d_rb, ts=ts, n_vocab=n_vocab, transient=P.transient, grads=sinks,
-                     d_emb_a=d_ea, d_emb_t=d_et, d_a_rows=d_a_rows, d_t_rows=d_t_rows)
+    with (torch.cuda.stream(aux) if aux is not None else contextlib.nullcontext()):
+        K.ray_consts_bwd(P.desc, sd, P.feat, d_rb, ts=ts, n_vocab=n_vocab, transient=P.transient, grads=sinks,
+                         d_emb_a=d_ea, d_emb_t=d_et, d_a_rows=d_a_rows, d_t_rows=d_t_rows)
+    if aux is not None:
+        torch.cuda.current_stream(dev).wait_stream(aux)
     return sinks, direct, (None if ea_direct else d_ea), (None if et_direct else d_et), d_a_rows, d_t_rows
 
 
@@ -173,16 +195,30 @@ class _RenderFn(torch.autograd.Function):
 
         common = dict(test_time=test_time, white_back=cfg["white_back"], noise_std=noise_std, dirs=dirs,
                       n_freq_dir=cfg["n_freq_dir"], n_freq_xyz=cfg["n_freq_xyz"], save=save)
+        # the fine pass's per-ray constants do not depend on the coarse pass: inside a graph capture they go on a side
+        # branch next to it
+        transient_f = bool(Ni > 0 and cfg["output_transient"] and fine.encode_transient)       # :281
+        consts_f = None
+        fork = Ni > 0 and _BWD_STREAMS and rays.is_cuda and torch.cuda.is_current_stream_capturing()
+        if fork:
+            cur, side = torch.cuda.current_stream(rays.device), _side_stream(rays.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                consts_f = _ray_consts(fine, dirs, cfg["n_freq_dir"], ts, emb_a_w, emb_t_w, a_embedded, t_embedded,
+                                       transient_f)
         Pc, res = _run_pass(coarse, rays, z, typ="coarse", noise=sigma_noise((n, Ns), "noise_coarse"),
                             transient=False, ts=None, emb_a=None, emb_t=None, a_rows=None, t_rows=None, **common)
+        if fork:
+            cur.wait_stream(side)
         Pf = None
         if Ni > 0:
             z_f = K.sample_pdf_merge(z, res["weights_coarse"], Ni, det=(perturb == 0),              # :267-272
                                      u=rng.get("u") if perturb > 0 else None, seed=seed ^ 0x5DEECE66D)
-            transient = bool(cfg["output_transient"] and fine.encode_transient)               # :281
+            transient = transient_f
             noise_f = None if transient else sigma_noise((n, Ns + Ni), "noise_fine")
             Pf, res_f = _run_pass(fine, rays, z_f, typ="fine", noise=noise_f, transient=transient, ts=ts,
-                                  emb_a=emb_a_w, emb_t=emb_t_w, a_rows=a_embedded, t_rows=t_embedded, **common)
+                                  emb_a=emb_a_w, emb_t=emb_t_w, a_rows=a_embedded, t_rows=t_embedded, consts=consts_f,
+                                  **common)
             res.update(res_f)
         cfg["keys"] = list(res.keys())
         ctx.cfg, ctx.Pc, ctx.Pf, ctx.n_c = cfg, Pc, Pf, n_c
@@ -215,15 +251,16 @@ class _RenderFn(torch.autograd.Function):
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
-                                                  params=params_c, **kw)
+                                                  params=params_c, aux=_side_stream(Pc.z.device, 1), **kw)
         else:
             sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
                                               params=params_c, **kw)
         out_params += [None if direct_c else sinks_c[k] for k in names_c]
         if Pf is not None:
             sinks_f, direct_f, d_ea, d_et, d_a, d_t = _bwd_pass(Pf, g, ts=ctx.ts, emb_a_w=ctx.emb_a_w,
-                                                                emb_t_w=ctx.emb_t_w, names=names_f,
-                                                                params=params_f, **kw)
+                                                                emb_t_w=ctx.emb_t_w, names=names_f, params=params_f,
+                                                                aux=_side_stream(Pc.z.device, 2) if fork else None,
+                                                                **kw)
             out_params += [None if direct_f else sinks_f[k] for k in names_f]
         if fork:
             cur.wait_stream(side)
