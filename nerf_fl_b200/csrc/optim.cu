@@ -3,6 +3,7 @@
 // One vectorised elementwise pass over the 1.3 M parameters: reads p, g, m, v, writes p, m, v and
 // (optionally) clears g for the next step's atomic accumulation -- HBM-bound, 7 floats per element.
 #include "field_pack.cuh"
+#include "field_dev.cuh"
 #include <algorithm>
 #include <math.h>
 
@@ -114,13 +115,50 @@ adam_pack_kernel(const AdamPackArgs a) {
         const FieldShape& fs = pa.fs;
         const int g = y - a.y0[f];
         if (g < fs.n_packed_layers()) {
-            const int N = fs.packed_n(g), K = fs.layer_kb(g) * 64;
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(a.packed[f] + fs.w_off(g));
-            for (int idx = tid; idx < N * K; idx += nth) {
-                const int n = idx / K, k = idx - n * K;
-                const float* src = pack_ptr(pa, g, n, k);
-                const float w = src ? step_at(src) : 0.0f;
-                if (!mark) dst[pack_dst_off(N, n, k) >> 1] = __float2bfloat16_rn(w);
+            // one thread per 16-byte image chunk = 8 consecutive k of one row: when the 8 sources are contiguous and
+            // 16 B aligned (every layer whose row length is a multiple of 4) p, g, m, v move as float4 pairs
+            const int N = fs.packed_n(g), K8 = fs.layer_kb(g) * 8;
+            uint8_t* dst = a.packed[f] + fs.w_off(g);
+            for (int c = tid; c < N * K8; c += nth) {
+                const int n = c / K8, k0 = (c - n * K8) << 3;
+                const float* s0 = pack_ptr(pa, g, n, k0);
+                const float* s7 = pack_ptr(pa, g, n, k0 + 7);
+                float w[8];
+                if (!mark && s0 != nullptr && s7 == s0 + 7 && (reinterpret_cast<uintptr_t>(s0) & 15u) == 0) {
+                    const size_t off = static_cast<size_t>(s0 - a.p);
+                    float4 pp[2], gg[2], mm[2], vv[2];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        pp[h] = reinterpret_cast<const float4*>(a.p + off)[h];
+                        gg[h] = reinterpret_cast<const float4*>(a.g + off)[h];
+                        mm[h] = reinterpret_cast<const float4*>(a.m + off)[h];
+                        vv[h] = reinterpret_cast<const float4*>(a.v + off)[h];
+                    }
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        adam_update(pp[h].x, gg[h].x, mm[h].x, vv[h].x, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
+                        adam_update(pp[h].y, gg[h].y, mm[h].y, vv[h].y, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
+                        adam_update(pp[h].z, gg[h].z, mm[h].z, vv[h].z, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
+                        adam_update(pp[h].w, gg[h].w, mm[h].w, vv[h].w, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
+                        reinterpret_cast<float4*>(a.p + off)[h] = pp[h];
+                        reinterpret_cast<float4*>(a.m + off)[h] = mm[h];
+                        reinterpret_cast<float4*>(a.v + off)[h] = vv[h];
+                        if (a.zero_grad) reinterpret_cast<float4*>(a.g + off)[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        w[4 * h] = pp[h].x; w[4 * h + 1] = pp[h].y; w[4 * h + 2] = pp[h].z; w[4 * h + 3] = pp[h].w;
+                    }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const float* src = pack_ptr(pa, g, n, k0 + q);
+                        w[q] = src ? step_at(src) : 0.0f;
+                    }
+                }
+                if (!mark) {
+                    uint4 o;
+                    o.x = pack_bf16(w[0], w[1]); o.y = pack_bf16(w[2], w[3]);
+                    o.z = pack_bf16(w[4], w[5]); o.w = pack_bf16(w[6], w[7]);
+                    *reinterpret_cast<uint4*>(dst + pack_dst_off(N, n, k0)) = o;
+                }
             }
         } else {
             float* c = reinterpret_cast<float*>(a.packed[f] + fs.w_bytes());

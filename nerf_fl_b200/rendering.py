@@ -224,6 +224,9 @@ class _RenderFn(torch.autograd.Function):
         ctx.cfg, ctx.Pc, ctx.Pf, ctx.n_c = cfg, Pc, Pf, n_c
         ctx.ts, ctx.emb_a_w, ctx.emb_t_w = ts, emb_a_w, emb_t_w
         ctx.params = params
+        # the loss touches 4 of the ~14 outputs (losses.py:37-45); the others' cotangents stay None instead of being
+        # materialised as zero tensors (one fill launch each) and the compositing backward skips their terms
+        ctx.set_materialize_grads(False)
         outs = tuple(res.values())
         if not save:
             ctx.mark_non_differentiable(*outs)
