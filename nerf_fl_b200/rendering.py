@@ -73,6 +73,7 @@ def _grad_sinks(names, params, dev):
 
 
 _BWD_STREAMS = os.environ.get("NWB_BWD_STREAMS", "1") != "0"
+_FORK_MAX_TILES = int(os.environ.get("NWB_FORK_MAX_TILES", "8192"))     # fine-pass 128-point tiles
 _side_streams = {}
 
 
@@ -248,7 +249,11 @@ class _RenderFn(torch.autograd.Function):
         # launches are host-bound and the extra stream switches only add to that ([B200] 1.93 vs 1.64 ms eager).
         fork = (Pf is not None and _BWD_STREAMS and Pc.z.is_cuda and torch.cuda.is_current_stream_capturing()
                 and all(getattr(p, "_nwb_direct_grad", False) and p.grad is not None for p in ctx.params))
-        if fork:
+        # Two whole chains side by side only pay while a kernel's last partial wave is a visible share of it ([B200]
+        # 1024 rays 64+64: +6 %, 4096: +1.5 %; 16384 rays 128+128: -7 %, long kernels of different kinds sharing SMs
+        # and L2): above _FORK_MAX_TILES fine tiles only the small side branches remain.
+        fork_chains = fork and Pf.z.numel() <= _FORK_MAX_TILES * 128
+        if fork_chains:
             cur = torch.cuda.current_stream(Pc.z.device)
             side = _side_stream(Pc.z.device)
             side.wait_stream(cur)
@@ -257,7 +262,7 @@ class _RenderFn(torch.autograd.Function):
                                                   params=params_c, aux=_side_stream(Pc.z.device, 1), **kw)
         else:
             sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
-                                              params=params_c, **kw)
+                                              params=params_c, aux=_side_stream(Pc.z.device, 1) if fork else None, **kw)
         out_params += [None if direct_c else sinks_c[k] for k in names_c]
         if Pf is not None:
             sinks_f, direct_f, d_ea, d_et, d_a, d_t = _bwd_pass(Pf, g, ts=ctx.ts, emb_a_w=ctx.emb_a_w,
@@ -265,7 +270,7 @@ class _RenderFn(torch.autograd.Function):
                                                                 aux=_side_stream(Pc.z.device, 2) if fork else None,
                                                                 **kw)
             out_params += [None if direct_f else sinks_f[k] for k in names_f]
-        if fork:
+        if fork_chains:
             cur.wait_stream(side)
         # inputs: cfg, rays, ts, view_dir, a_embedded, t_embedded, emb_a_w, emb_t_w, n_c, *params
         return (None, None, None, None, d_a, d_t, d_ea, d_et, None, *out_params)
