@@ -10,59 +10,8 @@ namespace nwb {
 
 constexpr int kCompWarps = 4;
 
-// Software prefetch of one 32-sample chunk: the chunk's AoS rows (<= 32*C floats, <= 3 float4 per lane) and this
-// lane's z / z_next are pulled into REGISTERS one chunk ahead of their use, so every warp keeps two chunks of HBM
-// traffic in flight instead of one (the kernels are latency-bound, not instruction-bound: ncu r01b, 37 % of HBM peak
-// with a single chunk in flight).
-template <int C>
-struct ChunkRegs {
-    static constexpr int kV4 = (32 * C / 4 + 31) / 32;     // float4 per lane (C=9: 3, C=4: 1, C=1: 1)
-    float4 v[kV4];
-    float s[(C == 1) ? 1 : 2];                             // unaligned fallback keeps a scalar tail only for tiny C
-    float zi, zn;
-    bool vec;
-};
-template <int C>
-__device__ __forceinline__ void chunk_load(ChunkRegs<C>& r, const float* __restrict__ raw, const float* __restrict__ z,
-                                           int64_t row, int base, int S, int lane) {
-    const int cnt = min(32, S - base);
-    const float* src = raw + (row + base) * C;
-    const int nfl = cnt * C;
-    r.vec = (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (nfl & 3) == 0;
-    if (r.vec) {
-        const float4* s4 = reinterpret_cast<const float4*>(src);
-#pragma unroll
-        for (int k = 0; k < ChunkRegs<C>::kV4; ++k) {
-            const int i = lane + 32 * k;
-            if (i < (nfl >> 2)) r.v[k] = __ldg(s4 + i);
-        }
-    }
-    const int i = base + lane;
-    r.zi = (lane < cnt) ? __ldg(z + row + i) : 0.0f;
-    r.zn = (lane < cnt && i + 1 < S) ? __ldg(z + row + i + 1) : 0.0f;
-}
-// registers -> the warp's shared-memory slab (falls back to a direct staged copy for unaligned / ragged chunks)
-template <int C>
-__device__ __forceinline__ void chunk_commit(const ChunkRegs<C>& r, float* slab, const float* __restrict__ raw,
-                                             int64_t row, int base, int S, int lane) {
-    const int cnt = min(32, S - base);
-    const int nfl = cnt * C;
-    if (r.vec) {
-        float4* d4 = reinterpret_cast<float4*>(slab);
-#pragma unroll
-        for (int k = 0; k < ChunkRegs<C>::kV4; ++k) {
-            const int i = lane + 32 * k;
-            if (i < (nfl >> 2)) d4[i] = r.v[k];
-        }
-    } else {
-        const float* src = raw + (row + base) * C;
-        for (int i = lane; i < nfl; i += 32) slab[i] = __ldg(src + i);
-    }
-    __syncwarp();
-}
-
-// ---- cp.async staging ring (forward) ------------------------------------------------------------------------------
-// The forward is latency-bound: with one chunk prefetched in registers a warp keeps 2 x 1.3 KB in flight and the SM
+// ---- cp.async staging ring ------------------------------------------------------------------------------
+// These kernels are latency-bound: with one chunk prefetched in registers a warp keeps 2 x 1.3 KB in flight and the SM
 // ~30 KB, which Little's law turns into ~50 % of HBM peak (ncu r01d).  Here each warp owns a ring of kRing stages in
 // shared memory filled by cp.async (no registers held by loads in flight), kRing-1 chunks ahead of the one it consumes.
 constexpr int kRing = 4;
@@ -246,7 +195,7 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 // backward.  With G_j the cotangent reaching each weight kind and q_j = G w + Gs ws + Gt wt,
 //   dL/dsigma^x_j = delta_j * [ T_j (G_j e_j + G^x_j e^x_j) - sum_{k>j} q_k ]     
 // pass 1 (forward order): recompute T, stash T_j in smem; pass 2 (reverse order): suffix scan.
-// dynamic smem per warp: 32*C staging floats + S floats of T.
+// dynamic smem per warp: kRing chunk stages (cp.async ring) + S floats of T.
 // ------------------------------------------------------------------------------------------------
 template <int C>
 __global__ void __launch_bounds__(kCompWarps * 32)
@@ -256,12 +205,35 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     extern __shared__ __align__(16) float dsm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int Sp = (S + 3) & ~3;
-    float* slab = dsm + warp * (32 * C + Sp);
-    float* Tbuf = slab + 32 * C;
+    constexpr int kStageFloats = sizeof(RingStage<C>) / sizeof(float);
+    float* wbase = dsm + warp * (kRing * kStageFloats + Sp);
+    RingStage<C>* my = reinterpret_cast<RingStage<C>*>(wbase);
+    float* Tbuf = wbase + kRing * kStageFloats;
     const bool transient = (C == 9) && (flags & NWB_COMP_TRANSIENT);
     const bool white = flags & NWB_COMP_WHITE_BACK;
+    // The warp's chunk sequence per ray: chunks 0..n-1 (pass 1), then n-1..0 (pass 2), then the next ray: one cp.async
+    // ring runs through all of it, kRing-1 chunks ahead of the consumer (the re-read of a chunk hits L1/L2).
+    const int n_chunks = (S + 31) >> 5;
+    const int stride = gridDim.x * kCompWarps;
+    int pf_ray = blockIdx.x * kCompWarps + warp, pf_k = 0;
+    uint32_t iss = 0, it = 0;
+    auto issue_next = [&]() {
+        const int c = pf_k < n_chunks ? pf_k : 2 * n_chunks - 1 - pf_k;
+        ring_issue<C>(&my[iss % kRing], raw, z, pf_ray, n_rays, c * 32, S, lane);
+        ++iss;
+        if (++pf_k == 2 * n_chunks) { pf_k = 0; pf_ray += stride; }
+    };
+    // consumer side: refill the stage freed one iteration ago, then wait for the oldest outstanding chunk
+    auto acquire = [&]() -> RingStage<C>* {
+        issue_next();
+        cp_async_wait<kRing - 1>();
+        __syncwarp();
+        return &my[(it++) % kRing];
+    };
+#pragma unroll
+    for (int k = 0; k < kRing - 1; ++k) issue_next();
 
-    for (int ray = blockIdx.x * kCompWarps + warp; ray < n_rays; ray += gridDim.x * kCompWarps) {
+    for (int ray = blockIdx.x * kCompWarps + warp; ray < n_rays; ray += stride) {
         const int64_t row = static_cast<int64_t>(ray) * S;
         // per-ray cotangents
         const float g_op = g.d_opacity ? __ldg(g.d_opacity + ray) : 0.0f;
@@ -276,39 +248,26 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         }
         const float g_bg = white ? -(Gs[0] + Gs[1] + Gs[2]) : 0.0f;   // d(1 - sum w)/dw
 
-        // pass 1: transmittance (this lane's loads for chunk k+1 are issued before chunk k's exp + scan)
+        // pass 1: transmittance
         const int last_base = ((S - 1) / 32) * 32;
-        ChunkRegs<C> cur;
-        chunk_load<C>(cur, raw, z, row, last_base, S, lane);       // pass 2 starts at the ray's last chunk
         float cT = 1.0f;
-        float p_zi = 0, p_zn = 0, p_s = 0, p_t = 0, p_n = 0;
-        auto p1_load = [&](int base) {
-            const int i = base + lane;
-            if (i < S) {
-                p_zi = __ldg(z + row + i);
-                p_zn = (i + 1 < S) ? __ldg(z + row + i + 1) : 0.0f;
-                p_s = (C == 1) ? __ldg(raw + row + i) : __ldg(raw + (row + i) * C + 3);
-                if (transient) p_t = __ldg(raw + (row + i) * C + 7);
-                else if (noise != nullptr) p_n = __ldg(noise + row + i);
-            }
-        };
-        p1_load(0);
         for (int base = 0; base < S; base += 32) {
+            const RingStage<C>* st = acquire();
             const int i = base + lane;
             const bool live = i < S;
-            const float zi = p_zi, zn = p_zn, s0 = p_s, t0 = p_t, n0 = p_n;
-            if (base + 32 < S) p1_load(base + 32);
             float alpha = 0.0f;
             if (live) {
-                const float delta = (i + 1 < S) ? __fsub_rn(zn, zi) : 1e2f;
-                float s = s0;
-                if (transient) s = __fadd_rn(s, t0);
+                const float zi = st->z[lane];
+                const float delta = (i + 1 < S) ? __fsub_rn(st->z[lane + 1], zi) : 1e2f;
+                float s = (C == 1) ? st->raw[lane] : st->raw[lane * C + 3];
+                if (transient) s = __fadd_rn(s, st->raw[lane * C + 7]);
                 else {
-                    if (noise != nullptr) s = __fadd_rn(s, __fmul_rn(n0, noise_std));
+                    if (noise != nullptr) s = __fadd_rn(s, __fmul_rn(__ldg(noise + row + i), noise_std));
                     s = fmaxf(s, 0.0f);
                 }
                 alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, s)));
             }
+            __syncwarp();                                   // every lane is done with the stage before it is refilled
             const float T = excl_prod_scan(__fsub_rn(1.0f, alpha), cT, lane);
             if (live) Tbuf[i] = T;
         }
@@ -318,9 +277,9 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         float suffix = 0.0f;   // sum of q over all samples after the current chunk
         for (int base = last_base; base >= 0; base -= 32) {
             const int cnt = min(32, S - base);
-            chunk_commit<C>(cur, slab, raw, row, base, S, lane);
-            const float zi_r = cur.zi, zn_r = cur.zn;
-            if (base >= 32) chunk_load<C>(cur, raw, z, row, base - 32, S, lane);
+            RingStage<C>* st = acquire();
+            float* slab = st->raw;                          // overwritten in place with the chunk's d_raw rows below
+            const float zi_r = st->z[lane], zn_r = st->z[lane + 1];
             const int i = base + lane;
             const bool live = lane < cnt;
             float q = 0.0f, dsig_s = 0.0f, dsig_t = 0.0f, dcs[3] = {0, 0, 0}, dct[3] = {0, 0, 0}, dbeta = 0.0f;
@@ -433,7 +392,7 @@ extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const 
     NWB_REQUIRE(!(flags & NWB_COMP_TRANSIENT) || C == 9, "nwb_composite_bwd: transient needs C==9");
     if (n_rays == 0) return NWB_OK;
     const int blocks = std::min((n_rays + kCompWarps - 1) / kCompWarps, kNumSMs * 16);
-    const size_t smem = static_cast<size_t>(kCompWarps) * (32 * C + ((S + 3) & ~3)) * sizeof(float);
+    const size_t smem = static_cast<size_t>(kCompWarps) * (kRing * (32 * C + 36) + ((S + 3) & ~3)) * sizeof(float);
     NWB_REQUIRE(smem <= 200 * 1024, "nwb_composite_bwd: S too large for shared memory");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define NWB_BWD(CC)                                                                                 \

@@ -63,8 +63,25 @@ nerfw_loss_fwd_kernel(const ObjArgs a, float* __restrict__ scratch, float* __res
     }
     if (a.beta != nullptr) {
         for (long long i = tid; i < a.n; i += nth) s_b += logf(__ldg(a.beta + i));
-        if (a.ts != nullptr)
-            for (long long i = tid; i < a.n_ts; i += nth) s_s += __ldg(a.ts + i);
+        if (a.ts != nullptr) {
+            // the one large input (n x S): float4 loads, two independent accumulators per thread
+            long long done = 0;
+            if ((reinterpret_cast<uintptr_t>(a.ts) & 15u) == 0) {
+                const float4* t4 = reinterpret_cast<const float4*>(a.ts);
+                const long long n4 = a.n_ts >> 2;
+                float s1 = 0.0f;
+                long long i = tid;
+                for (; i + nth < n4; i += 2 * nth) {
+                    const float4 u = __ldg(t4 + i), w = __ldg(t4 + i + nth);
+                    s_s += (u.x + u.y) + (u.z + u.w);
+                    s1 += (w.x + w.y) + (w.z + w.w);
+                }
+                if (i < n4) { const float4 u = __ldg(t4 + i); s_s += (u.x + u.y) + (u.z + u.w); }
+                s_s += s1;
+                done = n4 << 2;
+            }
+            for (long long i = done + tid; i < a.n_ts; i += nth) s_s += __ldg(a.ts + i);
+        }
     }
     const float r0 = block_sum(s_c, red), r1 = block_sum(s_f, red), r2 = block_sum(s_b, red), r3 = block_sum(s_s, red);
     unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + 4 * kObjMaxBlocks);   // fixed slot behind the partials

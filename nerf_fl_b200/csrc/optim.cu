@@ -66,6 +66,7 @@ __global__ void adam_tick_kernel(float* state, float beta1, float beta2) {
 // biases, the embedding tables, alignment padding).  The step state advances inside the same launch: every block derives
 // the new step's scalars from state[0], the last block to finish stores them (ticket in state[4]).
 constexpr int kAdamMaxFields = 4;
+constexpr int kAdamPackBlocksX = 24;      // blocks per grid slice: ~650 blocks of 256 threads = 1.5 waves at 3 blocks/SM
 
 struct AdamPackArgs {
     PackArgs f[kAdamMaxFields];
@@ -259,7 +260,7 @@ static int adam_pack_launch(float* p, float* g, float* m, float* v, int64_t n, f
     a.cover = cover;
     a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay; a.gscale = grad_scale; a.zero_grad = zero_grad;
     a.state = state;
-    dim3 grid(64, y + 1);
+    dim3 grid(kAdamPackBlocksX, y + 1);
     adam_pack_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
