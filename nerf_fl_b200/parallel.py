@@ -18,7 +18,7 @@ import math
 import torch
 import torch.distributed as dist
 
-__all__ = ["FlatTrainState", "shard_range", "gather_rays", "dist_info"]
+__all__ = ["FlatTrainState", "FlatAdam", "shard_range", "gather_rays", "dist_info"]
 
 
 def dist_info():
@@ -214,6 +214,39 @@ class FlatTrainState:
                        "covered": int(self.numel - rest.numel())}
         return self._fused
 
+    def pull_lr(self) -> None:
+        """Take the learning rate from the FlatAdam facade's param_groups when a torch scheduler moved it."""
+        src = getattr(self, "_lr_source", None)
+        if src is not None:
+            lr = float(src.param_groups[0]["lr"])
+            if lr != self._lr:
+                self.lr = lr
+
     def step(self, group=None):
         """all-reduce + Adam: everything that follows backward in one training iteration."""
+        self.pull_lr()
         self.adam_step(self.allreduce_grads(group))
+
+
+class FlatAdam(torch.optim.Optimizer):
+    """``torch.optim.Optimizer`` facade over a FlatTrainState, so the reference's optimizer / scheduler plumbing
+    (utils/__init__.py:24-61: ``get_optimizer`` -> Adam, ``get_scheduler`` -> MultiStepLR | CosineAnnealingLR | LambdaLR,
+    optionally wrapped by GradualWarmupScheduler; Lightning's ``configure_optimizers`` train.py:139-142) keeps working:
+    schedulers write ``param_groups[0]['lr']``, ``step()`` pushes it to the device-resident step state and runs the
+    all-reduce + the one Adam launch.  ``zero_grad`` is a no-op: the kernel clears the flat gradient buffer, and the
+    parameters' ``.grad`` views must stay attached to it."""
+
+    def __init__(self, state: FlatTrainState):
+        self.flat = state
+        super().__init__(state.params, dict(lr=state.lr, betas=state.betas, eps=state.eps,
+                                            weight_decay=state.weight_decay))
+        state._lr_source = self
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        self.flat.step()
+        return loss
+
+    def zero_grad(self, set_to_none: bool = False):
+        return None

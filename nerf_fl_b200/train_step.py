@@ -100,6 +100,7 @@ class TrainStep:
         if self._want_graph and rays.shape[0] == self.batch:
             if self.graph is None:
                 self._capture(rays, ts, rgbs)          # warm-up iterations + capture (the capture itself does not run)
+            self.state.pull_lr()                       # a torch scheduler may have moved FlatAdam's lr between steps
             self.s_rays.copy_(rays, non_blocking=True)
             self.s_ts.copy_(ts, non_blocking=True)
             self.s_rgbs.copy_(rgbs, non_blocking=True)

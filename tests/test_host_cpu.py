@@ -32,3 +32,40 @@ def test_tile_image_roundtrip_and_swizzle():
     assert off[0, :64].tolist() == list(range(64))
     assert off[1, 0].item() == 64 + 8 and off[1, 8].item() == 64
     assert off[0, 64].item() == 16 * 64 and off[8, 0].item() == 512
+
+
+def test_flat_adam_facade_follows_torch_schedulers():
+    """utils/__init__.py:44-61: the reference builds MultiStepLR / CosineAnnealingLR / LambdaLR over its optimizer;
+    FlatAdam lets the same schedulers drive the flat-buffer Adam.  CPU tensors take FlatTrainState's torch-op update."""
+    import torch
+    from torch.optim.lr_scheduler import CosineAnnealingLR, LambdaLR, MultiStepLR
+    from nerf_fl_b200.parallel import FlatAdam, FlatTrainState
+
+    def run(make_sched):
+        torch.manual_seed(0)
+        lin_a, lin_b = torch.nn.Linear(5, 7), torch.nn.Linear(5, 7)
+        lin_b.load_state_dict(lin_a.state_dict())
+        st = FlatTrainState([lin_a], lr=5e-4)
+        opt_a, opt_b = FlatAdam(st), torch.optim.Adam(lin_b.parameters(), lr=5e-4, eps=1e-8)
+        sch_a, sch_b = make_sched(opt_a), make_sched(opt_b)
+        g = torch.Generator().manual_seed(1)
+        for epoch in range(6):
+            for _ in range(3):
+                for pa, pb in zip(lin_a.parameters(), lin_b.parameters()):
+                    gr = torch.randn(pa.shape, generator=g)
+                    pa.grad.copy_(gr)                       # FlatTrainState's preassigned views
+                    pb.grad = gr.clone()
+                opt_a.step(); opt_b.step()
+                opt_a.zero_grad(); opt_b.zero_grad(set_to_none=False)
+                assert lin_a.weight.grad is not None and lin_a.weight.grad.data_ptr() == st.flat_g.data_ptr()
+            sch_a.step(); sch_b.step()
+            assert abs(opt_a.param_groups[0]["lr"] - opt_b.param_groups[0]["lr"]) < 1e-12
+        for pa, pb in zip(lin_a.parameters(), lin_b.parameters()):
+            assert (pa - pb).abs().max().item() <= 1e-6
+        return st
+
+    run(lambda o: MultiStepLR(o, milestones=[2, 4], gamma=0.1))
+    run(lambda o: CosineAnnealingLR(o, T_max=6, eta_min=1e-8))
+    st = run(lambda o: LambdaLR(o, lambda epoch: (1 - epoch / 6) ** 0.9))
+    st.pull_lr()
+    assert st.lr < 5e-4
