@@ -56,6 +56,10 @@ struct FieldShape {
 };
 
 // fp32 constant block that follows the weight slabs in the packed buffer (float offsets)
+// Bit of a 16-column sign-mask entry that holds column c (0..15) of its group: the forward epilogue builds the entry
+// from packed bf16 pairs, so even columns land in the high byte and odd columns in the low byte, each MSB first.
+__host__ __device__ constexpr int relu_mask_bit(int c) { return (c & 1) ? 7 - (c >> 1) : 15 - (c >> 1); }
+
 struct ConstOff {
     static constexpr int trunk_b = 0;              // 8 x 256
     static constexpr int final_b = 8 * 256;        // 256
@@ -83,7 +87,7 @@ inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
 
 // saved-activation layout per tile (forward NWB_MLP_SAVE): bf16 tile images followed by ReLU sign masks
 //   [X: kx*16K][h1..h8: 8 x 64K][feat: 64K][dir|t0: 32K or 64K][t2,t4,t6: 3 x 32K][masks: 13 x 4K]
-// masks: per layer g four 1 KB sub-blocks [sub][row] of 4 x uint16: bit (15-j) of entry q of (sub, row) = 1 iff the
+// masks: per layer g four 1 KB sub-blocks [sub][row] of 4 x uint16: bit relu_mask_bit(j) of entry q of (sub, row) = 1 iff the
 // pre-activation of column 64q + 16sub + j of that row was negative (ReLU gate closed).  A forward epilogue thread owns
 // one (sub, row) entry group: its warp writes 256 contiguous bytes.
 struct SaveLayout {

@@ -50,7 +50,8 @@ struct BwdArgs {
 #endif
 
 // one 32-column slice of dZ for this thread's row
-//   kAcc: take dA from TMEM;  kHeads > 0: add sum_h dp[h] * hw[h][c];  negmask bit (31-j): gate closed
+//   kAcc: take dA from TMEM;  kHeads > 0: add sum_h dp[h] * hw[h][c];  negmask: two 16-column entries (columns 0-15 in
+//   the high half), bit relu_mask_bit(c) of an entry set = gate closed
 //   Head weights arrive lane-distributed (lane l holds hw[h][c_out + l], one coalesced load per warp issued ahead of
 //   the accumulator wait) and are broadcast with shuffles: every thread of the warp needs the same 32 values, and a
 //   warp-uniform global load per value costs an L2 round trip each (shared memory is full, L1 is carved away).
@@ -79,7 +80,7 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, cons
     if (kMask) {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-            if ((negmask >> (31 - j)) & 1u) x[j] = 0.0f;
+            if ((negmask >> ((j < 16 ? 16 : 0) + relu_mask_bit(j & 15))) & 1u) x[j] = 0.0f;
     }
     store_slice_bf16(sD, row, c_out, x);
 }
@@ -272,14 +273,14 @@ field_dgrad_kernel(const BwdArgs a) {
 #pragma unroll
                 for (int w = 0; w < 8; ++w) mw[w] = 0u;
                 if (g != 8 && !ghost) {
-                    // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit (15-j) = column 64q+16sub+j);
+                    // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit relu_mask_bit(j) = column 64q+16sub+j);
                     // gathered here into the old per-row order, entry (sub, q) at sub*4 + q
                     const uint2* mp = reinterpret_cast<const uint2*>(save_tile + sl.mask_off(g, nl)) + row;
                     const uint2 a0 = __ldg(mp), a1 = __ldg(mp + 128), a2 = __ldg(mp + 256), a3 = __ldg(mp + 384);
                     const uint4 m0 = make_uint4(a0.x, a0.y, a1.x, a1.y), m1 = make_uint4(a2.x, a2.y, a3.x, a3.y);
                     const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
-                    for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31, bit (31-j) = column 32w+j
+                    for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31: entry of columns 32w..+15 in the high half
                         const int q = w >> 1, s0 = (w & 1) * 2;
                         const int ihi = s0 * 4 + q, ilo = (s0 + 1) * 4 + q;
                         const uint32_t hi = (m[ihi >> 1] >> ((ihi & 1) * 16)) & 0xFFFFu;

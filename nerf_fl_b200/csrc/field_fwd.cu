@@ -97,20 +97,19 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
     ptx::tmem_ld_wait();
     float x[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) x[j] = __uint_as_float(v[j]) + b[j];
+    for (int j = 0; j < 8; ++j)                  // packed fp32 adds (FADD2): the epilogue is issue-bound
+        ptx::fadd2(x[2 * j], x[2 * j + 1], __uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]), b[2 * j], b[2 * j + 1]);
     uint32_t pk[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(x[2 * j], x[2 * j + 1]);
     if (kRelu && kSave) {
-        // packed word j: bit 15 = sign of column 2j, bit 31 = sign of column 2j+1.  Two words at a time: the four
-        // sign-carrying bytes are gathered with one byte permute, reduced to 0/1 per byte, and one multiply lines the
-        // four bits up as a nibble, column 4k first (0x08040201: byte i -> bit 27-i, no carries can reach bit 24)
-        uint32_t neg = 0;
+        // packed word j: bit 15 = sign of column 2j, bit 31 = sign of column 2j+1.  One shift + one LOP3 per word
+        // drops them at bits 15-j and 31-j; the 16-bit entry is then [even columns, MSB first | odd columns, MSB first]
+        // (relu_mask_bit below is the one place that knows the order)
+        uint32_t acc = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t b = (__byte_perm(pk[2 * k], pk[2 * k + 1], 0x7531) >> 7) & 0x01010101u;
-            neg |= ((b * 0x08040201u) >> 24) << (12 - 4 * k);
-        }
+        for (int j = 0; j < 8; ++j) acc |= (pk[j] >> j) & (0x80008000u >> j);
+        const uint32_t neg = (acc & 0xFF00u) | (acc >> 24);
         neg_out = neg & 0xFFFFu;
     }
     if (kRelu) {

@@ -338,5 +338,11 @@ __host__ __device__ __forceinline__ uint32_t image_chunk_off(int r, int chunk /*
     return static_cast<uint32_t>((r >> 3) * 1024 + (r & 7) * 128 + ((chunk ^ (r & 7)) << 4));
 }
 
+// packed fp32 add (FADD2 on sm_100): {x0, x1} = {a0, a1} + {b0, b1}
+__device__ __forceinline__ void fadd2(float& x0, float& x1, float a0, float a1, float b0, float b1) {
+    asm("{ .reg .b64 ra, rb, rd; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; add.rn.f32x2 rd, ra, rb; mov.b64 {%0, %1}, rd; }"
+        : "=f"(x0), "=f"(x1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+
 }  // namespace ptx
 }  // namespace nwb
