@@ -112,7 +112,6 @@ def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, t
     P.model, P.typ, P.S, P.transient, P.z, P.noise = model, typ, S, transient, z, noise
     P.desc = model.nwb_desc()
     P.packed = model.nwb_packed()
-    sd = {k: v.detach() for k, v in model.nwb_params().items()}
     sigma_only = typ == "coarse" and test_time                     # rendering.py:103-111
     P.use_a = bool(model.encode_appearance)
     P.a_rows, P.t_rows = a_rows, t_rows
