@@ -76,6 +76,46 @@ posenc_kernel(const float* __restrict__ x, int64_t n, int n_freqs, float* __rest
     }
 }
 
+// Ascending bitonic sort of 32*R keys held in shared memory `a` (padded with +inf), done in registers: element
+// e = lane + 32*r lives in register r of `lane`, so partners at distance j < 32 are another lane's register r
+// (__shfl_xor) and partners at distance j >= 32 are this lane's register r ^ (j/32).
+template <int R>
+__device__ __forceinline__ void warp_bitonic_regs(float* a, int lane) {
+    float v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) v[r] = a[lane + 32 * r];
+#pragma unroll
+    for (int k = 2; k <= 32 * R; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= 32) {
+                const int jr = j >> 5;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if ((r & jr) == 0) {
+                        const int e = lane + 32 * r;
+                        const bool up = (e & k) == 0;
+                        const float lo = fminf(v[r], v[r | jr]), hi = fmaxf(v[r], v[r | jr]);
+                        v[r] = up ? lo : hi;
+                        v[r | jr] = up ? hi : lo;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int e = lane + 32 * r;
+                    const float o = __shfl_xor_sync(0xffffffffu, v[r], j);
+                    const bool up = (e & k) == 0, lower = (lane & j) == 0;
+                    v[r] = (up == lower) ? fminf(v[r], o) : fmaxf(v[r], o);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) a[lane + 32 * r] = v[r];
+    __syncwarp();
+}
+
 // ------------------------------------------------------------------------------------------------
 // (a6) models/rendering.py:7-46 + :267-272.  One warp per ray:
 //   stage z / w rows in smem (coalesced), warp-scan the CDF, per-lane binary search
@@ -83,7 +123,7 @@ posenc_kernel(const float* __restrict__ x, int64_t n, int n_freqs, float* __rest
 //   sorted whenever u is (det, or a sorted u_in) -- checked with a warp vote, otherwise z_new alone goes through a
 //   bitonic network -- and every element then finds its output slot by one binary search in the other list
 //   (rank of a coarse z = i + #{z_new < z}, rank of a new z = j + #{z_coarse <= z}: a stable merge, no collisions).
-// smem per warp: cdf[Ns-1], bins[Ns-1], zc[Ns], zn[P] with P = next_pow2(Ni), out[Ns+Ni].
+// smem per warp: cdf[Ns-1], bins[Ns-1], zc[Ns], zn[P] with P = max(32, next_pow2(Ni)), out[Ns+Ni].
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse,
@@ -169,7 +209,15 @@ sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restr
         // is z_new already ascending?
         bool ok = true;
         for (int j = lane; j + 1 < Ni; j += 32) ok = ok && (zn[j] <= zn[j + 1]);
-        if (!__all_sync(0xffffffffu, ok)) {
+        const bool unsorted = !__all_sync(0xffffffffu, ok);
+        if (unsorted && P <= 256) {
+            // stochastic u: bitonic sort in REGISTERS (P/32 keys per lane, exchanges across lanes by shuffle) -- the
+            // shared-memory network below costs a load/compare/store/__syncwarp round trip per stage (28 stages at P = 128)
+            if (P <= 32) warp_bitonic_regs<1>(zn, lane);
+            else if (P == 64) warp_bitonic_regs<2>(zn, lane);
+            else if (P == 128) warp_bitonic_regs<4>(zn, lane);
+            else warp_bitonic_regs<8>(zn, lane);
+        } else if (unsorted) {
             // warp bitonic sort of the P new keys in smem
             for (int k = 2; k <= P; k <<= 1) {
                 for (int j = k >> 1; j > 0; j >>= 1) {
@@ -248,7 +296,7 @@ extern "C" int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse
                 "nwb_sample_pdf_merge: need n_samples>=3, n_importance>=1");
     NWB_REQUIRE(n_samples + n_importance <= 4096, "nwb_sample_pdf_merge: too many samples per ray");
     if (n_rays == 0) return NWB_OK;
-    int P = 1;
+    int P = 32;                                  // sort width: >= one key per lane (register sort), +inf padded
     while (P < n_importance) P <<= 1;
     const int warps = 4;
     const size_t smem = static_cast<size_t>(warps) * (2 * (n_samples - 1) + P + 2 * n_samples + n_importance) * sizeof(float);

@@ -89,7 +89,8 @@ def test_sample_pdf_indices_bit_exact_given_cdf(det):
     assert inds.max().item() == 63 or det
 
 
-@pytest.mark.parametrize("ns,ni", [(64, 64), (128, 128), (64, 128), (33, 17)])
+# sort widths: 32 (padded), 64, 128 and 256 keys in registers, 512 through the shared-memory network
+@pytest.mark.parametrize("ns,ni", [(64, 64), (128, 128), (64, 128), (33, 17), (16, 5), (64, 200), (64, 300), (8, 1)])
 def test_sample_pdf_merge_own_cdf(ns, ni):
     gen = torch.Generator().manual_seed(9)
     N = 301
@@ -101,6 +102,8 @@ def test_sample_pdf_merge_own_cdf(ns, ni):
     want = torch.sort(torch.cat([z, s], -1), -1)[0]
     zo, zn, ii = K.sample_pdf_merge(z.to(DEV), w.to(DEV), ni, False, u.to(DEV), debug=True)
     assert (zo[:, 1:] >= zo[:, :-1]).all()                   # sortedness
+    # the merge itself is exact: the output is sort(cat) of the coarse depths and the kernel's own new samples
+    assert torch.equal(zo.cpu(), torch.sort(torch.cat([z, zn.cpu()], -1), -1)[0])
     # the in-kernel CDF is a warp scan, ATen's a sequential sum: cdf differs by ~1 ulp, which the
     # inverse-CDF lerp turns into <= ulp/pdf_bin of a bin width
     assert maxerr(zo, want) <= 1e-4, maxerr(zo, want)
