@@ -269,24 +269,15 @@ field_dgrad_kernel(const BwdArgs a) {
 
             for (int g = nl - 1; g >= 0; --g) {
                 // ReLU gates of layer g (prefetched before waiting for the accumulator)
-                uint32_t mw[8];
-#pragma unroll
-                for (int w = 0; w < 8; ++w) mw[w] = 0u;
-                if (g != 8 && !ghost) {
-                    // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit relu_mask_bit(j) = column 64q+16sub+j);
-                    // gathered here into the old per-row order, entry (sub, q) at sub*4 + q
+                // (the loads are issued here; their first use -- the decode into mw[] -- comes after the accumulator wait, so
+                // the L2/DRAM round trip of the masks overlaps the wait instead of preceding it: 7 % of all stall samples sat
+                // on the decode's first instruction, profiles/r01d_stalls_dgrad_fine.md)
+                uint2 a0 = make_uint2(0u, 0u), a1 = a0, a2 = a0, a3 = a0;
+                const bool gated = (g != 8 && !ghost);
+                if (gated) {
+                    // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit relu_mask_bit(j) = column 64q+16sub+j)
                     const uint2* mp = reinterpret_cast<const uint2*>(save_tile + sl.mask_off(g, nl)) + row;
-                    const uint2 a0 = __ldg(mp), a1 = __ldg(mp + 128), a2 = __ldg(mp + 256), a3 = __ldg(mp + 384);
-                    const uint4 m0 = make_uint4(a0.x, a0.y, a1.x, a1.y), m1 = make_uint4(a2.x, a2.y, a3.x, a3.y);
-                    const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-#pragma unroll
-                    for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31: entry of columns 32w..+15 in the high half
-                        const int q = w >> 1, s0 = (w & 1) * 2;
-                        const int ihi = s0 * 4 + q, ilo = (s0 + 1) * 4 + q;
-                        const uint32_t hi = (m[ihi >> 1] >> ((ihi & 1) * 16)) & 0xFFFFu;
-                        const uint32_t lo = (m[ilo >> 1] >> ((ilo & 1) * 16)) & 0xFFFFu;
-                        mw[w] = (hi << 16) | lo;
-                    }
+                    a0 = __ldg(mp); a1 = __ldg(mp + 128); a2 = __ldg(mp + 256); a3 = __ldg(mp + 384);
                 }
                 // head weights of this layer's head term, lane-distributed: hwl[slice][head] = hw[head][32*slice + lane]
                 float hwl[20];
@@ -304,6 +295,22 @@ field_dgrad_kernel(const BwdArgs a) {
                     ptx::mbar_wait(bar_acc, acc_ev & 1u);
                     ++acc_ev;
                     ptx::tc_fence_after_sync();
+                }
+                uint32_t mw[8];
+#pragma unroll
+                for (int w = 0; w < 8; ++w) mw[w] = 0u;
+                if (gated) {
+                    // gathered into per-row order, entry (sub, q) at sub*4 + q
+                    const uint4 m0 = make_uint4(a0.x, a0.y, a1.x, a1.y), m1 = make_uint4(a2.x, a2.y, a3.x, a3.y);
+                    const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+                    for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31: entry of columns 32w..+15 in the high half
+                        const int q = w >> 1, s0 = (w & 1) * 2;
+                        const int ihi = s0 * 4 + q, ilo = (s0 + 1) * 4 + q;
+                        const uint32_t hi = (m[ihi >> 1] >> ((ihi & 1) * 16)) & 0xFFFFu;
+                        const uint32_t lo = (m[ilo >> 1] >> ((ilo & 1) * 16)) & 0xFFFFu;
+                        mw[w] = (hi << 16) | lo;
+                    }
                 }
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 2);    // accumulator seen
                 if (leader) ptx::bulk_wait_read<0>();       // the previous image's bulk store has read sD
