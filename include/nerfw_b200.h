@@ -111,7 +111,7 @@ int nwb_composite_bwd(const float* raw, int C, const float* z, const float* nois
  * models/rendering.py:96-139.  W=256, D=8, skips=[4] (the only shape the reference ever builds).
  * ---------------------------------------------------------------------------------------- */
 typedef struct nwb_field_desc {
-    int in_xyz;        /* 3+6*N_emb_xyz, <= 128                      nerf.py:83  */
+    int in_xyz;        /* 3+6*N_emb_xyz, <= 64 (N_emb_xyz <= 10)     nerf.py:83  */
     int in_dir;        /* 3+6*N_emb_dir                              nerf.py:83  */
     int in_a;          /* appearance width, 0 = no encode_appearance nerf.py:84  */
     int in_t;          /* transient width,  0 = no encode_transient  nerf.py:85  */
@@ -201,6 +201,11 @@ size_t nwb_mlp_save_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mo
 int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const float* rays, int ray_stride,
                 const float* z, const float* x_enc, int n_freq_xyz, const float* ray_bias,
                 int n_rays, int S, uint32_t mode, float* raw_out, void* saved, void* stream);
+
+/* which kernel nwb_mlp_fwd launches: 0 (default) = chosen per launch -- whole rounds of 296 tiles on the CTA-pair
+ * kernel, a remainder of <= 148 tiles on the one-tile kernel; 1 = always the one-tile kernel; 2 = always the pair
+ * kernel.  Process-wide; results are identical, only speed differs (tests walk every branch with it). */
+int nwb_mlp_fwd_select(int gen);
 
 /* backward of nwb_mlp_fwd: raw (the forward's output) and its cotangent d_raw (n_points, C) ->
  * parameter gradients (ACCUMULATED into the sinks with fp32 atomics; the caller zeroes them) and the

@@ -15,6 +15,22 @@ int set_error(int code, const char* fmt, ...) {
     return code;
 }
 
+int current_device_checked(int* dev_out) {
+    static int sms[kMaxDevices] = {0};               // 0 = not queried yet
+    int dev = 0;
+    NWB_CUDA(cudaGetDevice(&dev));
+    NWB_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal %d out of range", dev);
+    if (sms[dev] == 0) {
+        int n = 0;
+        NWB_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+        sms[dev] = n;
+    }
+    NWB_REQUIRE(sms[dev] == kNumSMs, "device %d has %d SMs; the persistent grids of this build are sized for %d (B200)",
+                dev, sms[dev], kNumSMs);
+    *dev_out = dev;
+    return NWB_OK;
+}
+
 }  // namespace nwb
 
 extern "C" int nwb_abi_version(void) { return 1; }

@@ -41,6 +41,21 @@ int set_error(int code, const char* fmt, ...);
                                   cudaGetErrorString(e__), __FILE__, __LINE__);           \
     } while (0)
 
+// ---- per-device one-time kernel configuration --------------------------------------------------
+// cudaFuncSetAttribute is a per-device setting: every launcher keeps one flag per device ordinal (a process may
+// drive several GPUs from several host threads; the flag write is idempotent) and checks the SM count the
+// persistent grids were sized for.
+constexpr int kMaxDevices = 64;
+int current_device_checked(int* dev_out);       // cudaGetDevice + "148 SMs" check, cached per device (api.cu)
+
+#define NWB_CONFIGURE_ONCE(flags, ...)                                          \
+    do {                                                                        \
+        int dev__ = 0;                                                          \
+        int rc__ = nwb::current_device_checked(&dev__);                         \
+        if (rc__ != NWB_OK) return rc__;                                        \
+        if (!(flags)[dev__]) { __VA_ARGS__; (flags)[dev__] = true; }            \
+    } while (0)
+
 // ---- torch.linspace(0,1,n)[i] exactly as ATen computes it in fp32 ----------------------------
 // step = (end-start)/(n-1); lower half counts up from start, upper half counts down from end
 // with a fused multiply-add (verified bit-exact against torch.linspace for n = 2..1024).
@@ -56,9 +71,11 @@ __host__ __device__ __forceinline__ float linspace01(int i, int n) {
 }
 
 // ---- Philox4x32-10 counter RNG (timed runs; parity runs pass explicit tensors) ---------------
-__device__ __forceinline__ uint4 philox4x32(uint64_t seed, uint64_t ctr) {
+// `draw` names the draw site (0 = coarse stratified jitter, 1 = inverse-CDF uniforms): it occupies a counter word of
+// its own, so two sites keyed by the same seed never share a counter block.
+__device__ __forceinline__ uint4 philox4x32(uint64_t seed, uint64_t ctr, uint32_t draw) {
     uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
-    uint32_t c0 = static_cast<uint32_t>(ctr), c1 = static_cast<uint32_t>(ctr >> 32), c2 = 0x9E3779B9u,
+    uint32_t c0 = static_cast<uint32_t>(ctr), c1 = static_cast<uint32_t>(ctr >> 32), c2 = draw,
              c3 = 0xBB67AE85u;
 #pragma unroll
     for (int r = 0; r < 10; ++r) {

@@ -417,9 +417,11 @@ field_dgrad_kernel(const BwdArgs a) {
 
 using namespace nwb;
 
+#ifdef NWB_BWD_TRACE
 static long long* g_bwd_trace = nullptr;
-// debug hook (tools/trace_bwd.py): device buffer of >= 8*13 int64 that block 0 fills with clock64() stamps
+// tools/trace_bwd.py (a -DNWB_BWD_TRACE build only): device buffer of >= 8*13 int64 that block 0 fills with clock64() stamps
 extern "C" void nwb_debug_set_bwd_trace(void* buf) { g_bwd_trace = static_cast<long long*>(buf); }
+#endif
 
 int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* grads, const uint8_t* saved, size_t save_tile_bytes,
                      const uint8_t* dz, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st);
@@ -470,15 +472,17 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
     a.d_ray_bias = d_ray_bias;
     a.g_head_b[0] = grads->sigma_b; a.g_head_b[1] = grads->rgb_b; a.g_head_b[2] = grads->tsigma_b;
     a.g_head_b[3] = grads->trgb_b; a.g_head_b[4] = grads->tbeta_b;
-    a.S = S; a.mode = mode; a.trace = g_bwd_trace;
+    a.S = S; a.mode = mode;
+#ifdef NWB_BWD_TRACE
+    a.trace = g_bwd_trace;
+#endif
 
     if (run_dgrad) {
-        static bool configured = false;
-        if (!configured) {
+        static bool configured[kMaxDevices] = {};
+        NWB_CONFIGURE_ONCE(configured, {
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-            configured = true;
-        }
+        });
         const int grid = 2 * std::min((a.n_tiles + 1) / 2, kNumSMs);      // CTA pairs, two CTAs per SM
         field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
         NWB_LAUNCH_CHECK();

@@ -23,7 +23,6 @@
 // Activations never leave the SM unless NWB_MLP_SAVE asks for them (bf16 tile images for backward).
 #include "field_dev.cuh"
 #include <algorithm>
-#include <cstdlib>
 
 namespace nwb {
 
@@ -528,9 +527,20 @@ field_fwd_kernel(const FwdArgs a) {
 
 using namespace nwb;
 
+#ifdef NWB_FWD_TRACE
 static long long* g_fwd_trace = nullptr;
-// debug hook (tools/trace_fwd.py): device buffer of >= 16*13 int64 that block 0 fills with clock64() stamps
+// tools/trace_fwd.py (a -DNWB_FWD_TRACE build only): device buffer of >= 16*13 int64 that block 0 fills with clock64() stamps
 extern "C" void nwb_debug_set_fwd_trace(void* buf) { g_fwd_trace = static_cast<long long*>(buf); }
+#endif
+
+// which forward kernel nwb_mlp_fwd launches: 0 = per launch, whichever is faster (default); 1 = always the
+// one-tile kernel; 2 = always the CTA-pair kernel.  Process-wide, read at launch time.
+static int g_fwd_gen = 0;
+extern "C" int nwb_mlp_fwd_select(int gen) {
+    NWB_REQUIRE(gen >= 0 && gen <= 2, "nwb_mlp_fwd_select: gen must be 0, 1 or 2");
+    g_fwd_gen = gen;
+    return NWB_OK;
+}
 
 extern "C" size_t nwb_mlp_save_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode) {
     FieldShape fs;
@@ -569,31 +579,28 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
     a.mode = mode; a.raw_out = raw_out; a.saved = static_cast<uint8_t*>(saved);
     const SaveLayout sl{fs.kx, transient};
     a.save_tile_bytes = sl.tile_bytes(fs.n_layers(mode));
+#ifdef NWB_FWD_TRACE
     a.trace = g_fwd_trace;
+#endif
 
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[kMaxDevices] = {};
+    NWB_CONFIGURE_ONCE(configured, {
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
-        configured = true;
-    }
-    // second-generation kernel (CTA pairs, two tiles in flight per CTA); NWB_FWD_GEN=1 selects the first one
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
+    });
+    // second-generation kernel (CTA pairs, two tiles in flight per CTA); nwb_mlp_fwd_select(1) forces the first one
     // Two kernels, each used where it is faster [B200, tools/perf_fwd.py]: a round of the pair kernel (74 clusters x
     // 4 tiles) costs ~1.55x (inference) / ~1.75x (saving activations) a round of the one-tile kernel (148 CTAs x 1
     // tile).  So: whole rounds of 296 tiles go to the pair kernel, and a remainder of <= 148 tiles -- which would
     // cost it a full round -- goes to the one-tile kernel, launched behind it on the same stream.
-    static const int gen = [] { const char* e = getenv("NWB_FWD_GEN"); return e == nullptr ? 0 : atoi(e); }();   // 1 / 2 force a kernel
+    const int gen = g_fwd_gen;                                      // nwb_mlp_fwd_select: 1 / 2 force a kernel
     constexpr int kRound = 4 * (kNumSMs / 2);
     int pair_tiles = a.n_tiles;                                     // tiles [0, pair_tiles) -> pair kernel
     if (gen == 1) pair_tiles = 0;
     else if (gen != 2 && a.n_tiles % kRound != 0 && a.n_tiles % kRound <= kNumSMs) pair_tiles = a.n_tiles - a.n_tiles % kRound;
     if (pair_tiles > 0) {
-        static bool configured2 = false;
-        if (!configured2) {
-            NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
-            NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
-            configured2 = true;
-        }
         FwdArgs a2 = a;
         a2.n_tiles = pair_tiles;
         const int grid2 = 2 * std::min((pair_tiles + 3) / 4, kNumSMs / 2);
@@ -603,8 +610,7 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
         if (pair_tiles == a.n_tiles) return NWB_OK;
     }
     a.first_tile = pair_tiles;
-    int grid = std::min(a.n_tiles - a.first_tile, kNumSMs);
-    if (const char* e = getenv("NWB_DEBUG_GRID")) grid = std::max(1, std::min(grid, atoi(e)));   // bottleneck experiments only
+    const int grid = std::min(a.n_tiles - a.first_tile, kNumSMs);
     if (mode & NWB_MLP_SAVE) field_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
     else field_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
     NWB_LAUNCH_CHECK();

@@ -171,8 +171,7 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
     const bool transient = (mode & NWB_MLP_TRANSIENT) != 0;
     const SaveLayout sl{fs.kx, transient};
     const DzLayout dl{transient};
-    static WgArgs a;                       // host staging (passed by value at launch)
-    a = WgArgs{};
+    WgArgs a{};                            // passed by value at launch
     a.dz = dz; a.saved = saved; a.dz_tile_bytes = dz_tile_bytes; a.save_tile_bytes = save_tile_bytes;
     a.n_tiles = n_tiles;
     int nu = 0;
@@ -254,11 +253,10 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
         a.units[i].splits = static_cast<uint16_t>(sp[i]);
         cta += sp[i];
     }
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[kMaxDevices] = {};
+    NWB_CONFIGURE_ONCE(configured, {
         NWB_CUDA(cudaFuncSetAttribute(field_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
-        configured = true;
-    }
+    });
     field_wgrad_kernel<<<cta, kWgThreads, kWgSmem, st>>>(a);
     NWB_LAUNCH_CHECK();
     return NWB_OK;

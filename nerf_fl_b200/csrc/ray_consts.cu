@@ -185,13 +185,21 @@ ray_consts_bwd_kernel(FieldShape fs, nwb_field_params p, nwb_field_grads g, cons
         float acc = 0.0f;
 #pragma unroll 8
         for (int j = 0; j < kHalf; ++j) acc = fmaf(sw[j * ne + e], gr[j], acc);
+        // an index outside [0, n_vocab) was reported by the forward (err_flag) and gathered nothing there: it scatters
+        // nothing here either (the reference device-asserts, README.md:124)
         if (e < na) {
             if (d_a_rows) d_a_rows[static_cast<int64_t>(r0 + r) * na + e] = acc;
-            else if (d_emb_a) atomicAdd(d_emb_a + ts[r0 + r] * na + e, acc);
+            else if (d_emb_a) {
+                const int64_t t = ts[r0 + r];
+                if (t >= 0 && t < n_vocab) atomicAdd(d_emb_a + t * na + e, acc);
+            }
         } else {
             const int k = e - na;
             if (d_t_rows) d_t_rows[static_cast<int64_t>(r0 + r) * nt + k] = acc;
-            else if (d_emb_t) atomicAdd(d_emb_t + ts[r0 + r] * nt + k, acc);
+            else if (d_emb_t) {
+                const int64_t t = ts[r0 + r];
+                if (t >= 0 && t < n_vocab) atomicAdd(d_emb_t + t * nt + k, acc);
+            }
         }
     }
 }
@@ -245,10 +253,15 @@ extern "C" int nwb_ray_consts_bwd(const nwb_field_desc* d, const nwb_field_param
     const int ne = fs.in_a + (use_t ? fs.in_t : 0);
     const size_t smem = (static_cast<size_t>(kRcbRays) * (256 + feat_ld) + static_cast<size_t>(kHalf) * ne) * sizeof(float);
     NWB_REQUIRE(smem <= 200 * 1024, "nwb_ray_consts_bwd: feature rows too wide for the staging buffer");
-    static size_t configured = 0;
-    if (smem > configured) {
-        NWB_CUDA(cudaFuncSetAttribute(ray_consts_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        configured = smem;
+    static size_t configured[kMaxDevices] = {};
+    {
+        int dev = 0;
+        rc = current_device_checked(&dev);
+        if (rc != NWB_OK) return rc;
+        if (smem > configured[dev]) {
+            NWB_CUDA(cudaFuncSetAttribute(ray_consts_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            configured[dev] = smem;
+        }
     }
     const int blocks = (n_rays + kRcbRays - 1) / kRcbRays;
     ray_consts_bwd_kernel<<<blocks, kRcbThreads, smem, static_cast<cudaStream_t>(stream)>>>(

@@ -42,7 +42,7 @@ sample_coarse_kernel(const float* __restrict__ rays, int ray_stride, int n_rays,
             if (perturb_rand != nullptr) {
                 u = __ldg(perturb_rand + idx);
             } else {
-                const uint4 rnd = philox4x32(seed, static_cast<uint64_t>(idx) >> 2);
+                const uint4 rnd = philox4x32(seed, static_cast<uint64_t>(idx) >> 2, 0u);
                 const uint32_t w = (idx & 3) == 0 ? rnd.x : (idx & 3) == 1 ? rnd.y : (idx & 3) == 2 ? rnd.z : rnd.w;
                 u = u01(w);
             }
@@ -182,7 +182,7 @@ sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restr
                 u = __ldg(u_in + static_cast<int64_t>(ray) * Ni + j);
             } else {
                 const uint64_t ctr = static_cast<uint64_t>(ray) * Ni + j;
-                const uint4 rnd = philox4x32(seed ^ 0x5DEECE66DULL, ctr >> 2);
+                const uint4 rnd = philox4x32(seed, ctr >> 2, 1u);
                 const uint32_t w = (ctr & 3) == 0 ? rnd.x : (ctr & 3) == 1 ? rnd.y : (ctr & 3) == 2 ? rnd.z : rnd.w;
                 u = u01(w);
             }
@@ -300,7 +300,7 @@ extern "C" int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse
     while (P < n_importance) P <<= 1;
     const int warps = 4;
     const size_t smem = static_cast<size_t>(warps) * (2 * (n_samples - 1) + P + 2 * n_samples + n_importance) * sizeof(float);
-    if (smem > 48 * 1024)
+    if (smem > 48 * 1024)        // per device and per size: set on every such call (a host-side attribute write)
         NWB_CUDA(cudaFuncSetAttribute(sample_pdf_merge_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     const int blocks = std::min((n_rays + warps - 1) / warps, kNumSMs * 8);

@@ -11,7 +11,7 @@ struct SelftestParams {
     uint32_t idesc;
     uint32_t a_lbo, a_sbo, a_kstep, a_every, a_kblock;
     uint32_t b_lbo, b_sbo, b_kstep, b_every, b_kblock;
-    uint32_t n_ksteps, N, a_bytes, b_bytes;
+    uint32_t n_ksteps, N, a_bytes, b_bytes, f8;
 };
 
 __global__ void __launch_bounds__(128, 1)
@@ -45,8 +45,12 @@ umma_selftest_kernel(const uint8_t* __restrict__ a_img, const uint8_t* __restric
         for (uint32_t k = 0; k < p.n_ksteps; ++k) {
             const uint32_t ao = (k / p.a_every) * p.a_kblock + (k % p.a_every) * p.a_kstep;
             const uint32_t bo = (k / p.b_every) * p.b_kblock + (k % p.b_every) * p.b_kstep;
-            ptx::umma_bf16(tmem, ptx::umma_desc_sw128(a0 + ao, p.a_lbo, p.a_sbo),
-                           ptx::umma_desc_sw128(b0 + bo, p.b_lbo, p.b_sbo), p.idesc, k > 0);
+            if (p.f8)
+                ptx::umma_f8(tmem, ptx::umma_desc_sw128(a0 + ao, p.a_lbo, p.a_sbo),
+                             ptx::umma_desc_sw128(b0 + bo, p.b_lbo, p.b_sbo), p.idesc, k > 0);
+            else
+                ptx::umma_bf16(tmem, ptx::umma_desc_sw128(a0 + ao, p.a_lbo, p.a_sbo),
+                               ptx::umma_desc_sw128(b0 + bo, p.b_lbo, p.b_sbo), p.idesc, k > 0);
         }
         ptx::umma_commit(&bar_mma);
     }
@@ -74,13 +78,15 @@ using namespace nwb;
 
 // variant 0: A image of (128 x K), B image of (N x K), both K-major  (forward / dgrad shape)
 // variant 1: A image of (K x 128), B image of (K x N), both MN-major (wgrad shape: D = A^T B)
+// variant 3: the 8-bit wgrad shape: A image of (K x 128) e5m2, B image of (K x N) e4m3, both MN-major, images cut into
+//            128-column blocks of (K rows x 128 B); tcgen05.mma kind::f8f6f4, K = 32 per instruction
 // overrides (host pointer, may be NULL): 11 uint32 replacing idesc, a_{lbo,sbo,kstep,every,kblock},
 // b_{...}; a zero entry keeps the default.
 extern "C" int nwb_selftest_umma(const void* a_img, const void* b_img, int N, int K, int variant,
                                  const uint32_t* overrides, float* d_out, void* stream) {
     NWB_REQUIRE(a_img && b_img && d_out, "nwb_selftest_umma: null pointer");
     NWB_REQUIRE(N >= 16 && N <= 256 && N % 16 == 0, "nwb_selftest_umma: N must be a multiple of 16 in [16,256]");
-    NWB_REQUIRE(variant >= 0 && variant <= 2, "nwb_selftest_umma: variant must be 0, 1 or 2");
+    NWB_REQUIRE(variant >= 0 && variant <= 3, "nwb_selftest_umma: variant must be 0..3");
     SelftestParams p{};
     p.N = N;
     if (variant == 0) {
@@ -101,6 +107,16 @@ extern "C" int nwb_selftest_umma(const void* a_img, const void* b_img, int N, in
         p.n_ksteps = K / 16;
         p.a_lbo = 16; p.a_sbo = 1024; p.a_kstep = 32; p.a_every = 4; p.a_kblock = 128 * 128;
         p.b_lbo = K * 128; p.b_sbo = 1024; p.b_kstep = 2048; p.b_every = 1u << 30; p.b_kblock = 0;
+    } else if (variant == 3) {
+        NWB_REQUIRE(K % 32 == 0 && K >= 32 && K <= 128, "nwb_selftest_umma: variant 3 needs K multiple of 32, <=128");
+        NWB_REQUIRE(N % 128 == 0, "nwb_selftest_umma: variant 3 needs N multiple of 128");
+        p.f8 = 1;
+        p.idesc = ptx::umma_idesc_f8(128, N, 1, 0, true, true);
+        p.a_bytes = K * 128;              // one 128-column block of (K rows x 128 B)
+        p.b_bytes = K * N;
+        p.n_ksteps = K / 32;
+        p.a_lbo = K * 128; p.a_sbo = 1024; p.a_kstep = 4096; p.a_every = 1u << 30; p.a_kblock = 0;
+        p.b_lbo = K * 128; p.b_sbo = 1024; p.b_kstep = 4096; p.b_every = 1u << 30; p.b_kblock = 0;
     } else {
         NWB_REQUIRE(K % 16 == 0 && K >= 16 && K <= 128, "nwb_selftest_umma: variant 1 needs K multiple of 16, <=128");
         NWB_REQUIRE(N % 64 == 0, "nwb_selftest_umma: variant 1 needs N multiple of 64");

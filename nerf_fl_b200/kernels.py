@@ -20,12 +20,19 @@ launch_count = 0   # kernels launched through this module since import (bench.py
 class _timed:
     """Brackets one C-ABI call with CUDA events on the launching stream when timing is on."""
 
-    def __init__(self, name, units, mode=0):
+    def __init__(self, name, units, mode=0, dev=None):
         self.name, self.units, self.mode = name, units, mode
+        self.guard = None
+        if dev is not None:
+            dev = torch.device(dev)
+            if dev.type == "cuda" and dev.index is not None and dev.index != torch.cuda.current_device():
+                self.guard = torch.cuda.device(dev)      # kernels launch on the CURRENT device: make it the tensors'
 
     def __enter__(self):
         global launch_count
         launch_count += 1
+        if self.guard is not None:
+            self.guard.__enter__()
         if _timing is not None:
             self.e0 = torch.cuda.Event(enable_timing=True)
             self.e0.record()
@@ -36,6 +43,8 @@ class _timed:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
             _timing.append((self.name, self.units, self.mode, self.e0, e1))
+        if self.guard is not None:
+            self.guard.__exit__(*exc)
         return False
 
 
@@ -67,7 +76,7 @@ def sample_coarse(rays: torch.Tensor, n_samples: int, use_disp: bool = False, pe
     n = rays.shape[0]
     z = torch.empty(n, n_samples, device=rays.device, dtype=torch.float32)
     pr = _f32(perturb_rand) if perturb_rand is not None else None
-    with _timed("nwb_sample_coarse", n):
+    with _timed("nwb_sample_coarse", n, dev=rays.device):
         L.check(L.lib().nwb_sample_coarse(L.ptr(rays), rays.shape[1], n, n_samples, int(bool(use_disp)),
                                           float(perturb), L.ptr(pr), int(seed) & (2 ** 64 - 1), L.ptr(z),
                                           L.stream_ptr(rays.device)), "nwb_sample_coarse")
@@ -79,8 +88,9 @@ def posenc(x: torch.Tensor, n_freqs: int) -> torch.Tensor:
     x = _f32(x)
     assert x.dim() == 2 and x.shape[1] == 3, "PosEmbedding expects (B, 3)"
     out = torch.empty(x.shape[0], 3 + 6 * n_freqs, device=x.device, dtype=torch.float32)
-    L.check(L.lib().nwb_posenc(L.ptr(x), x.shape[0], n_freqs, L.ptr(out), L.stream_ptr(x.device)),
-            "nwb_posenc")
+    with _timed("nwb_posenc", x.shape[0], dev=x.device):
+        L.check(L.lib().nwb_posenc(L.ptr(x), x.shape[0], n_freqs, L.ptr(out), L.stream_ptr(x.device)),
+                "nwb_posenc")
     return out
 
 
@@ -96,7 +106,7 @@ def sample_pdf_merge(z_coarse: torch.Tensor, w_coarse: torch.Tensor, n_importanc
     inds = torch.empty(n, n_importance, device=dev, dtype=torch.int64) if debug else None
     u_ = _f32(u) if u is not None else None
     cdf_ = _f32(cdf) if cdf is not None else None
-    with _timed("nwb_sample_pdf_merge", n):
+    with _timed("nwb_sample_pdf_merge", n, dev=dev):
         L.check(L.lib().nwb_sample_pdf_merge(L.ptr(z_coarse), L.ptr(w_coarse), n, ns, n_importance,
                                              int(bool(det)), L.ptr(u_), int(seed) & (2 ** 64 - 1),
                                              L.ptr(cdf_), L.ptr(z_out), L.ptr(z_new), L.ptr(inds),
@@ -146,7 +156,7 @@ def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bo
         res[f"depth_{typ}"] = new(n)
         o.depth = L.ptr(res[f"depth_{typ}"])
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
-    with _timed("nwb_composite_fwd", n, Cc * 1000 + S):
+    with _timed("nwb_composite_fwd", n, Cc * 1000 + S, dev=dev):
         L.check(L.lib().nwb_composite_fwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
                                           composite_flags(transient, white_back, test_time, coarse),
                                           float(beta_min), C.byref(o), L.stream_ptr(dev)),
@@ -184,7 +194,7 @@ def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, 
         put("d_rgb", f"rgb_{typ}")
     d_raw = torch.empty_like(raw)
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
-    with _timed("nwb_composite_bwd", n, Cc * 1000 + S):
+    with _timed("nwb_composite_bwd", n, Cc * 1000 + S, dev=z.device):
         L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
                                           composite_flags(transient, white_back, False, typ == "coarse"),
                                           C.byref(g), L.ptr(d_raw), L.stream_ptr(z.device)),
@@ -265,7 +275,7 @@ def field_pack(desc: L.FieldDesc, sd: dict, out: torch.Tensor | None = None) -> 
     if out is None:
         out = aligned_empty(nbytes, dev)
     st, keep = field_slots(sd)
-    with _timed("nwb_field_pack", 1):
+    with _timed("nwb_field_pack", 1, dev=dev):
         L.check(_fn("nwb_field_pack", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp])(
             C.byref(desc), C.byref(st), L.ptr(out), L.stream_ptr(dev)), "nwb_field_pack")
     return out
@@ -286,7 +296,7 @@ def ray_consts_fwd(desc, sd, dirs, *, dir_is_encoded=False, n_freq_dir=4, ts=Non
     n_vocab = emb_a.shape[0] if emb_a is not None else (emb_t.shape[0] if emb_t is not None else 0)
     fn = _fn("nwb_ray_consts_fwd", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _i, _i, _i, _vp, _vp, _vp,
                                     _i, _vp, _vp, _i, _u32, _vp, _vp, _vp, _vp])
-    with _timed("nwb_ray_consts_fwd", n, mode):
+    with _timed("nwb_ray_consts_fwd", n, mode, dev=dev):
         L.check(fn(C.byref(desc), C.byref(st), L.ptr(dirs), dirs.shape[1], int(dir_is_encoded), n_freq_dir, L.ptr(ts),
                    L.ptr(emb_a), L.ptr(emb_t), n_vocab, L.ptr(a_rows), L.ptr(t_rows), n, mode, L.ptr(feat), L.ptr(bias),
                    L.ptr(err_flag), L.stream_ptr(dev)), "nwb_ray_consts_fwd")
@@ -310,11 +320,29 @@ def mlp_fwd(desc, packed, *, n_rays, S, mode, ray_bias=None, rays=None, z=None, 
     if out is None:
         out = torch.empty(n_rays * S, Cc, device=dev, dtype=torch.float32)
     fn = _fn("nwb_mlp_fwd", [C.POINTER(L.FieldDesc), _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _u32, _vp, _vp, _vp])
-    with _timed("nwb_mlp_fwd", n_rays * S, mode):
+    with _timed("nwb_mlp_fwd", n_rays * S, mode, dev=dev):
         L.check(fn(C.byref(desc), L.ptr(packed), L.ptr(rays), rays.shape[1] if rays is not None else 0, L.ptr(z),
                    L.ptr(x_enc), n_freq_xyz, L.ptr(ray_bias), n_rays, S, mode, L.ptr(out), L.ptr(saved),
                    L.stream_ptr(dev)), "nwb_mlp_fwd")
     return out
+
+
+def field_traffic_bytes_per_point(kind: str, fine: bool) -> float:
+    """HBM bytes per sample point one field kernel launch moves by design, from the library's own size queries (the
+    per-tile record sizes of nwb_mlp_save_bytes / nwb_mlp_bwd_workspace_bytes): fwd (saving) writes the saved record;
+    dgrad writes the dZ record and reads the sign masks; wgrad reads both records (without the masks) once."""
+    desc = field_desc(63, 27, 48 if fine else 0, 16 if fine else 0)
+    mode = (L.NWB_MLP_TRANSIENT if fine else 0) | L.NWB_MLP_SAVE
+    save = mlp_save_bytes(desc, 128, mode) / 128.0
+    ws = mlp_bwd_workspace_bytes(desc, 128, mode & ~L.NWB_MLP_SAVE) / 128.0
+    masks = 13 * 4096 / 128.0
+    return {"fwd": save, "dgrad": ws + masks, "wgrad": (save - masks) + ws}[kind]
+
+
+def mlp_fwd_select(gen: int) -> None:
+    """Which forward kernel nwb_mlp_fwd launches: 0 = per launch, whichever is faster (default); 1 = the one-tile
+    kernel; 2 = the CTA-pair kernel (parity tests walk every dispatch branch with it)."""
+    L.check(_fn("nwb_mlp_fwd_select", [_i])(int(gen)), "nwb_mlp_fwd_select")
 
 
 def mlp_bwd_workspace_bytes(desc, n_points: int, mode: int) -> int:
@@ -334,7 +362,7 @@ def mlp_bwd(desc, packed, raw, d_raw, saved, *, n_rays, S, mode, grads: dict, d_
     sig = [C.POINTER(L.FieldDesc), _vp, _vp, _vp, _vp, _i, _i, _u32, C.POINTER(L.FieldGrads), _vp, _vp, _vp]
     for ph in phases:
         name = "nwb_mlp_" + ph
-        with _timed(name, n_rays * S, mode):
+        with _timed(name, n_rays * S, mode, dev=dev):
             L.check(_fn(name, sig)(C.byref(desc), L.ptr(packed), L.ptr(raw), L.ptr(d_raw), L.ptr(saved), n_rays, S, mode,
                                    C.byref(st), L.ptr(d_ray_bias), L.ptr(workspace), L.stream_ptr(dev)), name)
     return workspace
@@ -349,7 +377,7 @@ def ray_consts_bwd(desc, sd, ray_feat, d_ray_bias, *, ts=None, n_vocab=0, transi
     gt, keep2 = field_slots(grads, L.FieldGrads)
     fn = _fn("nwb_ray_consts_bwd", [C.POINTER(L.FieldDesc), C.POINTER(L.FieldParams), _vp, _vp, _vp, _i, _i, _u32,
                                     C.POINTER(L.FieldGrads), _vp, _vp, _vp, _vp, _vp])
-    with _timed("nwb_ray_consts_bwd", ray_feat.shape[0], mode):
+    with _timed("nwb_ray_consts_bwd", ray_feat.shape[0], mode, dev=dev):
         L.check(fn(C.byref(desc), C.byref(st), L.ptr(ray_feat), L.ptr(d_ray_bias), L.ptr(ts), n_vocab, ray_feat.shape[0],
                    mode, C.byref(gt), L.ptr(d_emb_a), L.ptr(d_emb_t), L.ptr(d_a_rows), L.ptr(d_t_rows),
                    L.stream_ptr(dev)), "nwb_ray_consts_bwd")
@@ -373,7 +401,7 @@ def nerfw_loss_fwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda
     terms = torch.empty(5, device=dev, dtype=torch.float32)
     n_ts = transient_sigmas.numel() if transient_sigmas is not None else 0
     fn = _fn("nwb_nerfw_loss_fwd", [_vp] * 5 + [_i, _i64, C.c_float, C.c_float, _vp, _vp, _vp])
-    with _timed("nwb_nerfw_loss_fwd", rgb_coarse.shape[0]):
+    with _timed("nwb_nerfw_loss_fwd", rgb_coarse.shape[0], dev=dev):
         L.check(fn(L.ptr(rgb_coarse), L.ptr(rgb_fine), L.ptr(beta), L.ptr(transient_sigmas), L.ptr(targets),
                    rgb_coarse.shape[0], n_ts, lambda_u, coef, L.ptr(_loss_scratch_for(dev)), L.ptr(terms),
                    L.stream_ptr(dev)), "nwb_nerfw_loss_fwd")
@@ -390,7 +418,7 @@ def nerfw_loss_bwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda
     n_ts = transient_sigmas.numel() if transient_sigmas is not None else 0
     gp = (_vp * 5)(*[(g.data_ptr() if g is not None else None) for g in g_terms])
     fn = _fn("nwb_nerfw_loss_bwd", [_vp] * 5 + [_i, _i64, C.c_float, C.c_float, C.POINTER(_vp * 5), _vp, _vp, _vp, _vp, _vp])
-    with _timed("nwb_nerfw_loss_bwd", rgb_coarse.shape[0]):
+    with _timed("nwb_nerfw_loss_bwd", rgb_coarse.shape[0], dev=dev):
         L.check(fn(L.ptr(rgb_coarse), L.ptr(rgb_fine), L.ptr(beta), L.ptr(transient_sigmas), L.ptr(targets),
                    rgb_coarse.shape[0], n_ts, lambda_u, coef, C.byref(gp), L.ptr(d_c), L.ptr(d_f), L.ptr(d_b), L.ptr(d_s),
                    L.stream_ptr(dev)), "nwb_nerfw_loss_bwd")
@@ -406,7 +434,7 @@ def mse_psnr(pred: torch.Tensor, gt: torch.Tensor, clip01: bool = False) -> torc
     dev = pred.device
     out = torch.empty(2, device=dev, dtype=torch.float32)
     fn = _fn("nwb_mse_psnr", [_vp, _vp, _i64, _i, _vp, _vp, _vp])
-    with _timed("nwb_mse_psnr", pred.numel()):
+    with _timed("nwb_mse_psnr", pred.numel(), dev=dev):
         L.check(fn(L.ptr(pred), L.ptr(gt), pred.numel(), int(clip01), L.ptr(_loss_scratch_for(dev)), L.ptr(out),
                    L.stream_ptr(dev)), "nwb_mse_psnr")
     return out
@@ -425,7 +453,7 @@ def gen_rays(H: int, W: int, K, c2w, near: float, far: float, first_pixel: int =
         out = torch.empty(n, 8, device=device or torch.device("cuda"), dtype=torch.float32)
     cbuf = (C.c_float * 12)(*pose.reshape(-1).tolist())
     fn = _fn("nwb_gen_rays", [_i, _i] + [C.c_float] * 4 + [C.POINTER(C.c_float * 12), C.c_float, C.c_float, _i64, _i64, _vp, _vp])
-    with _timed("nwb_gen_rays", n):
+    with _timed("nwb_gen_rays", n, dev=out.device):
         L.check(fn(H, W, float(Kh[0, 0]), float(Kh[1, 1]), float(Kh[0, 2]), float(Kh[1, 2]), C.byref(cbuf), float(near),
                    float(far), int(first_pixel), n, L.ptr(out), L.stream_ptr(out.device)), "nwb_gen_rays")
     return out
@@ -437,6 +465,6 @@ def pack_rgb8(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     if out is None:
         out = torch.empty(x.shape, device=x.device, dtype=torch.uint8)
     fn = _fn("nwb_pack_rgb8", [_vp, _i64, _vp, _vp])
-    with _timed("nwb_pack_rgb8", x.numel()):
+    with _timed("nwb_pack_rgb8", x.numel(), dev=x.device):
         L.check(fn(L.ptr(x), x.numel(), L.ptr(out), L.stream_ptr(x.device)), "nwb_pack_rgb8")
     return out

@@ -33,3 +33,30 @@ def from_tile_image(img: torch.Tensor, R: int, Cc: int) -> torch.Tensor:
     """Inverse of tile_image -> (R, Cc) bf16."""
     off = image_offsets(R, Cc).to(img.device).flatten()
     return img.flatten()[off].reshape(R, Cc)
+
+
+# ---- 8-bit images (e4m3 / e5m2): same swizzle, 128 columns per 128-byte row --------------------------------------
+def image8_offsets(R: int, Cc: int) -> torch.Tensor:
+    """(R, Cc) int64: BYTE offset of element (r, c) inside an 8-bit tile image (R % 8 == 0, Cc % 128 == 0):
+    column block cb (128 columns = 128 B per row) at cb*R*128; row r at (r//8)*1024 + (r%8)*128; 16-byte chunk j
+    (16 columns) at chunk position j ^ (r%8)."""
+    assert R % 8 == 0 and Cc % 128 == 0, (R, Cc)
+    r = torch.arange(R).unsqueeze(1)
+    c = torch.arange(Cc).unsqueeze(0)
+    cb, j, e = c // 128, (c % 128) // 16, c % 16
+    return cb * (R * 128) + (r // 8) * 1024 + (r % 8) * 128 + ((j ^ (r % 8)) * 16) + e
+
+
+def tile_image8(m: torch.Tensor, dtype=torch.float8_e4m3fn) -> torch.Tensor:
+    """(R, Cc) float tensor -> flat uint8 tensor holding its 8-bit tile image (rounded to `dtype`)."""
+    R, Cc = m.shape
+    off = image8_offsets(R, Cc).to(m.device).flatten()
+    out = torch.empty(R * Cc, dtype=torch.uint8, device=m.device)
+    out[off] = m.to(dtype).view(torch.uint8).flatten()
+    return out
+
+
+def from_tile_image8(img: torch.Tensor, R: int, Cc: int, dtype=torch.float8_e4m3fn) -> torch.Tensor:
+    """Inverse of tile_image8 -> (R, Cc) float32."""
+    off = image8_offsets(R, Cc).to(img.device).flatten()
+    return img.flatten()[off].view(dtype).float().reshape(R, Cc)

@@ -2,41 +2,17 @@
 (ColorLoss :4-16, NerfWLoss :19-50; NeRF-W eq. 13), which sits just outside the per-ray hot path
  and decides which outputs receive cotangents: rgb_coarse, rgb_fine, beta and
 transient_sigmas.  ``NerfWLoss`` / ``ColorLoss`` / ``loss_dict`` keep the reference's names so train.py:80
-can import them from here.  On CUDA tensors ``NerfWLoss`` is one forward and one backward kernel
-(``csrc/objective.cu``: written with torch ops the same reductions are ~40 launches of 2-3 us, a tenth of a
-1024-ray training step); the torch-op expression below remains for CPU tensors (host-logic tests) and for
-``ColorLoss``.
+can import them from here.  Both are one forward and one backward kernel (``csrc/objective.cu``: written with
+torch ops the same reductions are ~40 launches of 2-3 us, a tenth of a 1024-ray training step).  There is no CPU
+or ATen path: CPU tensors raise (the torch-op restatement the tests compare against lives in tests/host_models.py
+and in the oracle).
 """
 from __future__ import annotations
 
 import torch
 from torch import nn
 
-__all__ = ["ColorLoss", "NerfWLoss", "loss_dict", "nerfw_terms"]
-
-
-def _sq_err(results, key, targets):
-    diff = results[key] - targets
-    return diff * diff
-
-
-def nerfw_terms(results: dict, targets: torch.Tensor, lambda_u: float = 0.01) -> dict:
-    """c_l: half the mean squared error of the coarse colour (:37).  With a fine pass: f_l is the same on
-    rgb_fine when there is no transient head (:40), otherwise the beta-weighted error mean(err / (2 beta^2))
-    (:42-43) together with b_l = 3 + mean(log beta) (the offset keeps it positive, :44) and
-    s_l = lambda_u * mean(transient_sigmas) (:45)."""
-    terms = {"c_l": _sq_err(results, "rgb_coarse", targets).mean() * 0.5}
-    if "rgb_fine" not in results:
-        return terms
-    err = _sq_err(results, "rgb_fine", targets)
-    beta = results.get("beta")
-    if beta is None:
-        terms["f_l"] = err.mean() * 0.5
-        return terms
-    terms["f_l"] = (err / (2.0 * beta[:, None] ** 2)).mean()
-    terms["b_l"] = beta.log().mean() + 3.0
-    terms["s_l"] = results["transient_sigmas"].mean() * lambda_u
-    return terms
+__all__ = ["ColorLoss", "NerfWLoss", "loss_dict"]
 
 
 class _NerfWLossFn(torch.autograd.Function):
@@ -73,7 +49,7 @@ class NerfWLoss(nn.Module):
 
     def forward(self, inputs, targets):
         if not targets.is_cuda:
-            return {name: self.coef * val for name, val in nerfw_terms(inputs, targets, self.lambda_u).items()}
+            raise RuntimeError("nerf_fl_b200.NerfWLoss needs CUDA tensors: there is no CPU path")
         rgb_f, beta = inputs.get("rgb_fine"), inputs.get("beta")
         ts = inputs.get("transient_sigmas") if beta is not None else None
         c_l, f_l, b_l, s_l, total = _NerfWLossFn.apply(inputs["rgb_coarse"], rgb_f, beta, ts, targets, self.lambda_u, self.coef)
@@ -87,17 +63,19 @@ class NerfWLoss(nn.Module):
 
 
 class ColorLoss(nn.Module):
-    """Plain-NeRF objective: mean squared error of rgb_coarse (+ rgb_fine), times coef (:10-16)."""
+    """Plain-NeRF objective (losses.py:4-16): coef * (mse(rgb_coarse) + mse(rgb_fine)).  The same kernel pair as
+    NerfWLoss without beta: its total is coef' * 0.5 * (mse_c + mse_f), so coef' = 2 * coef."""
 
     def __init__(self, coef=1):
         super().__init__()
         self.coef = coef
 
     def forward(self, inputs, targets):
-        total = _sq_err(inputs, "rgb_coarse", targets).mean()
-        if "rgb_fine" in inputs:
-            total = total + _sq_err(inputs, "rgb_fine", targets).mean()
-        return total * self.coef
+        if not targets.is_cuda:
+            raise RuntimeError("nerf_fl_b200.ColorLoss needs CUDA tensors: there is no CPU path")
+        *_, total = _NerfWLossFn.apply(inputs["rgb_coarse"], inputs.get("rgb_fine"), None, None, targets, 0.0,
+                                       2.0 * self.coef)
+        return total
 
 
 loss_dict = {"color": ColorLoss, "nerfw": NerfWLoss}

@@ -61,7 +61,12 @@ class FlatTrainState:
     (state_dict keys and shapes are untouched, so checkpoints keep loading) and the parameters are
     tagged so the render_rays backward accumulates into ``.grad`` in place."""
 
-    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, fused_pack=True):
+    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, fused_pack=True,
+                 host_update=None):
+        # host_update(state, world, zero_grad): the optimizer update for NON-CUDA buffers.  The product has none (the
+        # CUDA kernels run or the call raises); the gloo world-size-2 tests of the sharding / all-reduce plumbing
+        # inject a torch-op Adam from tests/host_models.py.
+        self._host_update = host_update
         self.modules = list(modules)
         params, seen = [], set()
         for m in self.modules:
@@ -132,15 +137,14 @@ class FlatTrainState:
 
     # ---- optimizer ---------------------------------------------------------------------------
     def adam_step(self, world: int = 1, zero_grad: bool = True):
-        """utils/__init__.py:31 Adam on the flat buffers (CUDA) -- or, for the gloo CPU tests of the
-        host logic, the same update written with torch ops."""
+        """utils/__init__.py:31 Adam on the flat buffers: one CUDA launch.  No CPU path (see ``host_update``)."""
         self.step_count += 1
         b1, b2 = self.betas
         if self.flat_p.is_cuda and self._fused_fields:
             from . import _lib as L
             from . import kernels as K
             fz = self._fused or self._fused_setup()
-            with K._timed("nwb_adam_pack_step_dev", 0):
+            with K._timed("nwb_adam_pack_step_dev", 0, dev=self.flat_p.device):
                 L.check(fz["fn"](self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
                                  self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay,
                                  self.hyper.data_ptr(), 1.0 / world, int(zero_grad), fz["n"], fz["descs"], fz["params"],
@@ -160,14 +164,11 @@ class FlatTrainState:
             L.check(fn(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
                        self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay, self.hyper.data_ptr(),
                        1.0 / world, int(zero_grad), L.stream_ptr(self.flat_p.device)), "nwb_adam_step_dev")
+        elif self._host_update is not None:
+            self._host_update(self, world, zero_grad)
         else:
-            g = self.flat_g / world + self.weight_decay * self.flat_p
-            self.exp_avg.mul_(b1).add_(g, alpha=1 - b1)
-            self.exp_avg_sq.mul_(b2).addcmul_(g, g, value=1 - b2)
-            bc1, bc2 = 1 - b1 ** self.step_count, 1 - b2 ** self.step_count
-            self.flat_p.addcdiv_(self.exp_avg, self.exp_avg_sq.sqrt() / math.sqrt(bc2) + self.eps, value=-self.lr / bc1)
-            if zero_grad:
-                self.flat_g.zero_()
+            raise RuntimeError("nerf_fl_b200.FlatTrainState: parameters are not on a CUDA device and there is no CPU "
+                               "optimizer path")
         for m in self.modules:                       # packed bf16 operand caches are stale now
             if hasattr(m, "_nwb_cache"):
                 m._nwb_dirty = True
@@ -214,6 +215,53 @@ class FlatTrainState:
                        "covered": int(self.numel - rest.numel())}
         return self._fused
 
+    # ---- checkpoint / resume (train.py:231 resume_from_checkpoint) -------------------------------
+    def optimizer_state(self) -> dict:
+        """The optimizer state in torch.optim.Adam's own layout ({index: {step, exp_avg, exp_avg_sq}}, per parameter
+        in ``self.params`` order), so a Lightning checkpoint of FlatAdam round-trips with one of torch.optim.Adam."""
+        out, off = {}, 0
+        for i, p in enumerate(self.params):
+            n = p.numel()
+            out[i] = {"step": torch.tensor(float(self.step_count)),
+                      "exp_avg": self.exp_avg[off:off + n].view(p.shape).clone(),
+                      "exp_avg_sq": self.exp_avg_sq[off:off + n].view(p.shape).clone()}
+            off += (n + 3) // 4 * 4
+        return out
+
+    def load_optimizer_state(self, state: dict) -> None:
+        off, step = 0, None
+        for i, p in enumerate(self.params):
+            n = p.numel()
+            st = state.get(i, state.get(str(i)))
+            if st is not None:
+                self.exp_avg[off:off + n].copy_(st["exp_avg"].reshape(-1))
+                self.exp_avg_sq[off:off + n].copy_(st["exp_avg_sq"].reshape(-1))
+                step = int(st["step"]) if step is None else step
+            off += (n + 3) // 4 * 4
+        self.step_count = int(step or 0)
+        if self.hyper is not None:                   # device-resident step word of nwb_adam_*_step_dev ({int32 step, ...})
+            self.hyper[0:1].copy_(torch.tensor([self.step_count], dtype=torch.int32).view(torch.float32))
+
+    def snapshot(self) -> dict:
+        """Everything an optimizer step changes (for TrainStep's warm-up, which must not move the model)."""
+        snap = {"flat_p": self.flat_p.clone(), "exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(),
+                "step_count": self.step_count}
+        if self.hyper is not None:
+            snap["hyper"] = self.hyper.clone()
+        return snap
+
+    def restore(self, snap: dict) -> None:
+        self.flat_p.copy_(snap["flat_p"])
+        self.exp_avg.copy_(snap["exp_avg"])
+        self.exp_avg_sq.copy_(snap["exp_avg_sq"])
+        self.step_count = snap["step_count"]
+        if self.hyper is not None:
+            self.hyper.copy_(snap["hyper"])
+        self.flat_g.zero_()
+        for m in self.modules:                       # parameters moved back: operand caches must follow
+            if hasattr(m, "_nwb_cache"):
+                m._nwb_dirty = True
+
     def pull_lr(self) -> None:
         """Take the learning rate from the FlatAdam facade's param_groups when a torch scheduler moved it."""
         src = getattr(self, "_lr_source", None)
@@ -250,3 +298,17 @@ class FlatAdam(torch.optim.Optimizer):
 
     def zero_grad(self, set_to_none: bool = False):
         return None
+
+    def state_dict(self):
+        """torch.optim.Adam-compatible: the moments and step live in the flat buffers, not in ``self.state``."""
+        sd = super().state_dict()
+        sd["state"] = self.flat.optimizer_state()
+        return sd
+
+    def load_state_dict(self, state_dict):
+        groups = state_dict.get("param_groups")
+        if groups:
+            for g, src in zip(self.param_groups, groups):
+                g.update({k: v for k, v in src.items() if k != "params"})
+            self.flat.lr = float(self.param_groups[0]["lr"])
+        self.flat.load_optimizer_state(state_dict.get("state", {}))

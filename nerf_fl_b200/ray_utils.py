@@ -1,41 +1,19 @@
-"""Host-side mirror of the reference's datasets/ray_utils.py for the render path.
-
-``get_ray_directions`` / ``get_rays`` keep the reference's names, argument meaning and results (torch
-ops on whatever device the inputs live on -- they are what a dataset class calls once per image).
-``image_rays`` is the path the renderer uses: the same rays for a pixel range of one view, generated by
-one kernel on the device (csrc/raygen.cu), so an eval loop ships a 48-byte pose instead of 32 B/ray.
-"""
+"""Rays of a view for the render path: ``image_rays`` makes the (n, 8) rows
+[rays_o, rays_d, near, far] of a pixel range of one view with one kernel on the device (csrc/raygen.cu restates
+datasets/ray_utils.py:5-55 + blender.py:97-100), so an eval loop ships a 48-byte pose instead of 32 B/ray.
+Dataset classes that build rays on the host once per image keep the reference's own ``get_ray_directions`` /
+``get_rays`` (datasets/ray_utils.py); nothing on this path calls them.  There is no CPU path."""
 from __future__ import annotations
 
 import torch
 
 from . import kernels as K_
 
-__all__ = ["get_ray_directions", "get_rays", "image_rays"]
-
-
-def get_ray_directions(H: int, W: int, K) -> torch.Tensor:
-    """(H, W, 3) ray directions in camera coordinates (ray_utils.py:5-26): pixel (i, j) = (column, row), no +0.5."""
-    K = torch.as_tensor(K)
-    j, i = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
-    fx, fy, cx, cy = float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2])
-    return torch.stack([(i - cx) / fx, -(j - cy) / fy, -torch.ones_like(i)], -1)
-
-
-def get_rays(directions: torch.Tensor, c2w: torch.Tensor):
-    """(rays_o, rays_d), each (H*W, 3): directions rotated to world space and normalised, origin = camera centre
-    (ray_utils.py:29-55).  c2w: (3,4) or (B,3,4) with B == number of directions."""
-    if c2w.dim() < 3:
-        c2w = c2w.unsqueeze(0)
-    rays_d = directions.reshape(-1, 1, 1, 3) @ c2w[..., :3].transpose(1, 2).reshape(-1, 1, 3, 3)
-    rays_d = rays_d.reshape(-1, 3)
-    rays_d = rays_d / torch.norm(rays_d, dim=-1, keepdim=True)
-    rays_o = c2w[:, :, 3].expand(rays_d.shape)
-    return rays_o.reshape(-1, 3), rays_d.reshape(-1, 3)
+__all__ = ["image_rays"]
 
 
 def image_rays(H: int, W: int, K, c2w, near: float, far: float, first_pixel: int = 0, n_rays: int | None = None,
                device=None, out: torch.Tensor | None = None) -> torch.Tensor:
     """(n, 8) rows [rays_o, rays_d, near, far] (blender.py:97-100) of pixels [first_pixel, first_pixel + n) of the view
-    with pose c2w, generated on the GPU.  There is no CPU path."""
+    with pose c2w, generated on the GPU."""
     return K_.gen_rays(H, W, K, c2w, near, far, first_pixel, n_rays, device, out)

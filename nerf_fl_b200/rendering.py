@@ -213,7 +213,7 @@ class _RenderFn(torch.autograd.Function):
         Pf = None
         if Ni > 0:
             z_f = K.sample_pdf_merge(z, res["weights_coarse"], Ni, det=(perturb == 0),              # :267-272
-                                     u=rng.get("u") if perturb > 0 else None, seed=seed ^ 0x5DEECE66D)
+                                     u=rng.get("u") if perturb > 0 else None, seed=seed)
             transient = transient_f
             noise_f = None if transient else sigma_noise((n, Ns + Ni), "noise_fine")
             Pf, res_f = _run_pass(fine, rays, z_f, typ="fine", noise=noise_f, transient=transient, ts=ts,

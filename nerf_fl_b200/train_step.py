@@ -76,13 +76,20 @@ class TrainStep:
         # ~60).  A collective inside a capture ties the graph to the communicator's internal streams and to the
         # process group's watchdog thread, and a hang there takes the whole job down.
         self._split = dist_info()[1] > 1
+        # warm-up iterations (allocator pools, lazy module state) run on a side stream as torch's capture recipe asks;
+        # they must not train: one call = one optimizer update (train.py:158-174), so the model, the Adam moments and
+        # the device-resident step counter are put back afterwards.  do_step=False also keeps a warm-up from issuing
+        # collectives other ranks do not match.
+        snap = self.state.snapshot() if self._warmup > 0 else None
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(side):
             for _ in range(self._warmup):
-                self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True)
+                self._iteration(self.s_rays, self.s_ts, self.s_rgbs, True, do_step=False)
         torch.cuda.current_stream(self.dev).wait_stream(side)
         torch.cuda.synchronize(self.dev)
+        if snap is not None:
+            self.state.restore(snap)
         if self.state.refreshes_caches:
             self.state.prepare()                       # pointer tables + rest list (synchronises): not inside a capture
         else:

@@ -36,16 +36,17 @@ def test_tile_image_roundtrip_and_swizzle():
 
 def test_flat_adam_facade_follows_torch_schedulers():
     """utils/__init__.py:44-61: the reference builds MultiStepLR / CosineAnnealingLR / LambdaLR over its optimizer;
-    FlatAdam lets the same schedulers drive the flat-buffer Adam.  CPU tensors take FlatTrainState's torch-op update."""
+    FlatAdam lets the same schedulers drive the flat-buffer Adam.  CPU tensors: the update is the torch-op Adam the tests inject (tests/host_models.py)."""
     import torch
     from torch.optim.lr_scheduler import CosineAnnealingLR, LambdaLR, MultiStepLR
     from nerf_fl_b200.parallel import FlatAdam, FlatTrainState
+    from tests.host_models import adam_update_torch
 
     def run(make_sched):
         torch.manual_seed(0)
         lin_a, lin_b = torch.nn.Linear(5, 7), torch.nn.Linear(5, 7)
         lin_b.load_state_dict(lin_a.state_dict())
-        st = FlatTrainState([lin_a], lr=5e-4)
+        st = FlatTrainState([lin_a], lr=5e-4, host_update=adam_update_torch)
         opt_a, opt_b = FlatAdam(st), torch.optim.Adam(lin_b.parameters(), lr=5e-4, eps=1e-8)
         sch_a, sch_b = make_sched(opt_a), make_sched(opt_b)
         g = torch.Generator().manual_seed(1)

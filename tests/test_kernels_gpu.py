@@ -43,6 +43,27 @@ def test_sample_coarse_philox_in_range():
     assert abs(jit.mean().item()) < 0.01 and abs(jit.std().item() - (1 / 12) ** 0.5) < 0.01
 
 
+def test_philox_streams_of_the_two_draw_sites_are_independent():
+    """the coarse stratified jitter (rendering.py:257) and the inverse-CDF uniforms (rendering.py:30) are
+    drawn from the same seed; they must come from disjoint Philox counter blocks (draw ids 0 / 1), not be the same
+    numbers.  Both are recovered from the kernels' outputs: z = lower + (upper-lower) u for the jitter, and with
+    uniform weights the inverse CDF is linear in u."""
+    n, Ns = 512, 64
+    rays = syn.blender_rays(n, seed=7).to(DEV)
+    z0 = K.sample_coarse(rays, Ns, False, 0.0)
+    z1 = K.sample_coarse(rays, Ns, False, 1.0, None, seed=99)
+    step = (z0[:, 1] - z0[:, 0])[:, None]
+    u_c = ((z1 - (z0 - step / 2)) / step)[:, 1:-1]
+    w = torch.ones(n, Ns, device=DEV)
+    _, z_new, _ = K.sample_pdf_merge(z0, w, Ns, det=False, seed=99, debug=True)
+    lo, hi = (z0[:, 0] + z0[:, 1]) / 2, (z0[:, -2] + z0[:, -1]) / 2
+    u_f = ((z_new - lo[:, None]) / (hi - lo)[:, None])[:, 1:-1]
+    assert u_c.min() >= -1e-4 and u_c.max() <= 1 + 1e-4 and u_f.min() >= -1e-4 and u_f.max() <= 1 + 1e-4
+    assert (u_c - u_f).abs().mean().item() > 0.25                      # independent uniforms: E|a - b| = 1/3
+    corr = torch.corrcoef(torch.stack([u_c.flatten(), u_f.flatten()]))[0, 1].item()
+    assert abs(corr) < 0.03, corr
+
+
 # ---- (a2) PosEmbedding -------------------------------------------------------------------------
 @pytest.mark.parametrize("L", [4, 10, 15])
 def test_posenc_golden(golden, L):
@@ -225,6 +246,19 @@ def test_umma_a_kmajor_b_mnmajor(N, Kd):
     d = K.selftest_umma(layout.tile_image(A).to(DEV), layout.tile_image(Wt).to(DEV), N, Kd, 2)
     want = A.float() @ Wt.float()
     assert maxerr(d, want) <= 1e-3 * Kd ** 0.5, maxerr(d, want)
+
+
+@pytest.mark.parametrize("N,Kd", [(256, 128), (128, 128), (256, 32), (128, 64)])
+def test_umma_f8_mn_major(N, Kd):
+    """The 8-bit weight-gradient shape: D = A^T . B with A (K x 128) e5m2 and B (K x N) e4m3, both read MN-major from
+    8-bit tile images (tcgen05.mma kind::f8f6f4, K = 32 per instruction, fp32 accumulate: products are exact)."""
+    gen = torch.Generator().manual_seed(N * 7 + Kd)
+    X = torch.randn(Kd, 128, generator=gen).to(torch.float8_e5m2)
+    Y = torch.randn(Kd, N, generator=gen).to(torch.float8_e4m3fn)
+    d = K.selftest_umma(layout.tile_image8(X.float(), torch.float8_e5m2).to(DEV),
+                        layout.tile_image8(Y.float(), torch.float8_e4m3fn).to(DEV), N, Kd, 3)
+    want = X.float().T @ Y.float()
+    assert maxerr(d, want) <= 1e-4 * Kd ** 0.5, maxerr(d, want)
 
 
 # ---- fused field forward (a3, a4) --------------------------------------------------------------

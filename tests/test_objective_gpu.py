@@ -16,7 +16,8 @@ def _inputs(n, S, seed, dev):
 @pytest.mark.parametrize("n,S", [(1, 1), (7, 5), (1024, 128), (4099, 33)])
 @pytest.mark.parametrize("variant", ["nerfw", "no_transient", "coarse_only"])
 def test_nerfw_loss_matches_torch_ops(n, S, variant):
-    from nerf_fl_b200.objective import NerfWLoss, nerfw_terms
+    from nerf_fl_b200.objective import NerfWLoss
+    from tests.host_models import nerfw_terms
     dev = torch.device("cuda")
     res, tgt = _inputs(n, S, 11 * n + S, dev)
     if variant != "nerfw":
@@ -64,3 +65,19 @@ def test_nerfw_loss_is_deterministic_and_reusable():
     first = f(res, tgt).total.item()
     for _ in range(5):
         assert f(res, tgt).total.item() == first
+
+
+@pytest.mark.parametrize("with_fine", [True, False])
+def test_color_loss_matches_torch_ops(with_fine):
+    """losses.py:4-16 through the same kernel pair (no beta: total = coef' * 0.5 * (mse_c + mse_f), coef' = 2 coef)."""
+    from nerf_fl_b200.objective import ColorLoss
+    from tests.host_models import color_loss
+    res, tgt = _inputs(777, 4, 9, torch.device("cuda"))
+    res = {k: v for k, v in res.items() if k == "rgb_coarse" or (with_fine and k == "rgb_fine")}
+    a = {k: v.clone().requires_grad_(True) for k, v in res.items()}
+    b = {k: v.clone().requires_grad_(True) for k, v in res.items()}
+    got, want = ColorLoss(coef=0.7)(a, tgt), color_loss(b, tgt, 0.7)
+    torch.testing.assert_close(got, want, rtol=2e-5, atol=1e-7)
+    got.backward(); want.backward()
+    for k in a:
+        torch.testing.assert_close(a[k].grad, b[k].grad, rtol=2e-5, atol=1e-9)

@@ -80,8 +80,10 @@ def test_render_rays_golden(golden, case, scale):
     if scale == 1:
         # north-star tolerance: 1e-3 absolute on the composited maps and weights against the fp32
         # reference (bf16 MLP operands, fp32 accumulate), on default-init weights
+        # (depth included, in scene units: near 2 / far 6; transient_sigmas is a raw Softplus head output, unbounded
+        # above, held relative to its size)
         for k, w in want.items():
-            lim = 1e-3 * max(1.0, w.abs().max().item()) if k.startswith(("depth", "transient_sigmas")) else 1e-3
+            lim = 1e-3 * max(1.0, w.abs().max().item()) if k == "transient_sigmas" else 1e-3
             assert maxerr(out[k], w) <= lim, (k, maxerr(out[k], w))
         return
     # x3 weights: every layer triples the sensitivity, so rounding the GEMM operands to bf16 ONCE moves the
@@ -219,8 +221,7 @@ def test_render_rays_kwargs_a_embedded_and_view_dir():
                              a_embedded=ea[3:4].expand(n, -1), output_transient=False, view_dir=vd)
     assert set(got) == set(want)
     for k in want:
-        lim = 1e-3 * (max(1.0, want[k].abs().max().item()) if k.startswith("depth") else 1.0)
-        assert maxerr(got[k], want[k]) <= lim, (k, maxerr(got[k], want[k]))
+        assert maxerr(got[k], want[k]) <= 1e-3, (k, maxerr(got[k], want[k]))
 
 
 def test_ts_out_of_range_is_reported():

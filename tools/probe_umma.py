@@ -3,14 +3,16 @@ import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from nerf_fl_b200 import _lib as L
-fn = L.lib().nwb_debug_umma_probe
+from tools.build_probes import build
+_P = C.CDLL(build())          # tools/libnwb_probes.so (not part of the product library)
+fn = _P.nwb_debug_umma_probe
 fn.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]; fn.restype = C.c_int
 out = torch.zeros(2, dtype=torch.int64, device="cuda")
 for N in (64, 128, 256):
     for commit_every in (0, 1):
         for rounds in (4, 64):
             for rep in range(2):
-                L.check(fn(N, rounds, commit_every, out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+                assert 0 == (fn(N, rounds, commit_every, out.data_ptr(), torch.cuda.current_stream().cuda_stream))
                 torch.cuda.synchronize()
             issue, total = out.tolist()
             n = rounds * 4

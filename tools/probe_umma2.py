@@ -5,7 +5,9 @@ import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from nerf_fl_b200 import _lib as L
-fn = L.lib().nwb_debug_umma_probe2
+from tools.build_probes import build
+_P = C.CDLL(build())          # tools/libnwb_probes.so (not part of the product library)
+fn = _P.nwb_debug_umma_probe2
 fn.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]; fn.restype = C.c_int
 src = torch.zeros(40 * 32768, dtype=torch.uint8, device="cuda")
 rounds = 256
@@ -14,7 +16,7 @@ for grid in (1, 148):
     for mode in (0, 1, 3, 1 | 16, 3 | 16, 8, 8 | 16, 4, 4 | 64, 4 | 32, 4 | 1, 4 | 3 | 8, 4 | 3 | 8 | 16, 4 | 3 | 8 | 16 | 32):
         for rep in range(2):
             out.zero_()
-            L.check(fn(grid, rounds, mode, src.data_ptr(), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+            assert 0 == (fn(grid, rounds, mode, src.data_ptr(), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
             torch.cuda.synchronize()
         cyc = out[:grid].float().mean().item()
         byt = out[grid:].float().mean().item()
