@@ -4,11 +4,15 @@
 // layers in reverse.  For every layer g it forms dZ_g = dA_g (.) relu'(z_g) -- dA_g comes out of
 // TMEM (the previous step's tcgen05 product dZ_{g+1} . W_{g+1}) and/or from the head cotangents on
 // CUDA cores, the ReLU gate from the sign masks the forward saved -- writes it as a bf16 tile image
-// into shared memory (the A operand of the next product, in place), streams the same image to the
-// workspace for the wgrad kernel (field_wgrad.cu), and lets the MMA warp issue
+// into shared memory (the A operand of the next product, in place), writes the same values as an e5m2
+// image straight from registers to the workspace for the wgrad kernel (field_wgrad.cu; 32-byte stores,
+// one full sector per 32 columns of a row), and lets the MMA warp issue
 // dA_{g-1} = dZ_g . W_g with W_g read MN-major from the very slab images the forward uses.
 // Also produced here: the head-bias gradients, the per-ray cotangent d_ray_bias (sum of dZ_9 over
 // the samples of a ray) and the head pre-activation cotangents (dpre block) for the wgrad kernel.
+// The whole chain runs on cotangents multiplied by ONE power of two per pass (DzHeader, field.cuh: amax|d_raw| ->
+// 2^kDzTop, found by dz_amax_kernel in front of this kernel) so that the 8-bit images use e5m2's range; bf16 and fp32
+// have the exponent range to spare, and everything that leaves in fp32 is multiplied by the inverse.
 #include "field_dev.cuh"
 #include <algorithm>
 
@@ -19,8 +23,6 @@ constexpr int kBStageBytes = 8192;                 // this CTA's half of a stage
 constexpr int kBChunkBytes = 4096;                 // one k-block's 32 rows
 constexpr int kBNumStages = 6;                  // the kernel is bound by the latency of the weight stream: depth matters
 constexpr int kBOffD = 0;                       // 64 KB  dZ image (A operand)
-constexpr int kBOffP = kBOffD;                  // 16 KB  dpre block image: aliases the dZ image (stored and read out
-                                                //        before layer nl-1 writes its dZ; same bulk_wait_read guard)
 constexpr int kBOffW = kBOffD + 65536;
 constexpr int kBOffBar = kBOffW + kBNumStages * kBStageBytes;
 constexpr int kBwdSmem = kBOffBar + 256;
@@ -32,7 +34,8 @@ struct BwdArgs {
     const float* d_raw;
     const uint8_t* saved;
     size_t save_tile_bytes;
-    uint8_t* dz;
+    const DzHeader* hdr;
+    uint8_t* dz;              // first tile record (behind the header)
     size_t dz_tile_bytes;
     float* d_ray_bias;
     float* g_head_b[5];       // sigma_b, rgb_b, tsigma_b, trgb_b, tbeta_b gradient sinks
@@ -55,9 +58,10 @@ struct BwdArgs {
 //   Head weights arrive lane-distributed (lane l holds hw[h][c_out + l], one coalesced load per warp issued ahead of
 //   the accumulator wait) and are broadcast with shuffles: every thread of the warp needs the same 32 values, and a
 //   warp-uniform global load per value costs an L2 round trip each (shared memory is full, L1 is carved away).
+//   g8: this row's 128-byte line of the layer's e5m2 image block that holds column c_out (nullptr: ghost tile)
 template <bool kAcc, int kHeads, bool kMask>
 __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, const float* dp, uint32_t negmask,
-                                          uint8_t* sD, int row, int c_out) {
+                                          uint8_t* sD, int row, int c_out, uint8_t* g8) {
     float x[32];
     if (kAcc) {
         uint32_t v[32];
@@ -83,12 +87,23 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, cons
             if ((negmask >> ((j < 16 ? 16 : 0) + relu_mask_bit(j & 15))) & 1u) x[j] = 0.0f;
     }
     store_slice_bf16(sD, row, c_out, x);
+    if (g8 != nullptr) {
+        // 32 columns = chunks 2m, 2m+1 of the row's line: they sit side by side in one 32-byte sector (the swizzle
+        // XORs both chunk indices with row%8, which swaps them when row is odd)
+        uint4 lo, hi;
+        lo.x = ptx::pack4_e5m2(x[0], x[1], x[2], x[3]);     lo.y = ptx::pack4_e5m2(x[4], x[5], x[6], x[7]);
+        lo.z = ptx::pack4_e5m2(x[8], x[9], x[10], x[11]);   lo.w = ptx::pack4_e5m2(x[12], x[13], x[14], x[15]);
+        hi.x = ptx::pack4_e5m2(x[16], x[17], x[18], x[19]); hi.y = ptx::pack4_e5m2(x[20], x[21], x[22], x[23]);
+        hi.z = ptx::pack4_e5m2(x[24], x[25], x[26], x[27]); hi.w = ptx::pack4_e5m2(x[28], x[29], x[30], x[31]);
+        const int pair = ((c_out & 127) >> 5) ^ ((row & 7) >> 1);
+        uint8_t* dst = g8 + (pair << 5);
+        if (row & 1) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
+    }
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 2)
 field_dgrad_kernel(const BwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sP = smem + kBOffP;
     uint8_t* sD = smem + kBOffD;
     uint8_t* sW = smem + kBOffW;
     uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + kBOffBar);
@@ -218,6 +233,9 @@ field_dgrad_kernel(const BwdArgs a) {
         const SaveLayout sl{fs.kx, transient};
         const DzLayout dl{transient};
         const int C = transient ? 9 : 4;
+        const float scale = dz_scale_from_amax_bits(__ldg(&a.hdr->amax_bits));
+        const float inv_scale = 1.0f / scale;               // both exact powers of two
+        const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an image block
         uint32_t acc_ev = 0;
         const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
         for (int pair = pair0; pair < n_pairs; pair += pair_step) {
@@ -250,22 +268,16 @@ field_dgrad_kernel(const BwdArgs a) {
             for (int i = 0; i < 9; ++i) {
                 const float s = warp_sum(dp[i]);
                 if (lane == 0 && s != 0.0f) atomicAdd(&s_hb[i], s);
+                dp[i] *= scale;                             // from here on the chain carries scaled cotangents
             }
-            if (leader) ptx::bulk_wait_read<0>();           // previous tile's bulk stores have read sP / sD
-            epi_bar();
-            {
-                uint4 c0, c1, zz = make_uint4(0, 0, 0, 0);
-                c0.x = pack_bf16(dp[0], dp[1]); c0.y = pack_bf16(dp[2], dp[3]);
-                c0.z = pack_bf16(dp[4], dp[5]); c0.w = pack_bf16(dp[6], dp[7]);
-                c1 = zz; c1.x = pack_bf16(dp[8], 0.0f);
-                *reinterpret_cast<uint4*>(sP + ptx::image_chunk_off(row, 0)) = c0;
-                *reinterpret_cast<uint4*>(sP + ptx::image_chunk_off(row, 1)) = c1;
-#pragma unroll
-                for (int q = 2; q < 8; ++q) *reinterpret_cast<uint4*>(sP + ptx::image_chunk_off(row, q)) = zz;
+            if (!ghost) {
+                // dpre block (e5m2): the wgrad kernel's head units read 16 columns = chunk 0 of every row; the other
+                // seven chunks of the block are never read and stay unwritten
+                uint4 c0;
+                c0.x = ptx::pack4_e5m2(dp[0], dp[1], dp[2], dp[3]); c0.y = ptx::pack4_e5m2(dp[4], dp[5], dp[6], dp[7]);
+                c0.z = ptx::pack4_e5m2(dp[8], 0.0f, 0.0f, 0.0f); c0.w = 0u;
+                *reinterpret_cast<uint4*>(dz_tile + dl.dpre_off() + ptx::image_chunk_off(row, 0)) = c0;
             }
-            ptx::fence_proxy_async_smem();
-            epi_bar();
-            if (leader && !ghost) { ptx::bulk_s2g(dz_tile + dl.dpre_off(), sP, 16384); ptx::bulk_commit(); }
 
             for (int g = nl - 1; g >= 0; --g) {
                 // ReLU gates of layer g (prefetched before waiting for the accumulator)
@@ -313,57 +325,52 @@ field_dgrad_kernel(const BwdArgs a) {
                     }
                 }
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 2);    // accumulator seen
-                if (leader) ptx::bulk_wait_read<0>();       // the previous image's bulk store has read sD
-                epi_bar();
+                epi_bar();                                  // everyone is done reading sD (the d_ray_bias sums of layer 9)
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 3);    // sD free
-                uint32_t dz_bytes = 65536;
+                // this row's line in block 0 / block 1 of the layer's e5m2 image
+                uint8_t* g8a = ghost ? nullptr : dz_tile + dl.dz_off(g) + line_off;
+                uint8_t* g8b = ghost ? nullptr : g8a + 16384;
                 if (g >= 10) {
-                    dz_bytes = 32768;
                     if (g == 12) {
 #pragma unroll
                         for (int sl4 = 0; sl4 < 4; ++sl4)
-                            bwd_slice<false, 5, true>(0, hwl + 5 * sl4, dp + 4, mw[sl4], sD, row, 32 * sl4);
+                            bwd_slice<false, 5, true>(0, hwl + 5 * sl4, dp + 4, mw[sl4], sD, row, 32 * sl4, g8a);
                     } else {
 #pragma unroll 1
                         for (int c0 = 0; c0 < 128; c0 += 32)
-                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
+                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0, g8a);
                     }
                 } else if (g == 9) {
 #pragma unroll
                     for (int sl4 = 0; sl4 < 4; ++sl4)
-                        bwd_slice<false, 3, true>(0, hwl + 3 * sl4, dp + 1, mw[sl4], sD, row, 32 * sl4);
+                        bwd_slice<false, 3, true>(0, hwl + 3 * sl4, dp + 1, mw[sl4], sD, row, 32 * sl4, g8a);
                     if (transient) {
 #pragma unroll 1
                         for (int c0 = 128; c0 < 256; c0 += 32)
-                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
-                    } else {
-                        dz_bytes = 32768;
+                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0, g8b);
                     }
                 } else if (g == 8) {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 0, false>(tlane + c0, nullptr, nullptr, 0u, sD, row, c0);
+                        bwd_slice<true, 0, false>(tlane + c0, nullptr, nullptr, 0u, sD, row, c0, c0 < 128 ? g8a : g8b);
                 } else if (g == 7) {
 #pragma unroll
                     for (int sl8 = 0; sl8 < 8; ++sl8)
-                        bwd_slice<true, 1, true>(tlane + 32 * sl8, hwl + sl8, dp, mw[sl8], sD, row, 32 * sl8);
+                        bwd_slice<true, 1, true>(tlane + 32 * sl8, hwl + sl8, dp, mw[sl8], sD, row, 32 * sl8, sl8 < 4 ? g8a : g8b);
                 } else {
 #pragma unroll 1
                     for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0);
+                        bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0, c0 < 128 ? g8a : g8b);
                 }
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 4);    // leader's slices written
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before_sync();                // this thread's tcgen05.ld of the accumulator are done
                 epi_bar();
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 5);    // all slices written
-                if (leader) {
-                    if (!ghost) { ptx::bulk_s2g(dz_tile + dl.dz_off(g), sD, dz_bytes); ptx::bulk_commit(); }
-                    if (g >= 1) { if (rank == 0) ptx::mbar_arrive(bar_act); else ptx::mbar_arrive_cluster(act_leader); }
-                }
+                if (leader && g >= 1) { if (rank == 0) ptx::mbar_arrive(bar_act); else ptx::mbar_arrive_cluster(act_leader); }
                 if (g == 9) {
                     // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples.  Runs
-                    // AFTER the handoff, next to layer 9's MMAs and the bulk store (all three only read the image);
+                    // AFTER the handoff, next to layer 9's MMAs (both only read the image);
                     // the next layer's epilogue rewrites it only behind its barrier.
                     const int ncols = transient ? 256 : 128;
                     const int c = 2 * et;
@@ -390,8 +397,8 @@ field_dgrad_kernel(const BwdArgs a) {
                                 const uint32_t w = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r, chunk));
                                 s0 += __uint_as_float(w << 16); s1 += __uint_as_float(w & 0xFFFF0000u);
                             }
-                            atomicAdd(a.d_ray_bias + ray * 256 + c, s0 + u0);
-                            atomicAdd(a.d_ray_bias + ray * 256 + c + 1, s1 + u1);
+                            atomicAdd(a.d_ray_bias + ray * 256 + c, (s0 + u0) * inv_scale);
+                            atomicAdd(a.d_ray_bias + ray * 256 + c + 1, (s1 + u1) * inv_scale);
                             ++ray;
                             seg_end = min(nrow, seg_end + a.S);
                         }
@@ -399,7 +406,6 @@ field_dgrad_kernel(const BwdArgs a) {
                 }
             }
         }
-        if (leader) ptx::bulk_wait_all<0>();
     }
     ptx::tc_fence_before_sync();
     __syncthreads();
@@ -410,6 +416,31 @@ field_dgrad_kernel(const BwdArgs a) {
         float* dst = (i == 0) ? a.g_head_b[0] : (i < 4) ? a.g_head_b[1] + (i - 1) : (i == 4) ? a.g_head_b[2]
                    : (i < 8) ? a.g_head_b[3] + (i - 5) : a.g_head_b[4];
         if (dst != nullptr && (i < 4 || transient)) atomicAdd(dst, s_hb[i]);
+    }
+}
+
+// max |d_raw| of the pass -> DzHeader.amax_bits (zeroed by a memset node in front): non-negative floats order like
+// their bit patterns, so one atomicMax per block does it; NaNs are skipped (they would poison the scale)
+__global__ void __launch_bounds__(256)
+dz_amax_kernel(const float* __restrict__ d_raw, long long n, DzHeader* __restrict__ hdr) {
+    float m = 0.0f;
+    const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
+    const long long n4 = ((reinterpret_cast<uintptr_t>(d_raw) & 15u) == 0) ? (n >> 2) : 0;
+    const float4* p4 = reinterpret_cast<const float4*>(d_raw);
+    for (long long i = tid; i < n4; i += nth) {
+        const float4 v = __ldg(p4 + i);
+        m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));    // fmaxf drops NaN operands
+    }
+    for (long long i = (n4 << 2) + tid; i < n; i += nth) m = fmaxf(m, fabsf(__ldg(d_raw + i)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    __shared__ float red[8];
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) m = fmaxf(m, red[w]);
+        if (m > 0.0f && m < INFINITY) atomicMax(&hdr->amax_bits, __float_as_uint(m));
     }
 }
 
@@ -424,14 +455,14 @@ extern "C" void nwb_debug_set_bwd_trace(void* buf) { g_bwd_trace = static_cast<l
 #endif
 
 int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* grads, const uint8_t* saved, size_t save_tile_bytes,
-                     const uint8_t* dz, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st);
+                     const uint8_t* workspace, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st);
 
 extern "C" size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n_points, uint32_t mode) {
     FieldShape fs;
     if (make_shape(d, &fs) != NWB_OK || n_points <= 0) return 0;
     const DzLayout dl{(mode & NWB_MLP_TRANSIENT) != 0};
     const int64_t n_tiles = (n_points + kTileM - 1) / kTileM;
-    return static_cast<size_t>(n_tiles) * dl.tile_bytes();
+    return kDzHeaderBytes + static_cast<size_t>(n_tiles) * dl.tile_bytes();
 }
 
 static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,
@@ -467,7 +498,8 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
     const SaveLayout sl{fs.kx, transient};
     const DzLayout dl{transient};
     a.save_tile_bytes = sl.tile_bytes(fs.n_layers(mode));
-    a.dz = static_cast<uint8_t*>(workspace);
+    a.hdr = static_cast<const DzHeader*>(workspace);
+    a.dz = static_cast<uint8_t*>(workspace) + kDzHeaderBytes;
     a.dz_tile_bytes = dl.tile_bytes();
     a.d_ray_bias = d_ray_bias;
     a.g_head_b[0] = grads->sigma_b; a.g_head_b[1] = grads->rgb_b; a.g_head_b[2] = grads->tsigma_b;
@@ -478,6 +510,12 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
 #endif
 
     if (run_dgrad) {
+        // the pass's scale: amax |d_raw| into the workspace header (a memset node and one small reduction)
+        NWB_CUDA(cudaMemsetAsync(workspace, 0, kDzHeaderBytes, st));
+        const long long n_raw = a.n_points * (transient ? 9 : 4);
+        const int ablocks = static_cast<int>(std::min<long long>((n_raw / 4 + 255) / 256 + 1, kNumSMs * 2));
+        dz_amax_kernel<<<ablocks, 256, 0, st>>>(d_raw, n_raw, static_cast<DzHeader*>(workspace));
+        NWB_LAUNCH_CHECK();
         static bool configured[kMaxDevices] = {};
         NWB_CONFIGURE_ONCE(configured, {
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
@@ -488,7 +526,8 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
         NWB_LAUNCH_CHECK();
     }
     if (run_wgrad)
-        return nwb_wgrad_launch(fs, grads, a.saved, a.save_tile_bytes, a.dz, a.dz_tile_bytes, a.n_tiles, mode, st);
+        return nwb_wgrad_launch(fs, grads, a.saved, a.save_tile_bytes, static_cast<const uint8_t*>(workspace), a.dz_tile_bytes,
+                                a.n_tiles, mode, st);
     return NWB_OK;
 }
 

@@ -14,24 +14,32 @@
 //                     5-stage ring with linear bulk copies (TMA engine, SASS UBLKCP) + mbarrier tx counts
 //   warp 1 / lane 0   MMA issuer: tcgen05.mma M=128 N=128 K=16, A = activation tile image in smem,
 //                     B = ring stage, D = fp32 accumulators in TMEM
-//   warp 2 / lane 0   (NWB_MLP_SAVE) activation storer: bulk-stores every finished quarter to the saved-
-//                     activation record and hands the buffer back when the copy engine has read it
-//   warps 3..10       epilogue, two threads per point (column halves of each quarter): build the encoded-
+//   warps 2..17       epilogue, four threads per point (column halves of each quarter): build the encoded-
 //                     xyz operand tile (o + d*z, sin/cos octaves, bf16, written straight into the swizzled
 //                     A image), then per layer tcgen05.ld -> +bias (+per-ray bias) -> ReLU -> bf16 -> next
 //                     layer's A image; sigma / rgb / transient heads on CUDA cores in fp32.
-// Activations never leave the SM unless NWB_MLP_SAVE asks for them (bf16 tile images for backward).
+// Activations never leave the SM unless NWB_MLP_SAVE asks for them: then every epilogue thread also writes its 16
+// columns of each quarter as e4m3 (one 16-byte store, straight from registers, behind the quarter's handoff) into the
+// layer's 8-bit image for the weight-gradient kernel, plus the ReLU sign masks for the dgrad chain.
 #include "field_dev.cuh"
 #include <algorithm>
 
 namespace nwb {
 
 constexpr int kMmaWarps = 1;                  // MMA-issuing warps, each owns 1/kMmaWarps of a layer's output columns
-constexpr int kStoreWarp = 1 + kMmaWarps;
-constexpr int kEpiWarp0 = 2 + kMmaWarps;      // first epilogue warp
+constexpr int kEpiWarp0 = 4;                  // first epilogue warp: warps 0..3 are one warpgroup (producer, MMA issuer, two spare
+                                              // warps) so that setmaxnreg can move its registers to the epilogue warpgroups
 constexpr int kEpiWarps = 16;
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kFwdThreads = (kEpiWarp0 + kEpiWarps) * 32;
+static_assert(1 + kMmaWarps <= kEpiWarp0, "producer + MMA issuers live in warpgroup 0");
+// Registers: setmaxnreg moves registers inside the CTA's own launch allocation (640 threads x 96 = 61 440; 104 at
+// launch would not fit the 65 536 of an SM).  Warpgroup 0 drops to 64 and the four epilogue warpgroups rise to 104:
+// 128 x 64 + 512 x 104 = 61 440.  ptxas: 28 bytes of spills in the saving pair kernel, none in the other three.
+constexpr int kFwdMaxRegs = 96;
+constexpr int kFwdRegsWg0 = 64;
+constexpr int kFwdRegsEpi = 104;
+static_assert(kFwdThreads * kFwdMaxRegs >= 128 * kFwdRegsWg0 + kEpiThreads * kFwdRegsEpi, "setmaxnreg pool is the launch allocation");
 constexpr int kStageBytes = 32768;            // 256 weight rows x 64 k (one SW128 K-block of a whole layer)
 constexpr int kNumStages = 3;
 constexpr int kHSlots = 6;                    // activation K-block slots (128 rows x 64 columns, 16 KB each)
@@ -72,11 +80,12 @@ __device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, %0;" :
 //   x = acc + bias[c] (+ rbias[c]);  optional head dot products (fp32, unrounded x, after ReLU);
 //   bf16 pack, ReLU on the packed pairs (rounding is monotonic and keeps the sign, so max(rn(x), 0) ==
 //   rn(max(x, 0))) -> chunks chunk0, chunk0+1 (16 B each) of this row in the K-block image blk.
-//   kSave: the sign bits of the 16 pre-activations are returned in neg_out, bit (15-j) = column j.
+//   kSave: the sign bits of the 16 pre-activations are returned in neg_out, bit (15-j) = column j, and the 16
+//   activations as e4m3 (ReLU applied by the conversion) in p8 -- one 16-byte chunk of the saved 8-bit image.
 template <bool kRelu, int kHeads, bool kSave>
 __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restrict__ bias,
                                             const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
-                                            float* hacc, uint8_t* blk, int row, int chunk0, uint32_t& neg_out) {
+                                            float* hacc, uint8_t* blk, int row, int chunk0, uint32_t& neg_out, uint4& p8) {
     uint32_t v[16];
     ptx::tmem_ld16(taddr, v);
     float b[16];
@@ -101,6 +110,10 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
     uint32_t pk[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(x[2 * j], x[2 * j + 1]);
+    if (kSave) {
+        p8.x = ptx::pack4_e4m3<kRelu>(x[0], x[1], x[2], x[3]);    p8.y = ptx::pack4_e4m3<kRelu>(x[4], x[5], x[6], x[7]);
+        p8.z = ptx::pack4_e4m3<kRelu>(x[8], x[9], x[10], x[11]);  p8.w = ptx::pack4_e4m3<kRelu>(x[12], x[13], x[14], x[15]);
+    }
     if (kRelu && kSave) {
         // packed word j: bit 15 = sign of column 2j, bit 31 = sign of column 2j+1.  One shift + one LOP3 per word
         // drops them at bits 15-j and 31-j; the 16-bit entry is then [even columns, MSB first | odd columns, MSB first]
@@ -160,7 +173,7 @@ __device__ __forceinline__ int layer_quarters(int g, bool transient) {
 __device__ __forceinline__ int first_quarter(int g) { return g <= 10 ? 4 * g : 42 + 2 * (g - 11); }   // transient chain: 40, 42, 44
 __device__ __forceinline__ int out_slot(int g, int q) { return (first_quarter(g) + q) % kHSlots; }
 template <bool kSave>
-__global__ void __launch_bounds__(kFwdThreads, 1)
+__global__ void __maxnreg__(kFwdMaxRegs)
 field_fwd_kernel(const FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sX = smem + kOffX;
@@ -172,9 +185,7 @@ field_fwd_kernel(const FwdArgs a) {
     uint64_t* bar_empty = bar_full + kNumStages;                        // [kNumStages] MMA -> producer
     uint64_t* bar_acc = bar_empty + kNumStages;                         // [1] MMA -> epilogue (layer accumulator complete)
     uint64_t* bar_act = bar_acc + 1;                                    // [7] epilogue -> MMA, per slot (+X)
-    uint64_t* bar_st = bar_act + 7;                                     // [7] epilogue -> storer, per slot (+X)
-    uint64_t* bar_done = bar_st + 7;                                    // [7] storer -> epilogue: slot read out, reusable
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 7);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_act + 7);
     uint32_t* s_woff = tmem_slot + 2;                                   // [kMaxG] slab offsets
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -191,11 +202,7 @@ field_fwd_kernel(const FwdArgs a) {
         }
         for (int s = 0; s < kNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], kMmaWarps); }
         ptx::mbar_init(bar_acc, kMmaWarps);
-        for (int q = 0; q < 7; ++q) {
-            ptx::mbar_init(&bar_act[q], kEpiWarps);                     // one arrival per epilogue warp
-            ptx::mbar_init(&bar_st[q], kEpiWarps);
-            ptx::mbar_init(&bar_done[q], 1);
-        }
+        for (int q = 0; q < 7; ++q) ptx::mbar_init(&bar_act[q], kEpiWarps);   // one arrival per epilogue warp
         ptx::fence_mbar_init();
         for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
     }
@@ -210,6 +217,8 @@ field_fwd_kernel(const FwdArgs a) {
     ptx::tc_fence_after_sync();
     const uint32_t tmem = *tmem_slot;
 
+    if (warp < kEpiWarp0) {
+    ptx::setmaxnreg_dec<kFwdRegsWg0>();
     if (warp == 0) {
         // ============================ weight producer ============================================
         // one stage = one 64-wide K-block of a whole layer: N x 64 bf16 = 32 KB (N = 256) or 16 KB (N = 128),
@@ -306,41 +315,10 @@ field_fwd_kernel(const FwdArgs a) {
                 }
             }
         }
-    } else if (warp == kStoreWarp) {
-        // ============================ activation storer (NWB_MLP_SAVE) ===========================
-        // Quarters are stored in the order they are produced.  After issuing store n, every group but the two
-        // newest has been read out of shared memory, so the slot of store n-2 goes back to the epilogue.
-        if (lane == 0 && save) {
-            const SaveLayout sl{fs.kx, transient};
-            uint32_t st_par = 0;                             // bit i = parity of the next phase of bar_st[i]
-            int prev1 = -1, prev2 = -1;                      // slots of the two newest stores
-            auto store = [&](int slot, const uint8_t* src, uint8_t* dst) {
-                ptx::mbar_wait_sleepy(&bar_st[slot], (st_par >> slot) & 1u);
-                st_par ^= 1u << slot;
-                ptx::bulk_s2g(dst, src, 16384);
-                ptx::bulk_commit();
-                ptx::bulk_wait_read<2>();
-                if (prev2 >= 0) ptx::mbar_arrive(&bar_done[prev2]);
-                prev2 = prev1;
-                prev1 = slot;
-            };
-            for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-                uint8_t* save_tile = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
-                store(kSlotX, sX, save_tile + sl.x_off());
-                for (int g = 0; g < nl; ++g) {
-                    const int nq = layer_quarters(g, transient);
-                    uint8_t* dst = save_tile + sl.act_off(g);
-                    for (int q = 0; q < nq; ++q) {
-                        const int slot = out_slot(g, q);
-                        store(slot, sH + slot * 16384, dst + q * 16384);
-                    }
-                }
-            }
-            ptx::bulk_wait_all<0>();
-        }
-        __syncwarp();
+    }
     } else {
         // ============================ epilogue warps (four threads per point) ====================
+        ptx::setmaxnreg_inc<kFwdRegsEpi>();
         const int ew = warp - kEpiWarp0;                   // 0..15
         const int quad = warp & 3;                         // TMEM lane quadrant this warp may read
         const int sub = ew >> 2;                           // 16-column slice of every 64-column quarter
@@ -349,9 +327,9 @@ field_fwd_kernel(const FwdArgs a) {
         const float* cst = reinterpret_cast<const float*>(smem + kOffC);
         const SaveLayout sl{fs.kx, transient};
         uint32_t acc_ev = 0;                               // layers consumed (parity of bar_acc)
-        uint32_t seen = 0, done_par = 0;                   // save mode: slots written before / parity of their next hand-back
-        uint32_t tcount = 0;                               // tiles done by this CTA
-        for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tcount) {
+        const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an 8-bit image block
+        const int s7 = row & 7;
+        for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const long long p = static_cast<long long>(tile) * kTileM + row;
             const bool valid = p < a.n_points;
             const long long ray = valid ? p / a.S : 0;
@@ -402,17 +380,27 @@ field_fwd_kernel(const FwdArgs a) {
                         for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(e[16 * s4 + 2 * j], e[16 * s4 + 2 * j + 1]);
                     }
                 }
-                // sX doubles as the head scratch of the previous tile and (save) is read by the storer: both are
-                // finished -- the last head combine ended with a barrier, the X hand-back was consumed at layer 7
+                uint4 x8 = make_uint4(0, 0, 0, 0);
+                if (save) {
+#pragma unroll
+                    for (int s4 = 0; s4 < 4; ++s4) {
+                        if (s4 == sub) {
+                            x8.x = ptx::pack4_e4m3<false>(e[16 * s4], e[16 * s4 + 1], e[16 * s4 + 2], e[16 * s4 + 3]);
+                            x8.y = ptx::pack4_e4m3<false>(e[16 * s4 + 4], e[16 * s4 + 5], e[16 * s4 + 6], e[16 * s4 + 7]);
+                            x8.z = ptx::pack4_e4m3<false>(e[16 * s4 + 8], e[16 * s4 + 9], e[16 * s4 + 10], e[16 * s4 + 11]);
+                            x8.w = ptx::pack4_e4m3<false>(e[16 * s4 + 12], e[16 * s4 + 13], e[16 * s4 + 14], e[16 * s4 + 15]);
+                        }
+                    }
+                }
+                // sX doubles as the head scratch of the previous tile: its last combine ended with a barrier
                 *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before_sync();
                 __syncwarp();
-                if (lane == 0) {
-                    ptx::mbar_arrive(&bar_act[kSlotX]);
-                    if (save) ptx::mbar_arrive(&bar_st[kSlotX]);
-                }
+                if (lane == 0) ptx::mbar_arrive(&bar_act[kSlotX]);
+                // saved 8-bit image of the encoded xyz: columns [16 sub, 16 sub + 16) = chunk `sub` of this row's line
+                if (save) *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
             }
 
             float sigma = 0.0f, rgb[3] = {0, 0, 0};
@@ -437,31 +425,25 @@ field_fwd_kernel(const FwdArgs a) {
                     const int c0 = q * 64 + sub * 16;       // this thread's 16 columns of quarter q
                     const int slot = out_slot(g, q);
                     uint8_t* blk = sH + slot * 16384;
-                    if (save) {                             // the storer must have read the slot's previous contents
-                        if ((seen >> slot) & 1u) {
-                            ptx::mbar_wait_sleepy(&bar_done[slot], (done_par >> slot) & 1u);
-                            done_par ^= 1u << slot;
-                        }
-                        seen |= 1u << slot;
-                    }
                     uint32_t md = 0;
+                    uint4 p8 = make_uint4(0, 0, 0, 0);
                     if (g < 7) {
-                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else if (g == 7) {
                         epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                                    hacc, blk, row, 2 * sub, md);
+                                                    hacc, blk, row, 2 * sub, md, p8);
                     } else if (g == 8) {
-                        epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else if (g == 9) {
                         // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md);
-                        else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md, p8);
+                        else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else if (g < 12) {
-                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else {
                         // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
                         epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                                    hacc, blk, row, 2 * sub, md);
+                                                    hacc, blk, row, 2 * sub, md, p8);
                     }
                     if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
                     ptx::fence_proxy_async_smem();
@@ -471,23 +453,29 @@ field_fwd_kernel(const FwdArgs a) {
                         // the dir half of layer 9 (transient mode) and the last layer feed no MMA
                         const bool feeds_mma = !last && !(g == 9 && transient && q < 2);
                         if (feeds_mma) ptx::mbar_arrive(&bar_act[slot]);
-                        if (save) ptx::mbar_arrive(&bar_st[slot]);
                         NWB_TRACE(tile == 0 && warp == kEpiWarp0, g * 16 + 11 + q);          // quarter q handed over
                     }
+                    // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
+                    // 16 columns are chunk 4(q%2) + sub of its row's line.  Behind the handoff, off the MMA's critical path.
+                    if (save)
+                        *reinterpret_cast<uint4*>(save_tile + sl.act_off(g) + (q >> 1) * 16384 + line_off + (((4 * (q & 1) + sub) ^ s7) << 4)) = p8;
                 }
                 if (save && g != 8)
                     *reinterpret_cast<unsigned long long*>(save_tile + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
                 // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                 const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                 if (nh_heads > 0) {
-                    if (save && g == 7) ptx::mbar_wait_sleepy(&bar_done[kSlotX], tcount & 1u);   // the storer has read this tile's X
                     if (sub > 0) {
-                        for (int h = 0; h < nh_heads; ++h) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
+#pragma unroll
+                        for (int h = 0; h < 5; ++h)          // static indices: hacc stays in registers
+                            if (h < nh_heads) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
                     }
                     epi_bar_all();
                     if (sub == 0) {
-                        for (int h = 0; h < nh_heads; ++h)
-                            hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
+#pragma unroll
+                        for (int h = 0; h < 5; ++h)
+                            if (h < nh_heads)
+                                hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
                         if (g == 7) sigma = softplus_f(hacc[0] + cst[ConstOff::head_b]);                // nerf.py:190
                         if (g == 9) {
 #pragma unroll

@@ -15,8 +15,8 @@
 //            Rank 0 issues; rank 1's MMA warp relays "my half has landed"; completions are multicast.
 // One handoff per (slot, layer) in each direction: bar_act[t] (epilogue -> MMA: the slot's operand image is
 // complete, arrivals from the epilogue warps of BOTH CTAs on rank 0's barrier) and bar_acc[t] (MMA -> epilogue).
-// NWB_MLP_SAVE: the storer warp bulk-stores each finished image; the epilogue waits for the copy engine to have
-// read a slot's previous image before it overwrites it (bar_done[t]).
+// NWB_MLP_SAVE: behind each handoff every epilogue thread writes its 16 columns of each quarter as e4m3 (16-byte
+// stores from registers into the layer's 8-bit image for the weight-gradient kernel) and its ReLU sign-mask words.
 #pragma once
 
 namespace nwb {
@@ -31,17 +31,11 @@ constexpr int kDOffBar = kDOffC + 16384;
 constexpr int kDSmem = kDOffBar + 256;
 static_assert(kDSmem <= 232448, "dual-tile forward exceeds the 227 KB shared-memory limit");
 
-// Sign masks of layers >= kDMaskSmemFrom go through shared memory (the upper half of the slot's xyz buffer, dead
-// once layer 4's MMAs are done; the lower half is the head scratch) and ride in the image's bulk store; a global
-// store from the epilogue threads makes the next proxy fence (MEMBAR) wait for it -- ~10 % of the kernel.
-constexpr int kDMaskOff = 8192;
-constexpr int kDMaskSmemFrom = 5;
-
 // first activation K-block (16 KB slot of the slot's H image) layer g reads, after the optional X block
 __device__ __forceinline__ int dual_in_slot0(int g) { return g == 10 ? 2 : 0; }
 
 template <bool kSave>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(kFwdMaxRegs)
 field_fwd_dual_kernel(const FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sW = smem + kDOffW;
@@ -49,9 +43,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
     uint64_t* bar_empty = bar_full + kDNumStages;                       // [3] MMA -> producers of both CTAs
     uint64_t* bar_acc = bar_empty + kDNumStages;                        // [2] MMA -> epilogue, per slot
     uint64_t* bar_act = bar_acc + 2;                                    // [2] epilogues of both CTAs -> MMA, per slot
-    uint64_t* bar_st = bar_act + 2;                                     // [2] epilogue -> storer, per slot
-    uint64_t* bar_done = bar_st + 2;                                    // [2] storer -> epilogue, per slot
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 2);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_act + 2);
     uint32_t* s_woff = tmem_slot + 2;                                   // [kMaxG]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -73,8 +65,6 @@ field_fwd_dual_kernel(const FwdArgs a) {
         for (int t = 0; t < 2; ++t) {
             ptx::mbar_init(&bar_acc[t], 1);
             ptx::mbar_init(&bar_act[t], 2 * kEpiWarps);
-            ptx::mbar_init(&bar_st[t], kEpiWarps);
-            ptx::mbar_init(&bar_done[t], 1);
         }
         ptx::fence_mbar_init();
         for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
@@ -91,6 +81,8 @@ field_fwd_dual_kernel(const FwdArgs a) {
     ptx::tc_fence_after_sync();
     const uint32_t tmem = *tmem_slot;
 
+    if (warp < kEpiWarp0) {
+    ptx::setmaxnreg_dec<kFwdRegsWg0>();
     if (warp == 0) {
         // ============================ weight producer ============================================
         // per (layer, slot, K-block): my N/2 rows x 64 k of the packed slab image, one bulk copy
@@ -173,42 +165,10 @@ field_fwd_dual_kernel(const FwdArgs a) {
             }
         }
         __syncwarp();
-    } else if (warp == kStoreWarp) {
-        // ============================ activation storer (NWB_MLP_SAVE) ===========================
-        // images are stored in the order the epilogue finishes them: X of slot 0, X of slot 1, then (layer, slot);
-        // a slot is handed back as soon as the copy engine has read the image out of shared memory
-        if (lane == 0 && save) {
-            const SaveLayout sl{fs.kx, transient};
-            uint32_t st_par = 0;
-            auto store = [&](int t, bool ghost, const uint8_t* src, uint8_t* dst, uint32_t bytes, uint8_t* mask_dst) {
-                ptx::mbar_wait_sleepy(&bar_st[t], (st_par >> t) & 1u);
-                st_par ^= 1u << t;
-                if (!ghost) ptx::bulk_s2g(dst, src, bytes);
-                if (!ghost && mask_dst != nullptr) ptx::bulk_s2g(mask_dst, smem + kDOffX + t * 16384 + kDMaskOff, 4096);
-                ptx::bulk_commit();
-                ptx::bulk_wait_read<0>();
-                ptx::mbar_arrive(&bar_done[t]);
-            };
-            for (int quad = quad0; quad < n_quads; quad += quad_step) {
-                uint8_t* save_tile[2];
-                bool ghost[2];
-                for (int t = 0; t < 2; ++t) {
-                    const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
-                    ghost[t] = tile >= a.n_tiles;
-                    save_tile[t] = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
-                }
-                for (int t = 0; t < 2; ++t) store(t, ghost[t], smem + kDOffX + t * 16384, save_tile[t] + sl.x_off(), 16384, nullptr);
-                for (int g = 0; g < nl; ++g)
-                    for (int t = 0; t < 2; ++t)
-                        store(t, ghost[t], smem + kDOffH + t * 65536, save_tile[t] + sl.act_off(g),
-                              static_cast<uint32_t>(layer_quarters(g, transient)) * 16384u,
-                              (g >= kDMaskSmemFrom && g != 8) ? save_tile[t] + sl.mask_off(g, nl) : nullptr);
-            }
-            ptx::bulk_wait_all<0>();
-        }
-        __syncwarp();
+    }
     } else {
         // ============================ epilogue warps (four threads per point) ====================
+        ptx::setmaxnreg_inc<kFwdRegsEpi>();
         const int ew = warp - kEpiWarp0;                   // 0..15
         const int quad_l = warp & 3;                       // TMEM lane quadrant this warp may read
         const int sub = ew >> 2;                           // 16-column slice of every 64-column quarter
@@ -218,48 +178,42 @@ field_fwd_dual_kernel(const FwdArgs a) {
         const SaveLayout sl{fs.kx, transient};
         const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
         uint32_t acc_par = 0;                              // bit t = parity of the next phase of bar_acc[t]
-        uint32_t n_writes[2] = {0, 0};                     // images written into slot t so far (save: each waits for the
-                                                           // previous one's store to have been read)
-        auto wait_slot_free = [&](int t) {
-            if (save && n_writes[t] > 0) ptx::mbar_wait_sleepy(&bar_done[t], (n_writes[t] - 1) & 1u);
-            ++n_writes[t];
-        };
+        const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an 8-bit image block
+        const int s7 = row & 7;
         auto hand_over = [&](int t, bool feeds_mma) {      // after this thread's shared-memory writes of the image
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before_sync();
             __syncwarp();
-            if (lane == 0) {
-                if (feeds_mma) { if (rank == 0) ptx::mbar_arrive(&bar_act[t]); else ptx::mbar_arrive_cluster(act_leader + 8 * t); }
-                if (save) ptx::mbar_arrive(&bar_st[t]);
-            }
+            if (lane == 0 && feeds_mma) { if (rank == 0) ptx::mbar_arrive(&bar_act[t]); else ptx::mbar_arrive_cluster(act_leader + 8 * t); }
         };
         for (int quad = quad0; quad < n_quads; quad += quad_step) {
-            long long p[2];
-            bool valid[2], ghost[2];
-            long long ray[2];
-            uint8_t* save_tile[2];
+            // per-slot state lives in scalar registers selected by t (arrays indexed by the runtime slot number would sit
+            // in local memory: their reloads queue behind the epilogue's global stores -- a third of all stall samples of
+            // the first 8-bit build, profiles/r02b); what is cheap to recompute from the tile number is recomputed
+            int ray0 = 0, ray1 = 0;
             // ---- encoded-xyz operand tiles of both slots: this thread packs columns [16*sub, 16*sub+16) of its row ----
 #pragma unroll 1
             for (int t = 0; t < 2; ++t) {
                 const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
-                ghost[t] = tile >= a.n_tiles;
-                p[t] = static_cast<long long>(tile) * kTileM + row;
-                valid[t] = p[t] < a.n_points;
-                ray[t] = valid[t] ? p[t] / a.S : 0;
-                save_tile[t] = save ? a.saved + static_cast<size_t>(tile) * a.save_tile_bytes : nullptr;
+                const bool ghost_t = tile >= a.n_tiles;
+                const long long p_t = static_cast<long long>(tile) * kTileM + row;
+                const bool valid_t = p_t < a.n_points;
+                const int ray_t = valid_t ? static_cast<int>(p_t / a.S) : 0;
+                if (t == 0) ray0 = ray_t; else ray1 = ray_t;
+                uint8_t* save_tile_t = save ? a.saved + static_cast<size_t>(tile) * a.save_tile_bytes : nullptr;
                 uint8_t* sX = smem + kDOffX + t * 16384;
                 float e[64];
 #pragma unroll
                 for (int c = 0; c < 64; ++c) e[c] = 0.0f;
-                if (valid[t]) {
+                if (valid_t) {
                     if (a.x_enc != nullptr) {
-                        const float* xr = a.x_enc + p[t] * fs.in_xyz;
+                        const float* xr = a.x_enc + p_t * fs.in_xyz;
 #pragma unroll
                         for (int c = 0; c < 64; ++c)
                             if (c < fs.in_xyz && (c >> 4) == sub) e[c] = __ldg(xr + c);
                     } else {
-                        const float* rr = a.rays + ray[t] * a.ray_stride;
-                        const float zz = __ldg(a.z + p[t]);
+                        const float* rr = a.rays + static_cast<long long>(ray_t) * a.ray_stride;
+                        const float zz = __ldg(a.z + p_t);
                         float sn[3], cs[3];
 #pragma unroll
                         for (int i = 0; i < 3; ++i) {
@@ -290,29 +244,45 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(e[16 * s4 + 2 * j], e[16 * s4 + 2 * j + 1]);
                     }
                 }
+                uint4 x8 = make_uint4(0, 0, 0, 0);
+                if (save) {
+#pragma unroll
+                    for (int s4 = 0; s4 < 4; ++s4) {
+                        if (s4 == sub) {
+                            x8.x = ptx::pack4_e4m3<false>(e[16 * s4], e[16 * s4 + 1], e[16 * s4 + 2], e[16 * s4 + 3]);
+                            x8.y = ptx::pack4_e4m3<false>(e[16 * s4 + 4], e[16 * s4 + 5], e[16 * s4 + 6], e[16 * s4 + 7]);
+                            x8.z = ptx::pack4_e4m3<false>(e[16 * s4 + 8], e[16 * s4 + 9], e[16 * s4 + 10], e[16 * s4 + 11]);
+                            x8.w = ptx::pack4_e4m3<false>(e[16 * s4 + 12], e[16 * s4 + 13], e[16 * s4 + 14], e[16 * s4 + 15]);
+                        }
+                    }
+                }
                 // X_t doubles as the head scratch of the previous quad (its last combine ended with a barrier)
-                wait_slot_free(t);
                 *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 hand_over(t, true);
+                // saved 8-bit image of the encoded xyz: columns [16 sub, 16 sub + 16) = chunk `sub` of this row's line
+                if (save && !ghost_t) *reinterpret_cast<uint4*>(save_tile_t + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
             }
 
-            float sigma[2] = {0.0f, 0.0f}, rgb[2][3] = {{0, 0, 0}, {0, 0, 0}};
+            float sg0 = 0.0f, sg1 = 0.0f, c00 = 0.0f, c01 = 0.0f, c02 = 0.0f, c10 = 0.0f, c11 = 0.0f, c12 = 0.0f;   // sigma / rgb of slot 0 / 1
             for (int g = 0; g < nl; ++g) {
                 const bool last = (g == nl - 1);
                 const int nq = layer_quarters(g, transient);
 #pragma unroll 1
                 for (int t = 0; t < 2; ++t) {
+                    const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
                     uint8_t* sH = smem + kDOffH + t * 65536;
                     float* s_part = reinterpret_cast<float*>(smem + kDOffX + t * 16384);    // [3][5][128] head partial sums:
                                                                                              // X_t is dead once layer 4 is done
-                    const float* rb = (a.ray_bias != nullptr) ? a.ray_bias + ray[t] * 256 : nullptr;
+                    const float* rb = (a.ray_bias != nullptr) ? a.ray_bias + static_cast<long long>(t ? ray1 : ray0) * 256 : nullptr;
                     const uint32_t tacc = tlane + t * 256 + sub * 16;
                     ptx::mbar_wait_sleepy(&bar_acc[t], (acc_par >> t) & 1u);
                     acc_par ^= 1u << t;
                     ptx::tc_fence_after_sync();
-                    wait_slot_free(t);                       // save: the storer has read the image this one overwrites
                     float hacc[5] = {0, 0, 0, 0, 0};
+                    // e4m3 chunks of this thread's four quarters, kept until the handoff is out (selected by predicated moves:
+                    // the quarter loop is not unrolled)
+                    uint4 q8a = make_uint4(0, 0, 0, 0), q8b = q8a, q8c = q8a, q8d = q8a;
                     // sign masks: per layer [sub][row] x 4 uint16 (one per quarter: a warp's store is 256 contiguous bytes); bit (15-j) of entry q =
                     // sign of the pre-activation of column 64q + 16sub + j; one 8-byte store per thread after the handoff
                     unsigned long long mbits = 0ull;
@@ -321,56 +291,79 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         const int c0 = q * 64 + sub * 16;   // this thread's 16 columns of quarter q
                         uint8_t* blk = sH + q * 16384;      // in place: quarter q = K-block q of the next layer's operand
                         uint32_t md = 0;
+                        uint4 p8 = make_uint4(0, 0, 0, 0);
                         if (g < 7) {
-                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                         } else if (g == 7) {
                             epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                                        hacc, blk, row, 2 * sub, md);
+                                                        hacc, blk, row, 2 * sub, md, p8);
                         } else if (g == 8) {
-                            epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                            epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                         } else if (g == 9) {
                             // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-                            if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md);
-                            else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                            if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md, p8);
+                            else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                         } else if (g < 12) {
-                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md);
+                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                         } else {
                             // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
                             epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                                        hacc, blk, row, 2 * sub, md);
+                                                        hacc, blk, row, 2 * sub, md, p8);
                         }
-                        if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
+                        if (save) {
+                            mbits |= static_cast<unsigned long long>(md) << (16 * q);
+                            if (q == 0) q8a = p8; else if (q == 1) q8b = p8; else if (q == 2) q8c = p8; else q8d = p8;
+                        }
                     }
-                    if (save && g >= kDMaskSmemFrom && g != 8)
-                        *reinterpret_cast<unsigned long long*>(smem + kDOffX + t * 16384 + kDMaskOff + sub * 1024 + row * 8) = mbits;
                     hand_over(t, !last);
-                    if (save && g < kDMaskSmemFrom && !ghost[t])
-                        *reinterpret_cast<unsigned long long*>(save_tile[t] + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
+                    if (save && tile < a.n_tiles) {
+                        // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
+                        // 16 columns are chunk 4(q%2) + sub of its row's line
+                        uint8_t* save_tile_t = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
+                        uint8_t* ln = save_tile_t + sl.act_off(g) + line_off;
+                        *reinterpret_cast<uint4*>(ln + ((sub ^ s7) << 4)) = q8a;
+                        *reinterpret_cast<uint4*>(ln + (((4 + sub) ^ s7) << 4)) = q8b;
+                        if (nq == 4) {
+                            *reinterpret_cast<uint4*>(ln + 16384 + ((sub ^ s7) << 4)) = q8c;
+                            *reinterpret_cast<uint4*>(ln + 16384 + (((4 + sub) ^ s7) << 4)) = q8d;
+                        }
+                        if (g != 8) *reinterpret_cast<unsigned long long*>(save_tile_t + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
+                    }
                     // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                     const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                     if (nh_heads > 0) {
                         if (sub > 0) {
-                            for (int h = 0; h < nh_heads; ++h) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
+#pragma unroll
+                            for (int h = 0; h < 5; ++h)      // static indices: hacc stays in registers
+                                if (h < nh_heads) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
                         }
                         epi_bar_all();
                         if (sub == 0) {
-                            for (int h = 0; h < nh_heads; ++h)
-                                hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
-                            if (g == 7) sigma[t] = softplus_f(hacc[0] + cst[ConstOff::head_b]);                // nerf.py:190
-                            if (g == 9) {
 #pragma unroll
-                                for (int i = 0; i < 3; ++i) rgb[t][i] = sigmoid_f(hacc[i] + cst[ConstOff::head_b + 1 + i]);   // nerf.py:197
+                            for (int h = 0; h < 5; ++h)
+                                if (h < nh_heads)
+                                    hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
+                            if (g == 7) {                                                                      // nerf.py:190
+                                const float v = softplus_f(hacc[0] + cst[ConstOff::head_b]);
+                                if (t == 0) sg0 = v; else sg1 = v;
+                            }
+                            if (g == 9) {                                                                      // nerf.py:197
+                                const float v0 = sigmoid_f(hacc[0] + cst[ConstOff::head_b + 1]);
+                                const float v1 = sigmoid_f(hacc[1] + cst[ConstOff::head_b + 2]);
+                                const float v2 = sigmoid_f(hacc[2] + cst[ConstOff::head_b + 3]);
+                                if (t == 0) { c00 = v0; c01 = v1; c02 = v2; } else { c10 = v0; c11 = v1; c12 = v2; }
                             }
                         }
                         epi_bar_all();                       // scratch is read before anyone rewrites it
                     }
                     // ---- tile outputs ---------------------------------------------------------------
-                    if (last && valid[t] && sub == 0) {
+                    const long long p_t = static_cast<long long>(tile) * kTileM + row;
+                    if (last && p_t < a.n_points && sub == 0) {
                         if (sigma_only) {
-                            a.raw_out[p[t]] = sigma[t];
+                            a.raw_out[p_t] = t ? sg1 : sg0;
                         } else {
-                            float* o = a.raw_out + p[t] * (transient ? 9 : 4);
-                            o[0] = rgb[t][0]; o[1] = rgb[t][1]; o[2] = rgb[t][2]; o[3] = sigma[t];   // nerf.py:198
+                            float* o = a.raw_out + p_t * (transient ? 9 : 4);
+                            o[0] = t ? c10 : c00; o[1] = t ? c11 : c01; o[2] = t ? c12 : c02; o[3] = t ? sg1 : sg0;   // nerf.py:198
                             if (transient) {
                                 const float* hb = cst + ConstOff::head_b;
                                 o[4] = sigmoid_f(hacc[1] + hb[5]);                           // nerf.py:206

@@ -1,34 +1,38 @@
 // Backward of the fused field network, part 2: weight / bias / head-weight gradients.
 //
-// Every parameter gradient of the field is a contraction over points of two bf16 tile images that
-// already sit in HBM: dW_g = dZ_g^T . A_g (dZ_g from the dgrad kernel's workspace, A_g = the layer's
-// input activation saved by the forward).  Both images have rows == points, so both are fed to
-// tcgen05.mma MN-major with no transpose anywhere.  The work is cut into "units" -- one 128-row half
-// of one layer's dZ (the M side) against one activation image (the N side, <= 256 columns) -- and each
-// unit is split over points across CTAs in proportion to its byte traffic (the kernel is HBM/L2-bound:
-// 96 KB of operands per 1024 tensor cycles).  A CTA keeps its (128 x <=256) fp32 partial in TMEM over
-// its whole tile range, and flushes it once with fp32 atomics.  Bias gradients ride along as one more
-// N=16 MMA per k-step against a constant block of ones; head-weight gradients are units whose M side
-// is the head's input activation and whose N side is the dpre block.
+// Every parameter gradient of the field is a contraction over points of two 8-bit tile images that
+// already sit in HBM: dW_g = dZ_g^T . A_g (dZ_g, e5m2 times the pass's power-of-two scale, from the dgrad
+// kernel's workspace; A_g, e4m3, the layer's input activation saved by the forward).  Both images have
+// rows == points, so both are fed to tcgen05.mma kind::f8f6f4 MN-major with no transpose anywhere (K = 32
+// points per instruction, fp32 accumulate -- the products of two 8-bit floats are exact in fp32).  The work
+// is cut into "units" -- one 128-column block of one layer's dZ (the M side, 16 KB per tile) against one
+// activation image (the N side, <= 256 columns, <= 32 KB per tile) -- and each unit is split over points
+// across CTAs in proportion to its byte traffic (the kernel is HBM-bound: 48 KB of operands per 512 tensor
+// cycles).  A CTA keeps its (128 x <=256) fp32 partial in TMEM over its whole tile range, and flushes it once
+// (times 1/scale) with fp32 atomics.  Bias gradients ride along as one more N=16 MMA per k-step against a
+// constant block of ones; head-weight gradients are units whose M side is the head's input activation and
+// whose N side is the dpre block.
 #include "field_dev.cuh"
 #include <algorithm>
 
 namespace nwb {
 
 constexpr int kWgThreads = 192;
-constexpr int kWgStages = 2;
-constexpr int kWgMBytes = 32768;                 // M side: 128 points x 128 columns
-constexpr int kWgNBytes = 65536;                 // N side: 128 points x <= 256 columns
+constexpr int kWgStages = 4;                     // 4 x 48 KB in flight per SM: the kernel lives on HBM latency x bandwidth
+constexpr int kWgMBytes = 16384;                 // M side: 128 points x 128 columns, 8-bit
+constexpr int kWgNBytes = 32768;                 // N side: 128 points x <= 256 columns, 8-bit
 constexpr int kWgStageBytes = kWgMBytes + kWgNBytes;
 constexpr int kWgOffOnes = kWgStages * kWgStageBytes;
-constexpr int kWgOffBar = kWgOffOnes + 2048;
+constexpr int kWgOffBar = kWgOffOnes + 4096;
 constexpr int kWgSmem = kWgOffBar + 128;
 constexpr int kWgMaxUnits = 40;
 
 struct WUnit {
     uint32_t m_off, n_off;        // byte offsets inside the tile record
     uint8_t m_src, n_src;         // 0 = dgrad workspace, 1 = forward save buffer
-    uint8_t n_blocks;             // N side 64-column blocks (1..4)
+    uint8_t n_blocks;             // N side 128-column blocks (1..2)
+    uint16_t n_mma;               // MMA N (a multiple of 16 up to 256; 16 for head units)
+    uint8_t m_e5m2;               // 1: M side is a dZ image (e5m2), N side e4m3; 0: head unit, M side e4m3, N side e5m2
     uint8_t ones;                 // also accumulate sum_p dZ[p, m] (bias gradient)
     uint8_t head_lo, head_hi;     // head unit: D[m][n], n in [head_lo, head_hi) -> head_out[n][m_base + m]
     uint16_t n_valid;             // valid N columns (e.g. 63 of 64 for the encoded-xyz block)
@@ -41,6 +45,7 @@ struct WUnit {
 };
 
 struct WgArgs {
+    const DzHeader* hdr;
     const uint8_t* dz;
     const uint8_t* saved;
     size_t dz_tile_bytes, save_tile_bytes;
@@ -70,7 +75,7 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
     const uint32_t n_stride = static_cast<uint32_t>(u.n_src ? a.save_tile_bytes : a.dz_tile_bytes);
     const uint8_t* m_base = (u.m_src ? a.saved : a.dz) + u.m_off;
     const uint8_t* n_base = (u.n_src ? a.saved : a.dz) + u.n_off;
-    const uint32_t n_bytes = static_cast<uint32_t>(u.n_blocks) * 16384u;
+    const uint32_t n_bytes = static_cast<uint32_t>(u.n_blocks) * 16384u;      // whole blocks travel, the MMA reads n_mma columns
 
     if (threadIdx.x == 0) {
         if ((ptx::smem_u32(smem) & 1023u) != 0) {
@@ -81,7 +86,7 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
         ptx::mbar_init(bar_done, 1);
         ptx::fence_mbar_init();
     }
-    for (int i = threadIdx.x; i < 512; i += blockDim.x) reinterpret_cast<uint32_t*>(sOnes)[i] = 0x3F803F80u;   // bf16 1.0
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) reinterpret_cast<uint32_t*>(sOnes)[i] = 0x38383838u;  // e4m3 1.0
     ptx::fence_proxy_async_smem();
     if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
     ptx::tc_fence_before_sync();
@@ -104,9 +109,9 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {
-            // D(128 m x N) += M_img^T (16 points x 128 m, MN-major) . N_img (16 points x N, MN-major)
-            const uint32_t idesc = ptx::umma_idesc_bf16(128, u.n_blocks * 64, true, true);
-            constexpr uint32_t idesc1 = ptx::umma_idesc_bf16(128, 16, true, true);
+            // D(128 m x N) += M_img^T (32 points x 128 m, MN-major) . N_img (32 points x N, MN-major)
+            const uint32_t idesc = ptx::umma_idesc_f8(128, u.n_mma, u.m_e5m2 ? 1 : 0, u.m_e5m2 ? 0 : 1, true, true);
+            constexpr uint32_t idesc1 = ptx::umma_idesc_f8(128, 16, 1, 0, true, true);
             const uint32_t ones = ptx::smem_u32(sOnes);
             uint32_t it = 0;
             for (int t = t0; t < t1; ++t, ++it) {
@@ -115,10 +120,10 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
                 ptx::tc_fence_after_sync();
                 const uint32_t ma = ptx::smem_u32(smem + s * kWgStageBytes), na = ma + kWgMBytes;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const uint64_t ad = ptx::umma_desc_sw128(ma + j * 2048, 16384, 1024);
-                    ptx::umma_bf16(tmem, ad, ptx::umma_desc_sw128(na + j * 2048, 16384, 1024), idesc, (it | j) != 0);
-                    if (u.ones) ptx::umma_bf16(tmem + 256, ad, ptx::umma_desc_sw128(ones, 16384, 1024), idesc1, (it | j) != 0);
+                for (int j = 0; j < 4; ++j) {            // 32 points = 4 groups of 8 rows, 1 KB apart
+                    const uint64_t ad = ptx::umma_desc_sw128(ma + j * 4096, 16384, 1024);
+                    ptx::umma_f8(tmem, ad, ptx::umma_desc_sw128(na + j * 4096, 16384, 1024), idesc, (it | j) != 0);
+                    if (u.ones) ptx::umma_f8(tmem + 256, ad, ptx::umma_desc_sw128(ones, 16384, 1024), idesc1, (it | j) != 0);
                 }
                 ptx::umma_commit(&bar_empty[s]);
             }
@@ -130,6 +135,7 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
         const int quad = warp & 3;
         const int m = quad * 32 + lane;
         const uint32_t tlane = tmem + (static_cast<uint32_t>(quad * 32) << 16);
+        const float inv = 1.0f / dz_scale_from_amax_bits(__ldg(&a.hdr->amax_bits));     // exact: a power of two
         ptx::mbar_wait(bar_done, 0);
         ptx::tc_fence_after_sync();
         if (u.head_hi > u.head_lo) {
@@ -138,7 +144,7 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
             ptx::tmem_ld_wait();
 #pragma unroll
             for (int n = 0; n < 9; ++n)
-                if (n >= u.head_lo && n < u.head_hi) atomicAdd(a.head_out[n] + u.m_base + m, __uint_as_float(v[n]));
+                if (n >= u.head_lo && n < u.head_hi) atomicAdd(a.head_out[n] + u.m_base + m, __uint_as_float(v[n]) * inv);
         } else {
             float* orow = u.out + static_cast<size_t>(u.m_base + m) * u.ld + u.n_base;
             for (int c0 = 0; c0 < u.n_valid; c0 += 32) {
@@ -147,13 +153,13 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
                 ptx::tmem_ld_wait();
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                    if (c0 + j < u.n_valid) atomicAdd(orow + c0 + j, __uint_as_float(v[j]));
+                    if (c0 + j < u.n_valid) atomicAdd(orow + c0 + j, __uint_as_float(v[j]) * inv);
             }
             if (u.ones && u.out_b != nullptr) {
                 uint32_t v[32];
                 ptx::tmem_ld32(tlane + 256, v);
                 ptx::tmem_ld_wait();
-                atomicAdd(u.out_b + u.m_base + m, __uint_as_float(v[0]));
+                atomicAdd(u.out_b + u.m_base + m, __uint_as_float(v[0]) * inv);
             }
         }
     }
@@ -167,60 +173,63 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
 using namespace nwb;
 
 int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8_t* saved, size_t save_tile_bytes,
-                     const uint8_t* dz, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st) {
+                     const uint8_t* ws, size_t dz_tile_bytes, int n_tiles, uint32_t mode, cudaStream_t st) {
     const bool transient = (mode & NWB_MLP_TRANSIENT) != 0;
     const SaveLayout sl{fs.kx, transient};
     const DzLayout dl{transient};
     WgArgs a{};                            // passed by value at launch
-    a.dz = dz; a.saved = saved; a.dz_tile_bytes = dz_tile_bytes; a.save_tile_bytes = save_tile_bytes;
+    a.hdr = reinterpret_cast<const DzHeader*>(ws);
+    a.dz = ws + kDzHeaderBytes; a.saved = saved; a.dz_tile_bytes = dz_tile_bytes; a.save_tile_bytes = save_tile_bytes;
     a.n_tiles = n_tiles;
     int nu = 0;
-    auto add = [&](uint32_t m_off, int m_src, uint32_t n_off, int n_src, int n_blocks, int n_valid, bool ones, float* out,
+    // n_cols: columns of the N-side image the MMA reads (64 for the encoded-xyz block, else 128 per block)
+    auto add = [&](uint32_t m_off, int m_src, uint32_t n_off, int n_src, int n_cols, int n_valid, bool ones, float* out,
                    int ld, int m_base_, int n_base_, float* out_b) -> WUnit& {
         WUnit& u = a.units[nu++];
         u.m_off = m_off; u.m_src = static_cast<uint8_t>(m_src); u.n_off = n_off; u.n_src = static_cast<uint8_t>(n_src);
-        u.n_blocks = static_cast<uint8_t>(n_blocks); u.n_valid = static_cast<uint16_t>(n_valid); u.ones = ones ? 1 : 0;
+        u.n_blocks = static_cast<uint8_t>((n_cols + 127) / 128); u.n_mma = static_cast<uint16_t>(n_cols);
+        u.n_valid = static_cast<uint16_t>(n_valid); u.ones = ones ? 1 : 0; u.m_e5m2 = 1;
         u.out = out; u.ld = static_cast<uint16_t>(ld); u.m_base = static_cast<uint16_t>(m_base_);
         u.n_base = static_cast<uint16_t>(n_base_); u.out_b = out_b; u.head_lo = u.head_hi = 0;
         return u;
     };
-    const int xcols = 64 * fs.kx;
+    const int xcols = (fs.in_xyz + 15) & ~15;        // MMA N: a multiple of 16 covering the valid encoded-xyz columns
     for (int gq = 0; gq <= 8; ++gq) {
         float* W = (gq < 8) ? g->trunk_w[gq] : g->final_w;
         float* B = (gq < 8) ? g->trunk_b[gq] : g->final_b;
         for (int mh = 0; mh < 2; ++mh) {
-            const uint32_t m_off = static_cast<uint32_t>(dl.dz_off(gq)) + mh * 32768u;
+            const uint32_t m_off = static_cast<uint32_t>(dl.dz_off(gq)) + mh * 16384u;
             if (gq == 0) {
-                add(m_off, 0, static_cast<uint32_t>(sl.x_off()), 1, fs.kx, fs.in_xyz, true, W, fs.in_xyz, mh * 128, 0, B);
+                add(m_off, 0, static_cast<uint32_t>(sl.x_off()), 1, xcols, fs.in_xyz, true, W, fs.in_xyz, mh * 128, 0, B);
             } else if (gq == 4) {
-                add(m_off, 0, static_cast<uint32_t>(sl.x_off()), 1, fs.kx, fs.in_xyz, false, W, fs.in_xyz + kW, mh * 128, 0, nullptr);
-                add(m_off, 0, static_cast<uint32_t>(sl.act_off(3)), 1, 4, 256, true, W, fs.in_xyz + kW, mh * 128, fs.in_xyz, B);
+                add(m_off, 0, static_cast<uint32_t>(sl.x_off()), 1, xcols, fs.in_xyz, false, W, fs.in_xyz + kW, mh * 128, 0, nullptr);
+                add(m_off, 0, static_cast<uint32_t>(sl.act_off(3)), 1, 256, 256, true, W, fs.in_xyz + kW, mh * 128, fs.in_xyz, B);
             } else {
-                add(m_off, 0, static_cast<uint32_t>(sl.act_off(gq - 1)), 1, 4, 256, true, W, kW, mh * 128, 0, B);
+                add(m_off, 0, static_cast<uint32_t>(sl.act_off(gq - 1)), 1, 256, 256, true, W, kW, mh * 128, 0, B);
             }
         }
     }
-    (void)xcols;
     // g = 9: feature columns of dir_encoding.0 / transient_encoding.0 (their other columns and biases
     // come from the per-ray operands, ray_consts.cu)
-    add(static_cast<uint32_t>(dl.dz_off(9)), 0, static_cast<uint32_t>(sl.act_off(8)), 1, 4, 256, false, g->dir_w,
+    add(static_cast<uint32_t>(dl.dz_off(9)), 0, static_cast<uint32_t>(sl.act_off(8)), 1, 256, 256, false, g->dir_w,
         kW + fs.in_dir + fs.in_a, 0, 0, nullptr);
     if (transient) {
-        add(static_cast<uint32_t>(dl.dz_off(9)) + 32768u, 0, static_cast<uint32_t>(sl.act_off(8)), 1, 4, 256, false, g->tenc_w[0],
+        add(static_cast<uint32_t>(dl.dz_off(9)) + 16384u, 0, static_cast<uint32_t>(sl.act_off(8)), 1, 256, 256, false, g->tenc_w[0],
             kW + fs.in_t, 0, 0, nullptr);
         for (int gq = 10; gq <= 12; ++gq) {
-            const uint32_t n_off = (gq == 10) ? static_cast<uint32_t>(sl.act_off(9)) + 32768u : static_cast<uint32_t>(sl.act_off(gq - 1));
-            add(static_cast<uint32_t>(dl.dz_off(gq)), 0, n_off, 1, 2, 128, true, g->tenc_w[gq - 9], kHalf, 0, 0, g->tenc_b[gq - 9]);
+            const uint32_t n_off = (gq == 10) ? static_cast<uint32_t>(sl.act_off(9)) + 16384u : static_cast<uint32_t>(sl.act_off(gq - 1));
+            add(static_cast<uint32_t>(dl.dz_off(gq)), 0, n_off, 1, 128, 128, true, g->tenc_w[gq - 9], kHalf, 0, 0, g->tenc_b[gq - 9]);
         }
     }
-    // heads: M side = the head's input activation, N side = dpre block
+    // heads: M side = the head's input activation (e4m3), N side = dpre block (e5m2, 16 columns read)
     const uint32_t dpre = static_cast<uint32_t>(dl.dpre_off());
-    for (int mh = 0; mh < 2; ++mh) {
-        WUnit& u = add(static_cast<uint32_t>(sl.act_off(7)) + mh * 32768u, 1, dpre, 0, 1, 16, false, nullptr, 0, mh * 128, 0, nullptr);
-        u.head_lo = 0; u.head_hi = 1;
-    }
-    { WUnit& u = add(static_cast<uint32_t>(sl.act_off(9)), 1, dpre, 0, 1, 16, false, nullptr, 0, 0, 0, nullptr); u.head_lo = 1; u.head_hi = 4; }
-    if (transient) { WUnit& u = add(static_cast<uint32_t>(sl.act_off(12)), 1, dpre, 0, 1, 16, false, nullptr, 0, 0, 0, nullptr); u.head_lo = 4; u.head_hi = 9; }
+    auto add_head = [&](uint32_t m_off, int m_base_, int lo, int hi) {
+        WUnit& u = add(m_off, 1, dpre, 0, 16, 16, false, nullptr, 0, m_base_, 0, nullptr);
+        u.m_e5m2 = 0; u.head_lo = static_cast<uint8_t>(lo); u.head_hi = static_cast<uint8_t>(hi);
+    };
+    for (int mh = 0; mh < 2; ++mh) add_head(static_cast<uint32_t>(sl.act_off(7)) + mh * 16384u, mh * 128, 0, 1);
+    add_head(static_cast<uint32_t>(sl.act_off(9)), 0, 1, 4);
+    if (transient) add_head(static_cast<uint32_t>(sl.act_off(12)), 0, 4, 9);
     a.head_out[0] = g->sigma_w;
     for (int i = 0; i < 3; ++i) a.head_out[1 + i] = g->rgb_w + i * kHalf;
     if (transient) {

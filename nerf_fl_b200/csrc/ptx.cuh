@@ -282,6 +282,13 @@ __device__ __forceinline__ uint32_t cluster_count_x() {
     asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r));
     return r;
 }
+// warpgroup-wide register reallocation (every warp of an aligned group of four executes the same one)
+template <int kRegs> __device__ __forceinline__ void setmaxnreg_inc() {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
+template <int kRegs> __device__ __forceinline__ void setmaxnreg_dec() {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
 __device__ __forceinline__ void cluster_sync_all() {   // every thread of both CTAs
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -353,6 +360,38 @@ __device__ __forceinline__ void umma2_commit_both(uint32_t bar_addr) {
 // MN-major (rows = contraction index) by the descriptor alone -- same bytes.
 __host__ __device__ __forceinline__ uint32_t image_chunk_off(int r, int chunk /*16B chunk index within row*/) {
     return static_cast<uint32_t>((r >> 3) * 1024 + (r & 7) * 128 + ((chunk ^ (r & 7)) << 4));
+}
+
+// ---- 8-bit float packing (F2FP): two fp32 -> two e4m3 / e5m2 in 16 bits, round to nearest, saturating ------------------
+// result bits [0,8) = lo, [8,16) = hi
+__device__ __forceinline__ uint32_t cvt_e4m3x2(float lo, float hi) {
+    uint16_t r;
+    asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ uint32_t cvt_e4m3x2_relu(float lo, float hi) {       // max(x, 0) first
+    uint16_t r;
+    asm("cvt.rn.satfinite.relu.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ uint32_t cvt_e5m2x2(float lo, float hi) {
+    uint16_t r;
+    asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+// four fp32 -> one 32-bit word of four 8-bit floats, element 0 in the low byte
+template <bool kRelu>
+__device__ __forceinline__ uint32_t pack4_e4m3(float a, float b, float c, float d) {
+    return kRelu ? (cvt_e4m3x2_relu(a, b) | (cvt_e4m3x2_relu(c, d) << 16)) : (cvt_e4m3x2(a, b) | (cvt_e4m3x2(c, d) << 16));
+}
+__device__ __forceinline__ uint32_t pack4_e5m2(float a, float b, float c, float d) {
+    return cvt_e5m2x2(a, b) | (cvt_e5m2x2(c, d) << 16);
+}
+// 32-byte global store (STG.256, sm_100): dst must be 32 B aligned
+__device__ __forceinline__ void st_global_256(void* dst, const uint4& a, const uint4& b) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w),
+                 "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+                 : "memory");
 }
 
 // packed fp32 add (FADD2 on sm_100): {x0, x1} = {a0, a1} + {b0, b1}

@@ -333,8 +333,9 @@ def field_traffic_bytes_per_point(kind: str, fine: bool) -> float:
     dgrad writes the dZ record and reads the sign masks; wgrad reads both records (without the masks) once."""
     desc = field_desc(63, 27, 48 if fine else 0, 16 if fine else 0)
     mode = (L.NWB_MLP_TRANSIENT if fine else 0) | L.NWB_MLP_SAVE
-    save = mlp_save_bytes(desc, 128, mode) / 128.0
-    ws = mlp_bwd_workspace_bytes(desc, 128, mode & ~L.NWB_MLP_SAVE) / 128.0
+    n = 128 * 1024                                   # many tiles: the workspace's 256-byte header vanishes
+    save = mlp_save_bytes(desc, n, mode) / float(n)
+    ws = mlp_bwd_workspace_bytes(desc, n, mode & ~L.NWB_MLP_SAVE) / float(n)
     masks = 13 * 4096 / 128.0
     return {"fwd": save, "dgrad": ws + masks, "wgrad": (save - masks) + ws}[kind]
 
