@@ -92,10 +92,12 @@ inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
 //   saved activations: e4m3, unscaled (post-ReLU values; the encoded-xyz block and `feat` are signed)
 //   dZ / dpre:         e5m2, times ONE power-of-two scale per backward pass (DzHeader), so that amax|d_raw| -> 2^kDzTop
 // tools/fp8_wgrad_study.py: against the fp32 oracle the model gradient moves from 1.29e-3 (bf16 images) to 1.55e-3.
+constexpr float kLoScale = 16.0f;
 constexpr int kDzTop = 10;       // e5m2 tops out at 57344 ~ 2^15.8: 2^5.8 of headroom for growth along the chain
 
 // saved-activation layout per tile (forward NWB_MLP_SAVE): e4m3 images followed by ReLU sign masks
 //   [X: 16K (64 of 128 columns written)][h1..h8: 8 x 32K][feat: 32K][dir|t0: 16K or 32K][t2,t4,t6: 3 x 16K][masks: 13 x 4K]
+//   [lo h8: 32K][lo dir: 16K][lo t6: 16K]
 // masks: per layer g four 1 KB sub-blocks [sub][row] of 4 x uint16: bit relu_mask_bit(j) of entry q of (sub, row) = 1 iff the
 // pre-activation of column 64q + 16sub + j of that row was negative (ReLU gate closed).  A forward epilogue thread owns
 // one (sub, row) entry group: its warp writes 256 contiguous bytes.
@@ -116,13 +118,25 @@ struct SaveLayout {
         return act_off(12) + 16384;
     }
     __host__ __device__ size_t mask_off(int g, int n_layers) const { return acts_bytes(n_layers) + static_cast<size_t>(g) * 4096; }
-    __host__ __device__ size_t tile_bytes(int n_layers) const { return acts_bytes(n_layers) + kMaxG * 4096; }
+    // residual images of the three activations that feed the fp32 heads (h8 -> sigma, dir hidden -> rgb, t6 -> transient
+    // heads): lo = e4m3(kLoScale (a - e4m3(a))), so that hi + lo / kLoScale carries ~7 significant bits into the
+    // head-weight gradients (a single 8-bit contraction there costs the coarse network 4x its gradient error,
+    // tools/fp8_wgrad_study.py heads).  The residual is at most 2^-4 of |a|; times 16 it stays below |a| <= 448 and
+    // clear of e4m3's subnormals (2^-9 steps below 2^-6), where a unit-scale residual of a small activation would vanish.
+    //   k = 0: h8 (32K, layer 7), k = 1: dir hidden (16K, layer 9 quarters 0-1), k = 2: t6 (16K, layer 12)
+    __host__ __device__ size_t lo_off(int k, int n_layers) const {
+        return acts_bytes(n_layers) + kMaxG * 4096 + (k == 0 ? 0 : (k == 1 ? 32768 : 49152));
+    }
+    __host__ __device__ size_t tile_bytes(int n_layers) const {
+        return acts_bytes(n_layers) + kMaxG * 4096 + (n_layers <= 8 ? 32768 : (n_layers <= 10 ? 49152 : 65536));
+    }
 };
 
 // backward workspace (written by the dgrad kernel, read by the wgrad kernel): a 256-byte header, then per tile
 //   [dZ g0..g8: 9 x 32K][dZ9: 32K (dir|t0) or 16K (dir)][dZ10..12: 3 x 16K][dpre: 16K]
-// dZ_g = cotangent of layer g's pre-activation (e5m2 image, scaled); dpre = cotangents of the head pre-activations,
-// one block of which 16 columns are read: [sigma, rgb(3), t_sigma, t_rgb(3), t_beta, 0...].
+// dZ_g = cotangent of layer g's pre-activation (e5m2 image, scaled); dpre = cotangents of the head pre-activations
+// [sigma, rgb(3), t_sigma, t_rgb(3), t_beta] as a THREE-term e5m2 expansion (term k = e5m2 of what terms < k left
+// over): one block of which 32 columns are read, column 9k + n = term k of head n, columns 27..31 zero.
 struct DzHeader {
     unsigned int amax_bits;      // max |d_raw| of the pass as fp32 bits (non-negative floats order like their bits)
     unsigned int pad[63];

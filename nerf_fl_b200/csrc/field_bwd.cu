@@ -271,12 +271,28 @@ field_dgrad_kernel(const BwdArgs a) {
                 dp[i] *= scale;                             // from here on the chain carries scaled cotangents
             }
             if (!ghost) {
-                // dpre block (e5m2): the wgrad kernel's head units read 16 columns = chunk 0 of every row; the other
-                // seven chunks of the block are never read and stay unwritten
-                uint4 c0;
-                c0.x = ptx::pack4_e5m2(dp[0], dp[1], dp[2], dp[3]); c0.y = ptx::pack4_e5m2(dp[4], dp[5], dp[6], dp[7]);
-                c0.z = ptx::pack4_e5m2(dp[8], 0.0f, 0.0f, 0.0f); c0.w = 0u;
-                *reinterpret_cast<uint4*>(dz_tile + dl.dpre_off() + ptx::image_chunk_off(row, 0)) = c0;
+                // dpre block (e5m2, three-term expansion: column 9k + n = e5m2 of what terms < k left of head n's scaled
+                // cotangent): the wgrad kernel's head units read 32 columns = chunks 0, 1 of every row -- one 32-byte
+                // sector, the swizzle swaps the two when the row is odd; the other six chunks stay unwritten
+                uint32_t by[32];
+#pragma unroll
+                for (int i = 27; i < 32; ++i) by[i] = 0u;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) {
+                    float r = dp[i];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const uint32_t b = ptx::cvt_e5m2x2(r, 0.0f) & 0xFFu;
+                        by[9 * k + i] = b;
+                        r -= ptx::dec_e5m2(b);
+                    }
+                }
+                uint32_t w[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) w[j] = by[4 * j] | (by[4 * j + 1] << 8) | (by[4 * j + 2] << 16) | (by[4 * j + 3] << 24);
+                const uint4 lo = make_uint4(w[0], w[1], w[2], w[3]), hi = make_uint4(w[4], w[5], w[6], w[7]);
+                uint8_t* dst = dz_tile + dl.dpre_off() + line_off + (((row & 7) >> 1) << 5);
+                if (row & 1) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
             }
 
             for (int g = nl - 1; g >= 0; --g) {

@@ -82,10 +82,12 @@ __device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 1, %0;" :
 //   rn(max(x, 0))) -> chunks chunk0, chunk0+1 (16 B each) of this row in the K-block image blk.
 //   kSave: the sign bits of the 16 pre-activations are returned in neg_out, bit (15-j) = column j, and the 16
 //   activations as e4m3 (ReLU applied by the conversion) in p8 -- one 16-byte chunk of the saved 8-bit image.
+//   l8 (kSave, layers that feed a head, may be null): the e4m3 chunk of what p8 left over (the residual image)
 template <bool kRelu, int kHeads, bool kSave>
 __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restrict__ bias,
                                             const float* __restrict__ rbias, const float* __restrict__ hw, int hw_ld,
-                                            float* hacc, uint8_t* blk, int row, int chunk0, uint32_t& neg_out, uint4& p8) {
+                                            float* hacc, uint8_t* blk, int row, int chunk0, uint32_t& neg_out, uint4& p8,
+                                            uint4* l8 = nullptr) {
     uint32_t v[16];
     ptx::tmem_ld16(taddr, v);
     float b[16];
@@ -113,6 +115,10 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
     if (kSave) {
         p8.x = ptx::pack4_e4m3<kRelu>(x[0], x[1], x[2], x[3]);    p8.y = ptx::pack4_e4m3<kRelu>(x[4], x[5], x[6], x[7]);
         p8.z = ptx::pack4_e4m3<kRelu>(x[8], x[9], x[10], x[11]);  p8.w = ptx::pack4_e4m3<kRelu>(x[12], x[13], x[14], x[15]);
+        if (kHeads > 0 && l8 != nullptr) {
+            l8->x = ptx::residual4_e4m3<kRelu>(p8.x, x[0], x[1], x[2], x[3], kLoScale);    l8->y = ptx::residual4_e4m3<kRelu>(p8.y, x[4], x[5], x[6], x[7], kLoScale);
+            l8->z = ptx::residual4_e4m3<kRelu>(p8.z, x[8], x[9], x[10], x[11], kLoScale);  l8->w = ptx::residual4_e4m3<kRelu>(p8.w, x[12], x[13], x[14], x[15], kLoScale);
+        }
     }
     if (kRelu && kSave) {
         // packed word j: bit 15 = sign of column 2j, bit 31 = sign of column 2j+1.  One shift + one LOP3 per word
@@ -149,6 +155,22 @@ __device__ __forceinline__ void epi_slice16(uint32_t taddr, const float* __restr
     }
     *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
     *reinterpret_cast<uint4*>(blk + ptx::image_chunk_off(row, chunk0 + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+}
+
+// The same residual chunk, recomputed behind the handoff from what is still at hand: the bf16 activations of this
+// thread's 16 columns in the shared-memory image (chunks chunk0, chunk0+1 of its row) and the e4m3 chunk it kept.
+// (The pair kernel hands a whole layer over at once; holding four more chunks until then would spill.)
+__device__ __forceinline__ uint4 residual_chunk(const uint8_t* blk, int row, int chunk0, const uint4& p8) {
+    const uint4 b0 = *reinterpret_cast<const uint4*>(blk + ptx::image_chunk_off(row, chunk0));
+    const uint4 b1 = *reinterpret_cast<const uint4*>(blk + ptx::image_chunk_off(row, chunk0 + 1));
+    auto lo = [](uint32_t w) { return __uint_as_float(w << 16); };
+    auto hi = [](uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); };
+    uint4 l8;
+    l8.x = ptx::residual4_e4m3<false>(p8.x, lo(b0.x), hi(b0.x), lo(b0.y), hi(b0.y), kLoScale);
+    l8.y = ptx::residual4_e4m3<false>(p8.y, lo(b0.z), hi(b0.z), lo(b0.w), hi(b0.w), kLoScale);
+    l8.z = ptx::residual4_e4m3<false>(p8.z, lo(b1.x), hi(b1.x), lo(b1.y), hi(b1.y), kLoScale);
+    l8.w = ptx::residual4_e4m3<false>(p8.w, lo(b1.z), hi(b1.z), lo(b1.w), hi(b1.w), kLoScale);
+    return l8;
 }
 
 #ifdef NWB_FWD_TRACE      // tools/trace_fwd.py: build with -DNWB_FWD_TRACE to get block 0's timeline
@@ -427,23 +449,27 @@ field_fwd_kernel(const FwdArgs a) {
                     uint8_t* blk = sH + slot * 16384;
                     uint32_t md = 0;
                     uint4 p8 = make_uint4(0, 0, 0, 0);
+                    // this thread's chunk of the residual image (layers that feed a head), same place as in the image proper
+                    uint4 l8v = make_uint4(0, 0, 0, 0);
+                    const bool has_lo = save && (g == 7 || (g == 9 && q < 2) || g == 12);
+                    uint4* lo8 = has_lo ? &l8v : nullptr;
                     if (g < 7) {
                         epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else if (g == 7) {
                         epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                                    hacc, blk, row, 2 * sub, md, p8);
+                                                    hacc, blk, row, 2 * sub, md, p8, lo8);
                     } else if (g == 8) {
                         epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else if (g == 9) {
                         // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md, p8);
+                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md, p8, lo8);
                         else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else if (g < 12) {
                         epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
                     } else {
                         // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
                         epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                                    hacc, blk, row, 2 * sub, md, p8);
+                                                    hacc, blk, row, 2 * sub, md, p8, lo8);
                     }
                     if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
                     ptx::fence_proxy_async_smem();
@@ -457,8 +483,11 @@ field_fwd_kernel(const FwdArgs a) {
                     }
                     // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
                     // 16 columns are chunk 4(q%2) + sub of its row's line.  Behind the handoff, off the MMA's critical path.
-                    if (save)
-                        *reinterpret_cast<uint4*>(save_tile + sl.act_off(g) + (q >> 1) * 16384 + line_off + (((4 * (q & 1) + sub) ^ s7) << 4)) = p8;
+                    if (save) {
+                        const uint32_t at = (q >> 1) * 16384 + line_off + (((4 * (q & 1) + sub) ^ s7) << 4);
+                        *reinterpret_cast<uint4*>(save_tile + sl.act_off(g) + at) = p8;
+                        if (has_lo) *reinterpret_cast<uint4*>(save_tile + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl) + at) = l8v;
+                    }
                 }
                 if (save && g != 8)
                     *reinterpret_cast<unsigned long long*>(save_tile + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;

@@ -328,6 +328,17 @@ field_fwd_dual_kernel(const FwdArgs a) {
                             *reinterpret_cast<uint4*>(ln + 16384 + (((4 + sub) ^ s7) << 4)) = q8d;
                         }
                         if (g != 8) *reinterpret_cast<unsigned long long*>(save_tile_t + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
+                        if (g == 7 || g == 9 || g == 12) {
+                            // residual image of a layer that feeds a head: same place as in the image proper (of layer 9
+                            // only the dir half, quarters 0-1)
+                            uint8_t* lo = save_tile_t + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl) + line_off;
+                            *reinterpret_cast<uint4*>(lo + ((sub ^ s7) << 4)) = residual_chunk(sH, row, 2 * sub, q8a);
+                            *reinterpret_cast<uint4*>(lo + (((4 + sub) ^ s7) << 4)) = residual_chunk(sH + 16384, row, 2 * sub, q8b);
+                            if (g == 7) {
+                                *reinterpret_cast<uint4*>(lo + 16384 + ((sub ^ s7) << 4)) = residual_chunk(sH + 2 * 16384, row, 2 * sub, q8c);
+                                *reinterpret_cast<uint4*>(lo + 16384 + (((4 + sub) ^ s7) << 4)) = residual_chunk(sH + 3 * 16384, row, 2 * sub, q8d);
+                            }
+                        }
                     }
                     // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                     const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));

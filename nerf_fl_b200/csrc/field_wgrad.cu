@@ -10,8 +10,11 @@
 // across CTAs in proportion to its byte traffic (the kernel is HBM-bound: 48 KB of operands per 512 tensor
 // cycles).  A CTA keeps its (128 x <=256) fp32 partial in TMEM over its whole tile range, and flushes it once
 // (times 1/scale) with fp32 atomics.  Bias gradients ride along as one more N=16 MMA per k-step against a
-// constant block of ones; head-weight gradients are units whose M side is the head's input activation and
-// whose N side is the dpre block.
+// constant block of ones; head-weight gradients are units whose M side is the head's input activation -- its
+// e4m3 image AND the e4m3 image of what that left over, two MMAs into one accumulator -- and whose N side is the
+// dpre block (three e5m2 terms per head, summed at the flush): ~8 significant bits on either side, because the heads
+// are fp32 in the forward and a single 8-bit contraction there is the largest error of the whole 8-bit scheme
+// (tools/fp8_wgrad_study.py heads).
 #include "field_dev.cuh"
 #include <algorithm>
 
@@ -31,10 +34,11 @@ struct WUnit {
     uint32_t m_off, n_off;        // byte offsets inside the tile record
     uint8_t m_src, n_src;         // 0 = dgrad workspace, 1 = forward save buffer
     uint8_t n_blocks;             // N side 128-column blocks (1..2)
-    uint16_t n_mma;               // MMA N (a multiple of 16 up to 256; 16 for head units)
+    uint16_t n_mma;               // MMA N (a multiple of 16 up to 256; 32 for head units)
     uint8_t m_e5m2;               // 1: M side is a dZ image (e5m2), N side e4m3; 0: head unit, M side e4m3, N side e5m2
     uint8_t ones;                 // also accumulate sum_p dZ[p, m] (bias gradient)
-    uint8_t head_lo, head_hi;     // head unit: D[m][n], n in [head_lo, head_hi) -> head_out[n][m_base + m]
+    uint8_t head_lo, head_hi;     // head unit: D[m][n] + D[m][9+n] + D[m][18+n], n in [head_lo, head_hi) -> head_out[n][m_base + m]
+    uint32_t lo_off;              // head unit: the residual image of the M side (forward save buffer), staged behind the dpre block
     uint16_t n_valid;             // valid N columns (e.g. 63 of 64 for the encoded-xyz block)
     uint16_t m_base;              // first output row (normal) / first head column (head unit)
     uint16_t n_base;              // first output column
@@ -76,6 +80,7 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
     const uint8_t* m_base = (u.m_src ? a.saved : a.dz) + u.m_off;
     const uint8_t* n_base = (u.n_src ? a.saved : a.dz) + u.n_off;
     const uint32_t n_bytes = static_cast<uint32_t>(u.n_blocks) * 16384u;      // whole blocks travel, the MMA reads n_mma columns
+    const bool head = u.head_hi > u.head_lo;
 
     if (threadIdx.x == 0) {
         if ((ptx::smem_u32(smem) & 1023u) != 0) {
@@ -100,10 +105,12 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
             for (int t = t0; t < t1; ++t, ++it) {
                 const uint32_t s = it % kWgStages;
                 ptx::mbar_wait(&bar_empty[s], ((it / kWgStages) & 1u) ^ 1u);
-                ptx::mbar_arrive_expect_tx(&bar_full[s], kWgMBytes + n_bytes);
+                ptx::mbar_arrive_expect_tx(&bar_full[s], kWgMBytes + n_bytes + (head ? 16384u : 0u));
                 uint8_t* st = smem + s * kWgStageBytes;
                 ptx::bulk_g2s(st, m_base + static_cast<size_t>(t) * m_stride, kWgMBytes, &bar_full[s]);
                 ptx::bulk_g2s(st + kWgMBytes, n_base + static_cast<size_t>(t) * n_stride, n_bytes, &bar_full[s]);
+                if (head)
+                    ptx::bulk_g2s(st + kWgMBytes + 16384, a.saved + u.lo_off + static_cast<size_t>(t) * a.save_tile_bytes, 16384, &bar_full[s]);
             }
         }
         __syncwarp();
@@ -124,6 +131,9 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
                     const uint64_t ad = ptx::umma_desc_sw128(ma + j * 4096, 16384, 1024);
                     ptx::umma_f8(tmem, ad, ptx::umma_desc_sw128(na + j * 4096, 16384, 1024), idesc, (it | j) != 0);
                     if (u.ones) ptx::umma_f8(tmem + 256, ad, ptx::umma_desc_sw128(ones, 16384, 1024), idesc1, (it | j) != 0);
+                    if (head)      // residual image (second half of the N slot) against the same dpre block, its own accumulator
+                        ptx::umma_f8(tmem + 32, ptx::umma_desc_sw128(na + 16384 + j * 4096, 16384, 1024),
+                                     ptx::umma_desc_sw128(na + j * 4096, 16384, 1024), idesc, (it | j) != 0);
                 }
                 ptx::umma_commit(&bar_empty[s]);
             }
@@ -139,12 +149,17 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
         ptx::mbar_wait(bar_done, 0);
         ptx::tc_fence_after_sync();
         if (u.head_hi > u.head_lo) {
-            uint32_t v[32];
+            uint32_t v[32], w[32];              // image proper / residual image (times kLoScale)
             ptx::tmem_ld32(tlane, v);
+            ptx::tmem_ld32(tlane + 32, w);
             ptx::tmem_ld_wait();
 #pragma unroll
             for (int n = 0; n < 9; ++n)
-                if (n >= u.head_lo && n < u.head_hi) atomicAdd(a.head_out[n] + u.m_base + m, __uint_as_float(v[n]) * inv);
+                if (n >= u.head_lo && n < u.head_hi) {
+                    const float hi = (__uint_as_float(v[n]) + __uint_as_float(v[9 + n])) + __uint_as_float(v[18 + n]);
+                    const float lo = (__uint_as_float(w[n]) + __uint_as_float(w[9 + n])) + __uint_as_float(w[18 + n]);
+                    atomicAdd(a.head_out[n] + u.m_base + m, fmaf(lo, 1.0f / kLoScale, hi) * inv);
+                }
         } else {
             float* orow = u.out + static_cast<size_t>(u.m_base + m) * u.ld + u.n_base;
             for (int c0 = 0; c0 < u.n_valid; c0 += 32) {
@@ -221,15 +236,17 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
             add(static_cast<uint32_t>(dl.dz_off(gq)), 0, n_off, 1, 128, 128, true, g->tenc_w[gq - 9], kHalf, 0, 0, g->tenc_b[gq - 9]);
         }
     }
-    // heads: M side = the head's input activation (e4m3), N side = dpre block (e5m2, 16 columns read)
+    // heads: M side = the head's input activation (e4m3 image + e4m3 residual image), N side = dpre block (e5m2, 32 columns read)
     const uint32_t dpre = static_cast<uint32_t>(dl.dpre_off());
-    auto add_head = [&](uint32_t m_off, int m_base_, int lo, int hi) {
-        WUnit& u = add(m_off, 1, dpre, 0, 16, 16, false, nullptr, 0, m_base_, 0, nullptr);
-        u.m_e5m2 = 0; u.head_lo = static_cast<uint8_t>(lo); u.head_hi = static_cast<uint8_t>(hi);
+    const int nl = fs.n_layers(mode);
+    auto add_head = [&](uint32_t m_off, uint32_t lo_off, int m_base_, int lo, int hi) {
+        WUnit& u = add(m_off, 1, dpre, 0, 32, 32, false, nullptr, 0, m_base_, 0, nullptr);
+        u.m_e5m2 = 0; u.head_lo = static_cast<uint8_t>(lo); u.head_hi = static_cast<uint8_t>(hi); u.lo_off = lo_off;
     };
-    for (int mh = 0; mh < 2; ++mh) add_head(static_cast<uint32_t>(sl.act_off(7)) + mh * 16384u, mh * 128, 0, 1);
-    add_head(static_cast<uint32_t>(sl.act_off(9)), 0, 1, 4);
-    if (transient) add_head(static_cast<uint32_t>(sl.act_off(12)), 0, 4, 9);
+    for (int mh = 0; mh < 2; ++mh)
+        add_head(static_cast<uint32_t>(sl.act_off(7)) + mh * 16384u, static_cast<uint32_t>(sl.lo_off(0, nl)) + mh * 16384u, mh * 128, 0, 1);
+    add_head(static_cast<uint32_t>(sl.act_off(9)), static_cast<uint32_t>(sl.lo_off(1, nl)), 0, 1, 4);
+    if (transient) add_head(static_cast<uint32_t>(sl.act_off(12)), static_cast<uint32_t>(sl.lo_off(2, nl)), 0, 4, 9);
     a.head_out[0] = g->sigma_w;
     for (int i = 0; i < 3; ++i) a.head_out[1 + i] = g->rgb_w + i * kHalf;
     if (transient) {
@@ -241,7 +258,10 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
     // split every unit over points in proportion to its operand bytes per tile
     double cost[kWgMaxUnits], total = 0;
     int sp[kWgMaxUnits], cta = 0;
-    for (int i = 0; i < nu; ++i) { cost[i] = kWgMBytes + 16384.0 * a.units[i].n_blocks; total += cost[i]; }
+    for (int i = 0; i < nu; ++i) {
+        cost[i] = kWgMBytes + 16384.0 * a.units[i].n_blocks + (a.units[i].head_hi > a.units[i].head_lo ? 16384.0 : 0.0);
+        total += cost[i];
+    }
     const int budget = std::max(nu, std::min(kNumSMs, nu * n_tiles));      // one CTA per SM, never a second wave
     for (int i = 0; i < nu; ++i) { sp[i] = std::max(1, std::min(static_cast<int>(cost[i] / total * budget), n_tiles)); cta += sp[i]; }
     while (cta > budget) {                       // trim the unit with the least work per CTA

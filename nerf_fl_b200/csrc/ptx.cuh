@@ -379,6 +379,16 @@ __device__ __forceinline__ uint32_t cvt_e5m2x2(float lo, float hi) {
     asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
     return r;
 }
+// decode: two e4m3 in a 16-bit word -> two fp32 (exact); one e5m2 byte -> fp32 (e5m2 is the high byte of an fp16)
+__device__ __forceinline__ void dec_e4m3x2(uint32_t h, float& lo, float& hi) {
+    uint32_t r;
+    asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"(static_cast<uint16_t>(h)));
+    const float2 f = __half22float2(*reinterpret_cast<__half2*>(&r));
+    lo = f.x; hi = f.y;
+}
+__device__ __forceinline__ float dec_e5m2(uint32_t b) {
+    return __half2float(__ushort_as_half(static_cast<unsigned short>((b & 0xFFu) << 8)));
+}
 // four fp32 -> one 32-bit word of four 8-bit floats, element 0 in the low byte
 template <bool kRelu>
 __device__ __forceinline__ uint32_t pack4_e4m3(float a, float b, float c, float d) {
@@ -386,6 +396,15 @@ __device__ __forceinline__ uint32_t pack4_e4m3(float a, float b, float c, float 
 }
 __device__ __forceinline__ uint32_t pack4_e5m2(float a, float b, float c, float d) {
     return cvt_e5m2x2(a, b) | (cvt_e5m2x2(c, d) << 16);
+}
+// residual word: e4m3 of scale * (x - value of the e4m3 word w already taken from x), four at a time
+template <bool kRelu>
+__device__ __forceinline__ uint32_t residual4_e4m3(uint32_t w, float a, float b, float c, float d, float scale) {
+    float h0, h1, h2, h3;
+    dec_e4m3x2(w & 0xFFFFu, h0, h1);
+    dec_e4m3x2(w >> 16, h2, h3);
+    if (kRelu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); c = fmaxf(c, 0.0f); d = fmaxf(d, 0.0f); }
+    return pack4_e4m3<false>((a - h0) * scale, (b - h1) * scale, (c - h2) * scale, (d - h3) * scale);
 }
 // 32-byte global store (STG.256, sm_100): dst must be 32 B aligned
 __device__ __forceinline__ void st_global_256(void* dst, const uint4& a, const uint4& b) {

@@ -330,14 +330,16 @@ def mlp_fwd(desc, packed, *, n_rays, S, mode, ray_bias=None, rays=None, z=None, 
 def field_traffic_bytes_per_point(kind: str, fine: bool) -> float:
     """HBM bytes per sample point one field kernel launch moves by design, from the library's own size queries (the
     per-tile record sizes of nwb_mlp_save_bytes / nwb_mlp_bwd_workspace_bytes): fwd (saving) writes the saved record;
-    dgrad writes the dZ record and reads the sign masks; wgrad reads both records (without the masks) once."""
+    dgrad writes the dZ record and reads the sign masks; wgrad reads both records (without the masks) once, and the
+    dpre block once per head unit."""
     desc = field_desc(63, 27, 48 if fine else 0, 16 if fine else 0)
     mode = (L.NWB_MLP_TRANSIENT if fine else 0) | L.NWB_MLP_SAVE
     n = 128 * 1024                                   # many tiles: the workspace's 256-byte header vanishes
     save = mlp_save_bytes(desc, n, mode) / float(n)
     ws = mlp_bwd_workspace_bytes(desc, n, mode & ~L.NWB_MLP_SAVE) / float(n)
     masks = 13 * 4096 / 128.0
-    return {"fwd": save, "dgrad": ws + masks, "wgrad": (save - masks) + ws}[kind]
+    dpre_again = ((4 if fine else 3) - 1) * 128.0     # every head unit of wgrad reads the dpre block (16 KB per tile)
+    return {"fwd": save, "dgrad": ws + masks, "wgrad": (save - masks) + ws + dpre_again}[kind]
 
 
 def mlp_fwd_select(gen: int) -> None:

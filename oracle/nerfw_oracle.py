@@ -17,6 +17,8 @@ Parameters are passed as plain ``state_dict``-style dicts using the reference's 
 """
 from __future__ import annotations
 
+import math
+
 import torch
 import torch.nn.functional as F
 
@@ -238,9 +240,11 @@ def render_rays(p_coarse: dict, p_fine: dict | None, emb_a: torch.Tensor | None,
                 test_time: bool = False, n_freq_xyz: int = 10, n_freq_dir: int = 4,
                 encode_a: bool = False, encode_t: bool = False, beta_min: float = 0.03,
                 rng: dict | None = None, a_embedded=None, t_embedded=None,
-                output_transient: bool = True, view_dir=None, bf16_operands: bool = False) -> dict:
+                output_transient: bool = True, view_dir=None, bf16_operands: bool = False,
+                wgrad8: bool = False) -> dict:
     """Functional restatement of render_rays.  ``bf16_operands=True`` swaps the field for
-    field_forward_bf16 (the operand-rounding model of the tensor-core path, bottom of this file).  ``rng`` may hold pre-drawn tensors
+    field_forward_bf16 (the operand-rounding model of the tensor-core path, bottom of this file), and ``wgrad8=True`` on top of it
+    for field_forward_q8 (same forward; weight gradients through the 8-bit images the kernels keep).  ``rng`` may hold pre-drawn tensors
     ``perturb_rand`` (N,Ns) U[0,1), ``noise_coarse`` (N,Ns) N(0,1), ``u`` (N,Ni) U[0,1),
     ``noise_fine`` (N,Ns+Ni) N(0,1); anything missing is drawn here in the reference's order
     (SURVEY.md §3.3), so under one ``torch.manual_seed`` this matches the reference bit for bit.
@@ -266,9 +270,9 @@ def render_rays(p_coarse: dict, p_fine: dict | None, emb_a: torch.Tensor | None,
         if bf16_operands:
             so = typ == "coarse" and test_time
             da = dir_e if a_e is None else torch.cat([dir_e, a_e], 1)
-            raw = field_forward_bf16(p, xe, None if so else da.repeat_interleave(S, dim=0),
-                                     t_e.repeat_interleave(S, dim=0) if transient else None, transient,
-                                     sigma_only=so)
+            fld = field_forward_q8 if wgrad8 else field_forward_bf16
+            raw = fld(p, xe, None if so else da.repeat_interleave(S, dim=0),
+                      t_e.repeat_interleave(S, dim=0) if transient else None, transient, sigma_only=so)
         elif typ == "coarse" and test_time:                                             # :103-111
             raw = field_forward(p, xe, sigma_only=True)
         else:                                                                           # :112-139
@@ -374,6 +378,125 @@ def field_forward_bf16(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor | None, t
         out += [torch.sigmoid(_lin(p, "transient_rgb.0", ht)), F.softplus(_lin(p, "transient_sigma.0", ht)),
                 F.softplus(_lin(p, "transient_beta.0", ht))]
     return torch.cat(out, 1)
+
+
+# ----------------------------------------------------------------------------------------------
+# Operand-rounding model of the 8-bit weight-gradient path (nerf_fl_b200/csrc/field.cuh "8-bit images").
+# The forward is field_forward_bf16's.  In the backward the cotangent chain stays bf16 (dx = bf16(dy) . bf16(W)),
+# but every WEIGHT / BIAS gradient of a tensor-core layer contracts the two images the kernels keep in HBM:
+#   dW = e5m2(s dy)^T . e4m3(bf16 x) / s,   db = sum e5m2(s dy) / s,
+# s = one power of two per backward pass, 2^(DZ_TOP - ceil(log2 amax|d_raw|)).  The fp32 heads keep their fp32
+# forward and dgrad; their weight gradient contracts a three-term e5m2 expansion of s dpre with the e4m3 image of the
+# head's input plus the e4m3 image of 16 x what that left over.  Per-ray operands (view direction, embeddings, the biases folded into them) never
+# pass through an image: plain fp32 autograd.  Test infrastructure, like everything else in this file: the kernels
+# must agree with THIS model tightly, and this model's distance from the fp32 functions above is what the north-star
+# tolerance has to cover.
+# ----------------------------------------------------------------------------------------------
+DZ_TOP = 10
+LO_SCALE = 16.0       # the residual image of a head's input is stored times 16 (field.cuh kLoScale)
+
+
+def _e4m3(x: torch.Tensor) -> torch.Tensor:          # cvt.rn.satfinite.e4m3x2.f32
+    return x.clamp(-448.0, 448.0).to(torch.float8_e4m3fn).float()
+
+
+def _e5m2(x: torch.Tensor) -> torch.Tensor:          # cvt.rn.satfinite.e5m2x2.f32
+    return x.clamp(-57344.0, 57344.0).to(torch.float8_e5m2).float()
+
+
+def _expand(x: torch.Tensor, rnd, terms: int) -> torch.Tensor:
+    """sum of `terms` 8-bit numbers, each the rounding of what the earlier ones left over"""
+    tot = torch.zeros_like(x)
+    for _ in range(terms):
+        tot = tot + rnd(x - tot)
+    return tot
+
+
+class DzScale:
+    """the pass's scale, set by a hook on the field's output cotangent (field_bwd.cu dz_amax_kernel)"""
+
+    def __init__(self):
+        self.s = 1.0
+
+    def set_from(self, d_raw: torch.Tensor) -> None:
+        amax = d_raw.abs().max().item()
+        if amax == 0.0 or not math.isfinite(amax):
+            self.s = 1.0
+            return
+        m, e = math.frexp(amax)                      # amax = m 2^e, 0.5 <= m < 1: ceil(log2 amax) = e, or e - 1 at a power of two
+        self.s = 2.0 ** (DZ_TOP - (e - 1 if m == 0.5 else e))
+
+
+class _Lin8(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, W, b, st):
+        xb, Wb = x.to(torch.bfloat16).float(), W.to(torch.bfloat16).float()
+        ctx.save_for_backward(xb, Wb)
+        ctx.st, ctx.has_b = st, b is not None
+        y = xb @ Wb.t()
+        return y + b if b is not None else y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xb, Wb = ctx.saved_tensors
+        s = ctx.st.s
+        dx = dy.to(torch.bfloat16).float() @ Wb
+        q = _e5m2(dy * s) / s
+        return dx, q.t() @ _e4m3(xb), (q.sum(0) if ctx.has_b else None), None
+
+
+class _Head8(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, W, b, st):
+        ctx.save_for_backward(h, W)
+        ctx.st = st
+        return F.linear(h, W, b)
+
+    @staticmethod
+    def backward(ctx, dy):
+        h, W = ctx.saved_tensors
+        s = ctx.st.s
+        hi = _e4m3(h)
+        dW = (_expand(dy * s, _e5m2, 3) / s).t() @ (hi + _e4m3((h - hi) * LO_SCALE) / LO_SCALE)
+        return dy @ W, dW, dy.sum(0), None
+
+
+def field_forward_q8(p: dict, xyz: torch.Tensor, dir_a: torch.Tensor | None, tt: torch.Tensor | None,
+                     output_transient: bool, sigma_only: bool = False) -> torch.Tensor:
+    st = DzScale()
+
+    def lin(n, x, cols=None, bias=True):
+        W = p[n + ".weight"]
+        return _Lin8.apply(x, W if cols is None else W[:, cols[0]:cols[1]], p[n + ".bias"] if bias else None, st)
+
+    def head(n, h):
+        return _Head8.apply(h, p[n + ".weight"], p[n + ".bias"], st)
+
+    h = xyz
+    for i in range(8):
+        if i == 4:
+            h = torch.cat([xyz, h], 1)
+        h = torch.relu(lin(f"xyz_encoding_{i + 1}.0", h))
+    sigma = F.softplus(head("static_sigma.0", h))
+    if sigma_only:
+        res = sigma
+    else:
+        feat = lin("xyz_encoding_final", h)
+        Wd = p["dir_encoding.0.weight"]
+        hd = torch.relu(lin("dir_encoding.0", feat, (0, 256), bias=False) + F.linear(dir_a, Wd[:, 256:], p["dir_encoding.0.bias"]))
+        out = [torch.sigmoid(head("static_rgb.0", hd)), sigma]
+        if output_transient:
+            Wt = p["transient_encoding.0.weight"]
+            ht = torch.relu(lin("transient_encoding.0", feat, (0, 256), bias=False) +
+                            F.linear(tt, Wt[:, 256:], p["transient_encoding.0.bias"]))
+            for j in (2, 4, 6):
+                ht = torch.relu(lin(f"transient_encoding.{j}", ht))
+            out += [torch.sigmoid(head("transient_rgb.0", ht)), F.softplus(head("transient_sigma.0", ht)),
+                    F.softplus(head("transient_beta.0", ht))]
+        res = torch.cat(out, 1)
+    if res.requires_grad:
+        res.register_hook(st.set_from)
+    return res
 
 
 # ---- data formats either side of render_rays (SURVEY.md 8f-3/4): rays, uint8 images, PSNR -------------------------

@@ -336,7 +336,8 @@ def _relerr(got, ref):
                                                      (130, 96, True, 1.0)])
 def test_field_backward_vs_oracle(n_rays, S, transient, scale):
     """Every parameter / embedding gradient of one field evaluation, with random cotangents, against
-    autograd through (i) the oracle's bf16-operand model of the kernel and (ii) the plain fp32 oracle.
+    autograd through (i) the oracle's operand-rounding model of the kernels (bf16 GEMM operands, 8-bit images in the
+    weight-gradient contraction: O.field_forward_q8) and (ii) the plain fp32 oracle.
     Per-sample gradients of a ReLU net are discontinuous in the forward's rounding (a gate whose
     pre-activation sits within 2^-9 of zero opens in one forward and not the other), so with bf16
     operands the fp32 comparison is bounded by gate noise, not by the kernel: (i) is the tight check,
@@ -359,7 +360,7 @@ def test_field_backward_vs_oracle(n_rays, S, transient, scale):
         dir_a = torch.cat([O.posenc(rays[:, 3:6], 4).repeat_interleave(S, 0), ea_o[ts].repeat_interleave(S, 0)], -1)
         tt = et_o[ts].repeat_interleave(S, 0) if transient else None
         if emulate:
-            raw_o = O.field_forward_bf16(sd_o, x_e, dir_a, tt, transient)
+            raw_o = O.field_forward_q8(sd_o, x_e, dir_a, tt, transient)
         else:
             raw_o = O.field_forward(sd_o, torch.cat([x_e, dir_a] + ([tt] if transient else []), -1), in_dir_a=27 + 48,
                                     output_transient=transient)

@@ -134,3 +134,55 @@ def test_render_rays_gradients(golden, scale):
         assert abs(gr.norm().item() - ref_norm.item()) <= 1e-4 * max(ref_norm.item(), 1e-6) + 1e-9, k
         ref_head = g[f"{tag}/grad_head/{k}"]
         close(gr.flatten()[:32], ref_head, 1e-5 * max(1.0, ref_head.abs().max().item()))
+
+
+def test_q8_model_forward_is_the_bf16_models_and_its_gradient_meets_the_bar(golden):
+    """O.field_forward_q8 models the 8-bit images of the weight-gradient kernels: same forward as the bf16-operand
+    model bit for bit, and on the golden training step its whole-model gradient stays within the north-star 1e-2 of
+    the fp32 functions that are pinned to the reference above."""
+    g = golden("render_rays")
+    rays, ts, rng, ea, et = _e2e_inputs(g)
+
+    def run(bf16, q8):
+        pc = syn.make_field_params(41, "coarse")
+        pf = syn.make_field_params(42, "fine", True, True)
+        ea_o, et_o = ea.clone(), et.clone()
+        named = [(f"coarse.{k}", v) for k, v in pc.items()] + [(f"fine.{k}", v) for k, v in pf.items()] \
+            + [("emb_a", ea_o), ("emb_t", et_o)]
+        for _, v in named:
+            v.requires_grad_(True)
+        out = O.render_rays(pc, pf, ea_o, et_o, rays, ts, n_samples=64, n_importance=64, perturb=1.0, noise_std=0.0,
+                            white_back=True, encode_a=True, encode_t=True, beta_min=0.1, rng=rng, bf16_operands=bf16,
+                            wgrad8=q8)
+        loss = sum(O.nerfw_loss(out, g["targets"]).values())
+        gr = torch.autograd.grad(loss, [v for _, v in named])
+        return loss.item(), {k: x.double() for (k, _), x in zip(named, gr)}
+
+    l32, g32 = run(False, False)
+    lbf, gbf = run(True, False)
+    lq8, gq8 = run(True, True)
+    assert lq8 == lbf
+
+    def rel(a, b, keys):
+        return (sum(((a[k] - b[k]).norm() ** 2).item() for k in keys) / sum((b[k].norm() ** 2).item() for k in keys)) ** 0.5
+
+    keys = list(g32)
+    for net in ("", "coarse.", "fine."):
+        ks = [k for k in keys if k.startswith(net)]
+        assert rel(gq8, g32, ks) <= 6e-3, (net, rel(gq8, g32, ks))
+        assert rel(gq8, g32, ks) <= rel(gbf, g32, ks) + 3e-3, (net, rel(gq8, g32, ks), rel(gbf, g32, ks))
+
+
+def test_q8_scale_is_a_power_of_two_that_puts_amax_at_or_below_the_top():
+    st = O.DzScale()
+    for amax, want in ((1.0, 2.0 ** 10), (1.5, 2.0 ** 9), (2.0, 2.0 ** 9), (3e-5, 2.0 ** 25), (0.0, 1.0), (float("inf"), 1.0)):
+        st.set_from(torch.tensor([amax, -amax / 2]))
+        assert st.s == want, (amax, st.s)
+        if 0 < amax < float("inf"):
+            assert 2.0 ** (O.DZ_TOP - 1) < amax * st.s <= 2.0 ** O.DZ_TOP
+    # image + scaled residual image carry ~7 bits down to small activations; three e5m2 terms carry ~9 bits
+    x = torch.rand(4096) * 4 + 2.0 ** -5
+    hi = O._e4m3(x)
+    assert (((hi + O._e4m3((x - hi) * O.LO_SCALE) / O.LO_SCALE) - x).abs() / x).max().item() <= 2.0 ** -7
+    y = torch.randn(4096) * 300
+    assert ((O._expand(y, O._e5m2, 3) - y).abs() / y.abs()).max().item() <= 2.0 ** -8

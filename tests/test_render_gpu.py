@@ -133,7 +133,7 @@ def _grad_check(scale):
             v.requires_grad_(True)
         oout = O.render_rays(pc, pf, ea_o, et_o, rays.cpu(), ts.cpu(), n_samples=64, n_importance=64, perturb=1.0,
                              noise_std=0.0, white_back=True, encode_a=True, encode_t=True, beta_min=0.1, rng=rng_c,
-                             bf16_operands=bf16)
+                             bf16_operands=bf16, wgrad8=bf16)
         oloss = sum(O.nerfw_loss(oout, tgt).values())
         return oloss.item(), {k: gr.double() for (k, _), gr in zip(onamed, torch.autograd.grad(oloss, [v for _, v in onamed]))}
 
@@ -279,7 +279,7 @@ def test_nerf_module_backward_and_state_dict():
     xo = x.clone().requires_grad_(True)
     (O.field_forward(sd, xo, in_dir_a=75) * d).sum().backward()
     sdb = {k: v.clone().requires_grad_(True) for k, v in syn.make_field_params(23, "fine", True, True).items()}
-    (O.field_forward_bf16(sdb, x[:, :63], x[:, 63:138], x[:, 138:], True) * d).sum().backward()
+    (O.field_forward_q8(sdb, x[:, :63], x[:, 63:138], x[:, 138:], True) * d).sum().backward()
     # random per-sample cotangents on 200 points: ReLU gates within bf16 rounding of zero differ between an fp32
     # and a bf16-operand forward, so fp32 bounds size and direction and the operand-rounding model is the tight check
     for k, p in m.named_parameters():
