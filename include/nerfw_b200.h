@@ -111,7 +111,7 @@ int nwb_composite_bwd(const float* raw, int C, const float* z, const float* nois
  * models/rendering.py:96-139.  W=256, D=8, skips=[4] (the only shape the reference ever builds).
  * ---------------------------------------------------------------------------------------- */
 typedef struct nwb_field_desc {
-    int in_xyz;        /* 3+6*N_emb_xyz, <= 64 (N_emb_xyz <= 10)     nerf.py:83  */
+    int in_xyz;        /* 3+6*N_emb_xyz, <= 128 (> 64: one-tile kernel) nerf.py:83  */
     int in_dir;        /* 3+6*N_emb_dir                              nerf.py:83  */
     int in_a;          /* appearance width, 0 = no encode_appearance nerf.py:84  */
     int in_t;          /* transient width,  0 = no encode_transient  nerf.py:85  */

@@ -10,7 +10,9 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnerfw_b200.so")
+# NWB_LIB_PATH: a differently-built libnerfw_b200.so (tools/build_variant.py: A/B runs of compile-time kernel options
+# inside one GPU session); read once, at import
+LIB_PATH = os.environ.get("NWB_LIB_PATH") or os.path.join(_HERE, "libnerfw_b200.so")
 
 NWB_COMP_TRANSIENT, NWB_COMP_WHITE_BACK, NWB_COMP_TEST_TIME, NWB_COMP_COARSE = 1, 2, 4, 8
 NWB_MLP_SIGMA_ONLY, NWB_MLP_TRANSIENT, NWB_MLP_SAVE = 1, 2, 4

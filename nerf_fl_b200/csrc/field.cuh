@@ -75,8 +75,8 @@ struct ConstOff {
 
 inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
     NWB_REQUIRE(d != nullptr, "field desc is null");
-    NWB_REQUIRE(d->in_xyz >= 3 && d->in_xyz <= 64,
-                "in_channels_xyz = %d unsupported (this build stages one 64-column xyz block; N_emb_xyz <= 10)",
+    NWB_REQUIRE(d->in_xyz >= 3 && d->in_xyz <= 128,
+                "in_channels_xyz = %d unsupported (at most two 64-column xyz blocks: N_emb_xyz <= 20 explicit, <= 15 in-kernel)",
                 d->in_xyz);
     NWB_REQUIRE(d->in_dir >= 3 && d->in_dir <= 256 && d->in_a >= 0 && d->in_a <= 256 && d->in_t >= 0 && d->in_t <= 256,
                 "unsupported dir/appearance/transient widths");

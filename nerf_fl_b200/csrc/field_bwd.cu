@@ -27,6 +27,15 @@ constexpr int kBOffW = kBOffD + 65536;
 constexpr int kBOffBar = kBOffW + kBNumStages * kBStageBytes;
 constexpr int kBwdSmem = kBOffBar + 256;
 
+// Waits of the single-thread roles.  ncu (profiles/r02e): 55 % of all warp-instructions this kernel issued were spin-wait
+// loops of the producer / MMA threads and of the epilogue warps waiting for an accumulator -- on schedulers they share
+// with the working epilogue warps of BOTH resident CTAs.  try_wait with a suspend-time hint parks the warp instead.
+#ifdef NWB_BWD_SPIN
+#define NWB_BWD_WAIT_A(addr, par) ptx::mbar_wait_a(addr, par)
+#else
+#define NWB_BWD_WAIT_A(addr, par) ptx::mbar_wait_sleepy_a(addr, par)
+#endif
+
 struct BwdArgs {
     FieldShape fs;
     const uint8_t* packed;
@@ -160,7 +169,7 @@ field_dgrad_kernel(const BwdArgs a) {
                     const int kshift = ((g == 4) ? fs.kx : 0) + static_cast<int>(rank) * KH;   // layer 4: skip the xyz slab
                     for (int c = 0; c < NC; ++c, ++it) {
                         const uint32_t s = it % kBNumStages;
-                        ptx::mbar_wait(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
+                        ptx::mbar_wait_sleepy(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
                         ptx::mbar_arrive_expect_tx(&bar_full[s], static_cast<uint32_t>(KH) * kBChunkBytes);
                         for (int kl = 0; kl < KH; ++kl)
                             ptx::bulk_g2s(sW + s * kBStageBytes + kl * kBChunkBytes,
@@ -182,7 +191,7 @@ field_dgrad_kernel(const BwdArgs a) {
             uint32_t it = 0, ev = 0;
             for (int pair = pair0; pair < n_pairs; pair += pair_step) {
                 for (int g = nl - 1; g >= 1; --g) {
-                    ptx::mbar_wait_a(act_a, ev & 1u);
+                    NWB_BWD_WAIT_A(act_a, ev & 1u);
                     ++ev;
                     ptx::tc_fence_after_sync();
                     NWB_BTRACE(pair == pair0, g * 8 + 0);      // dZ_g seen by the MMA thread
@@ -191,7 +200,7 @@ field_dgrad_kernel(const BwdArgs a) {
                     const uint32_t dcol = (g == 10) ? 128u : 0u;
                     for (int c = 0; c < NC; ++c, ++it) {
                         const uint32_t s = it % kBNumStages;
-                        ptx::mbar_wait_a(full_a + 8 * s, (it / kBNumStages) & 1u);
+                        NWB_BWD_WAIT_A(full_a + 8 * s, (it / kBNumStages) & 1u);
                         ptx::tc_fence_after_sync();
                         const uint32_t wb = wa + s * kBStageBytes;
                         const uint32_t ab = da + (c >> 1) * 16384 + (c & 1) * 64;
@@ -215,7 +224,7 @@ field_dgrad_kernel(const BwdArgs a) {
                     const int NC = fs.layer_n(g, a.mode) >> 5;
                     for (int c = 0; c < NC; ++c, ++it) {
                         const uint32_t s = it % kBNumStages;
-                        ptx::mbar_wait_a(full_a + 8 * s, (it / kBNumStages) & 1u);
+                        NWB_BWD_WAIT_A(full_a + 8 * s, (it / kBNumStages) & 1u);
                         ptx::mbar_arrive_cluster(full_leader + 8 * s);
                     }
                 }
@@ -320,7 +329,7 @@ field_dgrad_kernel(const BwdArgs a) {
                     for (int i = 0; i < 8; ++i) hwl[i] = __ldg(cst + ConstOff::sigma_w + i * 32 + lane);
                 }
                 if (g < nl - 1) {
-                    ptx::mbar_wait(bar_acc, acc_ev & 1u);
+                    ptx::mbar_wait_sleepy(bar_acc, acc_ev & 1u);
                     ++acc_ev;
                     ptx::tc_fence_after_sync();
                 }

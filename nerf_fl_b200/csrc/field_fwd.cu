@@ -194,11 +194,15 @@ __device__ __forceinline__ int layer_quarters(int g, bool transient) {
 }
 __device__ __forceinline__ int first_quarter(int g) { return g <= 10 ? 4 * g : 42 + 2 * (g - 11); }   // transient chain: 40, 42, 44
 __device__ __forceinline__ int out_slot(int g, int q) { return (first_quarter(g) + q) % kHSlots; }
-template <bool kSave>
+// kKx = 64-column blocks of the encoded-xyz operand.  kKx == 2 (in_channels_xyz up to 128: N_emb_xyz = 15 -> 93 columns,
+// models/nerf.py:83,121-128) keeps the second block where the third ring stage would be and runs a two-stage ring.
+template <bool kSave, int kKx>
 __global__ void __maxnreg__(kFwdMaxRegs)
 field_fwd_kernel(const FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
+    constexpr int kStages = (kKx == 2) ? kNumStages - 1 : kNumStages;
     uint8_t* sX = smem + kOffX;
+    uint8_t* sX1 = smem + kOffW + (kNumStages - 1) * kStageBytes;       // kKx == 2 only: columns 64..127 of the encoded xyz
     uint8_t* sH = smem + kOffH;                                          // six 16 KB K-block slots
     uint8_t* sW = smem + kOffW;
     float* s_part = reinterpret_cast<float*>(smem + kOffX);             // [3][5][128] head partial sums: sX is dead
@@ -222,7 +226,7 @@ field_fwd_kernel(const FwdArgs a) {
             printf("nwb: dynamic shared memory is not 1 KB aligned\n");
             __trap();
         }
-        for (int s = 0; s < kNumStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], kMmaWarps); }
+        for (int s = 0; s < kStages; ++s) { ptx::mbar_init(&bar_full[s], 1); ptx::mbar_init(&bar_empty[s], kMmaWarps); }
         ptx::mbar_init(bar_acc, kMmaWarps);
         for (int q = 0; q < 7; ++q) ptx::mbar_init(&bar_act[q], kEpiWarps);   // one arrival per epilogue warp
         ptx::fence_mbar_init();
@@ -256,7 +260,7 @@ field_fwd_kernel(const FwdArgs a) {
                         ptx::mbar_wait_sleepy(&bar_empty[s], ph ^ 1u);
                         ptx::mbar_arrive_expect_tx(&bar_full[s], bytes);
                         ptx::bulk_g2s(sW + s * kStageBytes, wsrc + static_cast<size_t>(kb) * PN * 128, bytes, &bar_full[s]);
-                        if (++s == kNumStages) { s = 0; ph ^= 1u; }
+                        if (++s == kStages) { s = 0; ph ^= 1u; }
                     }
                 }
             }
@@ -276,6 +280,7 @@ field_fwd_kernel(const FwdArgs a) {
             constexpr uint32_t idesc256 = ptx::umma_idesc_bf16(128, n256, false, false);
             constexpr uint32_t idesc128 = ptx::umma_idesc_bf16(128, n128, false, false);
             const uint32_t x_lo = ptx::umma_desc_lo(ptx::smem_u32(sX)), h_lo = ptx::umma_desc_lo(ptx::smem_u32(sH));
+            const uint32_t x1_lo = ptx::umma_desc_lo(ptx::smem_u32(sX1));
             const uint32_t w_lo = ptx::umma_desc_lo(ptx::smem_u32(sW));
             const uint32_t full_a = ptx::smem_u32(bar_full), empty_a = ptx::smem_u32(bar_empty);
             const uint32_t acc_a = ptx::smem_u32(bar_acc), act_a = ptx::smem_u32(bar_act);
@@ -299,11 +304,11 @@ field_fwd_kernel(const FwdArgs a) {
                     uint32_t a_lo = 0, b_lo = 0, empty_cur = 0;
                     // opens K-block kb: waits for its activation quarter and its weight stage, returns the descriptors
                     auto open_kb = [&](int kb, uint32_t& a_out, uint32_t& b_out, uint32_t& empty_out) {
-                        const bool is_x = (g == 0) || (g == 4 && kb == 0);
+                        const bool is_x = (g == 0) || (g == 4 && kb < kKx);
                         const int sl = is_x ? kSlotX : isl;
-                        a_out = is_x ? x_lo : h_lo + isl * 1024;                          // 16 KB >> 4
+                        a_out = is_x ? ((kKx == 2 && kb == 1) ? x1_lo : x_lo) : h_lo + isl * 1024;   // 16 KB >> 4
                         if (!is_x && ++isl == kHSlots) isl = 0;
-                        if (!(g == 4 && kb == 0)) {                                       // X was awaited by layer 0
+                        if (!is_x || (g == 0 && kb == 0)) {                               // X (all its blocks): awaited once, by layer 0
                             ptx::mbar_wait_a(act_a + 8 * sl, (act_par >> sl) & 1u);
                             act_par ^= 1u << sl;
                         }
@@ -311,7 +316,7 @@ field_fwd_kernel(const FwdArgs a) {
                         ptx::tc_fence_after_sync();
                         b_out = w_lo + s * (kStageBytes >> 4) + wrow_lo;
                         empty_out = empty_a + 8 * s;
-                        if (++s == kNumStages) { s = 0; ph ^= 1u; }
+                        if (++s == kStages) { s = 0; ph ^= 1u; }
                     };
                     open_kb(0, a_lo, b_lo, empty_cur);
                     NWB_TRACE(tile == 0 && lane == 0 && mw == 0, g * 16);                 // first operand ready
@@ -358,7 +363,7 @@ field_fwd_kernel(const FwdArgs a) {
             uint8_t* save_tile = save ? a.saved + static_cast<size_t>(tile) * a.save_tile_bytes : nullptr;
 
             // ---- encoded-xyz operand tile: this thread packs columns [16*sub, 16*sub+16) of its row ----
-            {
+            if constexpr (kKx == 1) {
                 float e[64];
 #pragma unroll
                 for (int c = 0; c < 64; ++c) e[c] = 0.0f;
@@ -423,6 +428,74 @@ field_fwd_kernel(const FwdArgs a) {
                 if (lane == 0) ptx::mbar_arrive(&bar_act[kSlotX]);
                 // saved 8-bit image of the encoded xyz: columns [16 sub, 16 sub + 16) = chunk `sub` of this row's line
                 if (save) *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
+            } else {
+                // two 64-column blocks (in_channels_xyz in (64, 128]): this thread owns columns [16 sub, 16 sub + 16) of
+                // EACH block; values go straight to their place (static register index, predicated on the owner) so that
+                // no 128-entry array is ever live
+                float v0[16], v1[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) { v0[j] = 0.0f; v1[j] = 0.0f; }
+                auto put = [&](int c, float val) {           // c is a compile-time constant after unrolling
+                    if (((c >> 4) & 3) == sub) { if (c < 64) v0[c & 15] = val; else v1[c & 15] = val; }
+                };
+                if (valid) {
+                    if (a.x_enc != nullptr) {
+                        const float* xr = a.x_enc + p * fs.in_xyz;
+#pragma unroll
+                        for (int c = 0; c < 128; ++c)
+                            if (c < fs.in_xyz && ((c >> 4) & 3) == sub) put(c, __ldg(xr + c));
+                    } else {
+                        const float* rr = a.rays + ray * a.ray_stride;
+                        const float zz = __ldg(a.z + p);
+                        float x3[3], sn[3], cs[3];
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) {
+                            x3[i] = __fadd_rn(__ldg(rr + i), __fmul_rn(__ldg(rr + 3 + i), zz));   // rendering.py:261
+                            put(i, x3[i]);
+                            sincosf(x3[i], &sn[i], &cs[i]);
+                        }
+                        // double-angle recurrences, re-anchored with an accurate sincosf at octave 8 (2^8 x is exact in fp32
+                        // and far below sincosf's slow-path threshold): the recurrence error stays <= ~2^7 ulp
+#pragma unroll
+                        for (int k = 0; k < 15; ++k) {
+                            if (k < a.n_freq_xyz) {
+                                if (k == 8) {
+#pragma unroll
+                                    for (int i = 0; i < 3; ++i) sincosf(256.0f * x3[i], &sn[i], &cs[i]);
+                                }
+#pragma unroll
+                                for (int i = 0; i < 3; ++i) {
+                                    put(3 + 6 * k + i, sn[i]);
+                                    put(6 + 6 * k + i, cs[i]);
+                                    const float s2 = 2.0f * sn[i] * cs[i];
+                                    const float c2 = fmaf(-2.0f * sn[i], sn[i], 1.0f);
+                                    sn[i] = s2; cs[i] = c2;
+                                }
+                            }
+                        }
+                    }
+                }
+                uint32_t pk0[8], pk1[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { pk0[j] = pack_bf16(v0[2 * j], v0[2 * j + 1]); pk1[j] = pack_bf16(v1[2 * j], v1[2 * j + 1]); }
+                *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub)) = make_uint4(pk0[0], pk0[1], pk0[2], pk0[3]);
+                *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk0[4], pk0[5], pk0[6], pk0[7]);
+                *reinterpret_cast<uint4*>(sX1 + ptx::image_chunk_off(row, 2 * sub)) = make_uint4(pk1[0], pk1[1], pk1[2], pk1[3]);
+                *reinterpret_cast<uint4*>(sX1 + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk1[4], pk1[5], pk1[6], pk1[7]);
+                ptx::fence_proxy_async_smem();
+                ptx::tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&bar_act[kSlotX]);
+                if (save) {
+                    // saved 8-bit image: ONE 128-column block; columns [16 sub, +16) = chunk sub, columns 64 + [16 sub, +16) = chunk 4 + sub
+                    uint4 x8, y8;
+                    x8.x = ptx::pack4_e4m3<false>(v0[0], v0[1], v0[2], v0[3]);     x8.y = ptx::pack4_e4m3<false>(v0[4], v0[5], v0[6], v0[7]);
+                    x8.z = ptx::pack4_e4m3<false>(v0[8], v0[9], v0[10], v0[11]);   x8.w = ptx::pack4_e4m3<false>(v0[12], v0[13], v0[14], v0[15]);
+                    y8.x = ptx::pack4_e4m3<false>(v1[0], v1[1], v1[2], v1[3]);     y8.y = ptx::pack4_e4m3<false>(v1[4], v1[5], v1[6], v1[7]);
+                    y8.z = ptx::pack4_e4m3<false>(v1[8], v1[9], v1[10], v1[11]);   y8.w = ptx::pack4_e4m3<false>(v1[12], v1[13], v1[14], v1[15]);
+                    *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
+                    *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + (((4 + sub) ^ s7) << 4)) = y8;
+                }
             }
 
             float sigma = 0.0f, rgb[3] = {0, 0, 0};
@@ -578,8 +651,8 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
     NWB_REQUIRE(packed && raw_out, "nwb_mlp_fwd: null pointer");
     NWB_REQUIRE((z != nullptr) != (x_enc != nullptr), "nwb_mlp_fwd: exactly one of z / x_enc must be given");
     NWB_REQUIRE(z == nullptr || (rays != nullptr && ray_stride >= 8), "nwb_mlp_fwd: z needs rays (stride >= 8)");
-    NWB_REQUIRE(z == nullptr || (fs.in_xyz == 3 + 6 * n_freq_xyz && n_freq_xyz <= 10),
-                "nwb_mlp_fwd: in_xyz must equal 3+6*n_freq_xyz with n_freq_xyz <= 10");
+    NWB_REQUIRE(z == nullptr || (fs.in_xyz == 3 + 6 * n_freq_xyz && n_freq_xyz <= 15),
+                "nwb_mlp_fwd: in_xyz must equal 3+6*n_freq_xyz with n_freq_xyz <= 15");
     const bool sigma_only = (mode & NWB_MLP_SIGMA_ONLY) != 0, transient = (mode & NWB_MLP_TRANSIENT) != 0;
     NWB_REQUIRE(!(sigma_only && transient), "nwb_mlp_fwd: sigma_only excludes transient");
     NWB_REQUIRE(!transient || fs.has_t(), "nwb_mlp_fwd: transient requested but the field has no transient head");
@@ -602,8 +675,10 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
 
     static bool configured[kMaxDevices] = {};
     NWB_CONFIGURE_ONCE(configured, {
-        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
-        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+        NWB_CUDA(cudaFuncSetAttribute(field_fwd_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
         NWB_CUDA(cudaFuncSetAttribute(field_fwd_dual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDSmem));
     });
@@ -615,7 +690,7 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
     const int gen = g_fwd_gen;                                      // nwb_mlp_fwd_select: 1 / 2 force a kernel
     constexpr int kRound = 4 * (kNumSMs / 2);
     int pair_tiles = a.n_tiles;                                     // tiles [0, pair_tiles) -> pair kernel
-    if (gen == 1) pair_tiles = 0;
+    if (gen == 1 || fs.kx == 2) pair_tiles = 0;                     // two xyz blocks do not fit the pair kernel's shared memory
     else if (gen != 2 && a.n_tiles % kRound != 0 && a.n_tiles % kRound <= kNumSMs) pair_tiles = a.n_tiles - a.n_tiles % kRound;
     if (pair_tiles > 0) {
         FwdArgs a2 = a;
@@ -628,8 +703,14 @@ extern "C" int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const fl
     }
     a.first_tile = pair_tiles;
     const int grid = std::min(a.n_tiles - a.first_tile, kNumSMs);
-    if (mode & NWB_MLP_SAVE) field_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
-    else field_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (fs.kx == 2) {
+        if (mode & NWB_MLP_SAVE) field_fwd_kernel<true, 2><<<grid, kFwdThreads, kFwdSmem, st>>>(a);
+        else field_fwd_kernel<false, 2><<<grid, kFwdThreads, kFwdSmem, st>>>(a);
+    } else {
+        if (mode & NWB_MLP_SAVE) field_fwd_kernel<true, 1><<<grid, kFwdThreads, kFwdSmem, st>>>(a);
+        else field_fwd_kernel<false, 1><<<grid, kFwdThreads, kFwdSmem, st>>>(a);
+    }
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }

@@ -21,6 +21,15 @@
 
 namespace nwb {
 
+// waits of the MMA-issuing / relay threads: parked with a suspend-time hint (default) or spinning (-DNWB_FWD_SPIN).
+// [B200, profiles/r02f_perf_*.log] 32 768-ray inference chunk: 4.71 ms parked vs 4.91 ms spinning (the spinning thread
+// shares a scheduler with four epilogue warps); no difference at 1024 rays.
+#ifdef NWB_FWD_SPIN
+#define NWB_FWD_WAIT_A(addr, par) ptx::mbar_wait_a(addr, par)
+#else
+#define NWB_FWD_WAIT_A(addr, par) ptx::mbar_wait_sleepy_a(addr, par)
+#endif
+
 constexpr int kDOffX = 0;                         // 2 x 16 KB
 constexpr int kDOffH = 32768;                     // 2 x 64 KB
 constexpr int kDStageBytes = 16384;               // this CTA's half of a weight K-block
@@ -33,6 +42,102 @@ static_assert(kDSmem <= 232448, "dual-tile forward exceeds the 227 KB shared-mem
 
 // first activation K-block (16 KB slot of the slot's H image) layer g reads, after the optional X block
 __device__ __forceinline__ int dual_in_slot0(int g) { return g == 10 ? 2 : 0; }
+
+
+// ---- one layer's epilogue for one slot, straight-line -------------------------------------------------------------
+// The quarter loop is fully unrolled and the layer kinds are template instances (dispatched once per (layer, slot) by
+// a switch), shared memory is addressed by 32-bit shared-space addresses: ncu counted 293 warp-instructions per
+// (warp, quarter) in the runtime-dispatched version (profiles/r02e_*), a third of them register moves, zeroing and
+// generic-address tests -- the kernel issues on 60 % of its scheduler slots, so instruction count is time.
+//   tacc    TMEM address of this thread's lane quadrant, slot and 16-column slice (quarter q adds 64 columns)
+//   bias_s  shared address of bias[16 sub] (quarter q adds 256 B); kRayBias: rbias = global per-ray bias + 16 sub
+//   hw_s    shared address of head 0's weights [16 sub] (head h adds 512 B -- every multi-head block has ld 128 --, quarter
+//           q adds 256 B); heads read quarters q < kHeadQ only
+//   img_s   shared address of the slot's activation image (quarter q = K-block q, 16 KB apart); off0 / off1 = this
+//           thread's two 16-byte chunks inside a K-block
+//   kSave:  p8[q] = the 16 activations as e4m3 (ReLU applied by the conversion); mlo / mhi = sign-mask entries of
+//           quarters 0-1 / 2-3 (16 bits each, relu_mask_bit order)
+template <bool kRelu, int kHeads, int kHeadQ, int kNQ, bool kRayBias, bool kSave>
+__device__ __forceinline__ void dual_layer_epi(uint32_t tacc, uint32_t bias_s, const float* __restrict__ rbias, uint32_t hw_s,
+                                               uint32_t img_s, uint32_t off0, uint32_t off1, float (&hacc)[5], uint4 (&p8)[4],
+                                               uint32_t& mlo, uint32_t& mhi) {
+#pragma unroll
+    for (int q = 0; q < kNQ; ++q) {
+        uint32_t v[16];
+        ptx::tmem_ld16(tacc + q * 64, v);
+        float4 b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (kRayBias) b[i] = __ldg(reinterpret_cast<const float4*>(rbias + q * 64) + i);
+            else b[i] = ptx::lds_f4(bias_s + q * 256 + i * 16);
+        }
+        ptx::tmem_ld_wait();
+        float x[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            ptx::fadd2(x[4 * i], x[4 * i + 1], __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), b[i].x, b[i].y);
+            ptx::fadd2(x[4 * i + 2], x[4 * i + 3], __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]), b[i].z, b[i].w);
+        }
+        uint32_t pk[8];
+        if (kRelu && !kSave) {
+            // inference: ReLU folded into the bf16 conversion (max(rn(x), 0) == rn(max(x, 0)))
+#pragma unroll
+            for (int j = 0; j < 8; ++j) pk[j] = ptx::pack_bf16_relu(x[2 * j], x[2 * j + 1]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(x[2 * j], x[2 * j + 1]);
+        }
+        if (kSave) {
+            p8[q].x = ptx::pack4_e4m3<kRelu>(x[0], x[1], x[2], x[3]);    p8[q].y = ptx::pack4_e4m3<kRelu>(x[4], x[5], x[6], x[7]);
+            p8[q].z = ptx::pack4_e4m3<kRelu>(x[8], x[9], x[10], x[11]);  p8[q].w = ptx::pack4_e4m3<kRelu>(x[12], x[13], x[14], x[15]);
+            if (kRelu) {
+                // sign bits of the packed pre-activations (bit 15 = column 2j, bit 31 = column 2j+1) -> one 16-bit entry,
+                // see epi_slice16 / relu_mask_bit
+                uint32_t acc = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc |= (pk[j] >> j) & (0x80008000u >> j);
+                const uint32_t neg = ((acc & 0xFF00u) | (acc >> 24)) & 0xFFFFu;
+                if (q < 2) mlo |= neg << (16 * q); else mhi |= neg << (16 * (q - 2));
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    __nv_bfloat162 t = *reinterpret_cast<__nv_bfloat162*>(&pk[j]);
+                    t = __hmax2(t, __floats2bfloat162_rn(0.0f, 0.0f));
+                    pk[j] = *reinterpret_cast<uint32_t*>(&t);
+                }
+            }
+        }
+        if (kHeads > 0 && q < kHeadQ) {
+#pragma unroll
+            for (int h = 0; h < kHeads; ++h) {
+                float a = hacc[h];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 t = ptx::lds_f4(hw_s + h * 512 + q * 256 + i * 16);
+                    a = fmaf(kRelu ? fmaxf(x[4 * i], 0.0f) : x[4 * i], t.x, a);
+                    a = fmaf(kRelu ? fmaxf(x[4 * i + 1], 0.0f) : x[4 * i + 1], t.y, a);
+                    a = fmaf(kRelu ? fmaxf(x[4 * i + 2], 0.0f) : x[4 * i + 2], t.z, a);
+                    a = fmaf(kRelu ? fmaxf(x[4 * i + 3], 0.0f) : x[4 * i + 3], t.w, a);
+                }
+                hacc[h] = a;
+            }
+        }
+        ptx::sts_u4(img_s + q * 16384 + off0, pk[0], pk[1], pk[2], pk[3]);
+        ptx::sts_u4(img_s + q * 16384 + off1, pk[4], pk[5], pk[6], pk[7]);
+    }
+}
+
+// residual chunk of a head-feeding layer, recomputed behind the handoff from the bf16 image (see residual_chunk)
+__device__ __forceinline__ uint4 residual_chunk_s(uint32_t blk_s, uint32_t off0, uint32_t off1, const uint4& p8) {
+    const uint4 b0 = ptx::lds_u4(blk_s + off0), b1 = ptx::lds_u4(blk_s + off1);
+    auto lo = [](uint32_t w) { return __uint_as_float(w << 16); };
+    auto hi = [](uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); };
+    uint4 l8;
+    l8.x = ptx::residual4_e4m3<false>(p8.x, lo(b0.x), hi(b0.x), lo(b0.y), hi(b0.y), kLoScale);
+    l8.y = ptx::residual4_e4m3<false>(p8.y, lo(b0.z), hi(b0.z), lo(b0.w), hi(b0.w), kLoScale);
+    l8.z = ptx::residual4_e4m3<false>(p8.z, lo(b1.x), hi(b1.x), lo(b1.y), hi(b1.y), kLoScale);
+    l8.w = ptx::residual4_e4m3<false>(p8.w, lo(b1.z), hi(b1.z), lo(b1.w), hi(b1.w), kLoScale);
+    return l8;
+}
 
 template <bool kSave>
 __global__ void __cluster_dims__(2, 1, 1) __maxnreg__(kFwdMaxRegs)
@@ -125,14 +230,14 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         const uint32_t dcol = tmem + t * 256;
                         // the slot's operand image (X for layer 0, the previous layer's output otherwise) is complete in
                         // both CTAs, and its previous accumulator has been read out
-                        ptx::mbar_wait_a(act_a + 8 * t, (act_par >> t) & 1u);
+                        NWB_FWD_WAIT_A(act_a + 8 * t, (act_par >> t) & 1u);
                         act_par ^= 1u << t;
                         ptx::tc_fence_after_sync();
                         int hs = dual_in_slot0(g);
                         for (int kb = 0; kb < KB; ++kb) {
                             const bool is_x = (g == 0) || (g == 4 && kb == 0);
                             const uint32_t a_lo = is_x ? x_lo : h_lo + (hs++) * 1024;
-                            ptx::mbar_wait_a(full_a + 8 * s, ph);
+                            NWB_FWD_WAIT_A(full_a + 8 * s, ph);
                             ptx::tc_fence_after_sync();
                             const uint32_t b_lo = w_lo + s * (kDStageBytes >> 4);
                             if (ptx::elect_one()) {
@@ -157,7 +262,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                 for (int g = 0; g < nl; ++g) {
                     const int n = 2 * fs.layer_kb(g);
                     for (int i = 0; i < n; ++i) {
-                        ptx::mbar_wait_a(full_a + 8 * s, ph);
+                        NWB_FWD_WAIT_A(full_a + 8 * s, ph);
                         ptx::mbar_arrive_cluster(full_leader + 8 * s);
                         if (++s == kDNumStages) { s = 0; ph ^= 1u; }
                     }
@@ -180,6 +285,9 @@ field_fwd_dual_kernel(const FwdArgs a) {
         uint32_t acc_par = 0;                              // bit t = parity of the next phase of bar_acc[t]
         const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an 8-bit image block
         const int s7 = row & 7;
+        const uint32_t smem_s = ptx::smem_u32(smem), cst_s = smem_s + kDOffC + sub * 64, acc_s = ptx::smem_u32(bar_acc);
+        const uint32_t off0 = ptx::image_chunk_off(row, 2 * sub), off1 = ptx::image_chunk_off(row, 2 * sub + 1);   // bf16 image chunks
+        const uint32_t so0 = line_off + ((sub ^ s7) << 4), so1 = line_off + (((4 + sub) ^ s7) << 4);               // 8-bit image chunks
         auto hand_over = [&](int t, bool feeds_mma) {      // after this thread's shared-memory writes of the image
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before_sync();
@@ -267,76 +375,61 @@ field_fwd_dual_kernel(const FwdArgs a) {
             float sg0 = 0.0f, sg1 = 0.0f, c00 = 0.0f, c01 = 0.0f, c02 = 0.0f, c10 = 0.0f, c11 = 0.0f, c12 = 0.0f;   // sigma / rgb of slot 0 / 1
             for (int g = 0; g < nl; ++g) {
                 const bool last = (g == nl - 1);
-                const int nq = layer_quarters(g, transient);
 #pragma unroll 1
                 for (int t = 0; t < 2; ++t) {
                     const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
-                    uint8_t* sH = smem + kDOffH + t * 65536;
-                    float* s_part = reinterpret_cast<float*>(smem + kDOffX + t * 16384);    // [3][5][128] head partial sums:
-                                                                                             // X_t is dead once layer 4 is done
-                    const float* rb = (a.ray_bias != nullptr) ? a.ray_bias + static_cast<long long>(t ? ray1 : ray0) * 256 : nullptr;
+                    const uint32_t img_s = smem_s + kDOffH + t * 65536;
+                    const uint32_t part_s = smem_s + kDOffX + t * 16384 + row * 4;     // [3][5][128] head partial sums: X_t is
+                                                                                         // dead once layer 4 is done
                     const uint32_t tacc = tlane + t * 256 + sub * 16;
-                    ptx::mbar_wait_sleepy(&bar_acc[t], (acc_par >> t) & 1u);
+                    ptx::mbar_wait_sleepy_a(acc_s + 8 * t, (acc_par >> t) & 1u);
                     acc_par ^= 1u << t;
                     ptx::tc_fence_after_sync();
                     float hacc[5] = {0, 0, 0, 0, 0};
-                    // e4m3 chunks of this thread's four quarters, kept until the handoff is out (selected by predicated moves:
-                    // the quarter loop is not unrolled)
-                    uint4 q8a = make_uint4(0, 0, 0, 0), q8b = q8a, q8c = q8a, q8d = q8a;
-                    // sign masks: per layer [sub][row] x 4 uint16 (one per quarter: a warp's store is 256 contiguous bytes); bit (15-j) of entry q =
-                    // sign of the pre-activation of column 64q + 16sub + j; one 8-byte store per thread after the handoff
-                    unsigned long long mbits = 0ull;
-#pragma unroll 1
-                    for (int q = 0; q < nq; ++q) {
-                        const int c0 = q * 64 + sub * 16;   // this thread's 16 columns of quarter q
-                        uint8_t* blk = sH + q * 16384;      // in place: quarter q = K-block q of the next layer's operand
-                        uint32_t md = 0;
-                        uint4 p8 = make_uint4(0, 0, 0, 0);
-                        if (g < 7) {
-                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                        } else if (g == 7) {
-                            epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                                        hacc, blk, row, 2 * sub, md, p8);
-                        } else if (g == 8) {
-                            epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                        } else if (g == 9) {
-                            // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-                            if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md, p8);
-                            else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                        } else if (g < 12) {
-                            epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                        } else {
-                            // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
-                            epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                                        hacc, blk, row, 2 * sub, md, p8);
-                        }
-                        if (save) {
-                            mbits |= static_cast<unsigned long long>(md) << (16 * q);
-                            if (q == 0) q8a = p8; else if (q == 1) q8b = p8; else if (q == 2) q8c = p8; else q8d = p8;
-                        }
+                    uint4 p8[4];                           // e4m3 chunks of this thread's quarters, kept until the handoff is out
+                    uint32_t mlo = 0, mhi = 0;             // sign-mask entries (one 8-byte store per thread after the handoff)
+                    if (g < 7) {
+                        dual_layer_epi<true, 0, 0, 4, false, kSave>(tacc, cst_s + (ConstOff::trunk_b + g * 256) * 4, nullptr, 0, img_s, off0, off1, hacc, p8, mlo, mhi);
+                    } else if (g == 7) {
+                        dual_layer_epi<true, 1, 4, 4, false, kSave>(tacc, cst_s + (ConstOff::trunk_b + 7 * 256) * 4, nullptr, cst_s + ConstOff::sigma_w * 4,
+                                                                    img_s, off0, off1, hacc, p8, mlo, mhi);
+                    } else if (g == 8) {
+                        dual_layer_epi<false, 0, 0, 4, false, kSave>(tacc, cst_s + ConstOff::final_b * 4, nullptr, 0, img_s, off0, off1, hacc, p8, mlo, mhi);
+                    } else if (g == 9) {
+                        // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias; rgb heads read the dir half
+                        const float* rb = a.ray_bias + static_cast<long long>(t ? ray1 : ray0) * 256 + sub * 16;
+                        if (transient) dual_layer_epi<true, 3, 2, 4, true, kSave>(tacc, 0, rb, cst_s + ConstOff::rgb_w * 4, img_s, off0, off1, hacc, p8, mlo, mhi);
+                        else dual_layer_epi<true, 3, 2, 2, true, kSave>(tacc, 0, rb, cst_s + ConstOff::rgb_w * 4, img_s, off0, off1, hacc, p8, mlo, mhi);
+                    } else if (g < 12) {
+                        dual_layer_epi<true, 0, 0, 2, false, kSave>(tacc, cst_s + (ConstOff::tenc_b + (g - 10) * 128) * 4, nullptr, 0, img_s, off0, off1, hacc, p8, mlo, mhi);
+                    } else {
+                        // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
+                        dual_layer_epi<true, 5, 2, 2, false, kSave>(tacc, cst_s + (ConstOff::tenc_b + 2 * 128) * 4, nullptr, cst_s + ConstOff::tsigma_w * 4,
+                                                                    img_s, off0, off1, hacc, p8, mlo, mhi);
                     }
                     hand_over(t, !last);
                     if (save && tile < a.n_tiles) {
                         // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
                         // 16 columns are chunk 4(q%2) + sub of its row's line
+                        const bool four = (g <= 8) || (g == 9 && transient);
                         uint8_t* save_tile_t = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
-                        uint8_t* ln = save_tile_t + sl.act_off(g) + line_off;
-                        *reinterpret_cast<uint4*>(ln + ((sub ^ s7) << 4)) = q8a;
-                        *reinterpret_cast<uint4*>(ln + (((4 + sub) ^ s7) << 4)) = q8b;
-                        if (nq == 4) {
-                            *reinterpret_cast<uint4*>(ln + 16384 + ((sub ^ s7) << 4)) = q8c;
-                            *reinterpret_cast<uint4*>(ln + 16384 + (((4 + sub) ^ s7) << 4)) = q8d;
+                        uint8_t* ln = save_tile_t + sl.act_off(g);
+                        *reinterpret_cast<uint4*>(ln + so0) = p8[0];
+                        *reinterpret_cast<uint4*>(ln + so1) = p8[1];
+                        if (four) {
+                            *reinterpret_cast<uint4*>(ln + 16384 + so0) = p8[2];
+                            *reinterpret_cast<uint4*>(ln + 16384 + so1) = p8[3];
                         }
-                        if (g != 8) *reinterpret_cast<unsigned long long*>(save_tile_t + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
+                        if (g != 8) *reinterpret_cast<uint2*>(save_tile_t + sl.mask_off(g, nl) + sub * 1024 + row * 8) = make_uint2(mlo, mhi);
                         if (g == 7 || g == 9 || g == 12) {
                             // residual image of a layer that feeds a head: same place as in the image proper (of layer 9
                             // only the dir half, quarters 0-1)
-                            uint8_t* lo = save_tile_t + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl) + line_off;
-                            *reinterpret_cast<uint4*>(lo + ((sub ^ s7) << 4)) = residual_chunk(sH, row, 2 * sub, q8a);
-                            *reinterpret_cast<uint4*>(lo + (((4 + sub) ^ s7) << 4)) = residual_chunk(sH + 16384, row, 2 * sub, q8b);
+                            uint8_t* lo = save_tile_t + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl);
+                            *reinterpret_cast<uint4*>(lo + so0) = residual_chunk_s(img_s, off0, off1, p8[0]);
+                            *reinterpret_cast<uint4*>(lo + so1) = residual_chunk_s(img_s + 16384, off0, off1, p8[1]);
                             if (g == 7) {
-                                *reinterpret_cast<uint4*>(lo + 16384 + ((sub ^ s7) << 4)) = residual_chunk(sH + 2 * 16384, row, 2 * sub, q8c);
-                                *reinterpret_cast<uint4*>(lo + 16384 + (((4 + sub) ^ s7) << 4)) = residual_chunk(sH + 3 * 16384, row, 2 * sub, q8d);
+                                *reinterpret_cast<uint4*>(lo + 16384 + so0) = residual_chunk_s(img_s + 2 * 16384, off0, off1, p8[2]);
+                                *reinterpret_cast<uint4*>(lo + 16384 + so1) = residual_chunk_s(img_s + 3 * 16384, off0, off1, p8[3]);
                             }
                         }
                     }
@@ -346,14 +439,14 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         if (sub > 0) {
 #pragma unroll
                             for (int h = 0; h < 5; ++h)      // static indices: hacc stays in registers
-                                if (h < nh_heads) s_part[((sub - 1) * 5 + h) * 128 + row] = hacc[h];
+                                if (h < nh_heads) ptx::sts_f(part_s + ((sub - 1) * 5 + h) * 512, hacc[h]);
                         }
                         epi_bar_all();
                         if (sub == 0) {
 #pragma unroll
                             for (int h = 0; h < 5; ++h)
                                 if (h < nh_heads)
-                                    hacc[h] = ((hacc[h] + s_part[h * 128 + row]) + s_part[(5 + h) * 128 + row]) + s_part[(10 + h) * 128 + row];
+                                    hacc[h] = ((hacc[h] + ptx::lds_f(part_s + h * 512)) + ptx::lds_f(part_s + (5 + h) * 512)) + ptx::lds_f(part_s + (10 + h) * 512);
                             if (g == 7) {                                                                      // nerf.py:190
                                 const float v = softplus_f(hacc[0] + cst[ConstOff::head_b]);
                                 if (t == 0) sg0 = v; else sg1 = v;

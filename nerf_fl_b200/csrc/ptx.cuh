@@ -353,6 +353,63 @@ __device__ __forceinline__ void umma2_commit_both(uint32_t bar_addr) {
                  : "memory");
 }
 
+
+// ---- shared memory by 32-bit shared-space address ---------------------------------------------------
+// A generic pointer that may or may not point into shared memory makes the compiler emit BOTH an LDS and an LDG path
+// behind an address-space test (and the window-base S2UR that goes with it) at every use; the epilogue loops are
+// issue-bound, so they address shared memory explicitly.  volatile: ordered among the other volatile asm (tcgen05.ld /
+// wait, fences, barriers), free to move across ordinary C++ memory operations.
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float lds_f(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_u4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void sts_f(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+// two fp32 -> packed bf16x2 (lo in the low half) with ReLU folded into the conversion
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ bool mbar_try_wait_hint_a(uint32_t bar_addr, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(bar_addr), "r"(parity), "r"(ns)
+        : "memory");
+    return ok != 0;
+}
+// sleepy wait by raw address; the watchdog counts attempts (each may suspend up to 2 us), no clock arithmetic in the loop
+__device__ __forceinline__ void mbar_wait_sleepy_a(uint32_t bar_addr, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait_hint_a(bar_addr, parity, 2000)) {
+        if (++spins > (1u << 22)) {
+            printf("nwb: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar_addr, parity);
+            __trap();
+        }
+    }
+}
+
 // ---- tile image addressing ------------------------------------------------------------------------
 // A "tile image" of an R x 64k bf16 matrix is what UMMA's SWIZZLE_128B canonical layout wants:
 // column block cb (64 cols = 128 B) at cb*R*128; row r at (r/8)*1024 + (r%8)*128; the 16-byte chunk
