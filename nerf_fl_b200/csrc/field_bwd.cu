@@ -18,7 +18,15 @@
 
 namespace nwb {
 
-constexpr int kBwdThreads = 192;
+// Eight epilogue warps per CTA (two column halves x four TMEM lane quadrants): with two CTAs per SM that is 16 working
+// warps, four per scheduler, as in the forward.  The four-warp version (one thread per row and layer, 256 columns
+// each) left two warps per scheduler to hide tcgen05.ld and shared-memory latencies, and its epilogue phase was twice
+// the MMA phase (profiles/r01g_stalls_dgrad_fine.md: a third of the epilogue warps' time was the accumulator wait of
+// the OTHER phase).  320 threads x <= 96 registers x 2 CTAs fit the register file.
+constexpr int kBwdEpiWarps = 8;
+constexpr int kBwdEpiThreads = kBwdEpiWarps * 32;
+constexpr int kBwdThreads = 64 + kBwdEpiThreads;
+__device__ __forceinline__ void epi_bar8() { asm volatile("bar.sync 1, %0;" ::"n"(kBwdEpiThreads) : "memory"); }
 constexpr int kBStageBytes = 8192;                 // this CTA's half of a stage: 2 of the 4 k-blocks x 32 n-rows x 128 B
 constexpr int kBChunkBytes = 4096;                 // one k-block's 32 rows
 constexpr int kBNumStages = 6;                  // the kernel is bound by the latency of the weight stream: depth matters
@@ -61,16 +69,21 @@ struct BwdArgs {
 #define NWB_BTRACE(cond, slot) do { } while (0)
 #endif
 
-// one 32-column slice of dZ for this thread's row
+// one 32-column slice of dZ for this thread's row, straight-line (every address term that does not depend on the thread
+// is a compile-time constant at the call site)
 //   kAcc: take dA from TMEM;  kHeads > 0: add sum_h dp[h] * hw[h][c];  negmask: two 16-column entries (columns 0-15 in
 //   the high half), bit relu_mask_bit(c) of an entry set = gate closed
 //   Head weights arrive lane-distributed (lane l holds hw[h][c_out + l], one coalesced load per warp issued ahead of
 //   the accumulator wait) and are broadcast with shuffles: every thread of the warp needs the same 32 values, and a
 //   warp-uniform global load per value costs an L2 round trip each (shared memory is full, L1 is carved away).
-//   g8: this row's 128-byte line of the layer's e5m2 image block that holds column c_out (nullptr: ghost tile)
+//   blk_s: shared address of the 16 KB bf16 image block that holds the slice; cb: its first 16-byte chunk there (0 | 4);
+//   rowx = this row's line offset | (row % 8) << 4, so that chunk c of the row sits at blk_s + (rowx ^ (c << 4))
+//   g8: this row's 128-byte line of the layer's e5m2 image block that holds the slice (nullptr: ghost tile); ps: the
+//   slice's 32-column group inside that block (0..3) -- its two chunks sit side by side in one 32-byte sector at
+//   (ps ^ (row%8)/2) << 5, swapped when the row is odd (the swizzle XORs both chunk indices with row % 8)
 template <bool kAcc, int kHeads, bool kMask>
 __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, const float* dp, uint32_t negmask,
-                                          uint8_t* sD, int row, int c_out, uint8_t* g8) {
+                                          uint32_t blk_s, uint32_t rowx, int cb, uint8_t* g8, int ps, int row) {
     float x[32];
     if (kAcc) {
         uint32_t v[32];
@@ -95,17 +108,17 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, cons
         for (int j = 0; j < 32; ++j)
             if ((negmask >> ((j < 16 ? 16 : 0) + relu_mask_bit(j & 15))) & 1u) x[j] = 0.0f;
     }
-    store_slice_bf16(sD, row, c_out, x);
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        ptx::sts_u4(blk_s + (rowx ^ static_cast<uint32_t>((cb + q) << 4)), pack_bf16(x[8 * q], x[8 * q + 1]), pack_bf16(x[8 * q + 2], x[8 * q + 3]),
+                    pack_bf16(x[8 * q + 4], x[8 * q + 5]), pack_bf16(x[8 * q + 6], x[8 * q + 7]));
     if (g8 != nullptr) {
-        // 32 columns = chunks 2m, 2m+1 of the row's line: they sit side by side in one 32-byte sector (the swizzle
-        // XORs both chunk indices with row%8, which swaps them when row is odd)
         uint4 lo, hi;
         lo.x = ptx::pack4_e5m2(x[0], x[1], x[2], x[3]);     lo.y = ptx::pack4_e5m2(x[4], x[5], x[6], x[7]);
         lo.z = ptx::pack4_e5m2(x[8], x[9], x[10], x[11]);   lo.w = ptx::pack4_e5m2(x[12], x[13], x[14], x[15]);
         hi.x = ptx::pack4_e5m2(x[16], x[17], x[18], x[19]); hi.y = ptx::pack4_e5m2(x[20], x[21], x[22], x[23]);
         hi.z = ptx::pack4_e5m2(x[24], x[25], x[26], x[27]); hi.w = ptx::pack4_e5m2(x[28], x[29], x[30], x[31]);
-        const int pair = ((c_out & 127) >> 5) ^ ((row & 7) >> 1);
-        uint8_t* dst = g8 + (pair << 5);
+        uint8_t* dst = g8 + ((ps ^ ((row & 7) >> 1)) << 5);
         if (row & 1) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
     }
 }
@@ -232,10 +245,11 @@ field_dgrad_kernel(const BwdArgs a) {
         }
         __syncwarp();
     } else {
-        // ============================ epilogue warps (thread == point) ===========================
-        const int quad = warp & 3;
+        // ============================ epilogue warps (two threads per point: column halves) =======
+        const int quad = warp & 3;                          // TMEM lane quadrant this warp may read
+        const int ch = (warp - 2) >> 2;                     // column half of every layer this thread converts
         const int row = quad * 32 + lane;
-        const int et = threadIdx.x - 64;                   // 0..127 among the epilogue threads
+        const int et = threadIdx.x - 64;                    // 0..255 among the epilogue threads
         const uint32_t tlane = tmem + (static_cast<uint32_t>(quad * 32) << 16);
         const bool leader = (et == 0);
         const float* cst = reinterpret_cast<const float*>(a.packed + fs.w_bytes());
@@ -245,6 +259,9 @@ field_dgrad_kernel(const BwdArgs a) {
         const float scale = dz_scale_from_amax_bits(__ldg(&a.hdr->amax_bits));
         const float inv_scale = 1.0f / scale;               // both exact powers of two
         const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an image block
+        const uint32_t rowx = line_off | static_cast<uint32_t>((row & 7) << 4);
+        const uint32_t sD_s = ptx::smem_u32(sD);
+        const uint32_t sh16 = 16u * ch;
         uint32_t acc_ev = 0;
         const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
         for (int pair = pair0; pair < n_pairs; pair += pair_step) {
@@ -256,7 +273,7 @@ field_dgrad_kernel(const BwdArgs a) {
             const uint8_t* save_tile = a.saved + static_cast<size_t>(tile) * a.save_tile_bytes;
             uint8_t* dz_tile = a.dz + static_cast<size_t>(tile) * a.dz_tile_bytes;
 
-            // ---- head pre-activation cotangents (nerf.py:190,197,205-207 backward) --------------
+            // ---- head pre-activation cotangents (nerf.py:190,197,205-207 backward): both threads of a row ----------
             float dp[9];                                    // [sigma, rgb3, tsigma, trgb3, tbeta]
 #pragma unroll
             for (int i = 0; i < 9; ++i) dp[i] = 0.0f;
@@ -273,13 +290,16 @@ field_dgrad_kernel(const BwdArgs a) {
                     dp[8] = __ldg(dy + 8) * (1.0f - expf(-__ldg(y + 8)));
                 }
             }
+            if (ch == 0) {                                  // head-bias gradients: one thread per row
 #pragma unroll
-            for (int i = 0; i < 9; ++i) {
-                const float s = warp_sum(dp[i]);
-                if (lane == 0 && s != 0.0f) atomicAdd(&s_hb[i], s);
-                dp[i] *= scale;                             // from here on the chain carries scaled cotangents
+                for (int i = 0; i < 9; ++i) {
+                    const float s = warp_sum(dp[i]);
+                    if (lane == 0 && s != 0.0f) atomicAdd(&s_hb[i], s);
+                }
             }
-            if (!ghost) {
+#pragma unroll
+            for (int i = 0; i < 9; ++i) dp[i] *= scale;     // from here on the chain carries scaled cotangents
+            if (!ghost && ch == 0) {
                 // dpre block (e5m2, three-term expansion: column 9k + n = e5m2 of what terms < k left of head n's scaled
                 // cotangent): the wgrad kernel's head units read 32 columns = chunks 0, 1 of every row -- one 32-byte
                 // sector, the swizzle swaps the two when the row is odd; the other six chunks stay unwritten
@@ -305,125 +325,119 @@ field_dgrad_kernel(const BwdArgs a) {
             }
 
             for (int g = nl - 1; g >= 0; --g) {
-                // ReLU gates of layer g (prefetched before waiting for the accumulator)
-                // (the loads are issued here; their first use -- the decode into mw[] -- comes after the accumulator wait, so
-                // the L2/DRAM round trip of the masks overlaps the wait instead of preceding it: 7 % of all stall samples sat
-                // on the decode's first instruction, profiles/r01d_stalls_dgrad_fine.md)
+                // ReLU gates of layer g, forward layout [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit
+                // relu_mask_bit(j) = column 64q + 16sub + j).  The loads are issued here; their first use comes after
+                // the accumulator wait, so their L2/DRAM round trip overlaps the wait
                 uint2 a0 = make_uint2(0u, 0u), a1 = a0, a2 = a0, a3 = a0;
                 const bool gated = (g != 8 && !ghost);
                 if (gated) {
-                    // forward layout: [sub][row] x 4 uint16 (entry q of sub-block `sub`: bit relu_mask_bit(j) = column 64q+16sub+j)
                     const uint2* mp = reinterpret_cast<const uint2*>(save_tile + sl.mask_off(g, nl)) + row;
                     a0 = __ldg(mp); a1 = __ldg(mp + 128); a2 = __ldg(mp + 256); a3 = __ldg(mp + 384);
                 }
-                // head weights of this layer's head term, lane-distributed: hwl[slice][head] = hw[head][32*slice + lane]
-                float hwl[20];
-                if (g == 12) {
+                // head weights of this layer's head term, lane-distributed over this thread's slices
+                float hwl[10];
+                if (g == 12) {          // columns [64 ch, +64): slices i = 0, 1, heads [tsigma | trgb(3) | tbeta] contiguous, ld 128
 #pragma unroll
-                    for (int i = 0; i < 20; ++i) hwl[i] = __ldg(cst + ConstOff::tsigma_w + (i % 5) * 128 + (i / 5) * 32 + lane);
-                } else if (g == 9) {
+                    for (int i = 0; i < 10; ++i) hwl[i] = __ldg(cst + ConstOff::tsigma_w + (i % 5) * 128 + 64 * ch + (i / 5) * 32 + lane);
+                } else if (g == 9) {    // dir columns [64 ch, +64)
 #pragma unroll
-                    for (int i = 0; i < 12; ++i) hwl[i] = __ldg(cst + ConstOff::rgb_w + (i % 3) * 128 + (i / 3) * 32 + lane);
-                } else if (g == 7) {
+                    for (int i = 0; i < 6; ++i) hwl[i] = __ldg(cst + ConstOff::rgb_w + (i % 3) * 128 + 64 * ch + (i / 3) * 32 + lane);
+                } else if (g == 7) {    // columns [128 ch, +128)
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) hwl[i] = __ldg(cst + ConstOff::sigma_w + i * 32 + lane);
+                    for (int i = 0; i < 4; ++i) hwl[i] = __ldg(cst + ConstOff::sigma_w + 128 * ch + i * 32 + lane);
                 }
                 if (g < nl - 1) {
                     ptx::mbar_wait_sleepy(bar_acc, acc_ev & 1u);
                     ++acc_ev;
                     ptx::tc_fence_after_sync();
                 }
-                uint32_t mw[8];
-#pragma unroll
-                for (int w = 0; w < 8; ++w) mw[w] = 0u;
-                if (gated) {
-                    // gathered into per-row order, entry (sub, q) at sub*4 + q
-                    const uint4 m0 = make_uint4(a0.x, a0.y, a1.x, a1.y), m1 = make_uint4(a2.x, a2.y, a3.x, a3.y);
-                    const uint32_t m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-#pragma unroll
-                    for (int w = 0; w < 8; ++w) {                 // word w = columns 32w..32w+31: entry of columns 32w..+15 in the high half
-                        const int q = w >> 1, s0 = (w & 1) * 2;
-                        const int ihi = s0 * 4 + q, ilo = (s0 + 1) * 4 + q;
-                        const uint32_t hi = (m[ihi >> 1] >> ((ihi & 1) * 16)) & 0xFFFFu;
-                        const uint32_t lo = (m[ilo >> 1] >> ((ilo & 1) * 16)) & 0xFFFFu;
-                        mw[w] = (hi << 16) | lo;
-                    }
-                }
+                // mask word of a 32-column slice: entries (s0, q) | (s0 + 1, q), q chosen by word (.x: q 0-1, .y: q 2-3) and shift
+                auto mword = [](uint32_t w_hi, uint32_t w_lo, uint32_t sh) { return (((w_hi >> sh) & 0xFFFFu) << 16) | ((w_lo >> sh) & 0xFFFFu); };
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 2);    // accumulator seen
-                epi_bar();                                  // everyone is done reading sD (the d_ray_bias sums of layer 9)
+                epi_bar8();                                 // everyone is done reading sD (the d_ray_bias sums of layer 9)
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 3);    // sD free
                 // this row's line in block 0 / block 1 of the layer's e5m2 image
                 uint8_t* g8a = ghost ? nullptr : dz_tile + dl.dz_off(g) + line_off;
                 uint8_t* g8b = ghost ? nullptr : g8a + 16384;
                 if (g >= 10) {
+                    // 128 columns: mine are [64 ch, +64) = bf16 image block ch, e5m2 groups 2 ch + i, gate entries q = ch
+                    const uint32_t blk = sD_s + ch * 16384;
                     if (g == 12) {
 #pragma unroll
-                        for (int sl4 = 0; sl4 < 4; ++sl4)
-                            bwd_slice<false, 5, true>(0, hwl + 5 * sl4, dp + 4, mw[sl4], sD, row, 32 * sl4, g8a);
+                        for (int i = 0; i < 2; ++i)
+                            bwd_slice<false, 5, true>(0, hwl + 5 * i, dp + 4, mword(i ? a2.x : a0.x, i ? a3.x : a1.x, sh16), blk, rowx, 4 * i, g8a, 2 * ch + i, row);
                     } else {
-#pragma unroll 1
-                        for (int c0 = 0; c0 < 128; c0 += 32)
-                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0, g8a);
+#pragma unroll
+                        for (int i = 0; i < 2; ++i)
+                            bwd_slice<true, 0, true>(tlane + 64 * ch + 32 * i, nullptr, nullptr, mword(i ? a2.x : a0.x, i ? a3.x : a1.x, sh16), blk, rowx, 4 * i,
+                                                     g8a, 2 * ch + i, row);
                     }
                 } else if (g == 9) {
+                    // dir half: columns [64 ch, +64), head term only; transient half: columns 128 + [64 ch, +64), accumulator only
 #pragma unroll
-                    for (int sl4 = 0; sl4 < 4; ++sl4)
-                        bwd_slice<false, 3, true>(0, hwl + 3 * sl4, dp + 1, mw[sl4], sD, row, 32 * sl4, g8a);
+                    for (int i = 0; i < 2; ++i)
+                        bwd_slice<false, 3, true>(0, hwl + 3 * i, dp + 1, mword(i ? a2.x : a0.x, i ? a3.x : a1.x, sh16), sD_s + ch * 16384, rowx, 4 * i, g8a,
+                                                  2 * ch + i, row);
                     if (transient) {
-#pragma unroll 1
-                        for (int c0 = 128; c0 < 256; c0 += 32)
-                            bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0, g8b);
-                    }
-                } else if (g == 8) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 0, false>(tlane + c0, nullptr, nullptr, 0u, sD, row, c0, c0 < 128 ? g8a : g8b);
-                } else if (g == 7) {
 #pragma unroll
-                    for (int sl8 = 0; sl8 < 8; ++sl8)
-                        bwd_slice<true, 1, true>(tlane + 32 * sl8, hwl + sl8, dp, mw[sl8], sD, row, 32 * sl8, sl8 < 4 ? g8a : g8b);
+                        for (int i = 0; i < 2; ++i)
+                            bwd_slice<true, 0, true>(tlane + 128 + 64 * ch + 32 * i, nullptr, nullptr, mword(i ? a2.y : a0.y, i ? a3.y : a1.y, sh16),
+                                                     sD_s + (2 + ch) * 16384, rowx, 4 * i, g8b, 2 * ch + i, row);
+                    }
                 } else {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < 256; c0 += 32)
-                        bwd_slice<true, 0, true>(tlane + c0, nullptr, nullptr, mw[c0 >> 5], sD, row, c0, c0 < 128 ? g8a : g8b);
+                    // 256 columns: mine are [128 ch, +128) = bf16 image blocks 2 ch, 2 ch + 1, e5m2 block ch, gate entries q = 2 ch + i / 2
+                    const uint32_t w0 = ch ? a0.y : a0.x, w1 = ch ? a1.y : a1.x, w2 = ch ? a2.y : a2.x, w3 = ch ? a3.y : a3.x;
+                    uint8_t* g8 = ch ? g8b : g8a;
+                    const uint32_t blk = sD_s + 2 * ch * 16384;
+                    const uint32_t tcol = tlane + 128 * ch;
+                    if (g == 8) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            bwd_slice<true, 0, false>(tcol + 32 * i, nullptr, nullptr, 0u, blk + (i >> 1) * 16384, rowx, 4 * (i & 1), g8, i, row);
+                    } else if (g == 7) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            bwd_slice<true, 1, true>(tcol + 32 * i, hwl + i, dp, mword((i & 1) ? w2 : w0, (i & 1) ? w3 : w1, 16 * (i >> 1)), blk + (i >> 1) * 16384,
+                                                     rowx, 4 * (i & 1), g8, i, row);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            bwd_slice<true, 0, true>(tcol + 32 * i, nullptr, nullptr, mword((i & 1) ? w2 : w0, (i & 1) ? w3 : w1, 16 * (i >> 1)), blk + (i >> 1) * 16384,
+                                                     rowx, 4 * (i & 1), g8, i, row);
+                    }
                 }
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 4);    // leader's slices written
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before_sync();                // this thread's tcgen05.ld of the accumulator are done
-                epi_bar();
+                epi_bar8();
                 NWB_BTRACE(leader && pair == pair0, g * 8 + 5);    // all slices written
                 if (leader && g >= 1) { if (rank == 0) ptx::mbar_arrive(bar_act); else ptx::mbar_arrive_cluster(act_leader); }
                 if (g == 9) {
                     // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples.  Runs
                     // AFTER the handoff, next to layer 9's MMAs (both only read the image);
-                    // the next layer's epilogue rewrites it only behind its barrier.
+                    // the next layer's epilogue rewrites it only behind its barrier.  One column per thread.
                     const int ncols = transient ? 256 : 128;
-                    const int c = 2 * et;
+                    const int c = et;
                     if (c < ncols) {
-                        const uint8_t* colp = sD + (c >> 6) * 16384 + (c & 7) * 2;
+                        const uint32_t colp = sD_s + (c >> 6) * 16384 + (c & 7) * 2;
                         const int chunk = (c & 63) >> 3;
                         long long ray = p0 / a.S;
                         const int nrow = static_cast<int>(min(static_cast<long long>(kTileM), a.n_points - p0));
                         int r = 0;
                         int seg_end = static_cast<int>(min(static_cast<long long>(nrow), (ray + 1) * a.S - p0));
                         while (r < nrow) {                      // one segment = the rows of one ray inside this tile
-                            float s0 = 0.0f, s1 = 0.0f, u0 = 0.0f, u1 = 0.0f;
-                            for (; r + 8 <= seg_end; r += 8) {
+                            float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+                            for (; r + 8 <= seg_end; r += 8) {  // r is a multiple of 8 here: rows r..r+7 = one 1 KB group
                                 uint32_t w[8];
 #pragma unroll
-                                for (int k = 0; k < 8; ++k) w[k] = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r + k, chunk));
-#pragma unroll
-                                for (int k = 0; k < 8; k += 2) {
-                                    s0 += __uint_as_float(w[k] << 16); s1 += __uint_as_float(w[k] & 0xFFFF0000u);
-                                    u0 += __uint_as_float(w[k + 1] << 16); u1 += __uint_as_float(w[k + 1] & 0xFFFF0000u);
-                                }
+                                for (int k = 0; k < 8; ++k) w[k] = ptx::lds_u16(colp + ptx::image_chunk_off(r + k, chunk));
+                                s0 += __uint_as_float(w[0] << 16); s1 += __uint_as_float(w[1] << 16);
+                                s2 += __uint_as_float(w[2] << 16); s3 += __uint_as_float(w[3] << 16);
+                                s0 += __uint_as_float(w[4] << 16); s1 += __uint_as_float(w[5] << 16);
+                                s2 += __uint_as_float(w[6] << 16); s3 += __uint_as_float(w[7] << 16);
                             }
-                            for (; r < seg_end; ++r) {
-                                const uint32_t w = *reinterpret_cast<const uint32_t*>(colp + ptx::image_chunk_off(r, chunk));
-                                s0 += __uint_as_float(w << 16); s1 += __uint_as_float(w & 0xFFFF0000u);
-                            }
-                            atomicAdd(a.d_ray_bias + ray * 256 + c, (s0 + u0) * inv_scale);
-                            atomicAdd(a.d_ray_bias + ray * 256 + c + 1, (s1 + u1) * inv_scale);
+                            for (; r < seg_end; ++r) s0 += __uint_as_float(ptx::lds_u16(colp + ptx::image_chunk_off(r, chunk)) << 16);
+                            atomicAdd(a.d_ray_bias + ray * 256 + c, ((s0 + s1) + (s2 + s3)) * inv_scale);
                             ++ray;
                             seg_end = min(nrow, seg_end + a.S);
                         }
