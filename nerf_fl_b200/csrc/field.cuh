@@ -86,9 +86,12 @@ inline int make_shape(const nwb_field_desc* d, FieldShape* s) {
 }
 
 // ---- 8-bit images (what the forward saves and dgrad writes for the weight-gradient kernel) ------------------------
-// An 8-bit tile image of a 128 x 128k matrix: column block cb (128 columns = 128 B per row) at cb * 16 KB, row r at
-// (r/8)*1024 + (r%8)*128, its 16-byte chunk j (16 columns) at chunk position j ^ (r%8) -- the SWIZZLE_128B canonical
-// layout again, read MN-major (rows = contraction index = points) by tcgen05.mma kind::f8f6f4.
+// An 8-bit tile image of a 128 x 32k matrix: 32-column group m (32 B per row) at m * 4 KB, row r at r * 32, its two
+// 16-byte chunks (16 columns each) swapped when bit 2 of r is set -- the SWIZZLE_32B canonical layout, read MN-major
+// (rows = contraction index = points) by tcgen05.mma kind::f8f6f4.  Why 32 B and not the 128 B swizzle of the bf16
+// images: the writers hold ROWS in lanes (a warp = 32 rows of one TMEM lane quadrant), so with 128-byte lines every
+// warp store touched 32 different lines (LSU: one line per cycle -- 2560 cycles of store issue per forward layer and
+// slot, profiles/r02h_trace_fwd_dual_save1.log); here a warp's 32 rows are 1 KB of contiguous bytes (8 lines).
 //   saved activations: e4m3, unscaled (post-ReLU values; the encoded-xyz block and `feat` are signed)
 //   dZ / dpre:         e5m2, times ONE power-of-two scale per backward pass (DzHeader), so that amax|d_raw| -> 2^kDzTop
 // tools/fp8_wgrad_study.py: against the fp32 oracle the model gradient moves from 1.29e-3 (bf16 images) to 1.55e-3.
@@ -136,7 +139,14 @@ struct SaveLayout {
 //   [dZ g0..g8: 9 x 32K][dZ9: 32K (dir|t0) or 16K (dir)][dZ10..12: 3 x 16K][dpre: 16K]
 // dZ_g = cotangent of layer g's pre-activation (e5m2 image, scaled); dpre = cotangents of the head pre-activations
 // [sigma, rgb(3), t_sigma, t_rgb(3), t_beta] as a THREE-term e5m2 expansion (term k = e5m2 of what terms < k left
-// over): one block of which 32 columns are read, column 9k + n = term k of head n, columns 27..31 zero.
+// over): one 32-column group (the first 4 KB of its 16 KB slot), column 9k + n = term k of head n, columns 27..31 zero.
+// byte offset of element (row, 16-byte chunk index c16 = column / 16) inside an 8-bit image (see above)
+__host__ __device__ __forceinline__ uint32_t image8_chunk_off(int row, int c16) {
+    return static_cast<uint32_t>((c16 >> 1) * 4096 + row * 32 + (((c16 & 1) ^ ((row >> 2) & 1)) << 4));
+}
+constexpr uint32_t kImg8GroupBytes = 4096;       // one 32-column group of 128 rows
+constexpr uint32_t kImg8DescLbo = 4096, kImg8DescSbo = 256, kImg8DescLayout = 6, kImg8KStep = 1024;   // UMMA descriptor terms (MN-major)
+
 struct DzHeader {
     unsigned int amax_bits;      // max |d_raw| of the pass as fp32 bits (non-negative floats order like their bits)
     unsigned int pad[63];

@@ -43,6 +43,17 @@ constexpr int kBwdSmem = kBOffBar + 256;
 #else
 #define NWB_BWD_WAIT_A(addr, par) ptx::mbar_wait_sleepy_a(addr, par)
 #endif
+// the two waits on the layer's critical path (MMA thread: operand image complete; polling epilogue warp: accumulator complete)
+#ifdef NWB_BWD_SPIN_ACT
+#define NWB_BWD_WAIT_ACT(addr, par) ptx::mbar_wait_a(addr, par)
+#else
+#define NWB_BWD_WAIT_ACT(addr, par) NWB_BWD_WAIT_A(addr, par)
+#endif
+#ifdef NWB_BWD_SPIN_ACC
+#define NWB_BWD_WAIT_ACC(addr, par) ptx::mbar_wait_a(addr, par)
+#else
+#define NWB_BWD_WAIT_ACC(addr, par) ptx::mbar_wait_sleepy_a(addr, par)
+#endif
 
 struct BwdArgs {
     FieldShape fs;
@@ -78,9 +89,9 @@ struct BwdArgs {
 //   warp-uniform global load per value costs an L2 round trip each (shared memory is full, L1 is carved away).
 //   blk_s: shared address of the 16 KB bf16 image block that holds the slice; cb: its first 16-byte chunk there (0 | 4);
 //   rowx = this row's line offset | (row % 8) << 4, so that chunk c of the row sits at blk_s + (rowx ^ (c << 4))
-//   g8: this row's 128-byte line of the layer's e5m2 image block that holds the slice (nullptr: ghost tile); ps: the
-//   slice's 32-column group inside that block (0..3) -- its two chunks sit side by side in one 32-byte sector at
-//   (ps ^ (row%8)/2) << 5, swapped when the row is odd (the swizzle XORs both chunk indices with row % 8)
+//   g8: this row's 32 bytes in 32-column group 0 of the 128-column block of the layer's e5m2 image that holds the slice
+//   (nullptr: ghost tile); ps: the slice's group inside that block (0..3, 4 KB apart).  The row's two 16-byte chunks
+//   are swapped when bit 2 of the row is set (SWIZZLE_32B); a warp's 32 rows are 1 KB of contiguous bytes
 template <bool kAcc, int kHeads, bool kMask>
 __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, const float* dp, uint32_t negmask,
                                           uint32_t blk_s, uint32_t rowx, int cb, uint8_t* g8, int ps, int row) {
@@ -118,8 +129,8 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, cons
         lo.z = ptx::pack4_e5m2(x[8], x[9], x[10], x[11]);   lo.w = ptx::pack4_e5m2(x[12], x[13], x[14], x[15]);
         hi.x = ptx::pack4_e5m2(x[16], x[17], x[18], x[19]); hi.y = ptx::pack4_e5m2(x[20], x[21], x[22], x[23]);
         hi.z = ptx::pack4_e5m2(x[24], x[25], x[26], x[27]); hi.w = ptx::pack4_e5m2(x[28], x[29], x[30], x[31]);
-        uint8_t* dst = g8 + ((ps ^ ((row & 7) >> 1)) << 5);
-        if (row & 1) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
+        uint8_t* dst = g8 + ps * kImg8GroupBytes;
+        if (row & 4) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
     }
 }
 
@@ -175,6 +186,7 @@ field_dgrad_kernel(const BwdArgs a) {
             // so one tcgen05.mma covers the layer's whole output width (N = 64*KBO) and the dZ operand is read once
             // per K-step instead of once per 64-column output block
             uint32_t it = 0;
+            const uint32_t empty_s = ptx::smem_u32(bar_empty);
             for (int pair = pair0; pair < n_pairs; pair += pair_step) {
                 for (int g = nl - 1; g >= 1; --g) {
                     const uint8_t* wsrc = a.packed + s_woff[g];
@@ -182,7 +194,7 @@ field_dgrad_kernel(const BwdArgs a) {
                     const int kshift = ((g == 4) ? fs.kx : 0) + static_cast<int>(rank) * KH;   // layer 4: skip the xyz slab
                     for (int c = 0; c < NC; ++c, ++it) {
                         const uint32_t s = it % kBNumStages;
-                        ptx::mbar_wait_sleepy(&bar_empty[s], ((it / kBNumStages) & 1u) ^ 1u);
+                        ptx::mbar_wait_sleepy_a(empty_s + 8 * s, ((it / kBNumStages) & 1u) ^ 1u);
                         ptx::mbar_arrive_expect_tx(&bar_full[s], static_cast<uint32_t>(KH) * kBChunkBytes);
                         for (int kl = 0; kl < KH; ++kl)
                             ptx::bulk_g2s(sW + s * kBStageBytes + kl * kBChunkBytes,
@@ -204,10 +216,10 @@ field_dgrad_kernel(const BwdArgs a) {
             uint32_t it = 0, ev = 0;
             for (int pair = pair0; pair < n_pairs; pair += pair_step) {
                 for (int g = nl - 1; g >= 1; --g) {
-                    NWB_BWD_WAIT_A(act_a, ev & 1u);
+                    NWB_BWD_WAIT_ACT(act_a, ev & 1u);
                     ++ev;
                     ptx::tc_fence_after_sync();
-                    NWB_BTRACE(pair == pair0, g * 8 + 0);      // dZ_g seen by the MMA thread
+                    NWB_BTRACE(pair == pair0 + pair_step, g * 8 + 0);      // dZ_g seen by the MMA thread
                     const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> 5;
                     const uint32_t idesc = ptx::umma_idesc_bf16(256, 64 * KBO, false, true);
                     const uint32_t dcol = (g == 10) ? 128u : 0u;
@@ -224,7 +236,7 @@ field_dgrad_kernel(const BwdArgs a) {
                         ptx::umma2_commit_both(empty_a + 8 * s);
                     }
                     ptx::umma2_commit_both(acc_a);
-                    NWB_BTRACE(pair == pair0, g * 8 + 1);      // all MMAs of layer g issued
+                    NWB_BTRACE(pair == pair0 + pair_step, g * 8 + 1);      // all MMAs of layer g issued
                 }
             }
         } else if (lane == 0) {
@@ -260,7 +272,7 @@ field_dgrad_kernel(const BwdArgs a) {
         const float inv_scale = 1.0f / scale;               // both exact powers of two
         const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an image block
         const uint32_t rowx = line_off | static_cast<uint32_t>((row & 7) << 4);
-        const uint32_t sD_s = ptx::smem_u32(sD);
+        const uint32_t sD_s = ptx::smem_u32(sD), acc_s = ptx::smem_u32(bar_acc);
         const uint32_t sh16 = 16u * ch;
         uint32_t acc_ev = 0;
         const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
@@ -301,8 +313,7 @@ field_dgrad_kernel(const BwdArgs a) {
             for (int i = 0; i < 9; ++i) dp[i] *= scale;     // from here on the chain carries scaled cotangents
             if (!ghost && ch == 0) {
                 // dpre block (e5m2, three-term expansion: column 9k + n = e5m2 of what terms < k left of head n's scaled
-                // cotangent): the wgrad kernel's head units read 32 columns = chunks 0, 1 of every row -- one 32-byte
-                // sector, the swizzle swaps the two when the row is odd; the other six chunks stay unwritten
+                // cotangent): one 32-column group, which is all the wgrad kernel's head units read
                 uint32_t by[32];
 #pragma unroll
                 for (int i = 27; i < 32; ++i) by[i] = 0u;
@@ -320,8 +331,8 @@ field_dgrad_kernel(const BwdArgs a) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) w[j] = by[4 * j] | (by[4 * j + 1] << 8) | (by[4 * j + 2] << 16) | (by[4 * j + 3] << 24);
                 const uint4 lo = make_uint4(w[0], w[1], w[2], w[3]), hi = make_uint4(w[4], w[5], w[6], w[7]);
-                uint8_t* dst = dz_tile + dl.dpre_off() + line_off + (((row & 7) >> 1) << 5);
-                if (row & 1) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
+                uint8_t* dst = dz_tile + dl.dpre_off() + row * 32;
+                if (row & 4) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
             }
 
             for (int g = nl - 1; g >= 0; --g) {
@@ -346,18 +357,22 @@ field_dgrad_kernel(const BwdArgs a) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) hwl[i] = __ldg(cst + ConstOff::sigma_w + 128 * ch + i * 32 + lane);
                 }
+                // Accumulator wait: ONE warp polls the mbarrier, the other seven park at the named barrier that follows
+                // anyway (a blocked bar.sync issues nothing; eight polling warps were 29 % of all instructions the kernel
+                // issued, profiles/r02g -- a parked try_wait wakes at every mbarrier event of the CTA, and the weight ring
+                // produces those all the time)
                 if (g < nl - 1) {
-                    ptx::mbar_wait_sleepy(bar_acc, acc_ev & 1u);
+                    if (warp == 2) NWB_BWD_WAIT_ACC(acc_s, acc_ev & 1u);
                     ++acc_ev;
-                    ptx::tc_fence_after_sync();
                 }
                 // mask word of a 32-column slice: entries (s0, q) | (s0 + 1, q), q chosen by word (.x: q 0-1, .y: q 2-3) and shift
                 auto mword = [](uint32_t w_hi, uint32_t w_lo, uint32_t sh) { return (((w_hi >> sh) & 0xFFFFu) << 16) | ((w_lo >> sh) & 0xFFFFu); };
-                NWB_BTRACE(leader && pair == pair0, g * 8 + 2);    // accumulator seen
-                epi_bar8();                                 // everyone is done reading sD (the d_ray_bias sums of layer 9)
-                NWB_BTRACE(leader && pair == pair0, g * 8 + 3);    // sD free
-                // this row's line in block 0 / block 1 of the layer's e5m2 image
-                uint8_t* g8a = ghost ? nullptr : dz_tile + dl.dz_off(g) + line_off;
+                NWB_BTRACE(leader && pair == pair0 + pair_step, g * 8 + 2);    // accumulator seen
+                epi_bar8();                                 // accumulator complete; everyone is done reading sD (the d_ray_bias sums of layer 9)
+                ptx::tc_fence_after_sync();
+                NWB_BTRACE(leader && pair == pair0 + pair_step, g * 8 + 3);    // sD free
+                // this row in group 0 of block 0 / block 1 of the layer's e5m2 image
+                uint8_t* g8a = ghost ? nullptr : dz_tile + dl.dz_off(g) + row * 32;
                 uint8_t* g8b = ghost ? nullptr : g8a + 16384;
                 if (g >= 10) {
                     // 128 columns: mine are [64 ch, +64) = bf16 image block ch, e5m2 groups 2 ch + i, gate entries q = ch
@@ -406,11 +421,11 @@ field_dgrad_kernel(const BwdArgs a) {
                                                      rowx, 4 * (i & 1), g8, i, row);
                     }
                 }
-                NWB_BTRACE(leader && pair == pair0, g * 8 + 4);    // leader's slices written
+                NWB_BTRACE(leader && pair == pair0 + pair_step, g * 8 + 4);    // leader's slices written
                 ptx::fence_proxy_async_smem();
                 ptx::tc_fence_before_sync();                // this thread's tcgen05.ld of the accumulator are done
                 epi_bar8();
-                NWB_BTRACE(leader && pair == pair0, g * 8 + 5);    // all slices written
+                NWB_BTRACE(leader && pair == pair0 + pair_step, g * 8 + 5);    // all slices written
                 if (leader && g >= 1) { if (rank == 0) ptx::mbar_arrive(bar_act); else ptx::mbar_arrive_cluster(act_leader); }
                 if (g == 9) {
                     // per-ray cotangent of the dir/appearance/transient bias: sum of dZ_9 over the ray's samples.  Runs

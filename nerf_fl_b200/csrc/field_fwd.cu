@@ -354,8 +354,8 @@ field_fwd_kernel(const FwdArgs a) {
         const float* cst = reinterpret_cast<const float*>(smem + kOffC);
         const SaveLayout sl{fs.kx, transient};
         uint32_t acc_ev = 0;                               // layers consumed (parity of bar_acc)
-        const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an 8-bit image block
-        const int s7 = row & 7;
+        // this thread's 16-byte chunk in an 8-bit image: quarter q = columns [64 q + 16 sub, +16) = chunk 4 q + sub
+        const uint32_t so0 = image8_chunk_off(row, sub), so1 = image8_chunk_off(row, 4 + sub);
         for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const long long p = static_cast<long long>(tile) * kTileM + row;
             const bool valid = p < a.n_points;
@@ -427,7 +427,7 @@ field_fwd_kernel(const FwdArgs a) {
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&bar_act[kSlotX]);
                 // saved 8-bit image of the encoded xyz: columns [16 sub, 16 sub + 16) = chunk `sub` of this row's line
-                if (save) *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
+                if (save) *reinterpret_cast<uint4*>(save_tile + sl.x_off() + so0) = x8;
             } else {
                 // two 64-column blocks (in_channels_xyz in (64, 128]): this thread owns columns [16 sub, 16 sub + 16) of
                 // EACH block; values go straight to their place (static register index, predicated on the owner) so that
@@ -493,8 +493,8 @@ field_fwd_kernel(const FwdArgs a) {
                     x8.z = ptx::pack4_e4m3<false>(v0[8], v0[9], v0[10], v0[11]);   x8.w = ptx::pack4_e4m3<false>(v0[12], v0[13], v0[14], v0[15]);
                     y8.x = ptx::pack4_e4m3<false>(v1[0], v1[1], v1[2], v1[3]);     y8.y = ptx::pack4_e4m3<false>(v1[4], v1[5], v1[6], v1[7]);
                     y8.z = ptx::pack4_e4m3<false>(v1[8], v1[9], v1[10], v1[11]);   y8.w = ptx::pack4_e4m3<false>(v1[12], v1[13], v1[14], v1[15]);
-                    *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
-                    *reinterpret_cast<uint4*>(save_tile + sl.x_off() + line_off + (((4 + sub) ^ s7) << 4)) = y8;
+                    *reinterpret_cast<uint4*>(save_tile + sl.x_off() + so0) = x8;
+                    *reinterpret_cast<uint4*>(save_tile + sl.x_off() + so1) = y8;
                 }
             }
 
@@ -557,7 +557,7 @@ field_fwd_kernel(const FwdArgs a) {
                     // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
                     // 16 columns are chunk 4(q%2) + sub of its row's line.  Behind the handoff, off the MMA's critical path.
                     if (save) {
-                        const uint32_t at = (q >> 1) * 16384 + line_off + (((4 * (q & 1) + sub) ^ s7) << 4);
+                        const uint32_t at = (q >> 1) * 16384 + ((q & 1) ? so1 : so0);
                         *reinterpret_cast<uint4*>(save_tile + sl.act_off(g) + at) = p8;
                         if (has_lo) *reinterpret_cast<uint4*>(save_tile + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl) + at) = l8v;
                     }

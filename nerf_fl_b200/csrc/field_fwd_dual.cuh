@@ -30,6 +30,15 @@ namespace nwb {
 #define NWB_FWD_WAIT_A(addr, par) ptx::mbar_wait_sleepy_a(addr, par)
 #endif
 
+// -DNWB_FWD_TRACE: clock64 stamps of cluster 0 / rank 0 during its SECOND quad of tiles (steady state), slot (g*2+t)*8 + k:
+//   k = 0 MMA thread sees the operand image, 1 its MMAs are issued, 2 epilogue (warp kEpiWarp0) sees the accumulator,
+//   3 its slices are written, 4 handoff issued, 5 save stores / head combine done
+#ifdef NWB_FWD_TRACE
+#define NWB_DTRACE(cond, g, t, k) do { if ((cond) && a.trace != nullptr && blockIdx.x == 0 && quad == quad0 + quad_step) a.trace[((g) * 2 + (t)) * 8 + (k)] = clock64(); } while (0)
+#else
+#define NWB_DTRACE(cond, g, t, k) do { } while (0)
+#endif
+
 constexpr int kDOffX = 0;                         // 2 x 16 KB
 constexpr int kDOffH = 32768;                     // 2 x 64 KB
 constexpr int kDStageBytes = 16384;               // this CTA's half of a weight K-block
@@ -233,6 +242,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         NWB_FWD_WAIT_A(act_a + 8 * t, (act_par >> t) & 1u);
                         act_par ^= 1u << t;
                         ptx::tc_fence_after_sync();
+                        NWB_DTRACE(lane == 0, g, t, 0);
                         int hs = dual_in_slot0(g);
                         for (int kb = 0; kb < KB; ++kb) {
                             const bool is_x = (g == 0) || (g == 4 && kb == 0);
@@ -251,6 +261,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                             __syncwarp();
                             if (++s == kDNumStages) { s = 0; ph ^= 1u; }
                         }
+                        NWB_DTRACE(lane == 0, g, t, 1);
                     }
                 }
             }
@@ -283,11 +294,10 @@ field_fwd_dual_kernel(const FwdArgs a) {
         const SaveLayout sl{fs.kx, transient};
         const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
         uint32_t acc_par = 0;                              // bit t = parity of the next phase of bar_acc[t]
-        const uint32_t line_off = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);   // this row inside an 8-bit image block
-        const int s7 = row & 7;
         const uint32_t smem_s = ptx::smem_u32(smem), cst_s = smem_s + kDOffC + sub * 64, acc_s = ptx::smem_u32(bar_acc);
         const uint32_t off0 = ptx::image_chunk_off(row, 2 * sub), off1 = ptx::image_chunk_off(row, 2 * sub + 1);   // bf16 image chunks
-        const uint32_t so0 = line_off + ((sub ^ s7) << 4), so1 = line_off + (((4 + sub) ^ s7) << 4);               // 8-bit image chunks
+        // this thread's 16-byte chunk in the 8-bit image of a layer: quarter q = columns [64 q + 16 sub, +16) = chunk 4 q + sub
+        const uint32_t so0 = image8_chunk_off(row, sub), so1 = image8_chunk_off(row, 4 + sub);                        // quarters 0, 1 (2, 3: + 16 KB)
         auto hand_over = [&](int t, bool feeds_mma) {      // after this thread's shared-memory writes of the image
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before_sync();
@@ -369,7 +379,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                 *reinterpret_cast<uint4*>(sX + ptx::image_chunk_off(row, 2 * sub + 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
                 hand_over(t, true);
                 // saved 8-bit image of the encoded xyz: columns [16 sub, 16 sub + 16) = chunk `sub` of this row's line
-                if (save && !ghost_t) *reinterpret_cast<uint4*>(save_tile_t + sl.x_off() + line_off + ((sub ^ s7) << 4)) = x8;
+                if (save && !ghost_t) *reinterpret_cast<uint4*>(save_tile_t + sl.x_off() + so0) = x8;
             }
 
             float sg0 = 0.0f, sg1 = 0.0f, c00 = 0.0f, c01 = 0.0f, c02 = 0.0f, c10 = 0.0f, c11 = 0.0f, c12 = 0.0f;   // sigma / rgb of slot 0 / 1
@@ -385,6 +395,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                     ptx::mbar_wait_sleepy_a(acc_s + 8 * t, (acc_par >> t) & 1u);
                     acc_par ^= 1u << t;
                     ptx::tc_fence_after_sync();
+                    NWB_DTRACE(threadIdx.x == kEpiWarp0 * 32, g, t, 2);
                     float hacc[5] = {0, 0, 0, 0, 0};
                     uint4 p8[4];                           // e4m3 chunks of this thread's quarters, kept until the handoff is out
                     uint32_t mlo = 0, mhi = 0;             // sign-mask entries (one 8-byte store per thread after the handoff)
@@ -407,7 +418,9 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         dual_layer_epi<true, 5, 2, 2, false, kSave>(tacc, cst_s + (ConstOff::tenc_b + 2 * 128) * 4, nullptr, cst_s + ConstOff::tsigma_w * 4,
                                                                     img_s, off0, off1, hacc, p8, mlo, mhi);
                     }
+                    NWB_DTRACE(threadIdx.x == kEpiWarp0 * 32, g, t, 3);
                     hand_over(t, !last);
+                    NWB_DTRACE(threadIdx.x == kEpiWarp0 * 32, g, t, 4);
                     if (save && tile < a.n_tiles) {
                         // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
                         // 16 columns are chunk 4(q%2) + sub of its row's line
@@ -460,6 +473,7 @@ field_fwd_dual_kernel(const FwdArgs a) {
                         }
                         epi_bar_all();                       // scratch is read before anyone rewrites it
                     }
+                    NWB_DTRACE(threadIdx.x == kEpiWarp0 * 32, g, t, 5);
                     // ---- tile outputs ---------------------------------------------------------------
                     const long long p_t = static_cast<long long>(tile) * kTileM + row;
                     if (last && p_t < a.n_points && sub == 0) {

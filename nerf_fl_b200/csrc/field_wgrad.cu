@@ -79,7 +79,8 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
     const uint32_t n_stride = static_cast<uint32_t>(u.n_src ? a.save_tile_bytes : a.dz_tile_bytes);
     const uint8_t* m_base = (u.m_src ? a.saved : a.dz) + u.m_off;
     const uint8_t* n_base = (u.n_src ? a.saved : a.dz) + u.n_off;
-    const uint32_t n_bytes = static_cast<uint32_t>(u.n_blocks) * 16384u;      // whole blocks travel, the MMA reads n_mma columns
+    // whole 32-column groups travel (the dpre block of a head unit is one group), the MMA reads n_mma columns
+    const uint32_t n_bytes = ((static_cast<uint32_t>(u.n_mma) + 31u) >> 5) * kImg8GroupBytes;
     const bool head = u.head_hi > u.head_lo;
 
     if (threadIdx.x == 0) {
@@ -109,7 +110,7 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
                 uint8_t* st = smem + s * kWgStageBytes;
                 ptx::bulk_g2s(st, m_base + static_cast<size_t>(t) * m_stride, kWgMBytes, &bar_full[s]);
                 ptx::bulk_g2s(st + kWgMBytes, n_base + static_cast<size_t>(t) * n_stride, n_bytes, &bar_full[s]);
-                if (head)
+                if (head)      // residual image of the M side, staged in the second half of the N slot
                     ptx::bulk_g2s(st + kWgMBytes + 16384, a.saved + u.lo_off + static_cast<size_t>(t) * a.save_tile_bytes, 16384, &bar_full[s]);
             }
         }
@@ -127,13 +128,13 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
                 ptx::tc_fence_after_sync();
                 const uint32_t ma = ptx::smem_u32(smem + s * kWgStageBytes), na = ma + kWgMBytes;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {            // 32 points = 4 groups of 8 rows, 1 KB apart
-                    const uint64_t ad = ptx::umma_desc_sw128(ma + j * 4096, 16384, 1024);
-                    ptx::umma_f8(tmem, ad, ptx::umma_desc_sw128(na + j * 4096, 16384, 1024), idesc, (it | j) != 0);
-                    if (u.ones) ptx::umma_f8(tmem + 256, ad, ptx::umma_desc_sw128(ones, 16384, 1024), idesc1, (it | j) != 0);
+                for (int j = 0; j < 4; ++j) {            // K = 32 points per instruction = 1 KB of every 32-column group
+                    const uint64_t ad = ptx::umma_desc_any(ma + j * kImg8KStep, kImg8DescLbo, kImg8DescSbo, kImg8DescLayout);
+                    const uint64_t nd = ptx::umma_desc_any(na + j * kImg8KStep, kImg8DescLbo, kImg8DescSbo, kImg8DescLayout);
+                    ptx::umma_f8(tmem, ad, nd, idesc, (it | j) != 0);
+                    if (u.ones) ptx::umma_f8(tmem + 256, ad, ptx::umma_desc_any(ones, kImg8DescLbo, kImg8DescSbo, kImg8DescLayout), idesc1, (it | j) != 0);
                     if (head)      // residual image (second half of the N slot) against the same dpre block, its own accumulator
-                        ptx::umma_f8(tmem + 32, ptx::umma_desc_sw128(na + 16384 + j * 4096, 16384, 1024),
-                                     ptx::umma_desc_sw128(na + j * 4096, 16384, 1024), idesc, (it | j) != 0);
+                        ptx::umma_f8(tmem + 32, ptx::umma_desc_any(na + 16384 + j * kImg8KStep, kImg8DescLbo, kImg8DescSbo, kImg8DescLayout), nd, idesc, (it | j) != 0);
                 }
                 ptx::umma_commit(&bar_empty[s]);
             }
@@ -259,7 +260,7 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
     double cost[kWgMaxUnits], total = 0;
     int sp[kWgMaxUnits], cta = 0;
     for (int i = 0; i < nu; ++i) {
-        cost[i] = kWgMBytes + 16384.0 * a.units[i].n_blocks + (a.units[i].head_hi > a.units[i].head_lo ? 16384.0 : 0.0);
+        cost[i] = kWgMBytes + 4096.0 * ((a.units[i].n_mma + 31) / 32) + (a.units[i].head_hi > a.units[i].head_lo ? 16384.0 : 0.0);
         total += cost[i];
     }
     const int budget = std::max(nu, std::min(kNumSMs, nu * n_tiles));      // one CTA per SM, never a second wave

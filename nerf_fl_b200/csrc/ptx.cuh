@@ -166,6 +166,17 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, uint32_t
     d |= 2ull << 61;
     return d;
 }
+// same with SWIZZLE_NONE ("interleaved" canonical layout: core matrices of 8 rows x 16 B, 128 contiguous bytes each).
+// MN-major operand: sbo = byte stride between 16-byte chunks along M/N, lbo = byte stride between 8-row groups along K.
+__device__ __forceinline__ uint64_t umma_desc_any(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+    uint64_t d = 0;                     // layout: 0 = no swizzle, 2 = 128 B, 4 = 64 B, 6 = 32 B
+    d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= 1ull << 46;
+    d |= static_cast<uint64_t>(layout & 7u) << 61;
+    return d;
+}
 // instruction descriptor for kind::f16, bf16 x bf16 -> fp32
 //   [4,6) D fmt=1(f32)  [7,10) A fmt=1(bf16)  [10,13) B fmt=1(bf16)  [15] A MN-major  [16] B MN-major
 //   [17,23) N>>3        [24,29) M>>4

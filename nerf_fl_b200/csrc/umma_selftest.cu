@@ -11,7 +11,7 @@ struct SelftestParams {
     uint32_t idesc;
     uint32_t a_lbo, a_sbo, a_kstep, a_every, a_kblock;
     uint32_t b_lbo, b_sbo, b_kstep, b_every, b_kblock;
-    uint32_t n_ksteps, N, a_bytes, b_bytes, f8;
+    uint32_t n_ksteps, N, a_bytes, b_bytes, f8, noswz;
 };
 
 __global__ void __launch_bounds__(128, 1)
@@ -45,7 +45,10 @@ umma_selftest_kernel(const uint8_t* __restrict__ a_img, const uint8_t* __restric
         for (uint32_t k = 0; k < p.n_ksteps; ++k) {
             const uint32_t ao = (k / p.a_every) * p.a_kblock + (k % p.a_every) * p.a_kstep;
             const uint32_t bo = (k / p.b_every) * p.b_kblock + (k % p.b_every) * p.b_kstep;
-            if (p.f8)
+            if (p.noswz)           // noswz = 1 + descriptor layout code (6 = 32 B swizzle)
+                ptx::umma_f8(tmem, ptx::umma_desc_any(a0 + ao, p.a_lbo, p.a_sbo, p.noswz - 1),
+                             ptx::umma_desc_any(b0 + bo, p.b_lbo, p.b_sbo, p.noswz - 1), p.idesc, k > 0);
+            else if (p.f8)
                 ptx::umma_f8(tmem, ptx::umma_desc_sw128(a0 + ao, p.a_lbo, p.a_sbo),
                              ptx::umma_desc_sw128(b0 + bo, p.b_lbo, p.b_sbo), p.idesc, k > 0);
             else
@@ -78,7 +81,8 @@ using namespace nwb;
 
 // variant 0: A image of (128 x K), B image of (N x K), both K-major  (forward / dgrad shape)
 // variant 1: A image of (K x 128), B image of (K x N), both MN-major (wgrad shape: D = A^T B)
-// variant 3: the 8-bit wgrad shape: A image of (K x 128) e5m2, B image of (K x N) e4m3, both MN-major, images cut into
+// variant 4: the 8-bit wgrad shape as the field kernels store it (SWIZZLE_32B images, field.cuh)
+// variant 3: the same contraction out of SWIZZLE_128B 8-bit images: A image of (K x 128) e5m2, B image of (K x N) e4m3, both MN-major, images cut into
 //            128-column blocks of (K rows x 128 B); tcgen05.mma kind::f8f6f4, K = 32 per instruction
 // overrides (host pointer, may be NULL): 11 uint32 replacing idesc, a_{lbo,sbo,kstep,every,kblock},
 // b_{...}; a zero entry keeps the default.
@@ -86,7 +90,7 @@ extern "C" int nwb_selftest_umma(const void* a_img, const void* b_img, int N, in
                                  const uint32_t* overrides, float* d_out, void* stream) {
     NWB_REQUIRE(a_img && b_img && d_out, "nwb_selftest_umma: null pointer");
     NWB_REQUIRE(N >= 16 && N <= 256 && N % 16 == 0, "nwb_selftest_umma: N must be a multiple of 16 in [16,256]");
-    NWB_REQUIRE(variant >= 0 && variant <= 3, "nwb_selftest_umma: variant must be 0..3");
+    NWB_REQUIRE(variant >= 0 && variant <= 4, "nwb_selftest_umma: variant must be 0..4");
     SelftestParams p{};
     p.N = N;
     if (variant == 0) {
@@ -107,6 +111,17 @@ extern "C" int nwb_selftest_umma(const void* a_img, const void* b_img, int N, in
         p.n_ksteps = K / 16;
         p.a_lbo = 16; p.a_sbo = 1024; p.a_kstep = 32; p.a_every = 4; p.a_kblock = 128 * 128;
         p.b_lbo = K * 128; p.b_sbo = 1024; p.b_kstep = 2048; p.b_every = 1u << 30; p.b_kblock = 0;
+    } else if (variant == 4) {
+        // variant 4: the layout the field kernels use for their 8-bit images: both MN-major, SWIZZLE_32B: 32-column groups of (K rows x 32 B), 8-row groups 256 B apart, the two
+        // 16-byte chunks of a row swapped when bit 2 of the row is set
+        NWB_REQUIRE(K % 32 == 0 && K >= 32 && K <= 128, "nwb_selftest_umma: variant 4 needs K multiple of 32, <=128");
+        p.f8 = 1; p.noswz = 1 + 6;
+        p.idesc = ptx::umma_idesc_f8(128, N, 1, 0, true, true);
+        p.a_bytes = K * 128;
+        p.b_bytes = K * N;
+        p.n_ksteps = K / 32;
+        p.a_lbo = K * 32; p.a_sbo = 256; p.a_kstep = 1024; p.a_every = 1u << 30; p.a_kblock = 0;
+        p.b_lbo = K * 32; p.b_sbo = 256; p.b_kstep = 1024; p.b_every = 1u << 30; p.b_kblock = 0;
     } else if (variant == 3) {
         NWB_REQUIRE(K % 32 == 0 && K >= 32 && K <= 128, "nwb_selftest_umma: variant 3 needs K multiple of 32, <=128");
         NWB_REQUIRE(N % 128 == 0, "nwb_selftest_umma: variant 3 needs N multiple of 128");

@@ -60,3 +60,21 @@ def from_tile_image8(img: torch.Tensor, R: int, Cc: int, dtype=torch.float8_e4m3
     """Inverse of tile_image8 -> (R, Cc) float32."""
     off = image8_offsets(R, Cc).to(img.device).flatten()
     return img.flatten()[off].view(dtype).float().reshape(R, Cc)
+
+
+# ---- SWIZZLE_32B 8-bit images: what the field kernels save for the weight-gradient contraction (csrc/field.cuh) ------
+def image8s32_offsets(R: int, Cc: int) -> torch.Tensor:
+    """SWIZZLE_32B 8-bit image: 32-column group m = c // 32 is (R rows x 32 B) contiguous, row r at r * 32, its two 16-byte
+    chunks swapped when bit 2 of r is set (Swizzle<1,4,3>: address bit 4 ^= address bit 7)."""
+    assert R % 8 == 0 and Cc % 32 == 0, (R, Cc)
+    r = torch.arange(R).unsqueeze(1)
+    c = torch.arange(Cc).unsqueeze(0)
+    return (c // 32) * (R * 32) + r * 32 + ((((c % 32) // 16) ^ ((r >> 2) & 1)) * 16) + c % 16
+
+
+def tile_image8s32(m: torch.Tensor, dtype=torch.float8_e4m3fn) -> torch.Tensor:
+    R, Cc = m.shape
+    off = image8s32_offsets(R, Cc).to(m.device).flatten()
+    out = torch.empty(R * Cc, dtype=torch.uint8, device=m.device)
+    out[off] = m.to(dtype).view(torch.uint8).flatten()
+    return out

@@ -261,6 +261,19 @@ def test_umma_f8_mn_major(N, Kd):
     assert maxerr(d, want) <= 1e-4 * Kd ** 0.5, maxerr(d, want)
 
 
+@pytest.mark.parametrize("N,Kd", [(256, 128), (128, 128), (256, 32), (96, 128), (32, 64)])
+def test_umma_f8_mn_major_swizzle32(N, Kd):
+    """The same contraction out of SWIZZLE_32B images -- the layout the field kernels store (32-column groups of rows x 32 B:
+    a warp of 32 rows writes 1 KB of contiguous bytes from registers)."""
+    gen = torch.Generator().manual_seed(N * 11 + Kd)
+    X = torch.randn(Kd, 128, generator=gen).to(torch.float8_e5m2)
+    Y = torch.randn(Kd, N, generator=gen).to(torch.float8_e4m3fn)
+    d = K.selftest_umma(layout.tile_image8s32(X.float(), torch.float8_e5m2).to(DEV),
+                        layout.tile_image8s32(Y.float(), torch.float8_e4m3fn).to(DEV), N, Kd, 4)
+    want = X.float().T @ Y.float()
+    assert maxerr(d, want) <= 1e-4 * Kd ** 0.5, maxerr(d, want)
+
+
 # ---- fused field forward (a3, a4) --------------------------------------------------------------
 def _sd_dev(sd):
     return {k: v.to(DEV).contiguous() for k, v in sd.items()}

@@ -44,7 +44,7 @@ for ph in ("dgrad", "wgrad"):
 t = tr.cpu().view(13, 8)
 if int(t.abs().sum()) != 0:
     t0 = int(t[12, 2])
-    print("dgrad block 0 first tile, cycles from the start of layer 12's epilogue:")
+    print("dgrad block 0 SECOND tile pair (steady state: weights in L2), cycles from the start of layer 12's epilogue:")
     print(" g | acc seen | sD free | leader slices done | all slices done | MMA sees dZ | MMAs issued")
     for g in range(12, -1, -1):
         r = [int(x) - t0 if int(x) else None for x in t[g]]
