@@ -260,7 +260,10 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
     double cost[kWgMaxUnits], total = 0;
     int sp[kWgMaxUnits], cta = 0;
     for (int i = 0; i < nu; ++i) {
-        cost[i] = kWgMBytes + 4096.0 * ((a.units[i].n_mma + 31) / 32) + (a.units[i].head_hi > a.units[i].head_lo ? 16384.0 : 0.0);
+        // empirical weights [B200, profiles/r02i_wgrad_split.log]: a unit's time per tile follows its 128-column blocks rather
+        // than its bytes (a head unit -- 36 KB in three copies, eight small MMAs -- takes as long as a 48 KB trunk unit);
+        // splitting by bytes left the head units' CTAs running 20 % longer than the rest
+        cost[i] = kWgMBytes + 16384.0 * a.units[i].n_blocks + (a.units[i].head_hi > a.units[i].head_lo ? 16384.0 : 0.0);
         total += cost[i];
     }
     const int budget = std::max(nu, std::min(kNumSMs, nu * n_tiles));      // one CTA per SM, never a second wave
