@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="launch the training step eagerly instead of replaying its CUDA graph")
     ap.add_argument("--no-infer", action="store_true", help="train workload: skip the configs[3] 800x800 render block")
     ap.add_argument("--no-parity", action="store_true", help="train workload: skip the loss check against the CPU oracle")
+    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: gradient exchange = our one-kernel all-reduce over NVLink peer memory inside the CUDA graph "
+                         "(default) or torch.distributed's NCCL all_reduce behind the graph")
     return ap.parse_args()
 
 
@@ -370,8 +373,12 @@ def workload_config(args, n_rays_step=None):
     else:
         name = (f"configs[3]: NeRF-W test_time render_rays (eval.py path), 800x800 synthetic image, chunk 32768, {ns}+{ns} samples, "
                 f"ray-sharded across ranks, rgb+depth gathered")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     cfg = {"workload": name, "rays_per_step_per_rank": n_rays_step if n_rays_step is not None else args.batch,
            "n_samples": ns, "n_importance": ns,
+           "gradient_exchange": ("none (1 GPU)" if world == 1 or args.workload != "train" else
+                                 ("nwb_p2p_allreduce: one kernel per rank over NVLink peer memory (CUDA IPC), inside the graph"
+                                  if args.allreduce == "p2p" else "NCCL all_reduce of the flat gradient buffer behind the graph")),
            "launch": "eager" if (args.no_graph or args.workload != "train") else "CUDA graph replay of the whole iteration",
            "l2": f"{N_ROTATE} distinct resident ray batches rotate; per-step working set (saved activation + dZ images, "
                  f">1 GB at batch 1024) exceeds the 126 MB L2"}
@@ -740,6 +747,8 @@ def run_product(args):
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
     from nerf_fl_b200.train_step import TrainStep
     state = FlatTrainState(list(c.models.values()) + [c.emb["a"], c.emb["t"]], lr=5e-4)
+    if world > 1 and args.allreduce == "p2p":
+        state.enable_p2p()
     # the public training-step API: forward, NerfWLoss, backward, NCCL all-reduce of the flat gradient buffer,
     # Adam, zero_grad -- captured once and replayed as a CUDA graph unless --no-graph
     step = TrainStep(c.models, c.emb, state, lossfn, batch=args.batch, N_samples=ns, N_importance=ni, perturb=1.0,

@@ -254,8 +254,9 @@ int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t n, float b
  * up to 4 fields whose parameters live inside the flat buffer [p, p+n): every weight-image element and constant
  * slot maps to one parameter, which is updated in place and written to the cache in the same pass (ends the
  * per-step nwb_field_pack launches); `rest` lists the flat offsets no cache refers to (int32, from
- * nwb_adam_pack_cover).  state is 32 B: the 16 B of nwb_adam_step_dev followed by a uint32 ticket (zeroed by
- * the caller once) and padding; the step advances inside the launch.  Results are identical to
+ * nwb_adam_pack_cover).  state is 48 B, zeroed by the caller once: the 16 B of nwb_adam_step_dev, a uint32 ticket, the
+ * int32 step for which the two doubles that follow (beta1^step, beta2^step, kept as running products) are valid;
+ * the step advances inside the launch.  Results are identical to
  * nwb_adam_step_dev followed by nwb_field_pack (tests/test_optim_gpu.py). */
 int nwb_adam_pack_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
                            float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
@@ -301,6 +302,27 @@ int nwb_gen_rays(int H, int W, float fx, float fy, float cx, float cy, const flo
 
 /* (f4) eval.py:201-203: out[i] = uint8(clip(x[i], 0, 1) * 255) (truncation, as numpy's astype) over n floats */
 int nwb_pack_rgb8(const float* x, int64_t n, unsigned char* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (e) multi-GPU gradient exchange over NVLink / NVSwitch peer memory -- replaces the all-reduce Lightning's DDP runs for
+ * the reference (train.py:235-236; one process per GPU).  Every rank owns one exchange region
+ *     [signal block 1 KB][flat gradient buffer: n floats][reduced slice: ceil(n / world) floats]
+ * allocated by nwb_p2p_alloc (plain cudaMalloc), exported as a 64-byte CUDA IPC handle, opened by every other rank.
+ * nwb_p2p_allreduce launches ONE kernel on `stream`: two-shot all-reduce (reduce-scatter by P2P loads, cross-GPU flag
+ * barrier, all-gather by P2P loads), sums in rank order -> bit-identical result on all ranks; in place on the gradient
+ * buffer at nwb_p2p_grad_offset() inside the own region.  No host synchronisation: capturable in a CUDA graph.  All
+ * ranks must launch it the same number of times; a peer that never arrives makes the kernel trap after ~2 s.
+ * ---------------------------------------------------------------------------------------- */
+size_t nwb_p2p_region_bytes(int64_t n_floats, int world);
+size_t nwb_p2p_grad_offset(void);
+int nwb_p2p_alloc(size_t bytes, void** ptr);                       /* zero-filled */
+int nwb_p2p_free(void* ptr);
+int nwb_p2p_export(const void* ptr, unsigned char handle[64]);
+int nwb_p2p_open(const unsigned char handle[64], void** ptr);       /* peer access enabled lazily */
+int nwb_p2p_close(void* ptr);
+/* regions[q]: base of rank q's region as mapped in this process (q == rank: the own pointer); counter: 16 zeroed bytes of
+ * local device memory owned by the communicator */
+int nwb_p2p_allreduce(void* const* regions, int rank, int world, int64_t n_floats, void* counter, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T

@@ -85,11 +85,27 @@ struct AdamPackArgs {
 __global__ void __launch_bounds__(256)
 adam_pack_kernel(const AdamPackArgs a) {
     __shared__ float s_hyp[2];
+    __shared__ double s_pow[2];
     const bool mark = a.cover != nullptr;
     int t_new = 0;
     if (threadIdx.x == 0 && !mark) {
-        t_new = *reinterpret_cast<const volatile int*>(a.state) + 1;
-        const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), t_new), bc2 = 1.0 - pow(static_cast<double>(a.beta2), t_new);
+        // beta^t as running products in double (state words 6..9, valid for the step in word 5): every block of the grid
+        // needs the step's scalars before its first update, and two double-precision pow() per block were the longest
+        // thing this launch did (FP64 runs at 1/64 rate here).  A state written from outside (resume: word 0 set, word 5
+        // not) falls back to pow() once.
+        const int t_old = *reinterpret_cast<const volatile int*>(a.state);
+        t_new = t_old + 1;
+        const volatile double* pw = reinterpret_cast<const volatile double*>(a.state + 6);
+        double b1t, b2t;
+        if (*reinterpret_cast<const volatile int*>(a.state + 5) == t_old && t_old > 0) {
+            b1t = pw[0] * static_cast<double>(a.beta1);
+            b2t = pw[1] * static_cast<double>(a.beta2);
+        } else {
+            b1t = pow(static_cast<double>(a.beta1), t_new);
+            b2t = pow(static_cast<double>(a.beta2), t_new);
+        }
+        s_pow[0] = b1t; s_pow[1] = b2t;
+        const double bc1 = 1.0 - b1t, bc2 = 1.0 - b2t;
         s_hyp[0] = static_cast<float>(static_cast<double>(a.state[1]) / bc1);
         s_hyp[1] = static_cast<float>(1.0 / sqrt(bc2));
     }
@@ -179,6 +195,9 @@ adam_pack_kernel(const AdamPackArgs a) {
             *reinterpret_cast<int*>(a.state) = t_new;
             a.state[2] = s_hyp[0];
             a.state[3] = s_hyp[1];
+            *reinterpret_cast<int*>(a.state + 5) = t_new;
+            reinterpret_cast<double*>(a.state + 6)[0] = s_pow[0];
+            reinterpret_cast<double*>(a.state + 6)[1] = s_pow[1];
             *ticket = 0u;
         }
     }
@@ -279,7 +298,7 @@ extern "C" int nwb_adam_pack_step_dev(float* p, float* g, float* m, float* v, in
                                       const nwb_field_desc* const* descs, const nwb_field_params* const* params,
                                       void* const* packed, const int32_t* rest, int64_t n_rest, void* stream) {
     NWB_REQUIRE(g && m && v && state, "nwb_adam_pack_step_dev: null pointer");
-    NWB_REQUIRE((reinterpret_cast<uintptr_t>(state) & 15u) == 0, "nwb_adam_pack_step_dev: state must be 16 B aligned (32 B long)");
+    NWB_REQUIRE((reinterpret_cast<uintptr_t>(state) & 15u) == 0, "nwb_adam_pack_step_dev: state must be 16 B aligned (48 B long)");
     return adam_pack_launch(p, g, m, v, n, beta1, beta2, eps, weight_decay, state, grad_scale, zero_grad, n_fields, descs,
                             params, packed, rest, n_rest, nullptr, stream, "nwb_adam_pack_step_dev");
 }

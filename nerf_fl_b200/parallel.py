@@ -18,7 +18,7 @@ import math
 import torch
 import torch.distributed as dist
 
-__all__ = ["FlatTrainState", "FlatAdam", "shard_range", "gather_rays", "dist_info"]
+__all__ = ["FlatTrainState", "FlatAdam", "P2PGradExchange", "shard_range", "gather_rays", "dist_info"]
 
 
 def dist_info():
@@ -52,6 +52,81 @@ def gather_rays(local: torch.Tensor, n_total: int, group=None) -> torch.Tensor:
         lo, hi = shard_range(n_total, r, world)
         parts.append(out[r * per:r * per + (hi - lo)])
     return torch.cat(parts, 0)
+
+
+class _DevArray:
+    """A raw device pointer as something torch.as_tensor can wrap without copying."""
+
+    def __init__(self, ptr: int, numel: int):
+        self.__cuda_array_interface__ = {"shape": (int(numel),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class P2PGradExchange:
+    """The gradient all-reduce as ONE kernel per rank over NVLink / NVSwitch peer memory (csrc/p2p.cu): every rank's flat
+    gradient buffer lives in a cudaMalloc'ed region that all other ranks map through CUDA IPC; ``allreduce()`` launches
+    ``nwb_p2p_allreduce`` on the current stream -- no NCCL call, no host synchronisation, so it can be captured inside the
+    training iteration's CUDA graph (``TrainStep``).  ``torch.distributed`` is used once, to exchange the 64-byte IPC
+    handles.  Sums are taken in rank order on every rank: all ranks end with bit-identical gradients."""
+
+    def __init__(self, numel: int, device: torch.device, group=None):
+        from . import _lib as L
+        rank, world = dist_info()
+        if world < 2 or device.type != "cuda":
+            raise RuntimeError("P2PGradExchange needs an initialised process group of >= 2 ranks and CUDA buffers")
+        lib = L.lib()
+        self.rank, self.world, self.numel, self.device = rank, world, int(numel), device
+        self._lib = lib
+        lib.nwb_p2p_region_bytes.restype = C.c_size_t
+        lib.nwb_p2p_region_bytes.argtypes = [C.c_int64, C.c_int]
+        lib.nwb_p2p_grad_offset.restype = C.c_size_t
+        lib.nwb_p2p_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+        lib.nwb_p2p_export.argtypes = [C.c_void_p, C.c_char_p]
+        lib.nwb_p2p_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        lib.nwb_p2p_close.argtypes = [C.c_void_p]
+        lib.nwb_p2p_free.argtypes = [C.c_void_p]
+        lib.nwb_p2p_allreduce.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
+        nbytes = lib.nwb_p2p_region_bytes(self.numel, world)
+        with torch.cuda.device(device):
+            base = C.c_void_p()
+            L.check(lib.nwb_p2p_alloc(nbytes, C.byref(base)), "nwb_p2p_alloc")
+            self._base = base.value
+            handle = C.create_string_buffer(64)
+            L.check(lib.nwb_p2p_export(self._base, handle), "nwb_p2p_export")
+            handles = [None] * world
+            dist.all_gather_object(handles, handle.raw, group=group)
+            self._regions = (C.c_void_p * world)()
+            self._opened = []
+            for q in range(world):
+                if q == rank:
+                    self._regions[q] = self._base
+                else:
+                    ptr = C.c_void_p()
+                    L.check(lib.nwb_p2p_open(handles[q], C.byref(ptr)), f"nwb_p2p_open(rank {q})")
+                    self._regions[q] = ptr.value
+                    self._opened.append(ptr.value)
+            self.counter = torch.zeros(4, dtype=torch.int32, device=device)
+            self.flat_g = torch.as_tensor(_DevArray(self._base + lib.nwb_p2p_grad_offset(), self.numel), device=device)
+            torch.cuda.synchronize(device)
+        dist.barrier(group=group)                      # every rank has mapped every region before anyone launches
+
+    def allreduce(self) -> None:
+        from . import _lib as L
+        from . import kernels as K
+        with K._timed("nwb_p2p_allreduce", self.numel, dev=self.device):
+            L.check(self._lib.nwb_p2p_allreduce(self._regions, self.rank, self.world, self.numel, self.counter.data_ptr(),
+                                                L.stream_ptr(self.device)), "nwb_p2p_allreduce")
+
+    def close(self) -> None:
+        """Unmap the peers' regions and free the own one (after a barrier: nobody may still be reading it)."""
+        if getattr(self, "_base", None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if dist.is_initialized():
+            dist.barrier()
+        for ptr in self._opened:
+            self._lib.nwb_p2p_close(ptr)
+        self._lib.nwb_p2p_free(self._base)
+        self._base, self._opened = None, []
 
 
 class FlatTrainState:
@@ -94,12 +169,15 @@ class FlatTrainState:
             p.data = self.flat_p[o:o + n].view(p.shape)
             p.grad = self.flat_g[o:o + n].view(p.shape)
             p._nwb_direct_grad = True
+        self._offs = offs
+        self._p2p = None
         self.betas, self.eps, self.weight_decay = betas, eps, weight_decay
         self.step_count = 0
         # step state of the CUDA optimizer kernel lives on the device ({int32 step, lr, lr/bc1, 1/sqrt(bc2)}), so a
         # captured CUDA graph of the whole iteration can be replayed (nwb_adam_step_dev)
         # (+ the ticket word of nwb_adam_pack_step_dev)
-        self.hyper = torch.zeros(8, dtype=torch.float32, device=dev) if dev.type == "cuda" else None
+        # 12 words: {int32 step, lr, lr/bc1, 1/sqrt(bc2), ticket, int32 step of the products, double beta1^t, double beta2^t}
+        self.hyper = torch.zeros(12, dtype=torch.float32, device=dev) if dev.type == "cuda" else None
         # (f2) fields whose packed operand caches the optimizer kernel refreshes itself: NeRF modules with every
         # parameter inside the flat buffer
         self._fused = None
@@ -124,12 +202,35 @@ class FlatTrainState:
             self.hyper[1:2].fill_(self._lr)
 
     # ---- collective -------------------------------------------------------------------------
+    def enable_p2p(self, group=None) -> bool:
+        """Move the flat gradient buffer into a peer-mapped exchange region and switch ``allreduce_grads`` from the NCCL
+        call to the one-kernel P2P all-reduce (csrc/p2p.cu).  Call once, after ``init_process_group`` and before the
+        first step / graph capture.  Returns False (and changes nothing) with a single rank or CPU buffers."""
+        if self._p2p is not None:
+            return True
+        if dist_info()[1] < 2 or not self.flat_g.is_cuda:
+            return False
+        ex = P2PGradExchange(self.numel, self.flat_g.device, group)
+        ex.flat_g.copy_(self.flat_g)
+        self.flat_g = ex.flat_g
+        for p, o in zip(self.params, self._offs):
+            p.grad = self.flat_g[o:o + p.numel()].view(p.shape)
+        self._p2p = ex
+        return True
+
+    @property
+    def p2p_enabled(self) -> bool:
+        return self._p2p is not None
+
     def allreduce_grads(self, group=None):
         """Sum over ranks, in place on the flat buffer, stream-ordered behind the wgrad kernels; the
         1/world of DDP's mean is folded into the optimizer kernel's grad_scale."""
         rank, world = dist_info()
         if world > 1:
-            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=group)
+            if self._p2p is not None:
+                self._p2p.allreduce()
+            else:
+                dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=group)
         return world
 
     def zero_grad(self):

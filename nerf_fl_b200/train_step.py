@@ -75,7 +75,9 @@ class TrainStep:
         # Adam kernels are enqueued behind the replay on the same stream (3 host calls per iteration instead of
         # ~60).  A collective inside a capture ties the graph to the communicator's internal streams and to the
         # process group's watchdog thread, and a hang there takes the whole job down.
-        self._split = dist_info()[1] > 1
+        # With FlatTrainState.enable_p2p() the exchange is one kernel of ours over peer memory (csrc/p2p.cu): no NCCL call, so
+        # the whole iteration -- all-reduce and Adam included -- is captured.
+        self._split = dist_info()[1] > 1 and not getattr(self.state, "p2p_enabled", False)
         # warm-up iterations (allocator pools, lazy module state) run on a side stream as torch's capture recipe asks;
         # they must not train: one call = one optimizer update (train.py:158-174), so the model, the Adam moments and
         # the device-resident step counter are put back afterwards.  do_step=False also keeps a warm-up from issuing
