@@ -323,6 +323,18 @@ int nwb_p2p_close(void* ptr);
 /* regions[q]: base of rank q's region as mapped in this process (q == rank: the own pointer); counter: 16 zeroed bytes of
  * local device memory owned by the communicator */
 int nwb_p2p_allreduce(void* const* regions, int rank, int world, int64_t n_floats, void* counter, void* stream);
+/* first half only (reduce-scatter): afterwards slice q of the summed gradient sits in rank q's reduced buffer, at
+ * nwb_p2p_reduced_offset(n) inside its region, nwb_p2p_slice_floats(n, world) floats per slice; the consumer is
+ * nwb_adam_pack_step_p2p, which reads the slices from the peers itself (the all-gather half never runs) */
+int nwb_p2p_reduce_scatter(void* const* regions, int rank, int world, int64_t n_floats, void* counter, void* stream);
+int64_t nwb_p2p_slice_floats(int64_t n_floats, int world);
+size_t nwb_p2p_reduced_offset(int64_t n_floats);
+/* nwb_adam_pack_step_dev with the gradient taken from the ranks' reduced slices (g itself is only cleared) */
+int nwb_adam_pack_step_p2p(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                           float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
+                           const nwb_field_desc* const* descs, const nwb_field_params* const* params,
+                           void* const* packed, const int32_t* rest, int64_t n_rest, void* const* regions, int world,
+                           void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * self-test of the tcgen05 tile engine (used by tests/ only): D(128,N) = A(128,K) * B(N,K)^T

@@ -80,7 +80,34 @@ struct AdamPackArgs {
     float beta1, beta2, eps, wd, gscale;
     int zero_grad;
     float* state;
+    // multi-GPU (csrc/p2p.cu): the summed gradient of flat offset i sits in rank (i / slice)'s reduced buffer -- read it from
+    // there (peer memory over NVLink) instead of from g; g is still cleared.  world == 0: plain g.
+    const float* red[16];
+    long long slice;
+    int world;
 };
+
+__device__ __forceinline__ float4 ld_sys_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_sys_f(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+// gradient of flat offset off (grad4: off % 4 == 0; a slice is a multiple of 4 floats, so the four share a slice)
+__device__ __forceinline__ float grad1(const AdamPackArgs& a, size_t off) {
+    if (a.world == 0) return a.g[off];
+    const long long q = static_cast<long long>(off) / a.slice;
+    return ld_sys_f(a.red[q] + (off - q * a.slice));
+}
+__device__ __forceinline__ float4 grad4(const AdamPackArgs& a, size_t off) {
+    if (a.world == 0) return *reinterpret_cast<const float4*>(a.g + off);
+    const long long q = static_cast<long long>(off) / a.slice;
+    return ld_sys_f4(a.red[q] + (off - q * a.slice));
+}
 
 __global__ void __launch_bounds__(256)
 adam_pack_kernel(const AdamPackArgs a) {
@@ -116,7 +143,7 @@ adam_pack_kernel(const AdamPackArgs a) {
         const size_t off = static_cast<size_t>(src - a.p);
         if (mark) { a.cover[off] = 1; return 0.0f; }
         float pp = a.p[off], mm = a.m[off], vv = a.v[off];
-        adam_update(pp, a.g[off], mm, vv, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
+        adam_update(pp, grad1(a, off), mm, vv, a.beta1, a.beta2, a.eps, a.wd, a.gscale, step_size, inv_sqrt_bc2);
         a.p[off] = pp; a.m[off] = mm; a.v[off] = vv;
         if (a.zero_grad) a.g[off] = 0.0f;
         return pp;
@@ -147,7 +174,7 @@ adam_pack_kernel(const AdamPackArgs a) {
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         pp[h] = reinterpret_cast<const float4*>(a.p + off)[h];
-                        gg[h] = reinterpret_cast<const float4*>(a.g + off)[h];
+                        gg[h] = grad4(a, off + 4 * h);
                         mm[h] = reinterpret_cast<const float4*>(a.m + off)[h];
                         vv[h] = reinterpret_cast<const float4*>(a.v + off)[h];
                     }
@@ -247,11 +274,14 @@ extern "C" int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t
     return NWB_OK;
 }
 
+extern "C" int64_t nwb_p2p_slice_floats(int64_t n_floats, int world);
+extern "C" size_t nwb_p2p_reduced_offset(int64_t n_floats);
+
 static int adam_pack_launch(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
                             float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
                             const nwb_field_desc* const* descs, const nwb_field_params* const* params,
                             void* const* packed, const int32_t* rest, int64_t n_rest, unsigned char* cover, void* stream,
-                            const char* who) {
+                            const char* who, void* const* regions = nullptr, int world = 0) {
     NWB_REQUIRE(n >= 1 && n < (1ll << 31) && p && n_fields >= 1 && n_fields <= kAdamMaxFields && descs && params && packed,
                 "%s: bad size / null pointer (at most %d fields)", who, kAdamMaxFields);
     NWB_REQUIRE(n_rest >= 0 && n_rest < (1ll << 31) && (n_rest == 0 || rest), "%s: bad rest list", who);
@@ -279,6 +309,16 @@ static int adam_pack_launch(float* p, float* g, float* m, float* v, int64_t n, f
     a.cover = cover;
     a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay; a.gscale = grad_scale; a.zero_grad = zero_grad;
     a.state = state;
+    if (regions != nullptr && world >= 2) {
+        NWB_REQUIRE(world <= 16, "%s: world > 16", who);
+        a.world = world;
+        a.slice = nwb_p2p_slice_floats(n, world);
+        const size_t roff = nwb_p2p_reduced_offset(n);
+        for (int q = 0; q < world; ++q) {
+            NWB_REQUIRE(regions[q] != nullptr, "%s: region %d is null", who, q);
+            a.red[q] = reinterpret_cast<const float*>(static_cast<const uint8_t*>(regions[q]) + roff);
+        }
+    }
     dim3 grid(kAdamPackBlocksX, y + 1);
     adam_pack_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
     NWB_LAUNCH_CHECK();
@@ -291,6 +331,20 @@ extern "C" int nwb_adam_pack_cover(float* p, int64_t n, int n_fields, const nwb_
     NWB_REQUIRE(cover, "nwb_adam_pack_cover: cover is null");
     return adam_pack_launch(p, nullptr, nullptr, nullptr, n, 0.f, 0.f, 0.f, 0.f, nullptr, 0.f, 0, n_fields, descs, params,
                             packed, nullptr, 0, cover, stream, "nwb_adam_pack_cover");
+}
+
+// the same launch as the second half of the multi-GPU gradient exchange: gradients are read from the ranks' reduced slices
+// (after nwb_p2p_reduce_scatter on the same stream), g is only cleared.  regions as for nwb_p2p_allreduce.
+extern "C" int nwb_adam_pack_step_p2p(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                                      float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
+                                      const nwb_field_desc* const* descs, const nwb_field_params* const* params,
+                                      void* const* packed, const int32_t* rest, int64_t n_rest, void* const* regions, int world,
+                                      void* stream) {
+    NWB_REQUIRE(g && m && v && state && regions, "nwb_adam_pack_step_p2p: null pointer");
+    NWB_REQUIRE((reinterpret_cast<uintptr_t>(state) & 15u) == 0, "nwb_adam_pack_step_p2p: state must be 16 B aligned (48 B long)");
+    NWB_REQUIRE(world >= 2, "nwb_adam_pack_step_p2p: world must be >= 2");
+    return adam_pack_launch(p, g, m, v, n, beta1, beta2, eps, weight_decay, state, grad_scale, zero_grad, n_fields, descs,
+                            params, packed, rest, n_rest, nullptr, stream, "nwb_adam_pack_step_p2p", regions, world);
 }
 
 extern "C" int nwb_adam_pack_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,

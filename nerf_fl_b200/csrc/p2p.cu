@@ -28,7 +28,10 @@ struct P2PSignal {
     unsigned int arrive[2][kP2PMaxWorld];  // written by the peers (system scope)
     unsigned int epoch;                    // launches completed by this rank (own writes only)
     unsigned int go[2];                    // block 0 -> the other blocks of this rank
-    unsigned int pad[256 - 2 * kP2PMaxWorld - 3];
+    unsigned int pad0;
+    unsigned long long stamp[6];           // %globaltimer of block 0 / thread 0 in the last launch: start, barrier A passed, phase 1
+                                           // done on this rank, barrier B passed, phase 2 done (tools/p2p_check.py prints them)
+    unsigned int pad[256 - 2 * kP2PMaxWorld - 4 - 12];
 };
 static_assert(sizeof(P2PSignal) == 1024, "signal block is 1 KB");
 
@@ -64,6 +67,12 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
     return v;
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 template <typename F>
 __device__ __forceinline__ void spin_until(F ready, const char* what) {
     const long long t0 = clock64();
@@ -97,13 +106,16 @@ __device__ __forceinline__ void p2p_barrier(const P2PArgs& a, unsigned int e, in
 
 // every block must have finished its phase-1 stores before block 0 tells the peers: count the blocks in
 __global__ void __launch_bounds__(kP2PThreads, 1)
-p2p_allreduce_kernel(const P2PArgs a, unsigned int* block_count) {
+p2p_allreduce_kernel(const P2PArgs a, unsigned int* block_count, int gather) {
     P2PSignal* mine = a.sig[a.rank];
     const unsigned int e = mine->epoch + 1;            // same on every rank: all ranks launch the same sequence
     const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
 
+    const bool stamper = blockIdx.x == 0 && threadIdx.x == 0;
+    if (stamper) mine->stamp[0] = globaltimer_ns();
     p2p_barrier(a, e, 0);
+    if (stamper) mine->stamp[1] = globaltimer_ns();
 
     // ---- phase 1: my slice of everybody's gradients, summed in rank order ----
     const long long lo = a.slice * a.rank;
@@ -131,14 +143,18 @@ p2p_allreduce_kernel(const P2PArgs a, unsigned int* block_count) {
         atomicAdd(block_count, 1u);
         if (blockIdx.x == 0) spin_until([&] { return ld_acquire_gpu(block_count) >= gridDim.x; }, "this rank's blocks");
     }
+    if (stamper) mine->stamp[2] = globaltimer_ns();
     p2p_barrier(a, e, 1);
+    if (stamper) mine->stamp[3] = globaltimer_ns();
 
-    // ---- phase 2: gather every rank's reduced slice into my g ----
-    for (long long i = 4 * tid; i < a.n; i += 4 * nth) {
+    // ---- phase 2: gather every rank's reduced slice into my g (gather == 0: the consumer -- the optimizer kernel -- reads the
+    // reduced slices from the peers itself, nwb_adam_pack_step_p2p) ----
+    for (long long i = 4 * tid; gather && i < a.n; i += 4 * nth) {
         const int q = static_cast<int>(i / a.slice);
         const float4 v = ld_peer_f4(a.red[q] + (i - a.slice * q));
         *reinterpret_cast<float4*>(a.g[a.rank] + i) = v;
     }
+    if (stamper) mine->stamp[4] = globaltimer_ns();
     // last block out resets the block counter and publishes the epoch (own memory, next launch on this stream reads it)
     __threadfence();
     __syncthreads();
@@ -194,7 +210,27 @@ extern "C" int nwb_p2p_close(void* ptr) {
 
 // regions[q] = base of rank q's exchange region as mapped in THIS process (own region: the local pointer);
 // counter: 4 zeroed bytes of local device memory (per communicator)
+static int p2p_launch(void* const* regions, int rank, int world, int64_t n_floats, void* counter, int gather, void* stream);
+
 extern "C" int nwb_p2p_allreduce(void* const* regions, int rank, int world, int64_t n_floats, void* counter, void* stream) {
+    return p2p_launch(regions, rank, world, n_floats, counter, 1, stream);
+}
+// first half only: on return (stream order) slice q of the summed gradient sits in rank q's reduced buffer
+// (nwb_p2p_reduced_slice gives the addresses); the gradient buffers themselves are left as they were
+extern "C" int nwb_p2p_reduce_scatter(void* const* regions, int rank, int world, int64_t n_floats, void* counter, void* stream) {
+    return p2p_launch(regions, rank, world, n_floats, counter, 0, stream);
+}
+// layout query shared with the optimizer kernel: floats per slice, and where rank q's reduced slice starts inside its region
+extern "C" int64_t nwb_p2p_slice_floats(int64_t n_floats, int world) {
+    if (n_floats <= 0 || world < 1) return 0;
+    const int64_t n4 = (n_floats + 3) / 4 * 4;
+    return ((n4 + world - 1) / world + 3) / 4 * 4;
+}
+extern "C" size_t nwb_p2p_reduced_offset(int64_t n_floats) {
+    return sizeof(P2PSignal) + static_cast<size_t>((n_floats + 3) / 4 * 4) * 4;
+}
+
+static int p2p_launch(void* const* regions, int rank, int world, int64_t n_floats, void* counter, int gather, void* stream) {
     NWB_REQUIRE(regions != nullptr && counter != nullptr, "nwb_p2p_allreduce: null pointer");
     NWB_REQUIRE(world >= 2 && world <= kP2PMaxWorld && rank >= 0 && rank < world, "nwb_p2p_allreduce: bad rank / world");
     NWB_REQUIRE(n_floats > 0, "nwb_p2p_allreduce: empty buffer");
@@ -212,7 +248,7 @@ extern "C" int nwb_p2p_allreduce(void* const* regions, int rank, int world, int6
     int dev = 0;
     int rc = current_device_checked(&dev);
     if (rc != NWB_OK) return rc;
-    p2p_allreduce_kernel<<<kP2PBlocks, kP2PThreads, 0, static_cast<cudaStream_t>(stream)>>>(a, static_cast<unsigned int*>(counter));
+    p2p_allreduce_kernel<<<kP2PBlocks, kP2PThreads, 0, static_cast<cudaStream_t>(stream)>>>(a, static_cast<unsigned int*>(counter), gather);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }

@@ -85,6 +85,7 @@ class P2PGradExchange:
         lib.nwb_p2p_close.argtypes = [C.c_void_p]
         lib.nwb_p2p_free.argtypes = [C.c_void_p]
         lib.nwb_p2p_allreduce.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
+        lib.nwb_p2p_reduce_scatter.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
         nbytes = lib.nwb_p2p_region_bytes(self.numel, world)
         with torch.cuda.device(device):
             base = C.c_void_p()
@@ -115,6 +116,15 @@ class P2PGradExchange:
         with K._timed("nwb_p2p_allreduce", self.numel, dev=self.device):
             L.check(self._lib.nwb_p2p_allreduce(self._regions, self.rank, self.world, self.numel, self.counter.data_ptr(),
                                                 L.stream_ptr(self.device)), "nwb_p2p_allreduce")
+
+    def reduce_scatter(self) -> None:
+        """First half only: slice q of the summed gradient ends in rank q's reduced buffer (consumer:
+        ``nwb_adam_pack_step_p2p``); ``flat_g`` keeps the local gradients."""
+        from . import _lib as L
+        from . import kernels as K
+        with K._timed("nwb_p2p_reduce_scatter", self.numel, dev=self.device):
+            L.check(self._lib.nwb_p2p_reduce_scatter(self._regions, self.rank, self.world, self.numel, self.counter.data_ptr(),
+                                                     L.stream_ptr(self.device)), "nwb_p2p_reduce_scatter")
 
     def close(self) -> None:
         """Unmap the peers' regions and free the own one (after a barrier: nobody may still be reading it)."""
@@ -237,10 +247,27 @@ class FlatTrainState:
         self.flat_g.zero_()
 
     # ---- optimizer ---------------------------------------------------------------------------
-    def adam_step(self, world: int = 1, zero_grad: bool = True):
-        """utils/__init__.py:31 Adam on the flat buffers: one CUDA launch.  No CPU path (see ``host_update``)."""
+    def adam_step(self, world: int = 1, zero_grad: bool = True, from_slices: bool = False):
+        """utils/__init__.py:31 Adam on the flat buffers: one CUDA launch.  No CPU path (see ``host_update``).
+        ``from_slices``: the gradients are the ranks' reduced slices (after ``P2PGradExchange.reduce_scatter``), read
+        from peer memory by the optimizer kernel itself."""
         self.step_count += 1
         b1, b2 = self.betas
+        if from_slices:
+            from . import _lib as L
+            from . import kernels as K
+            fz = self._fused or self._fused_setup()
+            ex = self._p2p
+            with K._timed("nwb_adam_pack_step_p2p", 0, dev=self.flat_p.device):
+                L.check(fz["fn_p2p"](self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
+                                     self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay,
+                                     self.hyper.data_ptr(), 1.0 / world, int(zero_grad), fz["n"], fz["descs"], fz["params"],
+                                     fz["packed"], fz["rest"].data_ptr(), fz["rest"].numel(), ex._regions, ex.world,
+                                     L.stream_ptr(self.flat_p.device)), "nwb_adam_pack_step_p2p")
+            for m in self.modules:
+                if hasattr(m, "_nwb_cache") and not any(m is f for f in self._fused_fields):
+                    m._nwb_dirty = True
+            return
         if self.flat_p.is_cuda and self._fused_fields:
             from . import _lib as L
             from . import kernels as K
@@ -312,8 +339,10 @@ class FlatTrainState:
         rest = torch.nonzero(cover == 0).flatten().to(torch.int32).contiguous()
         fn = L.bind("nwb_adam_pack_step_dev", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 4 +
                     [C.c_void_p, C.c_float, C.c_int] + tables + [C.c_void_p, C.c_int64, C.c_void_p])
-        self._fused = {"fn": fn, "n": n, "descs": descs, "params": params, "packed": packed, "rest": rest, "keep": keep,
-                       "covered": int(self.numel - rest.numel())}
+        fn_p2p = L.bind("nwb_adam_pack_step_p2p", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 4 +
+                        [C.c_void_p, C.c_float, C.c_int] + tables + [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p), C.c_int, C.c_void_p])
+        self._fused = {"fn": fn, "fn_p2p": fn_p2p, "n": n, "descs": descs, "params": params, "packed": packed, "rest": rest,
+                       "keep": keep, "covered": int(self.numel - rest.numel())}
         return self._fused
 
     # ---- checkpoint / resume (train.py:231 resume_from_checkpoint) -------------------------------
@@ -372,9 +401,15 @@ class FlatTrainState:
                 self.lr = lr
 
     def step(self, group=None):
-        """all-reduce + Adam: everything that follows backward in one training iteration."""
+        """all-reduce + Adam: everything that follows backward in one training iteration.  With the P2P exchange and the
+        cache-refreshing optimizer the all-gather half of the all-reduce never runs: the reduce-scatter kernel leaves
+        slice q of the summed gradient with rank q, and the optimizer kernel reads the slices over NVLink itself."""
         self.pull_lr()
-        self.adam_step(self.allreduce_grads(group))
+        if self._p2p is not None and self._fused_fields and self.flat_p.is_cuda:
+            self._p2p.reduce_scatter()
+            self.adam_step(self._p2p.world, from_slices=True)
+        else:
+            self.adam_step(self.allreduce_grads(group))
 
 
 class FlatAdam(torch.optim.Optimizer):

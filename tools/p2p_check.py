@@ -55,6 +55,15 @@ def timed(fn, iters=50):
     return t.item() * 1e3
 buf = torch.randn(n, device=dev)
 log(f"n = {n} floats ({n * 4 / 1e6:.2f} MB), world {world}: p2p all-reduce {timed(ex.allreduce):.1f} us, NCCL all_reduce {timed(lambda: dist.all_reduce(buf)):.1f} us (max over ranks, back-to-back launches)")
+torch.cuda.synchronize()
+import ctypes as C
+st = torch.zeros(6, dtype=torch.int64)
+from nerf_fl_b200 import _lib as L
+base = ex._base
+raw = torch.as_tensor(__import__("nerf_fl_b200.parallel", fromlist=["_DevArray"])._DevArray(base, 256), device=dev).view(torch.int32).cpu()
+stamps = raw[36:48].view(torch.int64)       # words 36..47 of the signal block
+d = [(int(stamps[i + 1]) - int(stamps[i])) / 1e3 for i in range(4)]
+log(f"last all-reduce launch on rank 0 (us): barrier A {d[0]:.1f}, phase 1 + local block count {d[1]:.1f}, barrier B {d[2]:.1f}, phase 2 {d[3]:.1f}")
 ex.close()
 
 # ---- (2) training steps: exchange inside the graph vs NCCL behind it -----------------------------------
