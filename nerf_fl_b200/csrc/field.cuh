@@ -163,6 +163,13 @@ __host__ __device__ __forceinline__ float dz_scale_from_amax_bits(unsigned int b
     c.u = static_cast<unsigned int>(p + 127) << 23;
     return c.f;
 }
+// Weight-gradient partials (behind the tile records of the workspace): one slot per CTA of the wgrad launch, written
+// with plain stores and summed in CTA order by wgrad_reduce_kernel -- no atomics, bit-reproducible gradients.
+//   [main: 128 rows x 256 columns, row-major like the sinks][bias: 128][heads: 9 x 128]   (floats)
+constexpr int kWgSlotMain = 128 * 256, kWgSlotBias = kWgSlotMain, kWgSlotHead = kWgSlotBias + 128;
+constexpr int kWgSlotFloats = kWgSlotHead + 9 * 128;
+constexpr size_t kWgPartialBytes = static_cast<size_t>(kNumSMs) * kWgSlotFloats * sizeof(float);
+
 struct DzLayout {
     bool transient;
     __host__ __device__ size_t dz_off(int g) const {

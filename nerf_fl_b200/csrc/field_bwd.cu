@@ -516,7 +516,7 @@ extern "C" size_t nwb_mlp_bwd_workspace_bytes(const nwb_field_desc* d, int64_t n
     if (make_shape(d, &fs) != NWB_OK || n_points <= 0) return 0;
     const DzLayout dl{(mode & NWB_MLP_TRANSIENT) != 0};
     const int64_t n_tiles = (n_points + kTileM - 1) / kTileM;
-    return kDzHeaderBytes + static_cast<size_t>(n_tiles) * dl.tile_bytes();
+    return kDzHeaderBytes + static_cast<size_t>(n_tiles) * dl.tile_bytes() + kWgPartialBytes;
 }
 
 static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const float* raw, const float* d_raw,

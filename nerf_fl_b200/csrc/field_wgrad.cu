@@ -55,6 +55,7 @@ struct WgArgs {
     size_t dz_tile_bytes, save_tile_bytes;
     int n_tiles, n_units;
     float* head_out[9];
+    float* partial;               // kNumSMs slots of kWgSlotFloats (field.cuh), behind the tile records of the workspace
     WUnit units[kWgMaxUnits];
 };
 
@@ -142,11 +143,12 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
         }
         __syncwarp();
     } else if (t1 > t0) {
-        // ---- flush: thread == D row m ------------------------------------------------------------
+        // ---- flush: thread == D row m; raw partial sums to this CTA's slot with plain stores (row-major, so that the reduce
+        // kernel reads and writes along rows), scaled and summed in CTA order by wgrad_reduce_kernel ------------
         const int quad = warp & 3;
         const int m = quad * 32 + lane;
         const uint32_t tlane = tmem + (static_cast<uint32_t>(quad * 32) << 16);
-        const float inv = 1.0f / dz_scale_from_amax_bits(__ldg(&a.hdr->amax_bits));     // exact: a power of two
+        float* slot = a.partial + static_cast<size_t>(blockIdx.x) * kWgSlotFloats;
         ptx::mbar_wait(bar_done, 0);
         ptx::tc_fence_after_sync();
         if (u.head_hi > u.head_lo) {
@@ -159,29 +161,80 @@ field_wgrad_kernel(const __grid_constant__ WgArgs a) {
                 if (n >= u.head_lo && n < u.head_hi) {
                     const float hi = (__uint_as_float(v[n]) + __uint_as_float(v[9 + n])) + __uint_as_float(v[18 + n]);
                     const float lo = (__uint_as_float(w[n]) + __uint_as_float(w[9 + n])) + __uint_as_float(w[18 + n]);
-                    atomicAdd(a.head_out[n] + u.m_base + m, fmaf(lo, 1.0f / kLoScale, hi) * inv);
+                    slot[kWgSlotHead + n * 128 + m] = fmaf(lo, 1.0f / kLoScale, hi);
                 }
         } else {
-            float* orow = u.out + static_cast<size_t>(u.m_base + m) * u.ld + u.n_base;
             for (int c0 = 0; c0 < u.n_valid; c0 += 32) {
                 uint32_t v[32];
                 ptx::tmem_ld32(tlane + c0, v);
                 ptx::tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (c0 + j < u.n_valid) atomicAdd(orow + c0 + j, __uint_as_float(v[j]) * inv);
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(slot + m * 256 + c0 + 4 * j) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             }
             if (u.ones && u.out_b != nullptr) {
                 uint32_t v[32];
                 ptx::tmem_ld32(tlane + 256, v);
                 ptx::tmem_ld_wait();
-                atomicAdd(u.out_b + u.m_base + m, __uint_as_float(v[0]) * inv);
+                slot[kWgSlotBias + m] = __uint_as_float(v[0]);
             }
         }
     }
     ptx::tc_fence_before_sync();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc<512>(tmem);
+}
+
+// Second phase: every output element belongs to exactly one unit; its value is the sum of that unit's CTAs' partials,
+// taken in CTA order (bit-reproducible), times the pass's inverse scale, ADDED to the sink (caller-zeroed accumulate
+// semantics; no other kernel touches these elements while the backward runs).  grid = (units, kWgReduceY).
+constexpr int kWgReduceY = 16;
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const __grid_constant__ WgArgs a) {
+    const WUnit& u = a.units[blockIdx.x];
+    const float inv = 1.0f / dz_scale_from_amax_bits(__ldg(&a.hdr->amax_bits));     // exact: a power of two
+    const int ns = u.splits;                    // every split has tiles (the host never gives a unit more CTAs than tiles)
+    const float* base = a.partial + static_cast<size_t>(u.cta0) * kWgSlotFloats;
+    const int tid = blockIdx.y * blockDim.x + threadIdx.x, nth = gridDim.y * blockDim.x;
+    if (u.head_hi > u.head_lo) {
+        const int nh = u.head_hi - u.head_lo;
+        for (int i = tid; i < nh * 128; i += nth) {
+            const int n = u.head_lo + i / 128, m = i % 128;
+            float acc = 0.0f;
+            for (int sp = 0; sp < ns; ++sp) acc += base[static_cast<size_t>(sp) * kWgSlotFloats + kWgSlotHead + n * 128 + m];
+            a.head_out[n][u.m_base + m] += acc * inv;
+        }
+        return;
+    }
+    // thread = (row m, column quad q), q fastest: partial rows and sink rows are both walked along their columns
+    const int nq = (u.n_valid + 3) >> 2;
+    for (int i = tid; i < nq * 128; i += nth) {
+        const int m = i / nq, q = i - m * nq;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int sp = 0; sp < ns; ++sp) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * kWgSlotFloats + m * 256 + 4 * q));
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        float* o = u.out + static_cast<size_t>(u.m_base + m) * u.ld + u.n_base + 4 * q;
+        const int left = u.n_valid - 4 * q;
+        if (left >= 4 && (reinterpret_cast<uintptr_t>(o) & 15u) == 0) {
+            float4 w = *reinterpret_cast<float4*>(o);
+            w.x += acc.x * inv; w.y += acc.y * inv; w.z += acc.z * inv; w.w += acc.w * inv;
+            *reinterpret_cast<float4*>(o) = w;
+        } else {
+            o[0] += acc.x * inv;
+            if (left > 1) o[1] += acc.y * inv;
+            if (left > 2) o[2] += acc.z * inv;
+            if (left > 3) o[3] += acc.w * inv;
+        }
+    }
+    if (u.ones && u.out_b != nullptr) {
+        for (int m = tid; m < 128; m += nth) {
+            float acc = 0.0f;
+            for (int sp = 0; sp < ns; ++sp) acc += base[static_cast<size_t>(sp) * kWgSlotFloats + kWgSlotBias + m];
+            u.out_b[u.m_base + m] += acc * inv;
+        }
+    }
 }
 
 }  // namespace nwb
@@ -197,6 +250,7 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
     a.hdr = reinterpret_cast<const DzHeader*>(ws);
     a.dz = ws + kDzHeaderBytes; a.saved = saved; a.dz_tile_bytes = dz_tile_bytes; a.save_tile_bytes = save_tile_bytes;
     a.n_tiles = n_tiles;
+    a.partial = reinterpret_cast<float*>(const_cast<uint8_t*>(ws) + kDzHeaderBytes + static_cast<size_t>(n_tiles) * dz_tile_bytes);
     int nu = 0;
     // n_cols: columns of the N-side image the MMA reads (64 for the encoded-xyz block, else 128 per block)
     auto add = [&](uint32_t m_off, int m_src, uint32_t n_off, int n_src, int n_cols, int n_valid, bool ones, float* out,
@@ -291,6 +345,8 @@ int nwb_wgrad_launch(const FieldShape& fs, const nwb_field_grads* g, const uint8
         NWB_CUDA(cudaFuncSetAttribute(field_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem));
     });
     field_wgrad_kernel<<<cta, kWgThreads, kWgSmem, st>>>(a);
+    NWB_LAUNCH_CHECK();
+    wgrad_reduce_kernel<<<dim3(nu, kWgReduceY), 256, 0, st>>>(a);
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }

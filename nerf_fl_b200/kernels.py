@@ -334,9 +334,9 @@ def field_traffic_bytes_per_point(kind: str, fine: bool) -> float:
     dpre block once per head unit."""
     desc = field_desc(63, 27, 48 if fine else 0, 16 if fine else 0)
     mode = (L.NWB_MLP_TRANSIENT if fine else 0) | L.NWB_MLP_SAVE
-    n = 128 * 1024                                   # many tiles: the workspace's 256-byte header vanishes
-    save = mlp_save_bytes(desc, n, mode) / float(n)
-    ws = mlp_bwd_workspace_bytes(desc, n, mode & ~L.NWB_MLP_SAVE) / float(n)
+    n = 128 * 1024                                   # per-point slope: the workspace's constant parts (header, wgrad partial slots) drop out
+    save = (mlp_save_bytes(desc, 2 * n, mode) - mlp_save_bytes(desc, n, mode)) / float(n)
+    ws = (mlp_bwd_workspace_bytes(desc, 2 * n, mode & ~L.NWB_MLP_SAVE) - mlp_bwd_workspace_bytes(desc, n, mode & ~L.NWB_MLP_SAVE)) / float(n)
     masks = 13 * 4096 / 128.0
     dpre_again = ((4 if fine else 3) - 1) * 128.0     # every head unit of wgrad reads the dpre block (16 KB per tile)
     return {"fwd": save, "dgrad": ws + masks, "wgrad": (save - masks) + ws + dpre_again}[kind]

@@ -334,3 +334,37 @@ def test_train_step_graph_replay_matches_eager():
     # p_* = displacement after 4 Adam steps.  Early Adam moves every weight by ~lr*sign(g), so the fp32-atomics
     # ordering noise of near-zero gradient entries shows up at full step size in a few elements: compare in L2
     assert (p_e - p_g).norm().item() <= 5e-2 * p_e.norm().item()
+
+
+def test_weight_gradients_are_bit_reproducible():
+    """The weight-gradient kernel writes per-CTA partials with plain stores and a second kernel sums them in CTA order
+    (no fp32 atomics): every tensor it owns -- all GEMM-layer weights and biases, the head weights -- must come out
+    bit-identical from two runs of the same step.  (Still atomically accumulated, outside that kernel: head biases, the
+    per-ray columns / biases of dir_encoding.0 and transient_encoding.0, the embedding tables.)"""
+    n = 1024
+    rays = syn.blender_rays(n, seed=21).to(DEV)
+    g = torch.Generator().manual_seed(4)
+    ts = torch.randint(0, 20, (n,), generator=g).to(DEV)
+    tgt = torch.rand(n, 3, generator=g).to(DEV)
+    rng = {"perturb_rand": torch.rand(n, 64, generator=g).to(DEV), "u": torch.rand(n, 64, generator=g).to(DEV)}
+
+    def grads():
+        models = {"coarse": build(1, "coarse"), "fine": build(2, "fine", True, True, beta_min=0.1)}
+        emb = embeddings(syn.make_embedding(3, 20, 48), syn.make_embedding(4, 20, 16))
+        out = render_rays(models, emb, rays, ts, 64, False, 1.0, 0.0, 64, 32768, True, rng=rng)
+        loss = sum(O.nerfw_loss(out, tgt).values())
+        named = [(f"coarse.{k}", p) for k, p in models["coarse"].named_parameters()] + \
+                [(f"fine.{k}", p) for k, p in models["fine"].named_parameters()]
+        return {k: gr.detach().clone() for (k, _), gr in zip(named, torch.autograd.grad(loss, [p for _, p in named]))}
+
+    a, b = grads(), grads()
+    check_errors()
+    owned = [k for k in a if k.endswith(".weight") and not any(s in k for s in ("dir_encoding.0", "transient_encoding.0"))]
+    owned += [k for k in a if k.endswith(".bias") and ("xyz_encoding" in k or "transient_encoding.2" in k or "transient_encoding.4" in k
+                                                       or "transient_encoding.6" in k)]
+    assert len(owned) >= 30
+    bad = [k for k in owned if not torch.equal(a[k], b[k])]
+    assert not bad, bad
+    # the feature columns of the two mixed layers come from the same kernel
+    for k in ("fine.dir_encoding.0.weight", "coarse.dir_encoding.0.weight", "fine.transient_encoding.0.weight"):
+        assert torch.equal(a[k][:, :256], b[k][:, :256]), k
