@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="launch the training step eagerly instead of replaying its CUDA graph")
     ap.add_argument("--no-infer", action="store_true", help="train workload: skip the configs[3] 800x800 render block")
     ap.add_argument("--no-parity", action="store_true", help="train workload: skip the loss check against the CPU oracle")
+    ap.add_argument("--dgrad-gen", type=int, default=0, choices=[0, 1, 2],
+                    help="dgrad kernel: 0 = the library's per-launch choice, 1 = first-generation, 2 = two-slot pair kernel (A/B runs)")
     ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: gradient exchange = our one-kernel all-reduce over NVLink peer memory inside the CUDA graph "
                          "(default) or torch.distributed's NCCL all_reduce behind the graph")
@@ -716,6 +718,8 @@ def run_product(args):
     from nerf_fl_b200.rendering import check_errors
 
     c = make_ctx(args)
+    if args.dgrad_gen:
+        K.mlp_dgrad_select(args.dgrad_gen)
     world, rank, dev, ns, ni = c.world, c.rank, c.dev, c.ns, c.ni
     warmup = max(args.warmup, 3)
 

@@ -207,6 +207,10 @@ int nwb_mlp_fwd(const nwb_field_desc* d, const void* packed, const float* rays, 
  * kernel.  Process-wide; results are identical, only speed differs (tests walk every branch with it). */
 int nwb_mlp_fwd_select(int gen);
 
+/* which dgrad kernel the backward launches: 0 (default) or 2 = CTA pairs with two tiles in flight per CTA, 1 = the
+ * first-generation kernel (two CTAs per SM).  Process-wide; only speed differs. */
+int nwb_mlp_dgrad_select(int gen);
+
 /* backward of nwb_mlp_fwd: raw (the forward's output) and its cotangent d_raw (n_points, C) ->
  * parameter gradients (ACCUMULATED into the sinks with fp32 atomics; the caller zeroes them) and the
  * per-ray cotangent d_ray_bias (n_rays,256), also accumulated (caller zeroes).  `saved` is the buffer

@@ -500,7 +500,23 @@ dz_amax_kernel(const float* __restrict__ d_raw, long long n, DzHeader* __restric
 
 }  // namespace nwb
 
+#include "field_bwd_dual.cuh"
+
 using namespace nwb;
+
+// which dgrad kernel nwb_mlp_bwd / nwb_mlp_dgrad launch: 0 (default) and 2 = the two-slot pair kernel; 1 = the first-
+// generation kernel (two CTAs per SM, one tile each).  Process-wide, read at launch time; results are identical up to the
+// fp32 summation order of the per-ray bias cotangent (tests walk both).
+// [B200, profiles/r02t_*, r02u_dgrad_ab.log] 1024 rays, kernels timed alone: static-only pass (10 layers, all 256 wide)
+// 0.121 ms two-slot vs 0.129 ms; a+t pass (13 layers, three of them 128 wide: short MMAs behind a fixed handoff chain) 0.283
+// vs 0.264 ms -- but inside the training step's graph, where the coarse and fine backward chains share the GPU, two-slot
+// everywhere is the fastest: 1.114 ms per step vs 1.118 (mixed) vs 1.127 (first generation everywhere).
+static int g_dgrad_gen = 0;
+extern "C" int nwb_mlp_dgrad_select(int gen) {
+    NWB_REQUIRE(gen >= 0 && gen <= 2, "nwb_mlp_dgrad_select: gen must be 0, 1 or 2");
+    g_dgrad_gen = gen;
+    return NWB_OK;
+}
 
 #ifdef NWB_BWD_TRACE
 static long long* g_bwd_trace = nullptr;
@@ -574,9 +590,15 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
         NWB_CONFIGURE_ONCE(configured, {
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            NWB_CUDA(cudaFuncSetAttribute(field_dgrad_dual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kB2Smem));
         });
-        const int grid = 2 * std::min((a.n_tiles + 1) / 2, kNumSMs);      // CTA pairs, two CTAs per SM
-        field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+        if (g_dgrad_gen == 1) {
+            const int grid = 2 * std::min((a.n_tiles + 1) / 2, kNumSMs);      // CTA pairs, two CTAs per SM
+            field_dgrad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(a);
+        } else {
+            const int grid = 2 * std::min((a.n_tiles + 3) / 4, kNumSMs / 2);  // CTA pairs, one CTA per SM, two tiles in flight each
+            field_dgrad_dual_kernel<<<grid, kB2Threads, kB2Smem, st>>>(a);
+        }
         NWB_LAUNCH_CHECK();
     }
     if (run_wgrad)

@@ -348,6 +348,12 @@ def mlp_fwd_select(gen: int) -> None:
     L.check(_fn("nwb_mlp_fwd_select", [_i])(int(gen)), "nwb_mlp_fwd_select")
 
 
+def mlp_dgrad_select(gen: int) -> None:
+    """Which dgrad kernel the backward launches: 0 / 2 = two-slot pair kernel (default); 1 = first-generation kernel (parity
+    tests walk both)."""
+    L.check(_fn("nwb_mlp_dgrad_select", [_i])(int(gen)), "nwb_mlp_dgrad_select")
+
+
 def mlp_bwd_workspace_bytes(desc, n_points: int, mode: int) -> int:
     return _fn("nwb_mlp_bwd_workspace_bytes", [C.POINTER(L.FieldDesc), _i64, _u32], _sz)(C.byref(desc), n_points, mode)
 

@@ -207,10 +207,21 @@ def test_field_forward_forced_generation(gen, n_tiles):
     assert maxerr(got, want) <= 2e-3 * max(1.0, want.abs().max().item()), maxerr(got, want)
 
 
-@pytest.mark.parametrize("n_tiles", [297, 640, 1024])
-def test_field_backward_beyond_one_round(n_tiles):
-    """dgrad (296 resident CTAs) and wgrad (tile ranges per CTA) at more than one round of tiles: all parameter
-    gradients of NeRF.forward under a smooth cotangent against autograd through the oracle's bf16-operand model."""
+@pytest.mark.parametrize("dgrad_gen", [1, 2])
+@pytest.mark.parametrize("n_tiles", [297, 640, 1024, 298])
+def test_field_backward_beyond_one_round(n_tiles, dgrad_gen):
+    """dgrad (both kernels: the two-slot pair kernel walks quads of four tiles per cluster, 296 per round, with ghost
+    tiles in the last quad; the first-generation kernel 296 resident CTAs) and wgrad (tile ranges per CTA) at more than one
+    round of tiles: all parameter gradients of NeRF.forward under a smooth cotangent against autograd through the oracle's
+    operand-rounding model."""
+    K.mlp_dgrad_select(dgrad_gen)
+    try:
+        _field_backward_case(n_tiles, dgrad_gen)
+    finally:
+        K.mlp_dgrad_select(0)
+
+
+def _field_backward_case(n_tiles, dgrad_gen):
     n_points = n_tiles * 128 - 5
     g = torch.Generator().manual_seed(n_tiles)
     x = torch.rand(n_points, 154, generator=g) * 2 - 1
@@ -228,7 +239,7 @@ def test_field_backward_beyond_one_round(n_tiles):
     keys = list(want)
     rel_all = _rel(got, want, keys)
     worst = max((_rel(got, want, [k]), k) for k in keys)
-    record(f"field_bwd_{n_tiles}_tiles", grad_rel_vs_operand_model=rel_all, worst_tensor=worst[0], worst_tensor_name=worst[1])
+    record(f"field_bwd_{n_tiles}_tiles_gen{dgrad_gen}", grad_rel_vs_operand_model=rel_all, worst_tensor=worst[0], worst_tensor_name=worst[1])
     # random per-sample cotangents: gates within bf16 rounding of zero differ between two bf16 forwards that sum in
     # different orders, so a few per-sample terms flip; over >= 38 000 points they average out
     assert rel_all <= 2e-2, (rel_all, worst)

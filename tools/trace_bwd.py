@@ -22,7 +22,9 @@ grads = {k: torch.zeros_like(v) for k, v in sd.items()}
 d_rb = torch.zeros(n_rays, 256, device=DEV)
 ws = K.aligned_empty(K.mlp_bwd_workspace_bytes(desc, n_rays * S, mode), DEV, 16)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
-tr = torch.zeros(8 * 13, dtype=torch.int64, device=DEV)
+tr = torch.zeros(8 * 13 * 2, dtype=torch.int64, device=DEV)
+GEN = int(os.environ.get("NWB_DGRAD_GEN", "2"))
+K.mlp_dgrad_select(GEN)
 fn = L.lib().nwb_debug_set_bwd_trace
 fn.argtypes = [C.c_void_p]; fn.restype = None
 for ph in ("dgrad", "wgrad"):
@@ -41,7 +43,17 @@ for ph in ("dgrad", "wgrad"):
     ms = sorted(ts)[len(ts) // 2]
     fl = (1296896 if ph == "dgrad" else 1368320) * n_rays * S
     print(f"{ph}: rays={n_rays} S={S}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s  {ms * 1e3 / (n_rays * S / 1e3):.3f} us/kpt")
-t = tr.cpu().view(13, 8)
+if GEN == 2 and int(tr.abs().sum()) != 0:
+    t = tr.cpu().view(13, 2, 8)
+    t0 = int(t[12, 0, 2])
+    print("two-slot dgrad kernel, cluster 0 / rank 0, SECOND quad (steady state), cycles from slot 0's layer-12 epilogue start:")
+    print(" g t | step top | before acc wait | acc seen | slices written | handoff out | MMA sees dZ | MMAs issued")
+    for g in range(12, -1, -1):
+        for sl in range(2):
+            r = [int(x) - t0 if int(x) else None for x in t[g, sl]]
+            print(f"{g:2d} {sl} | {r[6]} | {r[5]} | {r[2]} | {r[3]} | {r[4]} | {r[0]} | {r[1]}")
+    sys.exit(0)
+t = tr.cpu()[:104].view(13, 8)
 if int(t.abs().sum()) != 0:
     t0 = int(t[12, 2])
     print("dgrad block 0 SECOND tile pair (steady state: weights in L2), cycles from the start of layer 12's epilogue:")
