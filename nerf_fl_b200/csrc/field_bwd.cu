@@ -94,7 +94,7 @@ struct BwdArgs {
 //   are swapped when bit 2 of the row is set (SWIZZLE_32B); a warp's 32 rows are 1 KB of contiguous bytes
 template <bool kAcc, int kHeads, bool kMask>
 __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, const float* dp, uint32_t negmask,
-                                          uint32_t blk_s, uint32_t rowx, int cb, uint8_t* g8, int ps, int row) {
+                                          uint32_t blk_s, uint32_t rowx, int cb, uint8_t* g8, int ps, int row, uint32_t s8 = 0) {
     float x[32];
     if (kAcc) {
         uint32_t v[32];
@@ -123,14 +123,21 @@ __device__ __forceinline__ void bwd_slice(uint32_t taddr, const float* hwl, cons
     for (int q = 0; q < 4; ++q)
         ptx::sts_u4(blk_s + (rowx ^ static_cast<uint32_t>((cb + q) << 4)), pack_bf16(x[8 * q], x[8 * q + 1]), pack_bf16(x[8 * q + 2], x[8 * q + 3]),
                     pack_bf16(x[8 * q + 4], x[8 * q + 5]), pack_bf16(x[8 * q + 6], x[8 * q + 7]));
-    if (g8 != nullptr) {
+    // s8 != 0: the same 32 bytes go to a shared-memory copy of the image block instead (staged for one bulk store per layer)
+    if (g8 != nullptr || s8 != 0) {
         uint4 lo, hi;
         lo.x = ptx::pack4_e5m2(x[0], x[1], x[2], x[3]);     lo.y = ptx::pack4_e5m2(x[4], x[5], x[6], x[7]);
         lo.z = ptx::pack4_e5m2(x[8], x[9], x[10], x[11]);   lo.w = ptx::pack4_e5m2(x[12], x[13], x[14], x[15]);
         hi.x = ptx::pack4_e5m2(x[16], x[17], x[18], x[19]); hi.y = ptx::pack4_e5m2(x[20], x[21], x[22], x[23]);
         hi.z = ptx::pack4_e5m2(x[24], x[25], x[26], x[27]); hi.w = ptx::pack4_e5m2(x[28], x[29], x[30], x[31]);
-        uint8_t* dst = g8 + ps * kImg8GroupBytes;
-        if (row & 4) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
+        if (s8 != 0) {
+            const uint32_t d = s8 + ps * kImg8GroupBytes;
+            if (row & 4) { ptx::sts_u4(d, hi.x, hi.y, hi.z, hi.w); ptx::sts_u4(d + 16, lo.x, lo.y, lo.z, lo.w); }
+            else { ptx::sts_u4(d, lo.x, lo.y, lo.z, lo.w); ptx::sts_u4(d + 16, hi.x, hi.y, hi.z, hi.w); }
+        } else {
+            uint8_t* dst = g8 + ps * kImg8GroupBytes;
+            if (row & 4) ptx::st_global_256(dst, hi, lo); else ptx::st_global_256(dst, lo, hi);
+        }
     }
 }
 

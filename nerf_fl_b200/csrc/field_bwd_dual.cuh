@@ -26,12 +26,29 @@ static_assert(kB2Threads * kB2MaxRegs >= 128 * kB2RegsWg0 + kB2EpiWarps * 32 * k
 // 128 rows are contiguous in the slab image.  (32-row stages of 4 KB copies, as in the first-generation kernel, deliver
 // ~29 B/clk/SM from L2 against the 32 B/clk the tensor pipe consumes: the MMA phase of a layer took 4 700 cycles for
 // 2 048 of tensor work, profiles/r02r_trace_bwd_dual.log; 16 KB copies sustain ~55-64 B/clk.)
+#ifndef NWB_DGRAD_STAGE       // default: 3 x 32 KB ring of 16 KB copies, e5m2 images stored from registers
 constexpr int kB2Stages = 3;
-constexpr int kB2CopyBytes = 16384;
+constexpr int kB2RowsLog2 = 7;                               // contraction rows per stage = 128
+constexpr bool kB2Stage8 = false;
+#else                         // experiment (-DNWB_DGRAD_STAGE): e5m2 image staged in shared memory + one bulk store per layer, paid
+                              // for with a 4 x 16 KB ring of 8 KB copies.  [B200, profiles/r02w_*] SLOWER: 0.309 vs 0.279 ms (a+t
+                              // pass), 0.133 vs 0.119 (static) -- the slices got longer, not shorter (shared memory now carries the
+                              // bf16 image, the staged image, the bulk store's read and both MMA operands), and the MMA phase too
+                              // (8 KB copies)
+constexpr int kB2Stages = 4;
+constexpr int kB2RowsLog2 = 6;                               // 64
+constexpr bool kB2Stage8 = true;
+#endif
+constexpr int kB2Rows = 1 << kB2RowsLog2;
+constexpr int kB2CopyBytes = kB2Rows * 128;
 constexpr int kB2StageBytes = 2 * kB2CopyBytes;
 constexpr int kB2OffD = 0;                                   // 2 x 64 KB
 constexpr int kB2OffW = 2 * 65536;
-constexpr int kB2OffBar = kB2OffW + kB2Stages * kB2StageBytes;
+// (experiment) staged e5m2 image of the layer being converted (32 KB): register -> global stores move ~32 B/clk/SM and cost
+// a step of the chain ~1 000 of its ~4 000 cycles (profiles/r02t NOSTORE experiment); the idea was shared-memory stores plus
+// one bulk copy per layer issued by an otherwise idle warp
+constexpr int kB2OffS = kB2OffW + kB2Stages * kB2StageBytes;
+constexpr int kB2OffBar = kB2OffS + (kB2Stage8 ? 32768 : 0);
 constexpr int kB2Smem = kB2OffBar + 512;
 static_assert(kB2Smem <= 232448, "dual-slot dgrad exceeds the 227 KB shared-memory limit");
 
@@ -58,7 +75,9 @@ field_dgrad_dual_kernel(const BwdArgs a) {
     uint64_t* bar_empty = bar_full + kB2Stages;
     uint64_t* bar_acc = bar_empty + kB2Stages;                  // [2]
     uint64_t* bar_act = bar_acc + 2;                            // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_act + 2);
+    uint64_t* bar_staged = bar_act + 2;                         // epilogue warps -> store thread: the layer's e5m2 image is in sS
+    uint64_t* bar_free = bar_staged + 1;                        // store thread -> epilogue warps: sS has been read out
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_free + 1);
     uint32_t* s_woff = tmem_slot + 2;                           // [kMaxG]
     float* s_hb = reinterpret_cast<float*>(s_woff + kMaxG + 1); // [9] head-bias gradient partials
 
@@ -77,6 +96,8 @@ field_dgrad_dual_kernel(const BwdArgs a) {
         }
         for (int s = 0; s < kB2Stages; ++s) { ptx::mbar_init(&bar_full[s], rank == 0 ? 2 : 1); ptx::mbar_init(&bar_empty[s], 1); }
         for (int t = 0; t < 2; ++t) { ptx::mbar_init(&bar_acc[t], 1); ptx::mbar_init(&bar_act[t], 2 * kB2EpiWarps); }
+        ptx::mbar_init(bar_staged, kB2EpiWarps);
+        ptx::mbar_init(bar_free, 1);
         ptx::fence_mbar_init();
         for (int g = 0; g < kMaxG; ++g) s_woff[g] = static_cast<uint32_t>(fs.w_off(g));
         for (int i = 0; i < 9; ++i) s_hb[i] = 0.0f;
@@ -100,7 +121,7 @@ field_dgrad_dual_kernel(const BwdArgs a) {
             for (int quad = quad0; quad < n_quads; quad += quad_step) {
                 for (int g = nl - 1; g >= 1; --g) {
                     const uint8_t* wsrc = a.packed + s_woff[g];
-                    const int KH = (g >= 10) ? 1 : 2, NC = fs.layer_n(g, a.mode) >> 7, PN = fs.packed_n(g);
+                    const int KH = (g >= 10) ? 1 : 2, NC = fs.layer_n(g, a.mode) >> kB2RowsLog2, PN = fs.packed_n(g);
                     const int kshift = ((g == 4) ? fs.kx : 0) + static_cast<int>(rank) * KH;   // layer 4: skip the xyz slab
                     for (int t = 0; t < 2; ++t) {
                         for (int c = 0; c < NC; ++c, ++it) {
@@ -110,7 +131,7 @@ field_dgrad_dual_kernel(const BwdArgs a) {
                             const uint32_t s = it % kB2Stages;
                             ptx::mbar_wait_sleepy_a(empty_s + 8 * s, ((it / kB2Stages) & 1u) ^ 1u);
                             ptx::mbar_arrive_expect_tx(&bar_full[s], static_cast<uint32_t>(KH) * kB2CopyBytes);
-                            for (int kl = 0; kl < KH; ++kl)     // rows [128 c, +128) of k-block kl + kshift: 16 KB contiguous
+                            for (int kl = 0; kl < KH; ++kl)     // rows [kB2Rows c, +kB2Rows) of k-block kl + kshift: contiguous in the slab image
                                 ptx::bulk_g2s(sW + s * kB2StageBytes + kl * kB2CopyBytes,
                                               wsrc + static_cast<size_t>(kl + kshift) * PN * 128 + c * kB2CopyBytes, kB2CopyBytes, &bar_full[s]);
                         }
@@ -128,7 +149,7 @@ field_dgrad_dual_kernel(const BwdArgs a) {
             uint32_t it = 0, act_par = 0;
             for (int quad = quad0; quad < n_quads; quad += quad_step) {
                 for (int g = nl - 1; g >= 1; --g) {
-                    const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> 7;
+                    const int KBO = (g >= 10) ? 2 : 4, NC = fs.layer_n(g, a.mode) >> kB2RowsLog2;
                     const uint32_t idesc = ptx::umma_idesc_bf16(256, 64 * KBO, false, true);
                     for (int t = 0; t < 2; ++t) {
                         const uint32_t da = ptx::smem_u32(smem + kB2OffD + t * 65536);
@@ -147,9 +168,11 @@ field_dgrad_dual_kernel(const BwdArgs a) {
                             // D(256 x 64 KBO) += dZ(128 rows per CTA x 16 contraction columns, K-major) . W(16 n-rows x 64 KBO k-columns,
                             // MN-major: 8-row groups 1 KB apart, my k-blocks kB2CopyBytes apart inside the stage)
 #pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                ptx::umma2_bf16(dcol, ptx::umma_desc_sw128(da + (2 * c + (j >> 2)) * 16384 + (j & 3) * 32, 16, 1024),
+                            for (int j = 0; j < kB2Rows / 16; ++j) {
+                                const int col = c * kB2Rows + 16 * j;            // first contraction column of this MMA
+                                ptx::umma2_bf16(dcol, ptx::umma_desc_sw128(da + (col >> 6) * 16384 + ((col & 63) >> 4) * 32, 16, 1024),
                                                 ptx::umma_desc_sw128(wb + j * 2048, kB2CopyBytes, 1024), idesc, (c | j) != 0);
+                            }
                             ptx::umma2_commit_both(empty_a + 8 * s);
                         }
                         ptx::umma2_commit_both(acc_a + 8 * t);
@@ -163,7 +186,7 @@ field_dgrad_dual_kernel(const BwdArgs a) {
             uint32_t it = 0;
             for (int quad = quad0; quad < n_quads; quad += quad_step) {
                 for (int g = nl - 1; g >= 1; --g) {
-                    const int n = 2 * (fs.layer_n(g, a.mode) >> 7);
+                    const int n = 2 * (fs.layer_n(g, a.mode) >> kB2RowsLog2);
                     for (int c = 0; c < n; ++c, ++it) {
 #ifdef NWB_DGRAD_NOWEIGHTS
                         continue;
@@ -174,6 +197,29 @@ field_dgrad_dual_kernel(const BwdArgs a) {
                     }
                 }
             }
+        }
+        __syncwarp();
+    } else if (warp == 2 && kB2Stage8) {
+        // ============================ image store: one bulk copy per (layer, slot) =================
+        if (lane == 0) {
+            const DzLayout dl{transient};
+            uint32_t k = 0;
+            for (int quad = quad0; quad < n_quads; quad += quad_step) {
+                for (int g = nl - 1; g >= 0; --g) {
+                    const uint32_t bytes = (g <= 8 || (g == 9 && transient)) ? 32768u : 16384u;
+                    for (int t = 0; t < 2; ++t, ++k) {
+                        const int tile = 4 * quad + 2 * t + static_cast<int>(rank);
+                        ptx::mbar_wait_sleepy(bar_staged, k & 1u);
+                        if (tile < a.n_tiles) {
+                            ptx::bulk_s2g(a.dz + static_cast<size_t>(tile) * a.dz_tile_bytes + dl.dz_off(g), smem + kB2OffS, bytes);
+                            ptx::bulk_commit();
+                            ptx::bulk_wait_read<0>();
+                        }
+                        ptx::mbar_arrive(bar_free);
+                    }
+                }
+            }
+            ptx::bulk_wait_all<0>();
         }
         __syncwarp();
     }
@@ -194,12 +240,16 @@ field_dgrad_dual_kernel(const BwdArgs a) {
         const uint32_t rowx = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128) | static_cast<uint32_t>((row & 7) << 4);
         const uint32_t smem_s = ptx::smem_u32(smem), acc_s = ptx::smem_u32(bar_acc);
         const uint32_t act_leader = ptx::mapa(ptx::smem_u32(bar_act), 0);
-        uint32_t acc_par = 0;
+        uint32_t acc_par = 0, step_k = 0;
+        const uint32_t s8row = kB2Stage8 ? smem_s + kB2OffS + row * 32 : 0u;     // this row in group 0 of block 0 of the staged image
         auto hand_over = [&](int t, bool feeds_mma) {
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before_sync();
             __syncwarp();
-            if (lane == 0 && feeds_mma) { if (rank == 0) ptx::mbar_arrive(&bar_act[t]); else ptx::mbar_arrive_cluster(act_leader + 8 * t); }
+            if (lane == 0) {
+                if (feeds_mma) { if (rank == 0) ptx::mbar_arrive(&bar_act[t]); else ptx::mbar_arrive_cluster(act_leader + 8 * t); }
+                if (kB2Stage8) ptx::mbar_arrive(bar_staged);
+            }
         };
         auto mword = [](uint32_t e_hi, uint32_t e_lo) { return (e_hi << 16) | e_lo; };
         // ReLU gate entries of this thread's columns for step (g, t) of a quad (forward layout [sub][row] x 4 uint16, entry q of
@@ -320,38 +370,44 @@ field_dgrad_dual_kernel(const BwdArgs a) {
                         const uint32_t sh = 16u * static_cast<uint32_t>(g <= 7 ? (cq & 1) : (cq >> 1));
                         e0 = (e0 >> sh) & 0xFFFFu; e1 = (e1 >> sh) & 0xFFFFu; e2 = (e2 >> sh) & 0xFFFFu; e3 = (e3 >> sh) & 0xFFFFu;
                     }
+                    if (kB2Stage8) {                            // the previous step's image has left the staging buffer
+                        if (step_k > 0) ptx::mbar_wait_sleepy(bar_free, (step_k - 1) & 1u);
+                        ++step_k;
+                    }
                     if (g == 8) epi_bar16();                    // every warp is done with layer 9's d_ray_bias sums over this image
                     // this row in group 0 of block 0 / block 1 of the layer's e5m2 image
 #ifdef NWB_DGRAD_NOSTORE        // timing experiment only: no dZ images are written
                     uint8_t* g8a = nullptr;
                     uint8_t* g8b = nullptr;
 #else
-                    uint8_t* g8a = ghost ? nullptr : dz_tile + dl.dz_off(g) + row * 32;
-                    uint8_t* g8b = ghost ? nullptr : g8a + 16384;
+                    uint8_t* g8a = (ghost || kB2Stage8) ? nullptr : dz_tile + dl.dz_off(g) + row * 32;
+                    uint8_t* g8b = (ghost || kB2Stage8) ? nullptr : g8a + 16384;
 #endif
+                    const uint32_t s8a = s8row, s8b = s8row ? s8row + 16384 : 0u;
                     if (g >= 10) {
                         const uint32_t blk = sD_s + (cq >> 1) * 16384;
-                        if (g == 12) bwd_slice<false, 5, true>(0, hwl, dph, mword(e0, e1), blk, rowx, 4 * (cq & 1), g8a, cq, row);
-                        else bwd_slice<true, 0, true>(tacc + 32 * cq, nullptr, nullptr, mword(e0, e1), blk, rowx, 4 * (cq & 1), g8a, cq, row);
+                        if (g == 12) bwd_slice<false, 5, true>(0, hwl, dph, mword(e0, e1), blk, rowx, 4 * (cq & 1), g8a, cq, row, s8a);
+                        else bwd_slice<true, 0, true>(tacc + 32 * cq, nullptr, nullptr, mword(e0, e1), blk, rowx, 4 * (cq & 1), g8a, cq, row, s8a);
                     } else if (g == 9) {
-                        bwd_slice<false, 3, true>(0, hwl, dph, mword(e0, e1), sD_s + (cq >> 1) * 16384, rowx, 4 * (cq & 1), g8a, cq, row);
+                        bwd_slice<false, 3, true>(0, hwl, dph, mword(e0, e1), sD_s + (cq >> 1) * 16384, rowx, 4 * (cq & 1), g8a, cq, row, s8a);
                         if (transient)
                             bwd_slice<true, 0, true>(tacc + 128 + 32 * cq, nullptr, nullptr, mword(e2, e3), sD_s + (2 + (cq >> 1)) * 16384, rowx, 4 * (cq & 1),
-                                                     g8b, cq, row);
+                                                     g8b, cq, row, s8b);
                     } else {
                         uint8_t* g8 = (cq >> 1) ? g8b : g8a;
+                        const uint32_t s8 = (cq >> 1) ? s8b : s8a;
                         const uint32_t blk = sD_s + cq * 16384;
                         const uint32_t tcol = tacc + 64 * cq;
                         const int ps0 = 2 * (cq & 1);
                         if (g == 8) {
-                            bwd_slice<true, 0, false>(tcol, nullptr, nullptr, 0u, blk, rowx, 0, g8, ps0, row);
-                            bwd_slice<true, 0, false>(tcol + 32, nullptr, nullptr, 0u, blk, rowx, 4, g8, ps0 + 1, row);
+                            bwd_slice<true, 0, false>(tcol, nullptr, nullptr, 0u, blk, rowx, 0, g8, ps0, row, s8);
+                            bwd_slice<true, 0, false>(tcol + 32, nullptr, nullptr, 0u, blk, rowx, 4, g8, ps0 + 1, row, s8);
                         } else if (g == 7) {
-                            bwd_slice<true, 1, true>(tcol, hwl, dph, mword(e0, e1), blk, rowx, 0, g8, ps0, row);
-                            bwd_slice<true, 1, true>(tcol + 32, hwl + 1, dph, mword(e2, e3), blk, rowx, 4, g8, ps0 + 1, row);
+                            bwd_slice<true, 1, true>(tcol, hwl, dph, mword(e0, e1), blk, rowx, 0, g8, ps0, row, s8);
+                            bwd_slice<true, 1, true>(tcol + 32, hwl + 1, dph, mword(e2, e3), blk, rowx, 4, g8, ps0 + 1, row, s8);
                         } else {
-                            bwd_slice<true, 0, true>(tcol, nullptr, nullptr, mword(e0, e1), blk, rowx, 0, g8, ps0, row);
-                            bwd_slice<true, 0, true>(tcol + 32, nullptr, nullptr, mword(e2, e3), blk, rowx, 4, g8, ps0 + 1, row);
+                            bwd_slice<true, 0, true>(tcol, nullptr, nullptr, mword(e0, e1), blk, rowx, 0, g8, ps0, row, s8);
+                            bwd_slice<true, 0, true>(tcol + 32, nullptr, nullptr, mword(e2, e3), blk, rowx, 4, g8, ps0 + 1, row, s8);
                         }
                     }
                     NWB_B2TRACE(et == 0, g, t, 3);
