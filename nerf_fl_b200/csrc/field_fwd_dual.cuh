@@ -70,9 +70,25 @@ template <bool kRelu, int kHeads, int kHeadQ, int kNQ, bool kRayBias, bool kSave
 __device__ __forceinline__ void dual_layer_epi(uint32_t tacc, uint32_t bias_s, const float* __restrict__ rbias, uint32_t hw_s,
                                                uint32_t img_s, uint32_t off0, uint32_t off1, float (&hacc)[5], uint4 (&p8)[4],
                                                uint32_t& mlo, uint32_t& mhi) {
+#ifdef NWB_FWD_LD_PAIRS
+    // inference: the accumulator slices of two quarters are requested together (tcgen05.ld costs ~230 cycles from issue to
+    // wait::ld alone, ~160 each in pairs: tools/csrc/tmem_probe.cu); the saving build has no registers to spare
+    uint32_t vn[16];
+#endif
 #pragma unroll
     for (int q = 0; q < kNQ; ++q) {
         uint32_t v[16];
+#ifdef NWB_FWD_LD_PAIRS
+        if (!kSave) {
+            if ((q & 1) == 0) {
+                ptx::tmem_ld16(tacc + q * 64, v);
+                if (q + 1 < kNQ) ptx::tmem_ld16(tacc + (q + 1) * 64, vn);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = vn[i];
+            }
+        } else
+#endif
         ptx::tmem_ld16(tacc + q * 64, v);
         float4 b[4];
 #pragma unroll
@@ -80,6 +96,9 @@ __device__ __forceinline__ void dual_layer_epi(uint32_t tacc, uint32_t bias_s, c
             if (kRayBias) b[i] = __ldg(reinterpret_cast<const float4*>(rbias + q * 64) + i);
             else b[i] = ptx::lds_f4(bias_s + q * 256 + i * 16);
         }
+#ifdef NWB_FWD_LD_PAIRS
+        if (kSave || (q & 1) == 0)
+#endif
         ptx::tmem_ld_wait();
         float x[16];
 #pragma unroll
