@@ -440,7 +440,11 @@ field_fwd_dual_kernel(const FwdArgs a) {
                     NWB_DTRACE(threadIdx.x == kEpiWarp0 * 32, g, t, 3);
                     hand_over(t, !last);
                     NWB_DTRACE(threadIdx.x == kEpiWarp0 * 32, g, t, 4);
+#ifdef NWB_FWD_NOSTORE          // timing experiment only: conversions done, nothing written
+                    if (save && tile < a.n_tiles && p8[0].x == 0x12345678u && mlo == 0x9abcdefu) {
+#else
                     if (save && tile < a.n_tiles) {
+#endif
                         // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
                         // 16 columns are chunk 4(q%2) + sub of its row's line
                         const bool four = (g <= 8) || (g == 9 && transient);
