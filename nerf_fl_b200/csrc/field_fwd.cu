@@ -194,6 +194,100 @@ __device__ __forceinline__ int layer_quarters(int g, bool transient) {
 }
 __device__ __forceinline__ int first_quarter(int g) { return g <= 10 ? 4 * g : 42 + 2 * (g - 11); }   // transient chain: 40, 42, 44
 __device__ __forceinline__ int out_slot(int g, int q) { return (first_quarter(g) + q) % kHSlots; }
+
+// ---- one layer's epilogue of the one-tile kernel, straight-line (see dual_layer_epi in field_fwd_dual.cuh for the why) ------
+// Differences from the pair kernel's: every 64-column quarter is handed to the MMA warp on its own barrier as soon as it is
+// in shared memory (intra-tile pipelining), quarters land in the six rotating K-block slots, and the 8-bit chunks (image
+// proper + residual image for head-feeding layers) are stored right behind each quarter's handoff.
+//   slot0        slot of quarter 0 (quarter q -> (slot0 + q) mod 6);  act_s: shared address of bar_act[0]
+//   feed_from    first quarter that feeds an MMA (kNQ: none -- last layer; 2: the dir half of layer 9 in transient mode)
+//   save_act / save_lo   this tile's image of the layer / residual image (kSave)
+template <bool kRelu, int kHeads, int kHeadQ, int kNQ, bool kRayBias, bool kSave>
+__device__ __forceinline__ void single_layer_epi(uint32_t tacc, uint32_t bias_s, const float* __restrict__ rbias, uint32_t hw_s,
+                                                 uint32_t sH_s, int slot0, uint32_t act_s, int feed_from, uint32_t off0, uint32_t off1,
+                                                 int lane, float (&hacc)[5], uint8_t* save_act, uint8_t* save_lo, uint32_t so0, uint32_t so1,
+                                                 uint32_t& mlo, uint32_t& mhi) {
+#pragma unroll
+    for (int q = 0; q < kNQ; ++q) {
+        int slot = slot0 + q;
+        if (slot >= kHSlots) slot -= kHSlots;
+        const uint32_t blk = sH_s + slot * 16384;
+        uint32_t v[16];
+        ptx::tmem_ld16(tacc + q * 64, v);
+        float4 b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (kRayBias) b[i] = __ldg(reinterpret_cast<const float4*>(rbias + q * 64) + i);
+            else b[i] = ptx::lds_f4(bias_s + q * 256 + i * 16);
+        }
+        ptx::tmem_ld_wait();
+        float x[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            ptx::fadd2(x[4 * i], x[4 * i + 1], __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), b[i].x, b[i].y);
+            ptx::fadd2(x[4 * i + 2], x[4 * i + 3], __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]), b[i].z, b[i].w);
+        }
+        uint32_t pk[8];
+        if (kRelu && !kSave) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) pk[j] = ptx::pack_bf16_relu(x[2 * j], x[2 * j + 1]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) pk[j] = pack_bf16(x[2 * j], x[2 * j + 1]);
+        }
+        uint4 p8 = make_uint4(0, 0, 0, 0), l8 = make_uint4(0, 0, 0, 0);
+        if (kSave) {
+            p8.x = ptx::pack4_e4m3<kRelu>(x[0], x[1], x[2], x[3]);    p8.y = ptx::pack4_e4m3<kRelu>(x[4], x[5], x[6], x[7]);
+            p8.z = ptx::pack4_e4m3<kRelu>(x[8], x[9], x[10], x[11]);  p8.w = ptx::pack4_e4m3<kRelu>(x[12], x[13], x[14], x[15]);
+            if (kHeads > 0 && q < kHeadQ) {
+                l8.x = ptx::residual4_e4m3<kRelu>(p8.x, x[0], x[1], x[2], x[3], kLoScale);    l8.y = ptx::residual4_e4m3<kRelu>(p8.y, x[4], x[5], x[6], x[7], kLoScale);
+                l8.z = ptx::residual4_e4m3<kRelu>(p8.z, x[8], x[9], x[10], x[11], kLoScale);  l8.w = ptx::residual4_e4m3<kRelu>(p8.w, x[12], x[13], x[14], x[15], kLoScale);
+            }
+            if (kRelu) {
+                uint32_t acc = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc |= (pk[j] >> j) & (0x80008000u >> j);
+                const uint32_t neg = ((acc & 0xFF00u) | (acc >> 24)) & 0xFFFFu;
+                if (q < 2) mlo |= neg << (16 * q); else mhi |= neg << (16 * (q - 2));
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    __nv_bfloat162 t = *reinterpret_cast<__nv_bfloat162*>(&pk[j]);
+                    t = __hmax2(t, __floats2bfloat162_rn(0.0f, 0.0f));
+                    pk[j] = *reinterpret_cast<uint32_t*>(&t);
+                }
+            }
+        }
+        if (kHeads > 0 && q < kHeadQ) {
+#pragma unroll
+            for (int h = 0; h < kHeads; ++h) {
+                float acc = hacc[h];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 t = ptx::lds_f4(hw_s + h * 512 + q * 256 + i * 16);
+                    acc = fmaf(kRelu ? fmaxf(x[4 * i], 0.0f) : x[4 * i], t.x, acc);
+                    acc = fmaf(kRelu ? fmaxf(x[4 * i + 1], 0.0f) : x[4 * i + 1], t.y, acc);
+                    acc = fmaf(kRelu ? fmaxf(x[4 * i + 2], 0.0f) : x[4 * i + 2], t.z, acc);
+                    acc = fmaf(kRelu ? fmaxf(x[4 * i + 3], 0.0f) : x[4 * i + 3], t.w, acc);
+                }
+                hacc[h] = acc;
+            }
+        }
+        ptx::sts_u4(blk + off0, pk[0], pk[1], pk[2], pk[3]);
+        ptx::sts_u4(blk + off1, pk[4], pk[5], pk[6], pk[7]);
+        ptx::fence_proxy_async_smem();
+        ptx::tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0 && q >= feed_from) {
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(act_s + 8 * slot) : "memory");
+        }
+        if (kSave) {
+            const uint32_t at = (q >> 1) * 16384 + ((q & 1) ? so1 : so0);
+            *reinterpret_cast<uint4*>(save_act + at) = p8;
+            if (kHeads > 0 && q < kHeadQ) *reinterpret_cast<uint4*>(save_lo + at) = l8;
+        }
+    }
+}
+
 // kKx = 64-column blocks of the encoded-xyz operand.  kKx == 2 (in_channels_xyz up to 128: N_emb_xyz = 15 -> 93 columns,
 // models/nerf.py:83,121-128) keeps the second block where the third ring stage would be and runs a two-stage ring.
 template <bool kSave, int kKx>
@@ -356,6 +450,8 @@ field_fwd_kernel(const FwdArgs a) {
         uint32_t acc_ev = 0;                               // layers consumed (parity of bar_acc)
         // this thread's 16-byte chunk in an 8-bit image: quarter q = columns [64 q + 16 sub, +16) = chunk 4 q + sub
         const uint32_t so0 = image8_chunk_off(row, sub), so1 = image8_chunk_off(row, 4 + sub);
+        const uint32_t smem_s = ptx::smem_u32(smem), cst_s = smem_s + kOffC + sub * 64, sH_s = smem_s + kOffH, act_s = ptx::smem_u32(bar_act);
+        const uint32_t off0 = ptx::image_chunk_off(row, 2 * sub), off1 = ptx::image_chunk_off(row, 2 * sub + 1);
         for (int tile = a.first_tile + blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const long long p = static_cast<long long>(tile) * kTileM + row;
             const bool valid = p < a.n_points;
@@ -509,61 +605,37 @@ field_fwd_kernel(const FwdArgs a) {
                 ptx::tc_fence_after_sync();
                 NWB_TRACE(tile == 0 && warp == kEpiWarp0 && lane == 0, g * 16 + 10);          // accumulator seen
                 float hacc[5] = {0, 0, 0, 0, 0};
-                // sign masks: per layer [sub][row] x 4 uint16 (one per quarter: a warp's store is 256 contiguous bytes); bit (15-j) of entry q =
-                // sign of the pre-activation of column 64q + 16sub + j.  A thread owns the four entries of its sub
-                // and writes them as ONE 8-byte store after the quarter loop (a global store ahead of the per-
-                // quarter proxy fence would stall the handoff).
-                unsigned long long mbits = 0ull;
-                const int nq = layer_quarters(g, transient);
-#pragma unroll 1
-                for (int q = 0; q < nq; ++q) {
-                    const int c0 = q * 64 + sub * 16;       // this thread's 16 columns of quarter q
-                    const int slot = out_slot(g, q);
-                    uint8_t* blk = sH + slot * 16384;
-                    uint32_t md = 0;
-                    uint4 p8 = make_uint4(0, 0, 0, 0);
-                    // this thread's chunk of the residual image (layers that feed a head), same place as in the image proper
-                    uint4 l8v = make_uint4(0, 0, 0, 0);
-                    const bool has_lo = save && (g == 7 || (g == 9 && q < 2) || g == 12);
-                    uint4* lo8 = has_lo ? &l8v : nullptr;
-                    if (g < 7) {
-                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + g * 256 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                    } else if (g == 7) {
-                        epi_slice16<true, 1, kSave>(tacc + q * 64, cst + ConstOff::trunk_b + 7 * 256 + c0, nullptr, cst + ConstOff::sigma_w + c0, 0,
-                                                    hacc, blk, row, 2 * sub, md, p8, lo8);
-                    } else if (g == 8) {
-                        epi_slice16<false, 0, kSave>(tacc + q * 64, cst + ConstOff::final_b + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                    } else if (g == 9) {
-                        // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias
-                        if (q < 2) epi_slice16<true, 3, kSave>(tacc + q * 64, nullptr, rb + c0, cst + ConstOff::rgb_w + c0, 128, hacc, blk, row, 2 * sub, md, p8, lo8);
-                        else epi_slice16<true, 0, kSave>(tacc + q * 64, nullptr, rb + c0, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                    } else if (g < 12) {
-                        epi_slice16<true, 0, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + (g - 10) * 128 + c0, nullptr, nullptr, 0, hacc, blk, row, 2 * sub, md, p8);
-                    } else {
-                        // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
-                        epi_slice16<true, 5, kSave>(tacc + q * 64, cst + ConstOff::tenc_b + 2 * 128 + c0, nullptr, cst + ConstOff::tsigma_w + c0, 128,
-                                                    hacc, blk, row, 2 * sub, md, p8, lo8);
-                    }
-                    if (save) mbits |= static_cast<unsigned long long>(md) << (16 * q);
-                    ptx::fence_proxy_async_smem();
-                    ptx::tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) {
-                        // the dir half of layer 9 (transient mode) and the last layer feed no MMA
-                        const bool feeds_mma = !last && !(g == 9 && transient && q < 2);
-                        if (feeds_mma) ptx::mbar_arrive(&bar_act[slot]);
-                        NWB_TRACE(tile == 0 && warp == kEpiWarp0, g * 16 + 11 + q);          // quarter q handed over
-                    }
-                    // saved 8-bit image: quarter q = columns [64q, 64q+64) -> block q/2, chunks 4(q%2) .. +3; this thread's
-                    // 16 columns are chunk 4(q%2) + sub of its row's line.  Behind the handoff, off the MMA's critical path.
-                    if (save) {
-                        const uint32_t at = (q >> 1) * 16384 + ((q & 1) ? so1 : so0);
-                        *reinterpret_cast<uint4*>(save_tile + sl.act_off(g) + at) = p8;
-                        if (has_lo) *reinterpret_cast<uint4*>(save_tile + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl) + at) = l8v;
-                    }
+                // sign masks: per layer [sub][row] x 4 uint16 (one per quarter: a warp's store is 256 contiguous bytes); a thread
+                // owns the four entries of its sub and writes them as ONE 8-byte store after the layer
+                uint32_t mlo = 0, mhi = 0;
+                const int slot0 = first_quarter(g) % kHSlots;
+                uint8_t* sv_act = save ? save_tile + sl.act_off(g) : nullptr;
+                uint8_t* sv_lo = save ? save_tile + sl.lo_off(g == 7 ? 0 : (g == 9 ? 1 : 2), nl) : nullptr;
+                const int none = last ? 4 : 0;               // the last layer feeds no MMA
+                if (g < 7) {
+                    single_layer_epi<true, 0, 0, 4, false, kSave>(tacc, cst_s + (ConstOff::trunk_b + g * 256) * 4, nullptr, 0, sH_s, slot0, act_s, none, off0, off1,
+                                                                  lane, hacc, sv_act, sv_lo, so0, so1, mlo, mhi);
+                } else if (g == 7) {
+                    single_layer_epi<true, 1, 4, 4, false, kSave>(tacc, cst_s + (ConstOff::trunk_b + 7 * 256) * 4, nullptr, cst_s + ConstOff::sigma_w * 4, sH_s, slot0,
+                                                                  act_s, none, off0, off1, lane, hacc, sv_act, sv_lo, so0, so1, mlo, mhi);
+                } else if (g == 8) {
+                    single_layer_epi<false, 0, 0, 4, false, kSave>(tacc, cst_s + ConstOff::final_b * 4, nullptr, 0, sH_s, slot0, act_s, none, off0, off1, lane, hacc,
+                                                                   sv_act, sv_lo, so0, so1, mlo, mhi);
+                } else if (g == 9) {
+                    // per-ray bias already contains dir_encoding.0.bias / transient_encoding.0.bias; the dir half feeds no MMA
+                    if (transient) single_layer_epi<true, 3, 2, 4, true, kSave>(tacc, 0, rb + sub * 16, cst_s + ConstOff::rgb_w * 4, sH_s, slot0, act_s, last ? 4 : 2,
+                                                                                 off0, off1, lane, hacc, sv_act, sv_lo, so0, so1, mlo, mhi);
+                    else single_layer_epi<true, 3, 2, 2, true, kSave>(tacc, 0, rb + sub * 16, cst_s + ConstOff::rgb_w * 4, sH_s, slot0, act_s, 2, off0, off1, lane,
+                                                                      hacc, sv_act, sv_lo, so0, so1, mlo, mhi);
+                } else if (g < 12) {
+                    single_layer_epi<true, 0, 0, 2, false, kSave>(tacc, cst_s + (ConstOff::tenc_b + (g - 10) * 128) * 4, nullptr, 0, sH_s, slot0, act_s, none, off0, off1,
+                                                                  lane, hacc, sv_act, sv_lo, so0, so1, mlo, mhi);
+                } else {
+                    // transient heads: hw rows = [tsigma_w | trgb_w(3) | tbeta_w], contiguous, ld 128
+                    single_layer_epi<true, 5, 2, 2, false, kSave>(tacc, cst_s + (ConstOff::tenc_b + 2 * 128) * 4, nullptr, cst_s + ConstOff::tsigma_w * 4, sH_s, slot0,
+                                                                  act_s, 2, off0, off1, lane, hacc, sv_act, sv_lo, so0, so1, mlo, mhi);
                 }
-                if (save && g != 8)
-                    *reinterpret_cast<unsigned long long*>(save_tile + sl.mask_off(g, nl) + sub * 1024 + row * 8) = mbits;
+                if (save && g != 8) *reinterpret_cast<uint2*>(save_tile + sl.mask_off(g, nl) + sub * 1024 + row * 8) = make_uint2(mlo, mhi);
                 // ---- heads: combine the four column slices of a row through shared memory (fixed order) ----
                 const int nh_heads = (g == 7) ? 1 : (g == 9 ? 3 : (g == 12 ? 5 : 0));
                 if (nh_heads > 0) {
