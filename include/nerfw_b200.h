@@ -30,6 +30,8 @@ extern "C" {
 
 int nwb_abi_version(void);
 const char* nwb_last_error(void);
+/* number of kernels this library has launched in this process (diagnostics; bench.py gpu_launches) */
+long long nwb_kernel_launches(void);
 
 /* ------------------------------------------------------------------------------------------
  * (a1) coarse depth sampling -- models/rendering.py:244-259

@@ -1,9 +1,12 @@
 // Error plumbing and ABI version of libnerfw_b200.so.
 #include "common.cuh"
+#include <atomic>
 
 namespace nwb {
 
 static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 char* err_buf() { return g_err; }
 
@@ -34,4 +37,7 @@ int current_device_checked(int* dev_out) {
 }  // namespace nwb
 
 extern "C" int nwb_abi_version(void) { return 1; }
+// kernels this library has launched in this process (every <<<>>> of ours passes NWB_LAUNCH_CHECK): what bench.py reports
+// as gpu_launches; during a CUDA-graph capture it counts the kernels that end up as nodes of the graph
+extern "C" long long nwb_kernel_launches(void) { return nwb::g_launches.load(std::memory_order_relaxed); }
 extern "C" const char* nwb_last_error(void) { return nwb::err_buf(); }

@@ -18,6 +18,7 @@ constexpr int kNumSMs = 148;
 
 // ---- error plumbing: thread-local text, never throws / exits ---------------------------------
 char* err_buf();
+void note_launch();             // api.cu: counts kernel launches (nwb_kernel_launches)
 int set_error(int code, const char* fmt, ...);
 
 #define NWB_REQUIRE(cond, ...)                                   \
@@ -35,6 +36,7 @@ int set_error(int code, const char* fmt, ...);
 
 #define NWB_LAUNCH_CHECK()                                                                \
     do {                                                                                  \
+        nwb::note_launch();                                                               \
         cudaError_t e__ = cudaGetLastError();                                             \
         if (e__ != cudaSuccess)                                                           \
             return nwb::set_error(NWB_E_CUDA, "kernel launch failed: %s (%s:%d)",         \

@@ -14,7 +14,7 @@ from . import _lib as L
 
 # ---- optional per-call device timing (bench.py's roofline leg) -------------------------------------
 _timing = None     # None, or a list collecting (name, units, mode, start_event, end_event)
-launch_count = 0   # kernels launched through this module since import (bench.py's gpu_launches)
+launch_count = 0   # kernels the library has launched in this process (nwb_kernel_launches; bench.py's gpu_launches)
 
 
 class _timed:
@@ -29,8 +29,6 @@ class _timed:
                 self.guard = torch.cuda.device(dev)      # kernels launch on the CURRENT device: make it the tensors'
 
     def __enter__(self):
-        global launch_count
-        launch_count += 1
         if self.guard is not None:
             self.guard.__enter__()
         if _timing is not None:
@@ -39,6 +37,8 @@ class _timed:
         return self
 
     def __exit__(self, *exc):
+        global launch_count
+        launch_count = int(_launches())
         if _timing is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
@@ -46,6 +46,18 @@ class _timed:
         if self.guard is not None:
             self.guard.__exit__(*exc)
         return False
+
+
+_launches_fn = None
+
+
+def _launches():
+    global _launches_fn
+    if _launches_fn is None:
+        _launches_fn = L.lib().nwb_kernel_launches
+        _launches_fn.restype = C.c_longlong
+        _launches_fn.argtypes = []
+    return _launches_fn()
 
 
 def timing_start():

@@ -285,13 +285,12 @@ class FlatTrainState:
         if self.flat_p.is_cuda:
             from . import _lib as L
             from . import kernels as K
-            K.launch_count += 1
-            K.launch_count += 1              # tick + update kernels
             fn = L.bind("nwb_adam_step_dev", [C.c_void_p] * 4 + [C.c_int64] + [C.c_float] * 4 + [C.c_void_p, C.c_float, C.c_int,
                                                                                                C.c_void_p])
-            L.check(fn(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
-                       self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay, self.hyper.data_ptr(),
-                       1.0 / world, int(zero_grad), L.stream_ptr(self.flat_p.device)), "nwb_adam_step_dev")
+            with K._timed("nwb_adam_step_dev", 0, dev=self.flat_p.device):
+                L.check(fn(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
+                           self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay, self.hyper.data_ptr(),
+                           1.0 / world, int(zero_grad), L.stream_ptr(self.flat_p.device)), "nwb_adam_step_dev")
         elif self._host_update is not None:
             self._host_update(self, world, zero_grad)
         else:
