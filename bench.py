@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true", help="train workload: skip the loss check against the CPU oracle")
     ap.add_argument("--dgrad-gen", type=int, default=0, choices=[0, 1, 2],
                     help="dgrad kernel: 0 = the library's per-launch choice, 1 = first-generation, 2 = two-slot pair kernel (A/B runs)")
-    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
+    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "p2p-fused-adam", "nccl"],
                     help="N > 1: gradient exchange = our one-kernel all-reduce over NVLink peer memory inside the CUDA graph "
                          "(default) or torch.distributed's NCCL all_reduce behind the graph")
     return ap.parse_args()
@@ -751,8 +751,11 @@ def run_product(args):
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
     from nerf_fl_b200.train_step import TrainStep
     state = FlatTrainState(list(c.models.values()) + [c.emb["a"], c.emb["t"]], lr=5e-4)
-    if world > 1 and args.allreduce == "p2p":
-        state.enable_p2p()
+    if world > 1 and args.allreduce == "p2p-fused-adam":       # A/B: reduce-scatter kernel + optimizer reading the reduced slices from the peers
+        state.p2p_fused_adam = True
+        args.allreduce = "p2p"
+    if world > 1 and args.allreduce == "p2p" and not state.enable_p2p():
+        args.allreduce = "nccl"                        # peer mapping failed on some rank (all ranks agree): reported as the NCCL arm
     # the public training-step API: forward, NerfWLoss, backward, NCCL all-reduce of the flat gradient buffer,
     # Adam, zero_grad -- captured once and replayed as a CUDA graph unless --no-graph
     step = TrainStep(c.models, c.emb, state, lossfn, batch=args.batch, N_samples=ns, N_importance=ni, perturb=1.0,

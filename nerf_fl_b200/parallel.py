@@ -87,28 +87,43 @@ class P2PGradExchange:
         lib.nwb_p2p_allreduce.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
         lib.nwb_p2p_reduce_scatter.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
         nbytes = lib.nwb_p2p_region_bytes(self.numel, world)
+        self._base, self._opened, err = None, [], None
         with torch.cuda.device(device):
-            base = C.c_void_p()
-            L.check(lib.nwb_p2p_alloc(nbytes, C.byref(base)), "nwb_p2p_alloc")
-            self._base = base.value
+            # every step below is followed by a collective, so a rank that fails (no peer access, IPC not permitted, out
+            # of memory) must keep walking the same sequence: errors are collected and agreed on at the end
             handle = C.create_string_buffer(64)
-            L.check(lib.nwb_p2p_export(self._base, handle), "nwb_p2p_export")
+            try:
+                base = C.c_void_p()
+                L.check(lib.nwb_p2p_alloc(nbytes, C.byref(base)), "nwb_p2p_alloc")
+                self._base = base.value
+                L.check(lib.nwb_p2p_export(self._base, handle), "nwb_p2p_export")
+            except RuntimeError as e:
+                err = e
             handles = [None] * world
-            dist.all_gather_object(handles, handle.raw, group=group)
+            dist.all_gather_object(handles, (handle.raw, err is None), group=group)
             self._regions = (C.c_void_p * world)()
-            self._opened = []
-            for q in range(world):
-                if q == rank:
-                    self._regions[q] = self._base
-                else:
-                    ptr = C.c_void_p()
-                    L.check(lib.nwb_p2p_open(handles[q], C.byref(ptr)), f"nwb_p2p_open(rank {q})")
-                    self._regions[q] = ptr.value
-                    self._opened.append(ptr.value)
+            if err is None and all(ok for _, ok in handles):
+                try:
+                    for q in range(world):
+                        if q == rank:
+                            self._regions[q] = self._base
+                        else:
+                            ptr = C.c_void_p()
+                            L.check(lib.nwb_p2p_open(handles[q][0], C.byref(ptr)), f"nwb_p2p_open(rank {q})")
+                            self._regions[q] = ptr.value
+                            self._opened.append(ptr.value)
+                except RuntimeError as e:
+                    err = e
+            elif err is None:
+                err = RuntimeError("another rank could not allocate / export its exchange region")
+            ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)      # also: every rank has mapped every region
+            if int(ok.item()) == 0:
+                self.close(collective=False)
+                raise RuntimeError(f"P2PGradExchange: peer mapping failed on at least one rank ({err})")
             self.counter = torch.zeros(4, dtype=torch.int32, device=device)
             self.flat_g = torch.as_tensor(_DevArray(self._base + lib.nwb_p2p_grad_offset(), self.numel), device=device)
             torch.cuda.synchronize(device)
-        dist.barrier(group=group)                      # every rank has mapped every region before anyone launches
 
     def allreduce(self) -> None:
         from . import _lib as L
@@ -126,16 +141,17 @@ class P2PGradExchange:
             L.check(self._lib.nwb_p2p_reduce_scatter(self._regions, self.rank, self.world, self.numel, self.counter.data_ptr(),
                                                      L.stream_ptr(self.device)), "nwb_p2p_reduce_scatter")
 
-    def close(self) -> None:
+    def close(self, collective: bool = True) -> None:
         """Unmap the peers' regions and free the own one (after a barrier: nobody may still be reading it)."""
-        if getattr(self, "_base", None) is None:
+        if getattr(self, "_base", None) is None and not getattr(self, "_opened", None):
             return
         torch.cuda.synchronize(self.device)
-        if dist.is_initialized():
+        if collective and dist.is_initialized():
             dist.barrier()
         for ptr in self._opened:
             self._lib.nwb_p2p_close(ptr)
-        self._lib.nwb_p2p_free(self._base)
+        if self._base is not None:
+            self._lib.nwb_p2p_free(self._base)
         self._base, self._opened = None, []
 
 
@@ -220,7 +236,12 @@ class FlatTrainState:
             return True
         if dist_info()[1] < 2 or not self.flat_g.is_cuda:
             return False
-        ex = P2PGradExchange(self.numel, self.flat_g.device, group)
+        try:
+            ex = P2PGradExchange(self.numel, self.flat_g.device, group)
+        except RuntimeError as e:                        # agreed on by all ranks (see P2PGradExchange): NCCL stays the exchange
+            import warnings
+            warnings.warn(f"nerf_fl_b200: {e}; falling back to torch.distributed all_reduce")
+            return False
         ex.flat_g.copy_(self.flat_g)
         self.flat_g = ex.flat_g
         for p, o in zip(self.params, self._offs):
@@ -400,11 +421,14 @@ class FlatTrainState:
                 self.lr = lr
 
     def step(self, group=None):
-        """all-reduce + Adam: everything that follows backward in one training iteration.  With the P2P exchange and the
-        cache-refreshing optimizer the all-gather half of the all-reduce never runs: the reduce-scatter kernel leaves
-        slice q of the summed gradient with rank q, and the optimizer kernel reads the slices over NVLink itself."""
+        """all-reduce + Adam: everything that follows backward in one training iteration.  ``p2p_fused_adam = True`` (off by
+        default: measured slower) skips the all-gather half of the P2P all-reduce: the reduce-scatter kernel leaves slice q
+        of the summed gradient with rank q, and the optimizer kernel reads the slices over NVLink itself."""
         self.pull_lr()
-        if self._p2p is not None and self._fused_fields and self.flat_p.is_cuda:
+        # [B200, 2 GPUs, same box: profiles/r02z4_exchange_ab.log] full P2P all-reduce kernel + plain optimizer launch 1.147 ms per
+        # step; reduce-scatter + optimizer reading the slices from the peers 1.166 ms (its scattered system-scope loads over
+        # NVLink cost more than the all-gather half they replace); NCCL behind the graph 1.153 ms; one GPU 1.115 ms.
+        if self._p2p is not None and self._fused_fields and self.flat_p.is_cuda and getattr(self, "p2p_fused_adam", False):
             self._p2p.reduce_scatter()
             self.adam_step(self._p2p.world, from_slices=True)
         else:

@@ -79,6 +79,7 @@ def run(p2p):
     state = FlatTrainState(list(models.values()) + [emb["a"], emb["t"]], lr=5e-4)
     if p2p:
         assert state.enable_p2p()
+        state.p2p_fused_adam = (p2p == "fused")
     step = TrainStep(models, emb, state, NerfWLoss(), batch=512, N_samples=64, N_importance=64, perturb=0.0, noise_std=0.0, white_back=True)
     losses = []
     for i in range(4):
@@ -93,6 +94,8 @@ def run(p2p):
         state._p2p.close()
     return p, losses, step._split
 p_p2p, l_p2p, split_p2p = run(True)
+p_fus, l_fus, _ = run("fused")
+log(f"reduce-scatter + optimizer-from-peers variant vs full all-reduce: rel param diff {((p_fus - p_p2p).norm() / p_p2p.norm()).item():.3e}")
 p_nccl, l_nccl, split_nccl = run(False)
 rel = ((p_p2p - p_nccl).norm() / p_nccl.norm()).item()
 gathered = [torch.empty_like(p_p2p) for _ in range(world)]
