@@ -40,7 +40,14 @@ __device__ __forceinline__ void ring_issue(RingStage<C>* st, const float* __rest
         const int cnt = min(32, S - base);
         const float* src = raw + (row + base) * C;
         const int nfl = cnt * C;
-        if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (nfl & 3) == 0) {
+        if (cnt == 32 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+            // full chunk: 8 C float4, a fixed number of copies per lane (no loop counters, no tail tests)
+#pragma unroll
+            for (int k = 0; k < (8 * C + 31) / 32; ++k) {
+                const int i = lane + 32 * k;
+                if (8 * C % 32 == 0 || k + 1 < (8 * C + 31) / 32 || i < 8 * C) cp_async16(st->raw + 4 * i, src + 4 * i);
+            }
+        } else if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (nfl & 3) == 0) {
             for (int i = lane; i < (nfl >> 2); i += 32) cp_async16(st->raw + 4 * i, src + 4 * i);
         } else {
             for (int i = lane; i < nfl; i += 32) cp_async4(st->raw + i, src + i);
@@ -66,7 +73,9 @@ __device__ __forceinline__ float excl_prod_scan(float om, float& carry, int lane
     return T;
 }
 
-template <int C>
+// kV: bit 0 = transient (C == 9 only), bit 1 = test_time extras (transient only), bit 2 = weights / opacity only -- compile-time,
+// so that the per-chunk body carries no flag tests (the kernel issues on every scheduler slot it gets: ncu r02z)
+template <int C, uint32_t kV>
 __global__ void __launch_bounds__(kCompWarps * 32)
 composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                      const float* __restrict__ noise, float noise_std, int n_rays, int S,
@@ -74,10 +83,10 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     __shared__ __align__(16) RingStage<C> ring[kCompWarps][kRing];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     RingStage<C>* my = ring[warp];
-    const bool transient = (C == 9) && (flags & NWB_COMP_TRANSIENT);
+    constexpr bool transient = (C == 9) && (kV & 1u);
     const bool white = flags & NWB_COMP_WHITE_BACK;
-    const bool test_time = flags & NWB_COMP_TEST_TIME;
-    const bool weights_only = (C == 1) || (test_time && (flags & NWB_COMP_COARSE));
+    constexpr bool test_time = (kV & 2u) != 0;
+    constexpr bool weights_only = (C == 1) || (kV & 4u);
     // the warp's chunk sequence: (ray, 0), (ray, 32), ..., (ray + stride, 0), ...; `pf_*` is the next chunk to issue
     const int stride = gridDim.x * kCompWarps;
     int pf_ray = blockIdx.x * kCompWarps + warp, pf_base = 0;
@@ -197,7 +206,7 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 // pass 1 (forward order): recompute T, stash T_j in smem; pass 2 (reverse order): suffix scan.
 // dynamic smem per warp: kRing chunk stages (cp.async ring) + S floats of T.
 // ------------------------------------------------------------------------------------------------
-template <int C>
+template <int C, bool kTr>
 __global__ void __launch_bounds__(kCompWarps * 32)
 composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                      const float* __restrict__ noise, float noise_std, int n_rays, int S,
@@ -209,7 +218,7 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     float* wbase = dsm + warp * (kRing * kStageFloats + Sp);
     RingStage<C>* my = reinterpret_cast<RingStage<C>*>(wbase);
     float* Tbuf = wbase + kRing * kStageFloats;
-    const bool transient = (C == 9) && (flags & NWB_COMP_TRANSIENT);
+    constexpr bool transient = (C == 9) && kTr;
     const bool white = flags & NWB_COMP_WHITE_BACK;
     // The warp's chunk sequence per ray: chunks 0..n-1 (pass 1), then n-1..0 (pass 2), then the next ray: one cp.async
     // ring runs through all of it, kRing-1 chunks ahead of the consumer (the re-read of a chunk hits L1/L2).
@@ -375,9 +384,16 @@ extern "C" int nwb_composite_fwd(const float* raw, int C, const float* z, const 
     if (n_rays == 0) return NWB_OK;
     const int blocks = std::min((n_rays + kCompWarps - 1) / kCompWarps, kNumSMs * 16);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (C == 1) composite_fwd_kernel<1><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out);
-    else if (C == 4) composite_fwd_kernel<4><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out);
-    else composite_fwd_kernel<9><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out);
+    const bool tr = (flags & NWB_COMP_TRANSIENT) != 0, tt = (flags & NWB_COMP_TEST_TIME) != 0;
+    const bool wo = tt && (flags & NWB_COMP_COARSE);
+#define NWB_FWD(CC, VV) composite_fwd_kernel<CC, VV><<<blocks, kCompWarps * 32, 0, st>>>(raw, z, noise, noise_std, n_rays, S, flags, beta_min, *out)
+    if (C == 1) NWB_FWD(1, 0u);
+    else if (C == 4) { if (wo) NWB_FWD(4, 4u); else NWB_FWD(4, 0u); }
+    else if (wo) NWB_FWD(9, 4u);
+    else if (!tr) NWB_FWD(9, 0u);
+    else if (tt) NWB_FWD(9, 3u);
+    else NWB_FWD(9, 1u);
+#undef NWB_FWD
     NWB_LAUNCH_CHECK();
     return NWB_OK;
 }
@@ -395,17 +411,18 @@ extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const 
     const size_t smem = static_cast<size_t>(kCompWarps) * (kRing * (32 * C + 36) + ((S + 3) & ~3)) * sizeof(float);
     NWB_REQUIRE(smem <= 200 * 1024, "nwb_composite_bwd: S too large for shared memory");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-#define NWB_BWD(CC)                                                                                 \
+#define NWB_BWD(CC, TR)                                                                             \
     do {                                                                                            \
         if (smem > 48 * 1024)                                                                       \
-            NWB_CUDA(cudaFuncSetAttribute(composite_bwd_kernel<CC>,                                 \
+            NWB_CUDA(cudaFuncSetAttribute(composite_bwd_kernel<CC, TR>,                             \
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        composite_bwd_kernel<CC><<<blocks, kCompWarps * 32, smem, st>>>(raw, z, noise, noise_std,   \
-                                                                        n_rays, S, flags, *g, d_raw); \
+        composite_bwd_kernel<CC, TR><<<blocks, kCompWarps * 32, smem, st>>>(raw, z, noise, noise_std, \
+                                                                            n_rays, S, flags, *g, d_raw); \
     } while (0)
-    if (C == 1) NWB_BWD(1);
-    else if (C == 4) NWB_BWD(4);
-    else NWB_BWD(9);
+    if (C == 1) NWB_BWD(1, false);
+    else if (C == 4) NWB_BWD(4, false);
+    else if (flags & NWB_COMP_TRANSIENT) NWB_BWD(9, true);
+    else NWB_BWD(9, false);
 #undef NWB_BWD
     NWB_LAUNCH_CHECK();
     return NWB_OK;

@@ -12,7 +12,7 @@ ci = {n: i for i, n in enumerate(h)}
 tot = 0
 by = collections.Counter()
 for r in data:
-    if len(r) < len(h):
+    if len(r) < len(h) or not (r[ci["# Samples"]] or "0").isdigit():
         continue
     n = int(r[ci["Instructions Executed"]] or 0)
     tot += n

@@ -15,7 +15,7 @@ stalls = [n for n in h if n.startswith("stall_") and "Not Issued" not in n]
 tot = {n: 0 for n in stalls}
 total, recs = 0, []
 for r in data:
-    if len(r) < len(h):
+    if len(r) < len(h) or not (r[ci["# Samples"]] or "0").isdigit():
         continue
     ns = int(r[ci["# Samples"]] or 0)
     total += ns
