@@ -772,7 +772,7 @@ def run_product(args):
         e0.record()
         for i in range(n_steps):
             if from_host:
-                b = tuple(t.to(dev, non_blocking=True) for t in pinned[i % len(pinned)])
+                b = pinned[i % len(pinned)]             # TrainStep copies pinned host batches straight into its static buffers
             else:
                 b = resident[i % len(resident)]
             res = step(*b)

@@ -305,6 +305,195 @@ sample_pdf_merge_kernel(const float* __restrict__ z_coarse, const float* __restr
     }
 }
 
+
+// Ascending bitonic sort of 32*R keys held BLOCKED in registers: element e = lane*R + r is register r of `lane`.  Partners
+// at distance j < R are this lane's register r ^ j (two FMNMX per pair), partners at distance j >= R are register r of lane
+// ^ (j/R) (one shuffle and one FMNMX per key).  For R = 4 and 128 keys that is 13 register steps and 15 shuffle steps
+// (the strided layout above: 3 and 25).
+template <int R>
+__device__ __forceinline__ void warp_bitonic_blocked(float (&v)[R], int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32 * R; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j < R) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if ((r & j) == 0) {
+                        const bool up = ((lane * R + r) & k) == 0;
+                        const float a = v[r], b = v[r | j];
+                        v[r] = up ? fminf(a, b) : fmaxf(a, b);
+                        v[r | j] = up ? fmaxf(a, b) : fminf(a, b);
+                    }
+                }
+            } else {
+                const int jl = j / R;
+                const bool keep_min = (((lane * R) & k) == 0) == ((lane & jl) == 0);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const float o = __shfl_xor_sync(0xffffffffu, v[r], jl);
+                    v[r] = keep_min ? fminf(v[r], o) : fmaxf(v[r], o);
+                }
+            }
+        }
+    }
+}
+
+// #{k < n : !(a[k] > x)} for ascending a[0..n), n a power of two, without a data-dependent branch: log2(n) probes of the
+// first n-1 entries and one of the entry the walk stops at.  kStrict counts a[k] < x instead.  The same result as the
+// bisection loops of the general kernel on ascending input.
+template <int n, bool kStrict>
+__device__ __forceinline__ int count_below(const float* a, float x) {
+    int pos = 0;
+#pragma unroll
+    for (int s = n >> 1; s > 0; s >>= 1) {
+        const float c = a[pos + s - 1];
+        if (kStrict ? (c < x) : !(c > x)) pos += s;
+    }
+    const float c = a[pos];
+    return pos + ((kStrict ? (c < x) : !(c > x)) ? 1 : 0);
+}
+
+
+// (a6) for Ns = 32*RS, Ni = 32*RQ (RS, RQ in {2, 4}): the same arithmetic per value as sample_pdf_merge_kernel -- bit-
+// identical z_out / z_new / inds -- with every loop unrolled, the coarse row and the pdf kept in registers, the bisections
+// replaced by fixed-trip-count walks (RQ independent ones in flight per lane), the new samples BLOCKED over the lanes
+// (lane owns RQ consecutive j: one Philox block or one vector load of u per lane, the ascending check and the sort on
+// registers) and the row written back with 8-byte stores.
+// [B200, profiles/r02z9_*] the general kernel executes ~2000 warp instructions per ray at 128+128 and is issue-bound
+// (70 % of the issue slots, 0.10 of the copy bandwidth).
+template <int RS, int RQ>
+__global__ void __launch_bounds__(128)
+sample_pdf_merge_fast_kernel(const float* __restrict__ z_coarse, const float* __restrict__ w_coarse, int n_rays, int det,
+                             const float* __restrict__ u_in, uint64_t seed, const float* __restrict__ cdf_in,
+                             float* __restrict__ z_out, float* __restrict__ z_new_out, int64_t* __restrict__ inds_out) {
+    constexpr int Ns = 32 * RS, Ni = 32 * RQ;
+    constexpr int M = Ns - 2, nb = Ns - 1;
+    constexpr int per_warp = 3 * Ns + Ni + (Ns + Ni);        // cdf[Ns] (Ns-1 used), bins[Ns], zc[Ns], zn[Ni], out[Ns+Ni]
+    extern __shared__ __align__(16) float smem[];
+    const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* cdf = smem + warp * per_warp;
+    float* bins = cdf + Ns;
+    float* zc = bins + Ns;
+    float* zn = zc + Ns;
+    float* outb = zn + Ni;
+    const float eps = 1e-5f;
+
+    for (int ray = blockIdx.x * warps + warp; ray < n_rays; ray += gridDim.x * warps) {
+        const float* zr = z_coarse + static_cast<int64_t>(ray) * Ns;
+        const float* wr = w_coarse + static_cast<int64_t>(ray) * Ns;
+        float zv[RS], pw[RS];                                  // element i = lane + 32 r
+#pragma unroll
+        for (int r = 0; r < RS; ++r) {
+            const int i = lane + 32 * r;
+            zv[r] = __ldg(zr + i);
+            pw[r] = (i < M) ? __ldg(wr + 1 + i) + eps : 0.0f;
+            zc[i] = zv[r];
+        }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < RS; ++r) {
+            const int i = lane + 32 * r;
+            if (i < nb) bins[i] = __fmul_rn(0.5f, __fadd_rn(zv[r], zc[i + 1]));
+        }
+        // pdf normaliser: the general kernel's order (lane-strided partial sums, then the warp tree)
+        float part = 0.0f;
+#pragma unroll
+        for (int r = 0; r < RS; ++r)
+            if (lane + 32 * r < M) part += pw[r];
+        const float total = warp_sum(part);
+        if (cdf_in != nullptr) {
+#pragma unroll
+            for (int r = 0; r < RS; ++r) {
+                const int i = lane + 32 * r;
+                if (i < nb) cdf[i] = __ldg(cdf_in + static_cast<int64_t>(ray) * nb + i);
+            }
+        } else {
+            float carry = 0.0f;
+            if (lane == 0) cdf[0] = 0.0f;
+#pragma unroll
+            for (int r = 0; r < RS; ++r) {
+                const int i = lane + 32 * r;
+                float v = (i < M) ? __fdiv_rn(pw[r], total) : 0.0f;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const float t = __shfl_up_sync(0xffffffffu, v, o);
+                    if (lane >= o) v += t;
+                }
+                v += carry;
+                if (i < M) cdf[i + 1] = v;
+                carry = __shfl_sync(0xffffffffu, v, 31);
+            }
+        }
+        __syncwarp();
+        // inverse-CDF samples j = RQ*lane + q
+        float u[RQ], sv[RQ];
+        const int j0 = RQ * lane;
+        if (det) {
+#pragma unroll
+            for (int q = 0; q < RQ; ++q) u[q] = linspace01(j0 + q, Ni);
+        } else if (u_in != nullptr) {
+            const float* up = u_in + static_cast<int64_t>(ray) * Ni + j0;
+            if constexpr (RQ == 4) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(up));
+                u[0] = t.x; u[1] = t.y; u[2] = t.z; u[3] = t.w;
+            } else {
+                const float2 t = __ldg(reinterpret_cast<const float2*>(up));
+                u[0] = t.x; u[1] = t.y;
+            }
+        } else {
+            // counters ray*Ni + j: the RQ consecutive j of a lane sit in one Philox block (Ni and j0 are multiples of RQ)
+            const uint64_t ctr = static_cast<uint64_t>(ray) * Ni + j0;
+            const uint4 rnd = philox4x32(seed, ctr >> 2, 1u);
+            const uint32_t w4[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
+#pragma unroll
+            for (int q = 0; q < RQ; ++q) u[q] = u01(w4[(j0 + q) & 3]);
+        }
+        int lo[RQ];                                            // first index with cdf[idx] > u, idx in [0, nb]
+#pragma unroll
+        for (int q = 0; q < RQ; ++q) lo[q] = 0;
+#pragma unroll
+        for (int s2 = Ns >> 1; s2 > 0; s2 >>= 1) {             // the walk covers exactly the nb = Ns-1 entries
+#pragma unroll
+            for (int q = 0; q < RQ; ++q)
+                if (!(cdf[lo[q] + s2 - 1] > u[q])) lo[q] += s2;
+        }
+#pragma unroll
+        for (int q = 0; q < RQ; ++q) {
+            const int below = max(lo[q] - 1, 0);
+            const int above = min(lo[q], M);
+            const float c0 = cdf[below], c1 = cdf[above];
+            const float b0 = bins[below], b1 = bins[above];
+            float denom = __fsub_rn(c1, c0);
+            if (denom < eps) denom = 1.0f;
+            const float t = __fdiv_rn(__fsub_rn(u[q], c0), denom);
+            sv[q] = __fadd_rn(b0, __fmul_rn(t, __fsub_rn(b1, b0)));
+            if (z_new_out != nullptr) z_new_out[static_cast<int64_t>(ray) * Ni + j0 + q] = sv[q];
+            if (inds_out != nullptr) inds_out[static_cast<int64_t>(ray) * Ni + j0 + q] = lo[q];
+        }
+        // ascending already (det, or a sorted u)?  otherwise the register sort
+        bool ok = true;
+#pragma unroll
+        for (int q = 0; q + 1 < RQ; ++q) ok = ok && (sv[q] <= sv[q + 1]);
+        const float nxt = __shfl_down_sync(0xffffffffu, sv[0], 1);
+        ok = ok && (lane == 31 || sv[RQ - 1] <= nxt);
+        if (!__all_sync(0xffffffffu, ok)) warp_bitonic_blocked<RQ>(sv, lane);
+#pragma unroll
+        for (int q = 0; q < RQ; ++q) zn[j0 + q] = sv[q];
+        __syncwarp();
+        // merge by rank (stable: a coarse z goes before an equal new z)
+#pragma unroll
+        for (int r = 0; r < RS; ++r) outb[lane + 32 * r + count_below<Ni, true>(zn, zv[r])] = zv[r];
+#pragma unroll
+        for (int q = 0; q < RQ; ++q) outb[j0 + q + count_below<Ns, false>(zc, sv[q])] = sv[q];
+        __syncwarp();
+        float2* zo = reinterpret_cast<float2*>(z_out + static_cast<int64_t>(ray) * (Ns + Ni));
+#pragma unroll
+        for (int i = 0; i < (RS + RQ) / 2; ++i) zo[lane + 32 * i] = reinterpret_cast<const float2*>(outb)[lane + 32 * i];
+        __syncwarp();
+    }
+}
+
 }  // namespace nwb
 
 using namespace nwb;
@@ -352,6 +541,22 @@ extern "C" int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse
                 "nwb_sample_pdf_merge: need n_samples>=3, n_importance>=1");
     NWB_REQUIRE(n_samples + n_importance <= 4096, "nwb_sample_pdf_merge: too many samples per ray");
     if (n_rays == 0) return NWB_OK;
+    const cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(z_out) & 7u) == 0 && (reinterpret_cast<uintptr_t>(u) & 15u) == 0;
+    if (vec_ok && (n_samples == 64 || n_samples == 128) && (n_importance == 64 || n_importance == 128)) {
+        const int warps = 4;
+        const int blocks = std::min((n_rays + warps - 1) / warps, kNumSMs * 8);
+        const size_t smem = static_cast<size_t>(warps) * (4 * n_samples + 2 * n_importance) * sizeof(float);
+#define NWB_PDF_FAST(RS, RQ) sample_pdf_merge_fast_kernel<RS, RQ><<<blocks, warps * 32, smem, st>>>( \
+            z_coarse, w_coarse, n_rays, det, u, seed, cdf_in, z_out, z_new, inds)
+        if (n_samples == 64 && n_importance == 64) NWB_PDF_FAST(2, 2);
+        else if (n_samples == 64) NWB_PDF_FAST(2, 4);
+        else if (n_importance == 64) NWB_PDF_FAST(4, 2);
+        else NWB_PDF_FAST(4, 4);
+#undef NWB_PDF_FAST
+        NWB_LAUNCH_CHECK();
+        return NWB_OK;
+    }
     int P = 32;                                  // sort width: >= one key per lane (register sort), +inf padded
     while (P < n_importance) P <<= 1;
     const int warps = 4;

@@ -106,9 +106,12 @@ class TrainStep:
         self.graph = g
 
     def __call__(self, rays, ts, rgbs):
+        # Host batches (pinned memory, as a DataLoader with pin_memory=True hands them over) are accepted as they are: in
+        # graph mode each goes to its static device buffer in ONE asynchronous host-to-device copy, with no intermediate
+        # device tensor and no device-to-device copy behind it.
         if self._want_graph and rays.shape[0] == self.batch:
             if self.graph is None:
-                self._capture(rays, ts, rgbs)          # warm-up iterations + capture (the capture itself does not run)
+                self._capture(*(t.to(self.dev, non_blocking=True) for t in (rays, ts, rgbs)))   # warm-up + capture (the capture itself does not run)
             self.state.pull_lr()                       # a torch scheduler may have moved FlatAdam's lr between steps
             self.s_rays.copy_(rays, non_blocking=True)
             self.s_ts.copy_(ts, non_blocking=True)
@@ -123,5 +126,6 @@ class TrainStep:
                     m._nwb_dirty = True                # parameters moved: eager callers must repack
             self.terms = self.s_terms
             return self.s_loss
+        rays, ts, rgbs = (t.to(self.dev, non_blocking=True) for t in (rays, ts, rgbs))
         loss, self.terms = self._iteration(rays, ts, rgbs, False)
         return loss

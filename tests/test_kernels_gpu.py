@@ -111,7 +111,7 @@ def test_sample_pdf_indices_bit_exact_given_cdf(det):
 
 
 # sort widths: 32 (padded), 64, 128 and 256 keys in registers, 512 through the shared-memory network
-@pytest.mark.parametrize("ns,ni", [(64, 64), (128, 128), (64, 128), (33, 17), (16, 5), (64, 200), (64, 300), (8, 1)])
+@pytest.mark.parametrize("ns,ni", [(64, 64), (128, 128), (64, 128), (128, 64), (33, 17), (16, 5), (64, 200), (64, 300), (8, 1)])
 def test_sample_pdf_merge_own_cdf(ns, ni):
     gen = torch.Generator().manual_seed(9)
     N = 301
@@ -136,6 +136,48 @@ def test_sample_pdf_merge_own_cdf(ns, ni):
     zr = K.sample_pdf_merge(z.to(DEV), w.to(DEV), ni, False, None, seed=3)
     assert zr.shape == (N, ns + ni) and (zr[:, 1:] >= zr[:, :-1]).all()
     assert zr.min() >= z.min() - 1e-6 and zr.max() <= z.max() + 1e-6
+
+
+@pytest.mark.parametrize("ns,ni", [(64, 64), (128, 128), (64, 128), (128, 64)])
+@pytest.mark.parametrize("mode", ["u", "det", "sorted_u"])
+def test_sample_pdf_unrolled_kernel_matches_general_kernel(ns, ni, mode):
+    # 64 / 128 samples run the unrolled kernel; a u that is not 16-byte aligned sends the same call to the general one
+    gen = torch.Generator().manual_seed(21)
+    N = 777
+    z = torch.sort(torch.rand(N, ns, generator=gen) * 4 + 2, dim=-1)[0].to(DEV)
+    w = torch.rand(N, ns, generator=gen) ** 6
+    w[5] = 0.0
+    w[6, 3:] = 0.0
+    w = w.to(DEV)
+    u = torch.rand(N, ni, generator=gen)
+    u[7, -1] = 1.0
+    u[8, 0] = 0.0
+    if mode == "sorted_u":
+        u = torch.sort(u, -1)[0]
+    buf = torch.empty(N * ni + 1, device=DEV)
+    buf[1:] = u.reshape(-1).to(DEV)
+    u_odd = buf[1:].view(N, ni)
+    assert u_odd.data_ptr() % 16 == 4 and u_odd.is_contiguous()
+    det = mode == "det"
+    fast = K.sample_pdf_merge(z, w, ni, det, u.to(DEV), debug=True)
+    slow = K.sample_pdf_merge(z, w, ni, det, u_odd, debug=True)
+    for a, b, name in zip(fast, slow, ("z", "z_new", "inds")):
+        assert torch.equal(a, b), name
+    # in-kernel Philox stream: same counters, same words
+    if mode == "u":
+        assert torch.equal(K.sample_pdf_merge(z, w, ni, False, None, seed=11), _general_philox(z, w, ni, 11))
+
+
+def _general_philox(z, w, ni, seed):
+    # the general kernel with its own draws: an output buffer that is only 4-byte aligned
+    import ctypes as C
+    from nerf_fl_b200 import _lib as L
+    n, ns = z.shape
+    buf = torch.empty(n * (ns + ni) + 1, device=z.device)
+    out = buf[1:].view(n, ns + ni)
+    L.check(L.lib().nwb_sample_pdf_merge(L.ptr(z), L.ptr(w), n, ns, ni, 0, None, seed, None, L.ptr(out), None, None,
+                                         L.stream_ptr(z.device)), "nwb_sample_pdf_merge")
+    return out
 
 
 def test_sample_pdf_golden_det(golden):

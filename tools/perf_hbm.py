@@ -12,13 +12,15 @@ try:
 except Exception:
     PEAK = 6500.0
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
-def timed(fn, iters=10):
+ITERS = int(os.environ.get("NWB_PERF_ITERS", "10"))      # 1 under ncu (one profiled launch per kernel and call site)
+WARM = 3 if ITERS > 1 else 0
+def timed(fn, iters=ITERS):
     ts = []
-    for i in range(iters + 3):
+    for i in range(iters + WARM):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize()
-        if i >= 3: ts.append(e0.elapsed_time(e1))
+        if i >= WARM: ts.append(e0.elapsed_time(e1))
     return sorted(ts)[len(ts) // 2]
 def line(name, ms, nbytes):
     gbs = nbytes / (ms * 1e-3) / 1e9
