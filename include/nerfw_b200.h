@@ -286,6 +286,18 @@ size_t nwb_nerfw_loss_scratch_bytes(void);
 int nwb_nerfw_loss_fwd(const float* rgb_coarse, const float* rgb_fine, const float* beta,
                        const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
                        float lambda_u, float coef, void* scratch, float* terms, void* stream);
+/* nwb_nerfw_loss_fwd without the scratch argument, for callers that cannot allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  It has no counterpart in the reference.
+ * The partial sums and the ticket live in a file-scope device array of the library
+ * (2.4 KB, one per GPU that loads the library, held until exit); the call allocates nothing and calls no allocating
+ * routine: one 16-byte memset node (the ticket must start at zero) and the same kernel, so terms[0..4] are bit-identical
+ * to nwb_nerfw_loss_fwd's.  n_rays <= NWB_LOSS_STATIC_MAX_RAYS, else NWB_E_ARG with a message.  Every call on a device
+ * shares the array: calls that overlap on the GPU (different streams) race.  The first call on a device looks the
+ * array's address up (cudaGetSymbolAddress): make it outside a capture. */
+#define NWB_LOSS_STATIC_MAX_RAYS (1 << 20)
+int nwb_nerfw_loss_fwd_static(const float* rgb_coarse, const float* rgb_fine, const float* beta,
+                              const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
+                              float lambda_u, float coef, float* terms, void* stream);
 int nwb_nerfw_loss_bwd(const float* rgb_coarse, const float* rgb_fine, const float* beta,
                        const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
                        float lambda_u, float coef, const float* const* g_terms, float* d_rgb_coarse,

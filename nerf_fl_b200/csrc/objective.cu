@@ -210,6 +210,47 @@ extern "C" int nwb_nerfw_loss_fwd(const float* rgb_coarse, const float* rgb_fine
     return NWB_OK;
 }
 
+// ---- the same forward without caller scratch (no counterpart in the reference; added
+// for callers that cannot allocate: graph capture, serving loops, harnesses that forbid cudaMalloc) ---------
+// The partial sums and the ticket live in a file-scope device array, one per GPU that loads the library, held until exit.
+// Every call on a device shares it: calls that overlap on the GPU (two streams) race on the partials and the ticket.
+constexpr int kObjStaticMaxRays = 1 << 20;                   // NWB_LOSS_STATIC_MAX_RAYS in the header
+constexpr int kObjScratchFloats = 4 * kObjMaxBlocks + 4;
+static __device__ __align__(256) float g_obj_static_scratch[kObjScratchFloats];
+
+extern "C" int nwb_nerfw_loss_fwd_static(const float* rgb_coarse, const float* rgb_fine, const float* beta,
+                                         const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
+                                         float lambda_u, float coef, float* terms, void* stream) {
+    NWB_REQUIRE(n_rays >= 1 && rgb_coarse && targets && terms, "nwb_nerfw_loss_fwd_static: null pointer / empty batch");
+    NWB_REQUIRE(n_rays <= kObjStaticMaxRays,
+                "nwb_nerfw_loss_fwd_static: n_rays = %d is beyond the static scratch's maximum of %d rays "
+                "(use nwb_nerfw_loss_fwd with caller-owned scratch)", n_rays, kObjStaticMaxRays);
+    NWB_REQUIRE(!(beta && !rgb_fine), "nwb_nerfw_loss_fwd_static: beta without rgb_fine");
+    NWB_REQUIRE(!transient_sigmas || n_ts >= 1, "nwb_nerfw_loss_fwd_static: bad transient_sigmas size");
+    // In host code the array's name is a host-side stand-in, not a device address: the address is looked up once per
+    // device, with that device current, and it is the looked-up pointer that goes to the kernel.
+    static float* scratch_of[kMaxDevices] = {};
+    static bool resolved[kMaxDevices] = {};
+    int dev = 0;
+    int rc = current_device_checked(&dev);
+    if (rc != NWB_OK) return rc;
+    NWB_CONFIGURE_ONCE(resolved, {
+        float* ptr = nullptr;
+        NWB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_obj_static_scratch));
+        NWB_REQUIRE(ptr != nullptr, "nwb_nerfw_loss_fwd_static: no device address for the static scratch");
+        scratch_of[dev] = ptr;
+    });
+    float* scratch = scratch_of[dev];
+    const cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // the array keeps the last call's contents: the ticket must start at zero (a call that was cut short may have left it
+    // counting); every partial slot the grid reads is written by the grid first
+    NWB_CUDA(cudaMemsetAsync(scratch + 4 * kObjMaxBlocks, 0, 4 * sizeof(float), st));
+    ObjArgs a{rgb_coarse, rgb_fine, beta, transient_sigmas, targets, n_rays, n_ts, lambda_u, coef};
+    nerfw_loss_fwd_kernel<<<obj_grid(a), kObjThreads, 0, st>>>(a, scratch, terms);
+    NWB_LAUNCH_CHECK();
+    return NWB_OK;
+}
+
 extern "C" int nwb_nerfw_loss_bwd(const float* rgb_coarse, const float* rgb_fine, const float* beta,
                                   const float* transient_sigmas, const float* targets, int n_rays, int64_t n_ts,
                                   float lambda_u, float coef, const float* const* g_terms, float* d_rgb_coarse,
