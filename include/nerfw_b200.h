@@ -108,6 +108,29 @@ int nwb_composite_bwd(const float* raw, int C, const float* z, const float* nois
                       float noise_std, int n_rays, int S, uint32_t flags,
                       const nwb_composite_grads* g, float* d_raw, void* stream);
 
+/* The same backward seeding its own cotangents under NerfWLoss (losses.py:35-50; SURVEY.md 8f-1 "fold the loss into the
+ * compositing epilogue"): with `seed` the cotangents of this pass's rgb (and, fine pass with a transient head, of beta and
+ * transient_sigmas) are formed in the kernel from the maps and the targets -- the arithmetic of nwb_nerfw_loss_bwd, bit for
+ * bit -- and ADDED to whatever `g` carries (g may be NULL = all zero); no loss-backward launch, no (n,3)/(n)/(n,S)
+ * cotangent tensors.  g_terms: DEVICE scalars, cotangents of (c_l, f_l, b_l, s_l, total), NULL = 0.
+ * amax_bits (may be NULL): receives max |d_raw| as fp32 bits (cleared by a 4-byte memset node first) -- point it at the
+ * first word of the nwb_mlp_bwd workspace and pass NWB_MLP_DZ_AMAX_GIVEN there to skip that call's own reduction launch. */
+typedef struct nwb_loss_seed {
+    const float* rgb;          /* (n,3) rgb_coarse (fine == 0) or rgb_fine (fine != 0), as the forward produced it */
+    const float* beta;         /* (n)   fine pass with a transient head, else NULL                  losses.py:42-44 */
+    const float* targets;      /* (n,3)                                                                            */
+    const float* g_terms[5];
+    float coef, lambda_u;      /* NerfWLoss(coef, lambda_u)                                         losses.py:27-33 */
+    int n_rays;                /* batch size the means run over                                                     */
+    int64_t n_ts;              /* numel(transient_sigmas); 0: no s_l term                           losses.py:45   */
+    int fine;
+} nwb_loss_seed;
+
+int nwb_composite_bwd_seeded(const float* raw, int C, const float* z, const float* noise,
+                             float noise_std, int n_rays, int S, uint32_t flags,
+                             const nwb_composite_grads* g, const nwb_loss_seed* seed,
+                             unsigned int* amax_bits, float* d_raw, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (a3,a4) field network -- models/nerf.py:81-212 + the per-sample input assembly of
  * models/rendering.py:96-139.  W=256, D=8, skips=[4] (the only shape the reference ever builds).
@@ -172,6 +195,7 @@ int nwb_field_pack(const nwb_field_desc* d, const nwb_field_params* p, void* pac
 #define NWB_MLP_SIGMA_ONLY 1u   /* NeRF.forward(sigma_only=True)            nerf.py:191-192 */
 #define NWB_MLP_TRANSIENT 2u    /* output_transient=True                    nerf.py:200-212 */
 #define NWB_MLP_SAVE 4u         /* keep activations for the backward pass                   */
+#define NWB_MLP_DZ_AMAX_GIVEN 8u /* nwb_mlp_bwd / nwb_mlp_dgrad: workspace word 0 already holds max|d_raw| (fp32 bits) */
 
 /* per-ray operands of dir_encoding / transient_encoding.0: gathers embedding rows, encodes the
  * view direction and folds them through the matching weight columns into per-ray bias vectors

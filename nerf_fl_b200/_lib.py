@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("NWB_LIB_PATH") or os.path.join(_HERE, "libnerfw_b200.so")
 
 NWB_COMP_TRANSIENT, NWB_COMP_WHITE_BACK, NWB_COMP_TEST_TIME, NWB_COMP_COARSE = 1, 2, 4, 8
-NWB_MLP_SIGMA_ONLY, NWB_MLP_TRANSIENT, NWB_MLP_SAVE = 1, 2, 4
+NWB_MLP_SIGMA_ONLY, NWB_MLP_TRANSIENT, NWB_MLP_SAVE, NWB_MLP_DZ_AMAX_GIVEN = 1, 2, 4, 8
 
 _f32p = C.c_void_p   # device pointers travel as integers
 _vp = C.c_void_p
@@ -32,6 +32,12 @@ class CompositeGrads(C.Structure):
     _fields_ = [(n, _f32p) for n in (
         "d_weights", "d_opacity", "d_rgb", "d_depth", "d_transient_sigmas", "d_beta",
         "d_rgb_static", "d_rgb_transient")]
+
+
+class LossSeed(C.Structure):
+    """nwb_loss_seed: NerfWLoss cotangents formed inside the compositing backward (nwb_composite_bwd_seeded)."""
+    _fields_ = [("rgb", _f32p), ("beta", _f32p), ("targets", _f32p), ("g_terms", _f32p * 5), ("coef", C.c_float),
+                ("lambda_u", C.c_float), ("n_rays", C.c_int), ("n_ts", C.c_int64), ("fine", C.c_int)]
 
 
 class FieldDesc(C.Structure):
@@ -76,6 +82,8 @@ def lib() -> C.CDLL:
         "nwb_sample_pdf_merge": [_vp, _vp, i, i, i, i, _vp, u64, _vp, _vp, _vp, _vp, _vp],
         "nwb_composite_fwd": [_vp, i, _vp, _vp, f, i, i, u32, f, C.POINTER(CompositeOut), _vp],
         "nwb_composite_bwd": [_vp, i, _vp, _vp, f, i, i, u32, C.POINTER(CompositeGrads), _vp, _vp],
+        "nwb_composite_bwd_seeded": [_vp, i, _vp, _vp, f, i, i, u32, C.POINTER(CompositeGrads), C.POINTER(LossSeed), _vp,
+                                     _vp, _vp],
         "nwb_selftest_umma": [_vp, _vp, i, i, i, C.POINTER(u32), _vp, _vp],
     }
     for name, args in protos.items():

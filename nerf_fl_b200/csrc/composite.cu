@@ -3,7 +3,7 @@
 // sample) through a coalesced, float4-vectorised copy into its shared-memory slab, each lane
 // then owns one sample; transmittance is a warp product-scan carried across chunks.  Backward
 // keeps T in shared memory and runs the division-free reverse suffix scan of SURVEY.md A.3.
-#include "common.cuh"
+#include "objective.cuh"
 #include <algorithm>
 
 namespace nwb {
@@ -210,10 +210,21 @@ template <int C, bool kTr>
 __global__ void __launch_bounds__(kCompWarps * 32)
 composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                      const float* __restrict__ noise, float noise_std, int n_rays, int S,
-                     uint32_t flags, nwb_composite_grads g, float* __restrict__ d_raw) {
+                     uint32_t flags, nwb_composite_grads g, float* __restrict__ d_raw, const LossSeedDev seed,
+                     unsigned int* __restrict__ amax_bits) {
     extern __shared__ __align__(16) float dsm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int Sp = (S + 3) & ~3;
+    // seeded: the cotangents of rgb / beta / transient_sigmas under NerfWLoss are formed here from the maps themselves
+    // (objective.cuh) and ADDED to whatever g carries for them
+    const bool seeded = seed.tgt != nullptr;
+    LossScalars sc{};
+    float seed_ts = 0.0f;
+    if (seeded) {
+        sc = loss_scalars(seed.g[0], seed.g[1], seed.g[2], seed.g[3], seed.g[4], seed.coef, seed.n);
+        if (seed.fine && seed.beta != nullptr && seed.n_ts > 0) seed_ts = loss_d_tsigma(sc, seed.lambda_u, seed.n_ts);
+    }
+    float amax = 0.0f;                                       // max |d_raw| this lane wrote (amax_bits != nullptr)
     constexpr int kStageFloats = sizeof(RingStage<C>) / sizeof(float);
     float* wbase = dsm + warp * (kRing * kStageFloats + Sp);
     RingStage<C>* my = reinterpret_cast<RingStage<C>*>(wbase);
@@ -247,11 +258,30 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
         // per-ray cotangents
         const float g_op = g.d_opacity ? __ldg(g.d_opacity + ray) : 0.0f;
         const float g_dp = g.d_depth ? __ldg(g.d_depth + ray) : 0.0f;
-        const float g_be = (transient && g.d_beta) ? __ldg(g.d_beta + ray) : 0.0f;
+        float g_be = (transient && g.d_beta) ? __ldg(g.d_beta + ray) : 0.0f;
+        float seed_rgb[3] = {0.0f, 0.0f, 0.0f};
+        if (seeded) {
+            const bool has_beta = seed.fine && seed.beta != nullptr;
+            const float b = has_beta ? __ldg(seed.beta + ray) : 1.0f;
+            const float ib2 = loss_inv_beta2(b);
+            float err = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float t = __ldg(seed.tgt + ray * 3 + c), x = __ldg(seed.rgb + ray * 3 + c);
+                if (seed.fine) {
+                    const float df = __fsub_rn(x, t);
+                    seed_rgb[c] = loss_d_rgb_fine(sc, df, ib2, has_beta);
+                    err = __fmaf_rn(df, df, err);
+                } else {
+                    seed_rgb[c] = loss_d_rgb_coarse(sc, x, t);
+                }
+            }
+            if (transient && has_beta) g_be += loss_d_beta(sc, err, ib2, b);
+        }
         float Gs[3], Gt[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const float gr = g.d_rgb ? __ldg(g.d_rgb + ray * 3 + c) : 0.0f;
+            const float gr = (g.d_rgb ? __ldg(g.d_rgb + ray * 3 + c) : 0.0f) + seed_rgb[c];
             Gs[c] = gr + ((transient && g.d_rgb_static) ? __ldg(g.d_rgb_static + ray * 3 + c) : 0.0f);
             Gt[c] = gr + ((transient && g.d_rgb_transient) ? __ldg(g.d_rgb_transient + ray * 3 + c) : 0.0f);
         }
@@ -348,11 +378,15 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                 }
                 if (C == 9) {
                     if (transient) {
-                        dsig_t = delta * (head_t - R) + (g.d_transient_sigmas ? __ldg(g.d_transient_sigmas + row + i) : 0.0f);
+                        dsig_t = delta * (head_t - R) + ((g.d_transient_sigmas ? __ldg(g.d_transient_sigmas + row + i) : 0.0f) + seed_ts);
                         v[4] = dct[0]; v[5] = dct[1]; v[6] = dct[2]; v[7] = dsig_t; v[8] = dbeta;
                     } else {
                         v[4] = v[5] = v[6] = v[7] = v[8] = 0.0f;
                     }
+                }
+                if (amax_bits != nullptr) {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) amax = fmaxf(amax, fabsf(v[c]));       // fmaxf drops NaN operands
                 }
             }
             __syncwarp();
@@ -366,6 +400,21 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                 for (int k = lane; k < nfl; k += 32) dst[k] = slab[k];
             }
             __syncwarp();
+        }
+    }
+    if (amax_bits != nullptr) {
+        // max |d_raw| of the pass for the field backward's 8-bit scale (what dz_amax_kernel finds in a launch of its own):
+        // non-negative floats order like their bit patterns, one atomicMax per block
+        __shared__ float amax_red[kCompWarps];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        if (lane == 0) amax_red[warp] = amax;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float m = amax_red[0];
+#pragma unroll
+            for (int w = 1; w < kCompWarps; ++w) m = fmaxf(m, amax_red[w]);
+            if (m > 0.0f && m < INFINITY) atomicMax(amax_bits, __float_as_uint(m));
         }
     }
 }
@@ -398,26 +447,38 @@ extern "C" int nwb_composite_fwd(const float* raw, int C, const float* z, const 
     return NWB_OK;
 }
 
-extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const float* noise,
-                                 float noise_std, int n_rays, int S, uint32_t flags,
-                                 const nwb_composite_grads* g, float* d_raw, void* stream) {
-    NWB_REQUIRE(n_rays == 0 || (raw && z && g && d_raw), "nwb_composite_bwd: null pointer");
-    NWB_REQUIRE(C == 1 || C == 4 || C == 9, "nwb_composite_bwd: C must be 1, 4 or 9 (got %d)", C);
-    NWB_REQUIRE(S >= 1 && n_rays >= 0, "nwb_composite_bwd: bad shape");
-    NWB_REQUIRE(!(flags & NWB_COMP_TEST_TIME), "nwb_composite_bwd: test_time outputs carry no gradient");
-    NWB_REQUIRE(!(flags & NWB_COMP_TRANSIENT) || C == 9, "nwb_composite_bwd: transient needs C==9");
+static int composite_bwd_launch(const float* raw, int C, const float* z, const float* noise, float noise_std, int n_rays, int S,
+                                uint32_t flags, const nwb_composite_grads* g, const nwb_loss_seed* seed,
+                                unsigned int* amax_bits, float* d_raw, void* stream, const char* who) {
+    NWB_REQUIRE(n_rays == 0 || (raw && z && d_raw), "%s: null pointer", who);
+    NWB_REQUIRE(C == 1 || C == 4 || C == 9, "%s: C must be 1, 4 or 9 (got %d)", who, C);
+    NWB_REQUIRE(S >= 1 && n_rays >= 0, "%s: bad shape", who);
+    NWB_REQUIRE(!(flags & NWB_COMP_TEST_TIME), "%s: test_time outputs carry no gradient", who);
+    NWB_REQUIRE(!(flags & NWB_COMP_TRANSIENT) || C == 9, "%s: transient needs C==9", who);
+    LossSeedDev sd{};
+    if (seed != nullptr) {
+        NWB_REQUIRE(seed->rgb && seed->targets && seed->n_rays >= 1, "%s: seed needs rgb, targets and the batch size", who);
+        NWB_REQUIRE(C != 1, "%s: a sigma-only pass has no rgb to seed", who);
+        NWB_REQUIRE(!seed->beta || (seed->fine && (flags & NWB_COMP_TRANSIENT)), "%s: seed beta needs the fine transient pass", who);
+        sd.rgb = seed->rgb; sd.beta = seed->beta; sd.tgt = seed->targets;
+        for (int i = 0; i < 5; ++i) sd.g[i] = seed->g_terms[i];
+        sd.coef = seed->coef; sd.lambda_u = seed->lambda_u; sd.n = seed->n_rays; sd.n_ts = seed->n_ts; sd.fine = seed->fine;
+    }
     if (n_rays == 0) return NWB_OK;
+    const nwb_composite_grads none{};
+    if (g == nullptr) g = &none;
     const int blocks = std::min((n_rays + kCompWarps - 1) / kCompWarps, kNumSMs * 16);
     const size_t smem = static_cast<size_t>(kCompWarps) * (kRing * (32 * C + 36) + ((S + 3) & ~3)) * sizeof(float);
-    NWB_REQUIRE(smem <= 200 * 1024, "nwb_composite_bwd: S too large for shared memory");
+    NWB_REQUIRE(smem <= 200 * 1024, "%s: S too large for shared memory", who);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (amax_bits != nullptr) NWB_CUDA(cudaMemsetAsync(amax_bits, 0, sizeof(unsigned int), st));
 #define NWB_BWD(CC, TR)                                                                             \
     do {                                                                                            \
         if (smem > 48 * 1024)                                                                       \
             NWB_CUDA(cudaFuncSetAttribute(composite_bwd_kernel<CC, TR>,                             \
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         composite_bwd_kernel<CC, TR><<<blocks, kCompWarps * 32, smem, st>>>(raw, z, noise, noise_std, \
-                                                                            n_rays, S, flags, *g, d_raw); \
+                                                                            n_rays, S, flags, *g, d_raw, sd, amax_bits); \
     } while (0)
     if (C == 1) NWB_BWD(1, false);
     else if (C == 4) NWB_BWD(4, false);
@@ -426,4 +487,20 @@ extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const 
 #undef NWB_BWD
     NWB_LAUNCH_CHECK();
     return NWB_OK;
+}
+
+extern "C" int nwb_composite_bwd(const float* raw, int C, const float* z, const float* noise,
+                                 float noise_std, int n_rays, int S, uint32_t flags,
+                                 const nwb_composite_grads* g, float* d_raw, void* stream) {
+    NWB_REQUIRE(n_rays == 0 || g, "nwb_composite_bwd: null pointer");
+    return composite_bwd_launch(raw, C, z, noise, noise_std, n_rays, S, flags, g, nullptr, nullptr, d_raw, stream,
+                                "nwb_composite_bwd");
+}
+
+extern "C" int nwb_composite_bwd_seeded(const float* raw, int C, const float* z, const float* noise,
+                                        float noise_std, int n_rays, int S, uint32_t flags,
+                                        const nwb_composite_grads* g, const nwb_loss_seed* seed,
+                                        unsigned int* amax_bits, float* d_raw, void* stream) {
+    return composite_bwd_launch(raw, C, z, noise, noise_std, n_rays, S, flags, g, seed, amax_bits, d_raw, stream,
+                                "nwb_composite_bwd_seeded");
 }

@@ -566,6 +566,8 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
                     "nwb_mlp_bwd: transient head gradient sink is null");
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool amax_given = (mode & NWB_MLP_DZ_AMAX_GIVEN) != 0;      // nwb_composite_bwd_seeded left it in the header
+    mode &= ~NWB_MLP_DZ_AMAX_GIVEN;
 
     BwdArgs a{};
     a.fs = fs; a.packed = static_cast<const uint8_t*>(packed); a.raw = raw; a.d_raw = d_raw;
@@ -588,11 +590,13 @@ static int mlp_bwd_phases(const nwb_field_desc* d, const void* packed, const flo
 
     if (run_dgrad) {
         // the pass's scale: amax |d_raw| into the workspace header (a memset node and one small reduction)
-        NWB_CUDA(cudaMemsetAsync(workspace, 0, kDzHeaderBytes, st));
-        const long long n_raw = a.n_points * (transient ? 9 : 4);
-        const int ablocks = static_cast<int>(std::min<long long>((n_raw / 4 + 255) / 256 + 1, kNumSMs * 2));
-        dz_amax_kernel<<<ablocks, 256, 0, st>>>(d_raw, n_raw, static_cast<DzHeader*>(workspace));
-        NWB_LAUNCH_CHECK();
+        if (!amax_given) {
+            NWB_CUDA(cudaMemsetAsync(workspace, 0, kDzHeaderBytes, st));
+            const long long n_raw = a.n_points * (transient ? 9 : 4);
+            const int ablocks = static_cast<int>(std::min<long long>((n_raw / 4 + 255) / 256 + 1, kNumSMs * 2));
+            dz_amax_kernel<<<ablocks, 256, 0, st>>>(d_raw, n_raw, static_cast<DzHeader*>(workspace));
+            NWB_LAUNCH_CHECK();
+        }
         static bool configured[kMaxDevices] = {};
         NWB_CONFIGURE_ONCE(configured, {
             NWB_CUDA(cudaFuncSetAttribute(field_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));

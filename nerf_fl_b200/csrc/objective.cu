@@ -8,7 +8,7 @@
 //   s_l = coef * lambda_u * mean(transient_sigmas)                      losses.py:45
 // Without beta (no transient head) f_l = coef * 0.5 * mean((rgb_fine - t)^2) (:40) and b_l, s_l are absent;
 // without rgb_fine only c_l exists.  terms[4] = their sum.
-#include "common.cuh"
+#include "objective.cuh"
 #include <algorithm>
 
 namespace nwb {
@@ -120,31 +120,27 @@ __global__ void __launch_bounds__(kObjThreads)
 nerfw_loss_bwd_kernel(const ObjArgs a, const float* g0, const float* g1, const float* g2, const float* g3, const float* g4,
                       float* __restrict__ d_rgb_c, float* __restrict__ d_rgb_f, float* __restrict__ d_beta,
                       float* __restrict__ d_ts) {
-    const float gt = g4 ? __ldg(g4) : 0.0f;
-    const float gc = ((g0 ? __ldg(g0) : 0.0f) + gt) * a.coef, gf = ((g1 ? __ldg(g1) : 0.0f) + gt) * a.coef;
-    const float gb = ((g2 ? __ldg(g2) : 0.0f) + gt) * a.coef, gs = ((g3 ? __ldg(g3) : 0.0f) + gt) * a.coef;
+    const LossScalars sc = loss_scalars(g0, g1, g2, g3, g4, a.coef, a.n);
     const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long nth = static_cast<long long>(gridDim.x) * blockDim.x;
-    const float inv3 = 1.0f / static_cast<float>(3ll * a.n), invn = 1.0f / static_cast<float>(a.n);
     for (long long r = tid; r < a.n; r += nth) {
         float acc = 0.0f;
         const float b = a.beta ? __ldg(a.beta + r) : 1.0f;
-        const float ib2 = 1.0f / (b * b);
+        const float ib2 = loss_inv_beta2(b);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const float t = __ldg(a.tgt + 3 * r + c);
-            d_rgb_c[3 * r + c] = gc * (__ldg(a.rgb_c + 3 * r + c) - t) * inv3;       // d/dx 0.5 mean(x^2)
+            d_rgb_c[3 * r + c] = loss_d_rgb_coarse(sc, __ldg(a.rgb_c + 3 * r + c), t);
             if (a.rgb_f != nullptr) {
-                const float df = __ldg(a.rgb_f + 3 * r + c) - t;
-                d_rgb_f[3 * r + c] = a.beta ? gf * df * ib2 * inv3 : gf * df * inv3;
-                acc += df * df;
+                const float df = __fsub_rn(__ldg(a.rgb_f + 3 * r + c), t);
+                d_rgb_f[3 * r + c] = loss_d_rgb_fine(sc, df, ib2, a.beta != nullptr);
+                acc = __fmaf_rn(df, df, acc);
             }
         }
-        // d/dbeta [ mean(err / (2 beta^2)) ] = -err / beta^3 / (3N);  d/dbeta [ mean(log beta) ] = 1 / (beta N)
-        if (a.beta != nullptr && d_beta != nullptr) d_beta[r] = -gf * acc * ib2 / b * inv3 + gb * invn / b;
+        if (a.beta != nullptr && d_beta != nullptr) d_beta[r] = loss_d_beta(sc, acc, ib2, b);
     }
     if (a.ts != nullptr && d_ts != nullptr) {
-        const float v = gs * a.lambda_u / static_cast<float>(a.n_ts);
+        const float v = loss_d_tsigma(sc, a.lambda_u, a.n_ts);
         for (long long i = tid; i < a.n_ts; i += nth) d_ts[i] = v;
     }
 }

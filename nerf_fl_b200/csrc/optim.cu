@@ -150,8 +150,12 @@ adam_pack_kernel(const AdamPackArgs a) {
     };
     const int y = blockIdx.y;
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-    if (y == a.y0[a.n_fields]) {
-        for (int i = tid; i < a.n_rest; i += nth) step_at(a.p + a.rest[i]);
+    if (y >= a.y0[a.n_fields]) {
+        // the rest list takes as many grid slices as give every thread one element: walked by one slice each thread did
+        // ~18 dependent (index -> p, g, m, v -> store) round trips to memory one after the other, the longest thing in
+        // this launch
+        const int rs = y - a.y0[a.n_fields], n_rs = static_cast<int>(gridDim.y) - a.y0[a.n_fields];
+        for (int i = rs * nth + tid; i < a.n_rest; i += n_rs * nth) step_at(a.p + a.rest[i]);
     } else {
         int f = 0;
         while (f + 1 < a.n_fields && y >= a.y0[f + 1]) ++f;
@@ -319,7 +323,8 @@ static int adam_pack_launch(float* p, float* g, float* m, float* v, int64_t n, f
             a.red[q] = reinterpret_cast<const float*>(static_cast<const uint8_t*>(regions[q]) + roff);
         }
     }
-    dim3 grid(kAdamPackBlocksX, y + 1);
+    const int rest_slices = std::max<int>(1, static_cast<int>((n_rest + kAdamPackBlocksX * 256 - 1) / (kAdamPackBlocksX * 256)));
+    dim3 grid(kAdamPackBlocksX, y + std::min(rest_slices, 64));
     adam_pack_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
     NWB_LAUNCH_CHECK();
     return NWB_OK;

@@ -178,8 +178,13 @@ def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bo
 
 def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, transient: bool,
                   white_back: bool, noise: torch.Tensor | None = None,
-                  noise_std: float = 0.0) -> torch.Tensor:
-    """Cotangents keyed like the result dict -> d_raw (N,S,C)."""
+                  noise_std: float = 0.0, seed: dict | None = None, amax_out: torch.Tensor | None = None) -> torch.Tensor:
+    """Cotangents keyed like the result dict -> d_raw (N,S,C).
+
+    ``seed`` (nwb_composite_bwd_seeded): dict(rgb, beta, targets, g_terms (5 device scalars or None), coef, lambda_u,
+    n_rays, n_ts, fine) -- the NerfWLoss cotangents of this pass's rgb / beta / transient_sigmas are formed in the kernel
+    and added to ``grads``.  ``amax_out``: buffer whose first word receives max|d_raw| (fp32 bits) for
+    mlp_bwd(mode | NWB_MLP_DZ_AMAX_GIVEN)."""
     raw, z = _f32(raw), _f32(z)
     n, S = z.shape
     Cc = raw.shape[-1]
@@ -206,11 +211,34 @@ def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, 
         put("d_rgb", f"rgb_{typ}")
     d_raw = torch.empty_like(raw)
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
+    flags = composite_flags(transient, white_back, False, typ == "coarse")
+    if seed is None and amax_out is None:
+        with _timed("nwb_composite_bwd", n, Cc * 1000 + S, dev=z.device):
+            L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S, flags,
+                                              C.byref(g), L.ptr(d_raw), L.stream_ptr(z.device)),
+                    "nwb_composite_bwd")
+        return d_raw
+    sd = None
+    if seed is not None:
+        sd = L.LossSeed()
+        for k in ("rgb", "beta", "targets"):
+            t = seed.get(k)
+            if t is not None:
+                t = _f32(t)
+                keep.append(t)
+                setattr(sd, k, L.ptr(t))
+        for i, t in enumerate(seed.get("g_terms") or ()):
+            if t is not None:
+                t = _f32(t)
+                keep.append(t)
+                sd.g_terms[i] = L.ptr(t)
+        sd.coef, sd.lambda_u = float(seed["coef"]), float(seed["lambda_u"])
+        sd.n_rays, sd.n_ts, sd.fine = int(seed["n_rays"]), int(seed.get("n_ts") or 0), int(bool(seed["fine"]))
     with _timed("nwb_composite_bwd", n, Cc * 1000 + S, dev=z.device):
-        L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
-                                          composite_flags(transient, white_back, False, typ == "coarse"),
-                                          C.byref(g), L.ptr(d_raw), L.stream_ptr(z.device)),
-                "nwb_composite_bwd")
+        L.check(L.lib().nwb_composite_bwd_seeded(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S, flags,
+                                                 C.byref(g), C.byref(sd) if sd is not None else None, L.ptr(amax_out),
+                                                 L.ptr(d_raw), L.stream_ptr(z.device)),
+                "nwb_composite_bwd_seeded")
     return d_raw
 
 
@@ -383,7 +411,7 @@ def mlp_bwd(desc, packed, raw, d_raw, saved, *, n_rays, S, mode, grads: dict, d_
     sig = [C.POINTER(L.FieldDesc), _vp, _vp, _vp, _vp, _i, _i, _u32, C.POINTER(L.FieldGrads), _vp, _vp, _vp]
     for ph in phases:
         name = "nwb_mlp_" + ph
-        with _timed(name, n_rays * S, mode, dev=dev):
+        with _timed(name, n_rays * S, mode & ~L.NWB_MLP_DZ_AMAX_GIVEN, dev=dev):
             L.check(_fn(name, sig)(C.byref(desc), L.ptr(packed), L.ptr(raw), L.ptr(d_raw), L.ptr(saved), n_rays, S, mode,
                                    C.byref(st), L.ptr(d_ray_bias), L.ptr(workspace), L.stream_ptr(dev)), name)
     return workspace

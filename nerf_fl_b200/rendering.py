@@ -134,22 +134,28 @@ def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, t
     return P, res
 
 
-def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_w, emb_t_w, names, params, aux=None):
-    """Backward of _run_pass -> (param sinks, direct?, d_emb_a, d_emb_t, d_a_rows, d_t_rows)."""
+def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_w, emb_t_w, names, params, aux=None,
+              seed=None):
+    """Backward of _run_pass -> (param sinks, direct?, d_emb_a, d_emb_t, d_a_rows, d_t_rows).  ``seed``: the NerfWLoss
+    cotangents of this pass's maps are formed inside the compositing backward (K.composite_bwd)."""
     n, S = P.z.shape
     dev = P.z.device
+    # the compositing backward also leaves max|d_raw| in the field backward's workspace header (the 8-bit images' scale):
+    # no reduction launch between the two
+    ws = K.aligned_empty(K.mlp_bwd_workspace_bytes(P.desc, n * S, P.mode & ~L.NWB_MLP_SAVE), dev, 16)
     d_raw = K.composite_bwd(P.raw.view(n, S, -1), P.z, grads_by_key, typ=P.typ, transient=P.transient,
-                            white_back=white_back, noise=P.noise, noise_std=noise_std)
+                            white_back=white_back, noise=P.noise, noise_std=noise_std, seed=seed, amax_out=ws)
+    bwd_mode = P.mode | L.NWB_MLP_DZ_AMAX_GIVEN
     sinks, direct = _grad_sinks(names, params, dev)
     d_rb = torch.zeros(n, 256, device=dev, dtype=torch.float32)
     # dgrad produces d_ray_bias and the dZ images; wgrad (dZ -> weight gradients) and the per-ray constants' backward
     # (d_ray_bias -> tail columns, biases, embedding rows) are independent of each other: with `aux` (a stream, graph
     # capture only) the second runs next to the first
-    ws = K.mlp_bwd(P.desc, P.packed, P.raw, d_raw.view(n * S, -1), P.saved, n_rays=n, S=S, mode=P.mode, grads=sinks,
-                   d_ray_bias=d_rb, phases=("dgrad",))
+    K.mlp_bwd(P.desc, P.packed, P.raw, d_raw.view(n * S, -1), P.saved, n_rays=n, S=S, mode=bwd_mode, grads=sinks,
+              d_ray_bias=d_rb, workspace=ws, phases=("dgrad",))
     if aux is not None:
         aux.wait_stream(torch.cuda.current_stream(dev))
-    K.mlp_bwd(P.desc, P.packed, P.raw, d_raw.view(n * S, -1), P.saved, n_rays=n, S=S, mode=P.mode, grads=sinks,
+    K.mlp_bwd(P.desc, P.packed, P.raw, d_raw.view(n * S, -1), P.saved, n_rays=n, S=S, mode=bwd_mode, grads=sinks,
               d_ray_bias=d_rb, workspace=ws, phases=("wgrad",))
     sd = {k: v.detach() for k, v in zip(names, params)}
     d_a_rows = torch.empty_like(P.a_rows) if (P.use_a and P.a_rows is not None) else None
@@ -169,6 +175,13 @@ def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_
     if aux is not None:
         torch.cuda.current_stream(dev).wait_stream(aux)
     return sinks, direct, (None if ea_direct else d_ea), (None if et_direct else d_et), d_a_rows, d_t_rows
+
+
+_LOSS_KEYS = ("loss_c_l", "loss_f_l", "loss_b_l", "loss_s_l", "loss_total")
+
+
+def _detached(t):
+    return t.detach() if t is not None else None
 
 
 class _RenderFn(torch.autograd.Function):
@@ -220,6 +233,26 @@ class _RenderFn(torch.autograd.Function):
                                   emb_a=emb_a_w, emb_t=emb_t_w, a_rows=a_embedded, t_rows=t_embedded, consts=consts_f,
                                   **common)
             res.update(res_f)
+        # NerfWLoss over the maps, inside this node (cfg["loss"], set by render_rays(loss=...)): the five terms become
+        # extra outputs and the backward forms their cotangents in the compositing kernels (no loss-backward launch, no
+        # cotangent maps).  The forward launch is off the critical path when the caller promises a backward (TrainStep).
+        ctx.loss = None
+        spec = cfg.get("loss")
+        if spec is not None and save:
+            beta = res.get("beta")
+            tsig = res.get("transient_sigmas") if beta is not None else None
+            lstream = None
+            if fork and spec.get("join_in_backward"):
+                lstream = _side_stream(rays.device, 3)
+                lstream.wait_stream(torch.cuda.current_stream(rays.device))
+            with (torch.cuda.stream(lstream) if lstream is not None else contextlib.nullcontext()):
+                terms = K.nerfw_loss_fwd(res["rgb_coarse"], res.get("rgb_fine"), beta, tsig, spec["targets"],
+                                         spec["lambda_u"], spec["coef"])
+            ctx.loss = dict(rgb_c=res["rgb_coarse"].detach(), rgb_f=_detached(res.get("rgb_fine")), beta=_detached(beta),
+                            n_ts=tsig.numel() if tsig is not None else 0, targets=spec["targets"],
+                            coef=spec["coef"], lambda_u=spec["lambda_u"], stream=lstream)
+            for i, k in enumerate(_LOSS_KEYS):
+                res[k] = terms[i]
         cfg["keys"] = list(res.keys())
         ctx.cfg, ctx.Pc, ctx.Pf, ctx.n_c = cfg, Pc, Pf, n_c
         ctx.ts, ctx.emb_a_w, ctx.emb_t_w = ts, emb_a_w, emb_t_w
@@ -239,6 +272,16 @@ class _RenderFn(torch.autograd.Function):
         names_c, names_f = cfg["names_c"], cfg["names_f"]
         params_c, params_f = ctx.params[:n_c], ctx.params[n_c:]
         kw = dict(white_back=cfg["white_back"], noise_std=cfg["noise_std"])
+        seed_c = seed_f = None
+        if ctx.loss is not None:
+            lo = ctx.loss
+            g_terms = [g.pop(k, None) for k in _LOSS_KEYS]
+            if any(t is not None for t in g_terms):
+                common = dict(targets=lo["targets"], g_terms=g_terms, coef=lo["coef"], lambda_u=lo["lambda_u"],
+                              n_rays=Pc.z.shape[0])
+                seed_c = dict(rgb=lo["rgb_c"], beta=None, n_ts=0, fine=False, **common)
+                if lo["rgb_f"] is not None:
+                    seed_f = dict(rgb=lo["rgb_f"], beta=lo["beta"], n_ts=lo["n_ts"], fine=True, **common)
         out_params = []
         d_ea = d_et = d_a = d_t = None
         # The coarse and the fine chain (compositing bwd -> dgrad -> wgrad -> per-ray constants) share nothing but the
@@ -258,19 +301,22 @@ class _RenderFn(torch.autograd.Function):
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
-                                                  params=params_c, aux=_side_stream(Pc.z.device, 1), **kw)
+                                                  params=params_c, aux=_side_stream(Pc.z.device, 1), seed=seed_c, **kw)
         else:
             sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
-                                              params=params_c, aux=_side_stream(Pc.z.device, 1) if fork else None, **kw)
+                                              params=params_c, aux=_side_stream(Pc.z.device, 1) if fork else None,
+                                              seed=seed_c, **kw)
         out_params += [None if direct_c else sinks_c[k] for k in names_c]
         if Pf is not None:
             sinks_f, direct_f, d_ea, d_et, d_a, d_t = _bwd_pass(Pf, g, ts=ctx.ts, emb_a_w=ctx.emb_a_w,
                                                                 emb_t_w=ctx.emb_t_w, names=names_f, params=params_f,
                                                                 aux=_side_stream(Pc.z.device, 2) if fork else None,
-                                                                **kw)
+                                                                seed=seed_f, **kw)
             out_params += [None if direct_f else sinks_f[k] for k in names_f]
         if fork_chains:
             cur.wait_stream(side)
+        if ctx.loss is not None and ctx.loss["stream"] is not None:
+            torch.cuda.current_stream(Pc.z.device).wait_stream(ctx.loss["stream"])      # the loss value joins here
         # inputs: cfg, rays, ts, view_dir, a_embedded, t_embedded, emb_a_w, emb_t_w, n_c, *params
         return (None, None, None, None, d_a, d_t, d_ea, d_et, None, *out_params)
 
@@ -285,7 +331,10 @@ def render_rays(models, embeddings, rays, ts, N_samples=64, use_disp=False, pert
     ``view_dir``, ``current_epoch`` (ignored: BARF only); plus ``rng`` -- a dict of pre-drawn
     tensors ``perturb_rand`` (N,Ns) U[0,1), ``noise_coarse`` (N,Ns) N(0,1), ``u`` (N,Ni) U[0,1),
     ``noise_fine`` (N,Ns+Ni) N(0,1) replacing the draws of rendering.py:257,151,30 (parity runs) --
-    and ``seed`` for the in-kernel Philox streams used otherwise.
+    and ``seed`` for the in-kernel Philox streams used otherwise; ``loss`` -- ``dict(fn=NerfWLoss(...), targets=rgbs)``:
+    the objective (losses.py:35-50) is evaluated inside the same autograd node and comes back as
+    ``result['loss_terms']`` (the dict NerfWLoss returns, ``.total`` = their sum); its backward is folded into the
+    compositing kernels, so a training step launches neither a loss backward nor cotangent maps (TrainStep uses it).
     Gradients flow to every NeRF parameter, to ``embeddings['a'|'t'].weight`` and to explicit
     ``a_embedded`` / ``t_embedded`` rows; not to rays / view_dir (no pose refinement on this path).
     With ``test_time=True`` outputs carry no gradient (eval.py:80 runs under no_grad)."""
@@ -338,9 +387,27 @@ def render_rays(models, embeddings, rays, ts, N_samples=64, use_disp=False, pert
         cfg["rng"][k] = K._f32(v)
     if n == 0:
         raise RuntimeError("render_rays called with zero rays")
+    loss = kwargs.get("loss")
+    if loss is not None:
+        fn, targets = loss["fn"], K._f32(loss["targets"])
+        if targets.shape != (n, 3):
+            raise RuntimeError(f"loss targets must be ({n}, 3), got {tuple(targets.shape)}")
+        cfg["loss"] = dict(targets=targets, coef=float(fn.coef), lambda_u=float(fn.lambda_u),
+                           join_in_backward=bool(loss.get("join_in_backward")))
     outs = _RenderFn.apply(cfg, rays_c, ts, view_dir, a_embedded, t_embedded, emb_a_w, emb_t_w,
                            len(params_c), *params_c, *params_f)
-    return dict(zip(cfg["keys"], outs))
+    res = dict(zip(cfg["keys"], outs))
+    if _LOSS_KEYS[0] in res:
+        from .objective import LossTerms
+        c_l, f_l, b_l, s_l, total = (res.pop(k) for k in _LOSS_KEYS)
+        terms = LossTerms(c_l=c_l)
+        if "rgb_fine" in res:
+            terms["f_l"] = f_l
+        if "beta" in res:
+            terms["b_l"], terms["s_l"] = b_l, s_l
+        terms.total = total
+        res["loss_terms"] = terms
+    return res
 
 
 # ---- NeRF.forward on explicit embedded rows (models/nerf.py:153-212) ---------------------------------

@@ -30,7 +30,7 @@ class TrainStep:
 
     def __init__(self, models, embeddings, state: FlatTrainState, loss_fn, *, batch: int, N_samples=64,
                  N_importance=64, use_disp=False, perturb=1.0, noise_std=0.0, white_back=True, chunk=32 * 1024,
-                 graph=True, warmup=3):
+                 graph=True, warmup=3, fuse_loss=True):
         self.models, self.embeddings, self.state, self.loss_fn = models, embeddings, state, loss_fn
         self.batch = int(batch)
         self.args = (int(N_samples), bool(use_disp), float(perturb), float(noise_std), int(N_importance), int(chunk),
@@ -41,6 +41,9 @@ class TrainStep:
         self._warmup = warmup
         self._want_graph = bool(graph) and self.dev.type == "cuda"
         self.terms = None            # loss terms of the last call (dict of 0-dim tensors)
+        from .objective import NerfWLoss
+        self._fused_loss = bool(fuse_loss) and type(loss_fn) is NerfWLoss
+        self._unit = torch.ones((), device=self.dev, dtype=torch.float32)      # the standing cotangent of the loss
 
     # ---- the iteration itself ---------------------------------------------------------------------
     def _iteration(self, rays, ts, rgbs, graph_safe_rng: bool, do_step: bool = True):
@@ -54,13 +57,16 @@ class TrainStep:
                 if Ni > 0:
                     rng["u"] = torch.rand(n, Ni, device=rays.device)
             kw["rng"] = rng
+        if self._fused_loss:
+            # NerfWLoss inside the render node: its backward is formed in the compositing kernels (rendering.render_rays)
+            kw["loss"] = dict(fn=self.loss_fn, targets=rgbs, join_in_backward=True)
         res = render_rays(self.models, self.embeddings, rays, ts, Ns, use_disp, perturb, noise_std, Ni, chunk,
                           white_back, **kw)
-        terms = self.loss_fn(res, rgbs)
+        terms = res["loss_terms"] if self._fused_loss else self.loss_fn(res, rgbs)
         loss = getattr(terms, "total", None)
         if loss is None:
             loss = sum(terms.values())               # train.py:166
-        loss.backward()
+        loss.backward(gradient=self._unit)           # a standing cotangent of 1: no fill launch per step
         if do_step:
             self.state.step()
         return loss.detach(), {k: v.detach() for k, v in terms.items()}

@@ -368,3 +368,52 @@ def test_weight_gradients_are_bit_reproducible():
     # the feature columns of the two mixed layers come from the same kernel
     for k in ("fine.dir_encoding.0.weight", "coarse.dir_encoding.0.weight", "fine.transient_encoding.0.weight"):
         assert torch.equal(a[k][:, :256], b[k][:, :256]), k
+
+
+@pytest.mark.parametrize("case", ["nerfw", "no_transient", "coarse_only", "weighted_terms"])
+def test_loss_inside_the_render_node_matches_the_separate_loss(case):
+    """render_rays(loss=...) evaluates NerfWLoss inside its autograd node and forms the loss cotangents in the compositing
+    backward (nwb_composite_bwd_seeded, which also leaves max|d_raw| for the field backward): same terms, same gradients
+    as render_rays -> NerfWLoss -> nwb_nerfw_loss_bwd -> nwb_composite_bwd."""
+    from nerf_fl_b200.objective import NerfWLoss
+    n = 1024
+    rays = syn.blender_rays(n, seed=31).to(DEV)
+    g = torch.Generator().manual_seed(14)
+    ts = torch.randint(0, 20, (n,), generator=g).to(DEV)
+    tgt = torch.rand(n, 3, generator=g).to(DEV)
+    rng = {"perturb_rand": torch.rand(n, 64, generator=g).to(DEV), "u": torch.rand(n, 64, generator=g).to(DEV)}
+    transient = case in ("nerfw", "weighted_terms")
+    ni = 0 if case == "coarse_only" else 64
+    lossfn = NerfWLoss(coef=1.5, lambda_u=0.02)
+
+    def run(fused):
+        models = {"coarse": build(1, "coarse"), "fine": build(2, "fine", True, transient, beta_min=0.1)}
+        emb = embeddings(syn.make_embedding(3, 20, 48), syn.make_embedding(4, 20, 16))
+        kw = dict(loss=dict(fn=lossfn, targets=tgt)) if fused else {}
+        out = render_rays(models, emb, rays, ts, 64, False, 1.0, 0.0, ni, 32768, True, rng=rng, **kw)
+        terms = out["loss_terms"] if fused else lossfn(out, tgt)
+        if case == "weighted_terms":
+            loss = 0.5 * terms["c_l"] + 2.0 * terms["f_l"] + terms["b_l"] + 3.0 * terms["s_l"]
+        else:
+            loss = terms.total
+        named = [(f"coarse.{k}", p) for k, p in models["coarse"].named_parameters()]
+        if ni > 0:
+            named += [(f"fine.{k}", p) for k, p in models["fine"].named_parameters()]
+            named += [("emb.a", emb["a"].weight)] + ([("emb.t", emb["t"].weight)] if transient else [])
+        grads = torch.autograd.grad(loss, [p for _, p in named])
+        check_errors()
+        return dict(terms), {k: gr.detach().clone() for (k, _), gr in zip(named, grads)}
+
+    t_a, g_a = run(False)
+    t_b, g_b = run(True)
+    assert t_a.keys() == t_b.keys()
+    for k in t_a:
+        assert torch.equal(t_a[k], t_b[k]), k                     # the same forward kernel on the same maps
+    # tensors the weight-gradient kernel owns are deterministic: the seeded cotangents are the separate path's bit for bit
+    owned = [k for k in g_a if k.endswith(".weight") and "encoding" in k and not any(s in k for s in ("dir_encoding.0", "transient_encoding.0"))]
+    assert len(owned) >= 8
+    bad = [k for k in owned if not torch.equal(g_a[k], g_b[k])]
+    assert not bad, bad
+    for k in g_a:                                                  # the rest accumulate with fp32 atomics
+        scale = g_a[k].abs().max().item() + 1e-30
+        assert (g_a[k] - g_b[k]).abs().max().item() <= 1e-4 * scale, k
