@@ -11,13 +11,19 @@ try:
     PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     PEAK = 6500.0
-flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
+flush = torch.zeros(256 << 20, dtype=torch.uint8, device=DEV)
+flush_sink = torch.zeros((), dtype=torch.int64, device=DEV)
 ITERS = int(os.environ.get("NWB_PERF_ITERS", "10"))      # 1 under ncu (one profiled launch per kernel and call site)
 WARM = 3 if ITERS > 1 else 0
 def timed(fn, iters=ITERS):
     ts = []
     for i in range(iters + WARM):
-        flush.zero_()
+        # L2 flushed by streaming 256 MB THROUGH it with loads: flush.zero_() would leave the cache full of dirty lines
+        # whose write-back then competes with the timed kernel's own traffic (measured: +8 us on a 38 us launch)
+        flush_sink.copy_(flush.view(torch.int64).sum())
+        # the device spins ~150 us here so that the host has enqueued e0, the kernel and e1 before the first of them runs:
+        # the interval is the kernel plus the events' own ~2 us, not the host's launch latency
+        torch.cuda._sleep(300000)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize()
         if i >= WARM: ts.append(e0.elapsed_time(e1))
