@@ -287,7 +287,11 @@ int nwb_adam_step_dev(float* p, float* g, float* m, float* v, int64_t n, float b
  * nwb_adam_pack_cover).  state is 48 B, zeroed by the caller once: the 16 B of nwb_adam_step_dev, a uint32 ticket, the
  * int32 step for which the two doubles that follow (beta1^step, beta2^step, kept as running products) are valid;
  * the step advances inside the launch.  Results are identical to
- * nwb_adam_step_dev followed by nwb_field_pack (tests/test_optim_gpu.py). */
+ * nwb_adam_step_dev followed by nwb_field_pack (tests/test_optim_gpu.py).
+ * zero_grad | NWB_ADAM_NO_ADVANCE: the launch updates its fields with the scalars of step state+1 but leaves the state where
+ * it is -- one optimizer step split over several launches (a model whose backward is done is updated while the other's
+ * still runs); the LAST launch of the step comes without the flag and after the others have finished. */
+#define NWB_ADAM_NO_ADVANCE 2
 int nwb_adam_pack_step_dev(float* p, float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
                            float weight_decay, float* state, float grad_scale, int zero_grad, int n_fields,
                            const nwb_field_desc* const* descs, const nwb_field_params* const* params,

@@ -293,11 +293,13 @@ class FlatTrainState:
             from . import _lib as L
             from . import kernels as K
             fz = self._fused or self._fused_setup()
+            early, self._early = getattr(self, "_early", ()), ()
+            n_f, descs, params, packed = self._field_tables(fz, [i for i in range(fz["n"]) if i not in early])
             with K._timed("nwb_adam_pack_step_dev", 0, dev=self.flat_p.device):
                 L.check(fz["fn"](self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
                                  self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay,
-                                 self.hyper.data_ptr(), 1.0 / world, int(zero_grad), fz["n"], fz["descs"], fz["params"],
-                                 fz["packed"], fz["rest"].data_ptr(), fz["rest"].numel(),
+                                 self.hyper.data_ptr(), 1.0 / world, int(zero_grad), n_f, descs, params,
+                                 packed, fz["rest"].data_ptr(), fz["rest"].numel(),
                                  L.stream_ptr(self.flat_p.device)), "nwb_adam_pack_step_dev")
             for m in self.modules:                   # fields outside the fused set still repack on their own
                 if hasattr(m, "_nwb_cache") and not any(m is f for f in self._fused_fields):
@@ -330,6 +332,45 @@ class FlatTrainState:
         """One-time setup of the cache-refreshing optimizer launch; call before capturing a CUDA graph."""
         if self._fused_fields and self._fused is None:
             self._fused_setup()
+
+    def _field_tables(self, fz, idx):
+        """(n, descs, params, packed) pointer tables of a subset of the fused fields."""
+        idx = tuple(idx)
+        if len(idx) == fz["n"]:
+            return fz["n"], fz["descs"], fz["params"], fz["packed"]
+        sub = fz.setdefault("subsets", {})
+        if idx not in sub:
+            from . import _lib as L
+            n = len(idx)
+            descs = (C.POINTER(L.FieldDesc) * n)(*[fz["descs"][i] for i in idx])
+            params = (C.POINTER(L.FieldParams) * n)(*[fz["params"][i] for i in idx])
+            packed = (C.c_void_p * n)(*[fz["packed"][i] for i in idx])
+            sub[idx] = (n, descs, params, packed)
+        return sub[idx]
+
+    def adam_step_early(self, modules, zero_grad: bool = True) -> bool:
+        """This step's Adam update for some of the fused fields NOW, on the current stream, before the rest of the
+        iteration has finished (a model whose backward is complete, while another model's still runs): the same scalars as
+        the step's main launch, the step state left where it is (NWB_ADAM_NO_ADVANCE).  The next ``adam_step`` then covers
+        the remaining fields and everything else, and advances the state.  One GPU only (with a gradient exchange the
+        update waits for it); returns False, doing nothing, when it does not apply."""
+        if not (self.flat_p.is_cuda and self._fused_fields) or dist_info()[1] > 1:
+            return False
+        from . import _lib as L
+        from . import kernels as K
+        fz = self._fused or self._fused_setup()
+        idx = [i for i, f in enumerate(self._fused_fields) if any(f is m for m in modules)]
+        if not idx or len(idx) == fz["n"] or getattr(self, "_early", ()):
+            return False
+        n_f, descs, params, packed = self._field_tables(fz, idx)
+        b1, b2 = self.betas
+        with K._timed("nwb_adam_pack_step_dev", 0, 1, dev=self.flat_p.device):
+            L.check(fz["fn"](self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.exp_avg.data_ptr(),
+                             self.exp_avg_sq.data_ptr(), self.numel, b1, b2, self.eps, self.weight_decay,
+                             self.hyper.data_ptr(), 1.0, int(zero_grad) | 2, n_f, descs, params, packed, None, 0,
+                             L.stream_ptr(self.flat_p.device)), "nwb_adam_pack_step_dev")
+        self._early = tuple(idx)
+        return True
 
     def _fused_setup(self):
         """One-time: the packed caches' buffers, the C pointer tables and the `rest` offset list (flat offsets that no

@@ -302,6 +302,10 @@ class _RenderFn(torch.autograd.Function):
             with torch.cuda.stream(side):
                 sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
                                                   params=params_c, aux=_side_stream(Pc.z.device, 1), seed=seed_c, **kw)
+                # the coarse model's gradients are complete here while the fine chain is still running: a caller that owns
+                # the optimizer (TrainStep) updates the coarse model now, on this branch
+                if direct_c and cfg.get("after_coarse_chain") is not None:
+                    cfg["after_coarse_chain"]()
         else:
             sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
                                               params=params_c, aux=_side_stream(Pc.z.device, 1) if fork else None,
@@ -387,6 +391,8 @@ def render_rays(models, embeddings, rays, ts, N_samples=64, use_disp=False, pert
         cfg["rng"][k] = K._f32(v)
     if n == 0:
         raise RuntimeError("render_rays called with zero rays")
+    if kwargs.get("after_coarse_chain") is not None:
+        cfg["after_coarse_chain"] = kwargs["after_coarse_chain"]
     loss = kwargs.get("loss")
     if loss is not None:
         fn, targets = loss["fn"], K._f32(loss["targets"])

@@ -30,7 +30,7 @@ class TrainStep:
 
     def __init__(self, models, embeddings, state: FlatTrainState, loss_fn, *, batch: int, N_samples=64,
                  N_importance=64, use_disp=False, perturb=1.0, noise_std=0.0, white_back=True, chunk=32 * 1024,
-                 graph=True, warmup=3, fuse_loss=True):
+                 graph=True, warmup=3, fuse_loss=True, split_adam=True):
         self.models, self.embeddings, self.state, self.loss_fn = models, embeddings, state, loss_fn
         self.batch = int(batch)
         self.args = (int(N_samples), bool(use_disp), float(perturb), float(noise_std), int(N_importance), int(chunk),
@@ -43,6 +43,7 @@ class TrainStep:
         self.terms = None            # loss terms of the last call (dict of 0-dim tensors)
         from .objective import NerfWLoss
         self._fused_loss = bool(fuse_loss) and type(loss_fn) is NerfWLoss
+        self._split_adam = bool(split_adam) and dist_info()[1] == 1
         self._unit = torch.ones((), device=self.dev, dtype=torch.float32)      # the standing cotangent of the loss
 
     # ---- the iteration itself ---------------------------------------------------------------------
@@ -57,6 +58,10 @@ class TrainStep:
                 if Ni > 0:
                     rng["u"] = torch.rand(n, Ni, device=rays.device)
             kw["rng"] = rng
+        if do_step and graph_safe_rng and self._split_adam:
+            # one GPU: the coarse model is updated as soon as its backward chain is done, next to the fine chain's weight
+            # gradients; the step's main optimizer launch then covers the fine model, the embeddings and the step state
+            kw["after_coarse_chain"] = lambda: self.state.adam_step_early([self.models["coarse"]])
         if self._fused_loss:
             # NerfWLoss inside the render node: its backward is formed in the compositing kernels (rendering.render_rays)
             kw["loss"] = dict(fn=self.loss_fn, targets=rgbs, join_in_backward=True)

@@ -83,3 +83,25 @@ def test_fused_adam_rejects_foreign_parameters():
     st.adam_step()
     assert mods[0]._nwb_dirty or mods[0]._nwb_cache is None
     assert not mods[1]._nwb_dirty
+
+
+def test_optimizer_step_split_over_two_launches_is_bit_identical():
+    """adam_step_early (NWB_ADAM_NO_ADVANCE) updates one model ahead of the step's main launch: parameters, moments, packed
+    operand caches and the device step state come out exactly as from the single launch."""
+    a = FlatTrainState(_modules(7), lr=5e-4)
+    b = FlatTrainState(_modules(7), lr=5e-4)
+    for i, g in enumerate(_grads(a.numel, 4, 17)):
+        a.flat_g.copy_(g)
+        b.flat_g.copy_(g)
+        a.adam_step()
+        assert b.adam_step_early([b.modules[0]])
+        assert not b.adam_step_early([b.modules[0]])                   # once per step
+        b.adam_step()
+        torch.cuda.synchronize()
+        assert torch.equal(a.flat_p, b.flat_p), f"step {i}: parameters differ"
+        assert torch.equal(a.exp_avg, b.exp_avg) and torch.equal(a.exp_avg_sq, b.exp_avg_sq)
+        assert float(b.flat_g.abs().max()) == 0.0
+        assert torch.equal(a.hyper, b.hyper)
+        for ma, mb in zip(a.modules[:2], b.modules[:2]):
+            assert torch.equal(ma._nwb_cache[1], mb._nwb_cache[1]), f"step {i}: packed operand cache differs"
+    assert a.step_count == b.step_count == 4

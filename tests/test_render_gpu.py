@@ -316,12 +316,12 @@ def test_train_step_graph_replay_matches_eager():
     batches = [(syn.blender_rays(n, seed=20 + i).to(DEV), torch.randint(0, 20, (n,), generator=gen).to(DEV),
                 torch.rand(n, 3, generator=gen).to(DEV)) for i in range(4)]
 
-    def run(graph):
+    def run(graph, **kw):
         models = {"coarse": build(1, "coarse"), "fine": build(2, "fine", True, True, beta_min=0.1)}
         emb = embeddings(syn.make_embedding(3, 20, 48), syn.make_embedding(4, 20, 16))
         state = FlatTrainState(list(models.values()) + [emb["a"], emb["t"]], lr=5e-4)
         step = TrainStep(models, emb, state, NerfWLoss(), batch=n, N_samples=32, N_importance=32, perturb=0.0,
-                         noise_std=0.0, white_back=True, graph=graph, warmup=0)
+                         noise_std=0.0, white_back=True, graph=graph, warmup=0, **kw)
         p0 = state.flat_p.clone()
         losses = [float(step(*b)) for b in batches]
         check_errors()
@@ -330,6 +330,10 @@ def test_train_step_graph_replay_matches_eager():
     p_e, l_e, _ = run(False)
     p_g, l_g, step = run(True)
     assert step.graph is not None and step.launches_per_step >= 15
+    # the coarse model's early optimizer launch (split_adam, graph mode only) walks the same trajectory as one launch
+    p_1, l_1, _ = run(True, split_adam=False)
+    assert max(abs(a - b) for a, b in zip(l_1, l_g)) <= 1e-4 * max(l_1)
+    assert (p_1 - p_g).norm().item() <= 5e-2 * p_1.norm().item()
     assert max(abs(a - b) for a, b in zip(l_e, l_g)) <= 1e-4 * max(l_e)
     # p_* = displacement after 4 Adam steps.  Early Adam moves every weight by ~lr*sign(g), so the fp32-atomics
     # ordering noise of near-zero gradient entries shows up at full step size in a few elements: compare in L2

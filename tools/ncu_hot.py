@@ -11,7 +11,7 @@ rows = list(csv.reader(out.splitlines()))
 h, data = rows[1], rows[2:]
 ci = {n: i for i, n in enumerate(h)}
 stalls = [n for n in h if n.startswith("stall_") and "Not Issued" not in n]
-hot = [i for i, r in enumerate(data) if len(r) >= len(h) and int(r[ci["# Samples"]] or 0) >= thr]
+hot = [i for i, r in enumerate(data) if len(r) >= len(h) and (r[ci["# Samples"]] or "0").isdigit() and int(r[ci["# Samples"]] or 0) >= thr]
 shown = set()
 for i in hot:
     for j in range(max(0, i - ctx), min(len(data), i + 2)):
