@@ -72,6 +72,7 @@ int nwb_sample_pdf_merge(const float* z_coarse, const float* w_coarse, int n_ray
 #define NWB_COMP_WHITE_BACK 2u
 #define NWB_COMP_TEST_TIME 4u
 #define NWB_COMP_COARSE 8u      /* typ == 'coarse' (test_time: weights/opacity only) */
+#define NWB_COMP_AMAX_CLEARED 16u /* nwb_composite_bwd_seeded: *amax_bits is already 0 (nwb_composite_out.clear_word) */
 
 typedef struct nwb_composite_out {
     float* weights;          /* (n,S)  weights_{typ}                    rendering.py:162,165 */
@@ -86,6 +87,9 @@ typedef struct nwb_composite_out {
     float* tt_depth_static;  /* (n)    depth_fine_static                :206-207             */
     float* tt_rgb_transient; /* (n,3)  rgb_fine_transient               :209-215             */
     float* tt_depth_transient; /* (n)  depth_fine_transient             :216-217             */
+    unsigned int* clear_word;  /* may be NULL: the launch stores 0 there -- the amax word of the backward's workspace,
+                                * cleared a pass ahead so that nwb_composite_bwd_seeded needs no memset node
+                                * (NWB_COMP_AMAX_CLEARED)                                                             */
 } nwb_composite_out;
 
 int nwb_composite_fwd(const float* raw, int C, const float* z, const float* noise,

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # inside one GPU session); read once, at import
 LIB_PATH = os.environ.get("NWB_LIB_PATH") or os.path.join(_HERE, "libnerfw_b200.so")
 
-NWB_COMP_TRANSIENT, NWB_COMP_WHITE_BACK, NWB_COMP_TEST_TIME, NWB_COMP_COARSE = 1, 2, 4, 8
+NWB_COMP_TRANSIENT, NWB_COMP_WHITE_BACK, NWB_COMP_TEST_TIME, NWB_COMP_COARSE, NWB_COMP_AMAX_CLEARED = 1, 2, 4, 8, 16
 NWB_MLP_SIGMA_ONLY, NWB_MLP_TRANSIENT, NWB_MLP_SAVE, NWB_MLP_DZ_AMAX_GIVEN = 1, 2, 4, 8
 
 _f32p = C.c_void_p   # device pointers travel as integers
@@ -25,7 +25,7 @@ class CompositeOut(C.Structure):
     _fields_ = [(n, _f32p) for n in (
         "weights", "opacity", "rgb", "depth", "transient_sigmas", "beta", "rgb_static",
         "rgb_transient", "tt_rgb_static", "tt_depth_static", "tt_rgb_transient",
-        "tt_depth_transient")]
+        "tt_depth_transient", "clear_word")]
 
 
 class CompositeGrads(C.Structure):

@@ -82,6 +82,7 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                      uint32_t flags, float beta_min, nwb_composite_out o) {
     __shared__ __align__(16) RingStage<C> ring[kCompWarps][kRing];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (o.clear_word != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *o.clear_word = 0u;
     RingStage<C>* my = ring[warp];
     constexpr bool transient = (C == 9) && (kV & 1u);
     const bool white = flags & NWB_COMP_WHITE_BACK;
@@ -471,7 +472,7 @@ static int composite_bwd_launch(const float* raw, int C, const float* z, const f
     const size_t smem = static_cast<size_t>(kCompWarps) * (kRing * (32 * C + 36) + ((S + 3) & ~3)) * sizeof(float);
     NWB_REQUIRE(smem <= 200 * 1024, "%s: S too large for shared memory", who);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (amax_bits != nullptr) NWB_CUDA(cudaMemsetAsync(amax_bits, 0, sizeof(unsigned int), st));
+    if (amax_bits != nullptr && !(flags & NWB_COMP_AMAX_CLEARED)) NWB_CUDA(cudaMemsetAsync(amax_bits, 0, sizeof(unsigned int), st));
 #define NWB_BWD(CC, TR)                                                                             \
     do {                                                                                            \
         if (smem > 48 * 1024)                                                                       \

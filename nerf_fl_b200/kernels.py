@@ -133,7 +133,7 @@ def composite_flags(transient: bool, white_back: bool, test_time: bool, coarse: 
 
 def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bool, white_back: bool,
                   test_time: bool, beta_min: float = 0.0, noise: torch.Tensor | None = None,
-                  noise_std: float = 0.0) -> dict:
+                  noise_std: float = 0.0, clear_word: torch.Tensor | None = None) -> dict:
     """One inference() compositing pass (models/rendering.py:141-226) -> result-dict entries."""
     raw, z = _f32(raw), _f32(z)
     n, S = z.shape
@@ -168,6 +168,8 @@ def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bo
         res[f"depth_{typ}"] = new(n)
         o.depth = L.ptr(res[f"depth_{typ}"])
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
+    if clear_word is not None:
+        o.clear_word = L.ptr(clear_word)         # first word <- 0 (the backward workspace's amax word, see composite_bwd)
     with _timed("nwb_composite_fwd", n, Cc * 1000 + S, dev=dev):
         L.check(L.lib().nwb_composite_fwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S,
                                           composite_flags(transient, white_back, test_time, coarse),
@@ -178,7 +180,8 @@ def composite_fwd(raw: torch.Tensor, z: torch.Tensor, *, typ: str, transient: bo
 
 def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, transient: bool,
                   white_back: bool, noise: torch.Tensor | None = None,
-                  noise_std: float = 0.0, seed: dict | None = None, amax_out: torch.Tensor | None = None) -> torch.Tensor:
+                  noise_std: float = 0.0, seed: dict | None = None, amax_out: torch.Tensor | None = None,
+                  amax_cleared: bool = False) -> torch.Tensor:
     """Cotangents keyed like the result dict -> d_raw (N,S,C).
 
     ``seed`` (nwb_composite_bwd_seeded): dict(rgb, beta, targets, g_terms (5 device scalars or None), coef, lambda_u,
@@ -212,6 +215,8 @@ def composite_bwd(raw: torch.Tensor, z: torch.Tensor, grads: dict, *, typ: str, 
     d_raw = torch.empty_like(raw)
     nz = _f32(noise) if (noise is not None and not transient and noise_std != 0.0) else None
     flags = composite_flags(transient, white_back, False, typ == "coarse")
+    if amax_cleared:
+        flags |= L.NWB_COMP_AMAX_CLEARED          # composite_fwd(clear_word=amax_out) of the same pass already zeroed it
     if seed is None and amax_out is None:
         with _timed("nwb_composite_bwd", n, Cc * 1000 + S, dev=z.device):
             L.check(L.lib().nwb_composite_bwd(L.ptr(raw), Cc, L.ptr(z), L.ptr(nz), float(noise_std), n, S, flags,

@@ -87,7 +87,7 @@ def _side_stream(dev, which: int = 0) -> torch.cuda.Stream:
 class _Pass:
     """Everything one inference() call (rendering.py:83-226) leaves behind for its backward."""
     __slots__ = ("model", "typ", "S", "transient", "mode", "desc", "packed", "feat", "raw", "z", "saved",
-                 "noise", "keys", "use_a", "a_rows", "t_rows")
+                 "noise", "keys", "use_a", "a_rows", "t_rows", "ws")
 
 
 def _ray_consts(model, dirs, n_freq_dir, ts, emb_a, emb_t, a_rows, t_rows, transient):
@@ -128,8 +128,12 @@ def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, t
     P.saved = K.aligned_empty(K.mlp_save_bytes(P.desc, n * S, P.mode), dev, 16) if save else None
     P.raw = K.mlp_fwd(P.desc, P.packed, n_rays=n, S=S, mode=P.mode, ray_bias=rb, rays=rays, z=z,
                       n_freq_xyz=n_freq_xyz, saved=P.saved)
+    # the field backward's workspace exists from here on: its first word (max|d_raw|, filled by the compositing backward)
+    # is cleared by the compositing forward, a whole pass ahead of its use
+    P.ws = K.aligned_empty(K.mlp_bwd_workspace_bytes(P.desc, n * S, P.mode & ~L.NWB_MLP_SAVE), dev, 16) if save else None
     res = K.composite_fwd(P.raw.view(n, S, -1), z, typ=typ, transient=transient, white_back=white_back,
-                          test_time=test_time, beta_min=float(model.beta_min), noise=noise, noise_std=noise_std)
+                          test_time=test_time, beta_min=float(model.beta_min), noise=noise, noise_std=noise_std,
+                          clear_word=P.ws)
     P.keys = list(res.keys())
     return P, res
 
@@ -142,9 +146,10 @@ def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_
     dev = P.z.device
     # the compositing backward also leaves max|d_raw| in the field backward's workspace header (the 8-bit images' scale):
     # no reduction launch between the two
-    ws = K.aligned_empty(K.mlp_bwd_workspace_bytes(P.desc, n * S, P.mode & ~L.NWB_MLP_SAVE), dev, 16)
+    ws = P.ws
     d_raw = K.composite_bwd(P.raw.view(n, S, -1), P.z, grads_by_key, typ=P.typ, transient=P.transient,
-                            white_back=white_back, noise=P.noise, noise_std=noise_std, seed=seed, amax_out=ws)
+                            white_back=white_back, noise=P.noise, noise_std=noise_std, seed=seed, amax_out=ws,
+                            amax_cleared=True)
     bwd_mode = P.mode | L.NWB_MLP_DZ_AMAX_GIVEN
     sinks, direct = _grad_sinks(names, params, dev)
     d_rb = torch.zeros(n, 256, device=dev, dtype=torch.float32)
