@@ -138,8 +138,16 @@ def _run_pass(model, rays, z, *, typ, test_time, white_back, noise_std, noise, t
     return P, res
 
 
+def _bwd_composite(P: _Pass, grads_by_key: dict, *, white_back, noise_std, seed=None):
+    """First stage of _bwd_pass: cotangents of the maps -> d_raw (and max|d_raw| into the workspace header)."""
+    n, S = P.z.shape
+    return K.composite_bwd(P.raw.view(n, S, -1), P.z, grads_by_key, typ=P.typ, transient=P.transient,
+                           white_back=white_back, noise=P.noise, noise_std=noise_std, seed=seed, amax_out=P.ws,
+                           amax_cleared=True)
+
+
 def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_w, emb_t_w, names, params, aux=None,
-              seed=None):
+              seed=None, d_raw=None):
     """Backward of _run_pass -> (param sinks, direct?, d_emb_a, d_emb_t, d_a_rows, d_t_rows).  ``seed``: the NerfWLoss
     cotangents of this pass's maps are formed inside the compositing backward (K.composite_bwd)."""
     n, S = P.z.shape
@@ -147,9 +155,8 @@ def _bwd_pass(P: _Pass, grads_by_key: dict, *, white_back, noise_std, ts, emb_a_
     # the compositing backward also leaves max|d_raw| in the field backward's workspace header (the 8-bit images' scale):
     # no reduction launch between the two
     ws = P.ws
-    d_raw = K.composite_bwd(P.raw.view(n, S, -1), P.z, grads_by_key, typ=P.typ, transient=P.transient,
-                            white_back=white_back, noise=P.noise, noise_std=noise_std, seed=seed, amax_out=ws,
-                            amax_cleared=True)
+    if d_raw is None:
+        d_raw = _bwd_composite(P, grads_by_key, white_back=white_back, noise_std=noise_std, seed=seed)
     bwd_mode = P.mode | L.NWB_MLP_DZ_AMAX_GIVEN
     sinks, direct = _grad_sinks(names, params, dev)
     d_rb = torch.zeros(n, 256, device=dev, dtype=torch.float32)
@@ -300,9 +307,13 @@ class _RenderFn(torch.autograd.Function):
         # 1024 rays 64+64: +6 %, 4096: +1.5 %; 16384 rays 128+128: -7 %, long kernels of different kinds sharing SMs
         # and L2): above _FORK_MAX_TILES fine tiles only the small side branches remain.
         fork_chains = fork and Pf.z.numel() <= _FORK_MAX_TILES * 128
+        d_raw_f = None
         if fork_chains:
             cur = torch.cuda.current_stream(Pc.z.device)
             side = _side_stream(Pc.z.device)
+            # the fine pass's compositing backward goes first and alone: it heads the longer chain, and next to the coarse
+            # pass's it takes twice as long ([B200, tools/graph_timeline.py] 18 us against 8)
+            d_raw_f = _bwd_composite(Pf, g, seed=seed_f, **kw)
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
@@ -320,7 +331,7 @@ class _RenderFn(torch.autograd.Function):
             sinks_f, direct_f, d_ea, d_et, d_a, d_t = _bwd_pass(Pf, g, ts=ctx.ts, emb_a_w=ctx.emb_a_w,
                                                                 emb_t_w=ctx.emb_t_w, names=names_f, params=params_f,
                                                                 aux=_side_stream(Pc.z.device, 2) if fork else None,
-                                                                seed=seed_f, **kw)
+                                                                seed=seed_f, d_raw=d_raw_f, **kw)
             out_params += [None if direct_f else sinks_f[k] for k in names_f]
         if fork_chains:
             cur.wait_stream(side)
