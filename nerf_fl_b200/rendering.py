@@ -210,7 +210,6 @@ class _RenderFn(torch.autograd.Function):
         save = cfg["save"]
         seed = cfg["seed"]
         dirs = view_dir if view_dir is not None else rays[:, 3:6].contiguous()                # rendering.py:238
-        z = K.sample_coarse(rays, Ns, cfg["use_disp"], perturb, rng.get("perturb_rand"), seed)   # :244-259
 
         def sigma_noise(shape, key):                                                          # :151
             if noise_std == 0.0:
@@ -223,7 +222,7 @@ class _RenderFn(torch.autograd.Function):
         # the fine pass's per-ray constants do not depend on the coarse pass: inside a graph capture they go on a side
         # branch next to it
         transient_f = bool(Ni > 0 and cfg["output_transient"] and fine.encode_transient)       # :281
-        consts_f = None
+        consts_c = consts_f = None
         fork = Ni > 0 and _BWD_STREAMS and rays.is_cuda and torch.cuda.is_current_stream_capturing()
         if fork:
             cur, side = torch.cuda.current_stream(rays.device), _side_stream(rays.device)
@@ -231,8 +230,18 @@ class _RenderFn(torch.autograd.Function):
             with torch.cuda.stream(side):
                 consts_f = _ray_consts(fine, dirs, cfg["n_freq_dir"], ts, emb_a_w, emb_t_w, a_embedded, t_embedded,
                                        transient_f)
+            if not test_time:
+                # the coarse pass's constants do not depend on the sample depths either: next to the depth sampling
+                side_c = _side_stream(rays.device, 5)
+                side_c.wait_stream(cur)
+                with torch.cuda.stream(side_c):
+                    consts_c = _ray_consts(coarse, dirs, cfg["n_freq_dir"], None, None, None, None, None, False)
+        z = K.sample_coarse(rays, Ns, cfg["use_disp"], perturb, rng.get("perturb_rand"), seed)   # :244-259
+        if consts_c is not None:
+            cur.wait_stream(side_c)
         Pc, res = _run_pass(coarse, rays, z, typ="coarse", noise=sigma_noise((n, Ns), "noise_coarse"),
-                            transient=False, ts=None, emb_a=None, emb_t=None, a_rows=None, t_rows=None, **common)
+                            transient=False, ts=None, emb_a=None, emb_t=None, a_rows=None, t_rows=None, consts=consts_c,
+                            **common)
         if fork:
             cur.wait_stream(side)
         Pf = None
