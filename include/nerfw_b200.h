@@ -306,6 +306,10 @@ int nwb_adam_pack_cover(float* p, int64_t n, int n_fields, const nwb_field_desc*
                         const nwb_field_params* const* params, void* const* packed, unsigned char* cover,
                         void* stream);
 
+/* n <= 8 device-to-device copies in ONE launch: a training step's batch (rays, ts, rgbs; train.py:158-161 receives them from
+ * the DataLoader) into the static input buffers of the step's CUDA graph.  Buffers must not overlap. */
+int nwb_copy_segments(int n, const void* const* src, void* const* dst, const int64_t* bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (f1) NerfWLoss -- losses.py:19-50 -- the objective over the maps render_rays returns, forward and
  * backward as one launch each.  terms[5] = {c_l, f_l, b_l, s_l, their sum} (device); rgb_fine / beta /

@@ -126,6 +126,19 @@ def sample_pdf_merge(z_coarse: torch.Tensor, w_coarse: torch.Tensor, n_importanc
     return (z_out, z_new, inds) if debug else z_out
 
 
+def copy_segments(pairs) -> None:
+    """[(dst, src), ...] contiguous CUDA tensors of equal byte size, <= 8 of them, copied by one launch."""
+    n = len(pairs)
+    srcs, dsts, nbytes = (C.c_void_p * n)(), (C.c_void_p * n)(), (C.c_int64 * n)()
+    for i, (d, s_) in enumerate(pairs):
+        if d.numel() * d.element_size() != s_.numel() * s_.element_size() or d.dtype != s_.dtype:
+            raise RuntimeError("copy_segments: source and destination must have the same dtype and size")
+        srcs[i], dsts[i], nbytes[i] = L.ptr(s_), L.ptr(d), d.numel() * d.element_size()
+    fn = _fn("nwb_copy_segments", [_i, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), _vp])
+    with _timed("nwb_copy_segments", n, dev=pairs[0][0].device):
+        L.check(fn(n, srcs, dsts, nbytes, L.stream_ptr(pairs[0][0].device)), "nwb_copy_segments")
+
+
 def composite_flags(transient: bool, white_back: bool, test_time: bool, coarse: bool) -> int:
     return ((L.NWB_COMP_TRANSIENT if transient else 0) | (L.NWB_COMP_WHITE_BACK if white_back else 0)
             | (L.NWB_COMP_TEST_TIME if test_time else 0) | (L.NWB_COMP_COARSE if coarse else 0))

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import torch
 
+from . import kernels as K
 from .parallel import FlatTrainState, dist_info
 from .rendering import render_rays
 
@@ -124,9 +125,14 @@ class TrainStep:
             if self.graph is None:
                 self._capture(*(t.to(self.dev, non_blocking=True) for t in (rays, ts, rgbs)))   # warm-up + capture (the capture itself does not run)
             self.state.pull_lr()                       # a torch scheduler may have moved FlatAdam's lr between steps
-            self.s_rays.copy_(rays, non_blocking=True)
-            self.s_ts.copy_(ts, non_blocking=True)
-            self.s_rgbs.copy_(rgbs, non_blocking=True)
+            if rays.is_cuda and ts.is_cuda and rgbs.is_cuda and ts.dtype == self.s_ts.dtype and rays.dtype == rgbs.dtype == torch.float32 \
+                    and rays.is_contiguous() and ts.is_contiguous() and rgbs.is_contiguous():
+                # a resident batch: one launch instead of three copies
+                K.copy_segments(((self.s_rays, rays), (self.s_ts, ts), (self.s_rgbs, rgbs)))
+            else:                                      # host batches (pinned): three asynchronous host-to-device copies
+                self.s_rays.copy_(rays, non_blocking=True)
+                self.s_ts.copy_(ts, non_blocking=True)
+                self.s_rgbs.copy_(rgbs, non_blocking=True)
             self.graph.replay()
             if self._split:
                 self.state.step()                      # all-reduce + Adam, stream-ordered behind the replay

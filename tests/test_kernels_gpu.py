@@ -461,3 +461,17 @@ def test_field_backward_vs_oracle(n_rays, S, transient, scale):
         if not ok:
             bad.append((k, round(l2e, 4), round(cose, 5), round(l2f, 4), round(cosf, 5)))
     assert not bad, bad
+
+
+def test_copy_segments_one_launch():
+    g = torch.Generator().manual_seed(2)
+    src = [torch.rand(1024, 8, generator=g).to(DEV), torch.randint(0, 1500, (1024,), generator=g).to(DEV),
+           torch.rand(1024, 3, generator=g).to(DEV), torch.rand(7, generator=g).to(DEV),
+           torch.randint(0, 255, (13,), generator=g).to(torch.uint8).to(DEV)]
+    src.append(torch.rand(33, generator=g).to(DEV)[1:])                # 4-byte aligned only
+    dst = [torch.zeros_like(s) for s in src]
+    K.copy_segments(list(zip(dst, src)))
+    for d, s in zip(dst, src):
+        assert torch.equal(d, s)
+    with pytest.raises(RuntimeError):
+        K.copy_segments([(torch.zeros(4, device=DEV), torch.zeros(5, device=DEV))])
