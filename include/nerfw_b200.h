@@ -111,6 +111,9 @@ typedef struct nwb_composite_grads {
 int nwb_composite_bwd(const float* raw, int C, const float* z, const float* noise,
                       float noise_std, int n_rays, int S, uint32_t flags,
                       const nwb_composite_grads* g, float* d_raw, void* stream);
+/* which kernel the compositing backward launches: 0 (default) = the one that keeps the whole ray in shared memory for S <= 128,
+ * 1 = always the chunk-ring kernel, 2 = the resident one wherever it fits (S <= 256).  Process-wide; same results (tests walk all). */
+int nwb_composite_bwd_select(int gen);
 
 /* The same backward seeding its own cotangents under NerfWLoss (losses.py:35-50; SURVEY.md 8f-1 "fold the loss into the
  * compositing epilogue"): with `seed` the cotangents of this pass's rgb (and, fine pass with a transient head, of beta and

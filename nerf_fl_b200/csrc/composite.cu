@@ -420,6 +420,227 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// The same backward with the WHOLE ray resident in shared memory (S <= 32*NCH samples, NCH chunks of 32): one round of
+// cp.async per ray, no second read for the reverse pass, and the chunks' scans run as NCH independent chains instead of
+// one after the other -- the carries (transmittance in, suffix sum out) only enter a final multiply / add, exactly where
+// the kernel above applies them, so every value comes out bit for bit the same.  At the training batch (one ray per warp,
+// 7 warps per SM) the kernel above is a latency chain of 2*S/32 chunk steps: [B200, tools/graph_timeline.py] 16 us for
+// 1024 x 128 x 9 at the head of the backward's critical path.
+// ------------------------------------------------------------------------------------------------
+template <int C, bool kTr, int NCH>
+__global__ void __launch_bounds__(kCompWarps * 32)
+composite_bwd_resident_kernel(const float* __restrict__ raw, const float* __restrict__ z,
+                              const float* __restrict__ noise, float noise_std, int n_rays, int S,
+                              uint32_t flags, nwb_composite_grads g, float* __restrict__ d_raw, const LossSeedDev seed,
+                              unsigned int* __restrict__ amax_bits) {
+    static_assert(C == 4 || C == 9, "sigma-only passes have no backward");
+    extern __shared__ __align__(16) float dsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    RingStage<C>* my = reinterpret_cast<RingStage<C>*>(dsm) + warp * NCH;
+    constexpr bool transient = (C == 9) && kTr;
+    const bool white = flags & NWB_COMP_WHITE_BACK;
+    const bool seeded = seed.tgt != nullptr;
+    LossScalars sc{};
+    float seed_ts = 0.0f;
+    if (seeded) {
+        sc = loss_scalars(seed.g[0], seed.g[1], seed.g[2], seed.g[3], seed.g[4], seed.coef, seed.n);
+        if (seed.fine && seed.beta != nullptr && seed.n_ts > 0) seed_ts = loss_d_tsigma(sc, seed.lambda_u, seed.n_ts);
+    }
+    float amax = 0.0f;
+    const int n_chunks = (S + 31) >> 5;                      // <= NCH (host)
+    const int stride = gridDim.x * kCompWarps;
+    for (int ray = blockIdx.x * kCompWarps + warp; ray < n_rays; ray += stride) {
+        const int64_t row = static_cast<int64_t>(ray) * S;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c)
+            if (c < n_chunks) ring_issue<C>(&my[c], raw, z, ray, n_rays, c * 32, S, lane);
+        // per-ray cotangents (their loads overlap the copies)
+        const float g_op = g.d_opacity ? __ldg(g.d_opacity + ray) : 0.0f;
+        const float g_dp = g.d_depth ? __ldg(g.d_depth + ray) : 0.0f;
+        float g_be = (transient && g.d_beta) ? __ldg(g.d_beta + ray) : 0.0f;
+        float seed_rgb[3] = {0.0f, 0.0f, 0.0f};
+        if (seeded) {
+            const bool has_beta = seed.fine && seed.beta != nullptr;
+            const float b = has_beta ? __ldg(seed.beta + ray) : 1.0f;
+            const float ib2 = loss_inv_beta2(b);
+            float err = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float t = __ldg(seed.tgt + ray * 3 + c), x = __ldg(seed.rgb + ray * 3 + c);
+                if (seed.fine) {
+                    const float df = __fsub_rn(x, t);
+                    seed_rgb[c] = loss_d_rgb_fine(sc, df, ib2, has_beta);
+                    err = __fmaf_rn(df, df, err);
+                } else {
+                    seed_rgb[c] = loss_d_rgb_coarse(sc, x, t);
+                }
+            }
+            if (transient && has_beta) g_be += loss_d_beta(sc, err, ib2, b);
+        }
+        float Gs[3], Gt[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float gr = (g.d_rgb ? __ldg(g.d_rgb + ray * 3 + c) : 0.0f) + seed_rgb[c];
+            Gs[c] = gr + ((transient && g.d_rgb_static) ? __ldg(g.d_rgb_static + ray * 3 + c) : 0.0f);
+            Gt[c] = gr + ((transient && g.d_rgb_transient) ? __ldg(g.d_rgb_transient + ray * 3 + c) : 0.0f);
+        }
+        const float g_bg = white ? -(Gs[0] + Gs[1] + Gs[2]) : 0.0f;   // d(1 - sum w)/dw
+        cp_async_wait<0>();
+        __syncwarp();
+
+        // pass 1: transmittance -- NCH local scans side by side, then the carries in chunk order
+        float T[NCH];
+        {
+            float p[NCH];
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                float alpha = 0.0f;
+                const int i = c * 32 + lane;
+                if (c < n_chunks && i < S) {
+                    const RingStage<C>* st = &my[c];
+                    const float zi = st->z[lane];
+                    const float delta = (i + 1 < S) ? __fsub_rn(st->z[lane + 1], zi) : 1e2f;
+                    float sg = st->raw[lane * C + 3];
+                    if (transient) sg = __fadd_rn(sg, st->raw[lane * C + 7]);
+                    else {
+                        if (noise != nullptr) sg = __fadd_rn(sg, __fmul_rn(__ldg(noise + row + i), noise_std));
+                        sg = fmaxf(sg, 0.0f);
+                    }
+                    alpha = __fsub_rn(1.0f, expf(-__fmul_rn(delta, sg)));
+                }
+                p[c] = __fsub_rn(1.0f, alpha);
+            }
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) {
+                    const float t = __shfl_up_sync(0xffffffffu, p[c], o);
+                    if (lane >= o) p[c] *= t;
+                }
+            }
+            float carry = 1.0f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                float ex = __shfl_up_sync(0xffffffffu, p[c], 1);
+                if (lane == 0) ex = 1.0f;
+                T[c] = carry * ex;
+                carry *= __shfl_sync(0xffffffffu, p[c], 31);
+            }
+        }
+        // pass 2a: per chunk (independent) everything that does not need the suffix sum: the finished columns go into the
+        // slab in place of the raw values, head_s / head_t wait in the sigma columns
+        float q[NCH];
+        uint32_t pass_mask = 0;                                // bit c: sigma_c > 0 (non-transient clamp)
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            q[c] = 0.0f;
+            const int i = c * 32 + lane;
+            if (c < n_chunks && i < S) {
+                RingStage<C>* st = &my[c];
+                float* v = st->raw + lane * C;
+                const float zi = st->z[lane];
+                const float delta = (i + 1 < S) ? __fsub_rn(st->z[lane + 1], zi) : 1e2f;
+                const float Tc = T[c];
+                float Gw = g_op + g_dp * zi + g_bg + (g.d_weights ? __ldg(g.d_weights + row + i) : 0.0f);
+                if (transient) {
+                    const float ss = v[3], stt = v[7];
+                    const float es = expf(-__fmul_rn(delta, ss)), et = expf(-__fmul_rn(delta, stt));
+                    const float e = expf(-__fmul_rn(delta, __fadd_rn(ss, stt)));
+                    const float ws = (1.0f - es) * Tc, wt = (1.0f - et) * Tc, w = (1.0f - e) * Tc;
+                    const float Gws = Gs[0] * v[0] + Gs[1] * v[1] + Gs[2] * v[2];
+                    const float Gwt = Gt[0] * v[4] + Gt[1] * v[5] + Gt[2] * v[6] + g_be * v[8];
+                    q[c] = Gw * w + Gws * ws + Gwt * wt;
+                    const float head_s = Tc * (Gw * e + Gws * es);
+                    const float head_t = Tc * (Gw * e + Gwt * et);
+                    v[0] = ws * Gs[0]; v[1] = ws * Gs[1]; v[2] = ws * Gs[2]; v[3] = head_s;
+                    v[4] = wt * Gt[0]; v[5] = wt * Gt[1]; v[6] = wt * Gt[2]; v[7] = head_t; v[8] = wt * g_be;
+                    pass_mask |= 1u << c;
+                } else {
+                    float sg = v[3];
+                    if (noise != nullptr) sg = __fadd_rn(sg, __fmul_rn(__ldg(noise + row + i), noise_std));
+                    if (sg > 0.0f) pass_mask |= 1u << c;
+                    const float e = expf(-__fmul_rn(delta, fmaxf(sg, 0.0f)));
+                    const float w = (1.0f - e) * Tc;
+                    Gw += Gs[0] * v[0] + Gs[1] * v[1] + Gs[2] * v[2];
+                    q[c] = Gw * w;
+                    v[0] = w * Gs[0]; v[1] = w * Gs[1]; v[2] = w * Gs[2]; v[3] = Tc * Gw * e;
+                    if (C == 9) v[4] = v[5] = v[6] = v[7] = v[8] = 0.0f;
+                }
+            }
+        }
+        // NCH local inclusive suffix scans side by side, then the carried suffix in reverse chunk order
+        float R[NCH];
+        {
+            float incl[NCH];
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) incl[c] = q[c];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) {
+                    const float t = __shfl_down_sync(0xffffffffu, incl[c], o);
+                    if (lane + o < 32) incl[c] += t;
+                }
+            }
+            float suffix = 0.0f;
+#pragma unroll
+            for (int c = NCH - 1; c >= 0; --c) {
+                if (c < n_chunks) {
+                    R[c] = suffix + (incl[c] - q[c]);
+                    suffix += __shfl_sync(0xffffffffu, incl[c], 0);
+                } else {
+                    R[c] = 0.0f;
+                }
+            }
+        }
+        // pass 2b: the two columns that needed it, then the coalesced write-back of each chunk's rows
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            if (c < n_chunks) {
+                const int base = c * 32, i = base + lane, cnt = min(32, S - base);
+                RingStage<C>* st = &my[c];
+                if (lane < cnt) {
+                    float* v = st->raw + lane * C;
+                    const float delta = (i + 1 < S) ? __fsub_rn(st->z[lane + 1], st->z[lane]) : 1e2f;
+                    v[3] = ((pass_mask >> c) & 1u) ? delta * (v[3] - R[c]) : 0.0f;
+                    if (transient)
+                        v[7] = delta * (v[7] - R[c]) + ((g.d_transient_sigmas ? __ldg(g.d_transient_sigmas + row + i) : 0.0f) + seed_ts);
+                    if (amax_bits != nullptr) {
+#pragma unroll
+                        for (int k = 0; k < C; ++k) amax = fmaxf(amax, fabsf(v[k]));
+                    }
+                }
+                __syncwarp();
+                float* dst = d_raw + (row + base) * C;
+                const float* slab = st->raw;
+                const int nfl = cnt * C;
+                if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0 && (nfl & 3) == 0) {
+                    for (int k = lane; k < (nfl >> 2); k += 32)
+                        reinterpret_cast<float4*>(dst)[k] = reinterpret_cast<const float4*>(slab)[k];
+                } else {
+                    for (int k = lane; k < nfl; k += 32) dst[k] = slab[k];
+                }
+            }
+        }
+        __syncwarp();                                          // the stages are refilled for the warp's next ray
+    }
+    if (amax_bits != nullptr) {
+        __shared__ float amax_red[kCompWarps];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        if (lane == 0) amax_red[warp] = amax;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float m = amax_red[0];
+#pragma unroll
+            for (int w = 1; w < kCompWarps; ++w) m = fmaxf(m, amax_red[w]);
+            if (m > 0.0f && m < INFINITY) atomicMax(amax_bits, __float_as_uint(m));
+        }
+    }
+}
+
 }  // namespace nwb
 
 using namespace nwb;
@@ -448,6 +669,15 @@ extern "C" int nwb_composite_fwd(const float* raw, int C, const float* z, const 
     return NWB_OK;
 }
 
+// which compositing backward runs: 0 (default) = the whole-ray-resident kernel for S <= 128, 1 = always the ring kernel,
+// 2 = the resident kernel wherever it fits (S <= 256).  Process-wide; tests walk all three.
+static int g_comp_bwd_gen = 0;
+extern "C" int nwb_composite_bwd_select(int gen) {
+    NWB_REQUIRE(gen >= 0 && gen <= 2, "nwb_composite_bwd_select: gen must be 0, 1 or 2");
+    g_comp_bwd_gen = gen;
+    return NWB_OK;
+}
+
 static int composite_bwd_launch(const float* raw, int C, const float* z, const float* noise, float noise_std, int n_rays, int S,
                                 uint32_t flags, const nwb_composite_grads* g, const nwb_loss_seed* seed,
                                 unsigned int* amax_bits, float* d_raw, void* stream, const char* who) {
@@ -473,6 +703,24 @@ static int composite_bwd_launch(const float* raw, int C, const float* z, const f
     NWB_REQUIRE(smem <= 200 * 1024, "%s: S too large for shared memory", who);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (amax_bits != nullptr && !(flags & NWB_COMP_AMAX_CLEARED)) NWB_CUDA(cudaMemsetAsync(amax_bits, 0, sizeof(unsigned int), st));
+    // the kernel that keeps the whole ray in shared memory (2, 4 or 8 chunks of 32 samples).  [B200, tools/perf_hbm.py, 16384
+    // rays] C = 4, S = 128: 26.7 us against the ring kernel's 32.8; C = 9, S = 256 (8 chunks, 41 KB per block): 92 against 84 --
+    // so by default up to 4 chunks only; gen 2 forces it wherever it fits (tests)
+    if (C != 1 && S <= (g_comp_bwd_gen == 2 ? 256 : 128) && g_comp_bwd_gen != 1) {
+        const int nch = S <= 64 ? 2 : (S <= 128 ? 4 : 8);
+        const size_t rsmem = static_cast<size_t>(kCompWarps) * nch * (32 * C + 36) * sizeof(float);
+        const bool tr = (flags & NWB_COMP_TRANSIENT) != 0;
+#define NWB_RES(CC, TR, NN) composite_bwd_resident_kernel<CC, TR, NN><<<blocks, kCompWarps * 32, rsmem, st>>>( \
+            raw, z, noise, noise_std, n_rays, S, flags, *g, d_raw, sd, amax_bits)
+#define NWB_RES_N(CC, TR) do { if (nch == 2) NWB_RES(CC, TR, 2); else if (nch == 4) NWB_RES(CC, TR, 4); else NWB_RES(CC, TR, 8); } while (0)
+        if (C == 4) NWB_RES_N(4, false);
+        else if (tr) NWB_RES_N(9, true);
+        else NWB_RES_N(9, false);
+#undef NWB_RES_N
+#undef NWB_RES
+        NWB_LAUNCH_CHECK();
+        return NWB_OK;
+    }
 #define NWB_BWD(CC, TR)                                                                             \
     do {                                                                                            \
         if (smem > 48 * 1024)                                                                       \

@@ -139,6 +139,11 @@ def copy_segments(pairs) -> None:
         L.check(fn(n, srcs, dsts, nbytes, L.stream_ptr(pairs[0][0].device)), "nwb_copy_segments")
 
 
+def composite_bwd_select(gen: int) -> None:
+    """0 = whole-ray-resident compositing backward for S <= 128 (default), 1 = always the chunk-ring kernel, 2 = resident up to S = 256."""
+    L.check(_fn("nwb_composite_bwd_select", [_i])(int(gen)), "nwb_composite_bwd_select")
+
+
 def composite_flags(transient: bool, white_back: bool, test_time: bool, coarse: bool) -> int:
     return ((L.NWB_COMP_TRANSIENT if transient else 0) | (L.NWB_COMP_WHITE_BACK if white_back else 0)
             | (L.NWB_COMP_TEST_TIME if test_time else 0) | (L.NWB_COMP_COARSE if coarse else 0))
@@ -462,10 +467,11 @@ def _loss_scratch_for(dev) -> torch.Tensor:
     return _loss_scratch[key]
 
 
-def nerfw_loss_fwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda_u: float, coef: float) -> torch.Tensor:
+def nerfw_loss_fwd(rgb_coarse, rgb_fine, beta, transient_sigmas, targets, lambda_u: float, coef: float,
+                   out: torch.Tensor | None = None) -> torch.Tensor:
     """-> terms (5,) = [c_l, f_l, b_l, s_l, total] on the device (one launch)."""
     dev = rgb_coarse.device
-    terms = torch.empty(5, device=dev, dtype=torch.float32)
+    terms = out if out is not None else torch.empty(5, device=dev, dtype=torch.float32)
     n_ts = transient_sigmas.numel() if transient_sigmas is not None else 0
     fn = _fn("nwb_nerfw_loss_fwd", [_vp] * 5 + [_i, _i64, C.c_float, C.c_float, _vp, _vp, _vp])
     with _timed("nwb_nerfw_loss_fwd", rgb_coarse.shape[0], dev=dev):

@@ -262,16 +262,21 @@ class _RenderFn(torch.autograd.Function):
         if spec is not None and save:
             beta = res.get("beta")
             tsig = res.get("transient_sigmas") if beta is not None else None
-            lstream = None
+            lstream, deferred = None, None
+            loss_args = (res["rgb_coarse"].detach(), _detached(res.get("rgb_fine")), _detached(beta), _detached(tsig),
+                         spec["targets"], spec["lambda_u"], spec["coef"])
             if fork and spec.get("join_in_backward"):
+                # the caller promises a backward inside the same capture (TrainStep): the terms are only read after the
+                # step, so their kernel is launched from the backward, on a branch of its own behind the fine pass's
+                # compositing backward (next to it, at the head of the backward's critical path, it was in the way)
                 lstream = _side_stream(rays.device, 3)
-                lstream.wait_stream(torch.cuda.current_stream(rays.device))
-            with (torch.cuda.stream(lstream) if lstream is not None else contextlib.nullcontext()):
-                terms = K.nerfw_loss_fwd(res["rgb_coarse"], res.get("rgb_fine"), beta, tsig, spec["targets"],
-                                         spec["lambda_u"], spec["coef"])
+                terms = torch.empty(5, device=rays.device, dtype=torch.float32)
+                deferred = lambda: K.nerfw_loss_fwd(*loss_args, out=terms)
+            else:
+                terms = K.nerfw_loss_fwd(*loss_args)
             ctx.loss = dict(rgb_c=res["rgb_coarse"].detach(), rgb_f=_detached(res.get("rgb_fine")), beta=_detached(beta),
                             n_ts=tsig.numel() if tsig is not None else 0, targets=spec["targets"],
-                            coef=spec["coef"], lambda_u=spec["lambda_u"], stream=lstream)
+                            coef=spec["coef"], lambda_u=spec["lambda_u"], stream=lstream, deferred=deferred)
             for i, k in enumerate(_LOSS_KEYS):
                 res[k] = terms[i]
         cfg["keys"] = list(res.keys())
@@ -324,6 +329,11 @@ class _RenderFn(torch.autograd.Function):
             # pass's it takes twice as long ([B200, tools/graph_timeline.py] 18 us against 8)
             d_raw_f = _bwd_composite(Pf, g, seed=seed_f, **kw)
             side.wait_stream(cur)
+            if ctx.loss is not None and ctx.loss.get("deferred") is not None:
+                ctx.loss["stream"].wait_stream(cur)
+                with torch.cuda.stream(ctx.loss["stream"]):
+                    ctx.loss["deferred"]()
+                ctx.loss["deferred"] = None
             with torch.cuda.stream(side):
                 sinks_c, direct_c, *_ = _bwd_pass(Pc, g, ts=None, emb_a_w=None, emb_t_w=None, names=names_c,
                                                   params=params_c, aux=_side_stream(Pc.z.device, 1), seed=seed_c, **kw)
@@ -345,7 +355,11 @@ class _RenderFn(torch.autograd.Function):
         if fork_chains:
             cur.wait_stream(side)
         if ctx.loss is not None and ctx.loss["stream"] is not None:
-            torch.cuda.current_stream(Pc.z.device).wait_stream(ctx.loss["stream"])      # the loss value joins here
+            if ctx.loss.get("deferred") is not None:         # no forked chains in this backward: launch it here
+                ctx.loss["deferred"]()
+                ctx.loss["deferred"] = None
+            else:
+                torch.cuda.current_stream(Pc.z.device).wait_stream(ctx.loss["stream"])      # the loss value joins here
         # inputs: cfg, rays, ts, view_dir, a_embedded, t_embedded, emb_a_w, emb_t_w, n_c, *params
         return (None, None, None, None, d_a, d_t, d_ea, d_et, None, *out_params)
 

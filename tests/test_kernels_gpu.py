@@ -253,6 +253,42 @@ def test_composite_fwd_bwd_vs_oracle(S, C):
     assert maxerr(d_got, d_ref) <= 2e-5 * max(scale, 1.0), (maxerr(d_got, d_ref), scale)
 
 
+@pytest.mark.parametrize("S,C,transient", [(1, 4, False), (33, 9, True), (64, 4, False), (100, 9, False), (128, 9, True),
+                                          (128, 4, False), (200, 9, True), (256, 9, True), (256, 4, False)])
+def test_composite_bwd_resident_kernel_matches_ring_kernel(S, C, transient):
+    # nwb_composite_bwd_select: 2 = the whole-ray-resident backward up to S = 256, 1 = the ring kernel
+    gen = torch.Generator().manual_seed(S * 7 + C)
+    N = 517
+    z = torch.sort(torch.rand(N, S, generator=gen) * 4 + 2, dim=-1)[0].to(DEV)
+    raw = torch.rand(N, S, C, generator=gen)
+    raw[..., 3] = raw[..., 3] ** 3 * 20 - (0.0 if transient else 1.0)      # static-only passes clamp sigma + noise at 0
+    if C == 9:
+        raw[..., 7] = raw[..., 7] ** 3 * 6
+    raw = raw.to(DEV)
+    typ = "fine" if C == 9 else "coarse"
+    noise = None if transient else torch.randn(N, S, generator=gen).to(DEV)
+    keys = [f"weights_{typ}", f"opacity_{typ}", f"depth_{typ}", "rgb_fine" if transient else f"rgb_{typ}"]
+    shapes = {f"weights_{typ}": (N, S), f"opacity_{typ}": (N,), f"depth_{typ}": (N,), "rgb_fine": (N, 3), f"rgb_{typ}": (N, 3),
+              "transient_sigmas": (N, S), "beta": (N,), "_rgb_fine_static": (N, 3), "_rgb_fine_transient": (N, 3)}
+    if transient:
+        keys += ["transient_sigmas", "beta", "_rgb_fine_static", "_rgb_fine_transient"]
+    cot = {k: torch.randn(shapes[k], generator=gen).to(DEV) for k in keys}
+    kw = dict(typ=typ, transient=transient, white_back=True, noise=noise, noise_std=0.5)
+    amax_a, amax_b = torch.zeros(64, dtype=torch.int32, device=DEV), torch.zeros(64, dtype=torch.int32, device=DEV)
+    try:
+        K.composite_bwd_select(2)
+        a = K.composite_bwd(raw, z, cot, amax_out=amax_a, **kw)
+        K.composite_bwd_select(1)
+        b = K.composite_bwd(raw, z, cot, amax_out=amax_b, **kw)
+    finally:
+        K.composite_bwd_select(0)
+    scale = b.abs().max().item()
+    assert maxerr(a, b) <= 2e-6 * max(scale, 1.0), (maxerr(a, b), scale)
+    # max|d_raw| as fp32 bits, from either kernel, is the maximum of what it wrote
+    assert amax_a[0].item() == a.abs().max().view(torch.int32).item()
+    assert amax_b[0].item() == b.abs().max().view(torch.int32).item()
+
+
 def test_composite_empty():
     out = K.composite_fwd(torch.zeros(0, 8, 4, device=DEV), torch.zeros(0, 8, device=DEV), typ="coarse",
                           transient=False, white_back=False, test_time=False)

@@ -47,13 +47,12 @@ enter0, exit0 = K._timed.__enter__, K._timed.__exit__
 
 def enter(self):
     r = enter0(self)
-    if recording:
-        self._s0 = stamp()
+    self._s0 = stamp() if (recording and torch.cuda.is_current_stream_capturing()) else None     # the capture's calls only
     return r
 
 
 def exit_(self, *exc):
-    if recording:
+    if self._s0 is not None:
         calls.append((self.name, self.mode, torch.cuda.current_stream(dev).cuda_stream, self._s0, stamp()))
     return exit0(self, *exc)
 
@@ -92,19 +91,6 @@ def time_step(step, iters=100):
 plain = time_step(build())
 K._timed.__enter__, K._timed.__exit__ = enter, exit_
 step = build()
-# the warm-up iterations of the capture also pass through the hooks: only the calls of the capture itself are kept
-orig_capture = torch.cuda.graph.__enter__
-
-
-def graph_enter(self):
-    global recording
-    calls.clear()
-    stamp.next = 0
-    recording = True
-    return orig_capture(self)
-
-
-torch.cuda.graph.__enter__ = graph_enter
 recording = True
 stamped = time_step(step)
 recording = False

@@ -51,3 +51,7 @@ for C, S, typ, tr in ((4, Ns, "coarse", False), (9, Ns + Ni, "fine", True)):
     if not tr:
         grads = {k: v for k, v in grads.items() if k in (f"rgb_{typ}",)}
     line(f"composite_bwd<{C}> S={S}", timed(lambda: K.composite_bwd(raw, zz, grads, typ=typ, transient=tr, white_back=True)), n * bb)
+    for gen, what in ((1, "ring kernel"), (2, "whole ray resident")):
+        K.composite_bwd_select(gen)
+        line(f"composite_bwd<{C}> S={S} ({what})", timed(lambda: K.composite_bwd(raw, zz, grads, typ=typ, transient=tr, white_back=True)), n * bb)
+    K.composite_bwd_select(0)
