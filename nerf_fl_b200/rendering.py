@@ -352,6 +352,10 @@ class _RenderFn(torch.autograd.Function):
                                                                 aux=_side_stream(Pc.z.device, 2) if fork else None,
                                                                 seed=seed_f, d_raw=d_raw_f, **kw)
             out_params += [None if direct_f else sinks_f[k] for k in names_f]
+            # the fine chain was started first and holds the SMs first: its gradients are complete here, while the coarse
+            # chain's last kernels still run on the other branch -- a caller that owns the optimizer updates the fine model now
+            if fork_chains and direct_f and cfg.get("after_fine_chain") is not None:
+                cfg["after_fine_chain"]()
         if fork_chains:
             cur.wait_stream(side)
         if ctx.loss is not None and ctx.loss["stream"] is not None:
@@ -430,8 +434,9 @@ def render_rays(models, embeddings, rays, ts, N_samples=64, use_disp=False, pert
         cfg["rng"][k] = K._f32(v)
     if n == 0:
         raise RuntimeError("render_rays called with zero rays")
-    if kwargs.get("after_coarse_chain") is not None:
-        cfg["after_coarse_chain"] = kwargs["after_coarse_chain"]
+    for hook in ("after_coarse_chain", "after_fine_chain"):
+        if kwargs.get(hook) is not None:
+            cfg[hook] = kwargs[hook]
     loss = kwargs.get("loss")
     if loss is not None:
         fn, targets = loss["fn"], K._f32(loss["targets"])

@@ -60,9 +60,10 @@ class TrainStep:
                     rng["u"] = torch.rand(n, Ni, device=rays.device)
             kw["rng"] = rng
         if do_step and graph_safe_rng and self._split_adam:
-            # one GPU: the coarse model is updated as soon as its backward chain is done, next to the fine chain's weight
-            # gradients; the step's main optimizer launch then covers the fine model, the embeddings and the step state
-            kw["after_coarse_chain"] = lambda: self.state.adam_step_early([self.models["coarse"]])
+            # one GPU: the fine model (its backward chain is started first and finishes first, [B200] tools/graph_timeline.py)
+            # is updated as soon as its weight gradients are done, next to the coarse chain's last kernels; the step's main
+            # optimizer launch then covers the coarse model, the embeddings and the step state
+            kw["after_fine_chain"] = lambda: self.state.adam_step_early([self.models["fine"]])
         if self._fused_loss:
             # NerfWLoss inside the render node: its backward is formed in the compositing kernels (rendering.render_rays)
             kw["loss"] = dict(fn=self.loss_fn, targets=rgbs, join_in_backward=True)
