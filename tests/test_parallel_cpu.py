@@ -69,7 +69,9 @@ def _worker(rank, world, port, out):
         lo, hi = shard_range(n, rank, world)
         local = torch.arange(lo, hi, dtype=torch.float32)[:, None].repeat(1, 4)
         full = gather_rays(local, n)
-        out.put((rank, state.flat_p.clone(), full))
+        # plain arrays, not torch tensors: a tensor travels through a Queue as a file descriptor that the parent has to fetch
+        # from this process while it is still alive (torch.multiprocessing's resource sharer) -- a race once the worker exits
+        out.put((rank, state.flat_p.detach().clone().numpy(), full.numpy()))
     finally:
         dist.destroy_process_group()
 
@@ -85,6 +87,7 @@ def test_allreduce_adam_and_gather_world2_gloo():
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    res = [(r, torch.from_numpy(p_), torch.from_numpy(f_)) for r, p_, f_ in res]
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
